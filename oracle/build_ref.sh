@@ -1,0 +1,70 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE ONLY. Builds oracle/_ref/libsrsran_ref.so from the UNMODIFIED reference sources where they lie
+# under /root/reference (nothing is copied into this repo). The reference's own CMake tree cannot configure in this
+# image (MbedTLS / yaml-cpp / gtest / SCTP absent), so the translation units of the PUSCH code-block
+# decode path are compiled one by one with the reference's Release flags (CMakeLists.txt:206,564) and the per-file SIMD
+# flags of lib/phy/upper/channel_coding/{,ldpc/}CMakeLists.txt. Baseline ISA is x86-64-v3 (instead of -march=native)
+# so that the library also loads on the GPU box's host, whose CPU model may differ from this container's.
+set -euo pipefail
+REF=${REF:-/root/reference}
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+OUT="$HERE/_ref"
+OBJ="$OUT/obj"
+if [ ! -d "$REF/lib/phy/upper/channel_coding/ldpc" ]; then
+  echo "reference tree not found at $REF: keeping prebuilt $OUT (if any)" >&2
+  exit 0
+fi
+mkdir -p "$OBJ"
+CXX=${CXX:-g++}
+INC="-I$REF/include -I$REF/external/fmt/include -I$REF/external -I$REF/lib -I$REF/lib/phy/upper/channel_coding"
+BASE="-std=c++17 -O3 -fPIC -march=x86-64-v3 -mtune=generic -fno-trapping-math -fno-math-errno -DFMT_HEADER_ONLY -DASSERTS_ENABLED -w"
+
+CC_DIR=lib/phy/upper/channel_coding
+declare -A EXTRA=(
+  ["$CC_DIR/ldpc/ldpc_decoder_avx2.cpp"]="-mavx2"
+  ["$CC_DIR/ldpc/ldpc_decoder_avx512.cpp"]="-mavx512f -mavx512bw"
+  ["$CC_DIR/ldpc/ldpc_encoder_avx2.cpp"]="-mavx2"
+  ["$CC_DIR/ldpc/ldpc_rate_dematcher_avx2_impl.cpp"]="-mavx2"
+  ["$CC_DIR/ldpc/ldpc_rate_dematcher_avx512_impl.cpp"]="-mavx512f -mavx512bw -mavx512vbmi"
+  ["$CC_DIR/crc_calculator_clmul_impl.cpp"]="-mpclmul -msse4.1"
+)
+SRCS=(
+  $CC_DIR/ldpc/ldpc_graph_impl.cpp
+  $CC_DIR/ldpc/ldpc_luts_impl.cpp
+  $CC_DIR/ldpc/ldpc_decoder_impl.cpp
+  $CC_DIR/ldpc/ldpc_decoder_generic.cpp
+  $CC_DIR/ldpc/ldpc_decoder_avx2.cpp
+  $CC_DIR/ldpc/ldpc_decoder_avx512.cpp
+  $CC_DIR/ldpc/ldpc_rate_dematcher_impl.cpp
+  $CC_DIR/ldpc/ldpc_rate_dematcher_avx2_impl.cpp
+  $CC_DIR/ldpc/ldpc_rate_dematcher_avx512_impl.cpp
+  $CC_DIR/ldpc/ldpc_encoder_impl.cpp
+  $CC_DIR/ldpc/ldpc_encoder_generic.cpp
+  $CC_DIR/ldpc/ldpc_encoder_avx2.cpp
+  $CC_DIR/ldpc/ldpc_rate_matcher_impl.cpp
+  $CC_DIR/ldpc/ldpc_segmenter_rx_impl.cpp
+  $CC_DIR/crc_calculator_generic_impl.cpp
+  $CC_DIR/crc_calculator_lut_impl.cpp
+  $CC_DIR/crc_calculator_clmul_impl.cpp
+  lib/phy/upper/log_likelihood_ratio.cpp
+  lib/srsvec/compare.cpp
+  lib/srsvec/bit.cpp
+)
+# Extra reference units may be appended by the caller (e.g. the whole pusch_decoder for the TB-level harness).
+SRCS+=(${REF_EXTRA_SRCS:-})
+
+pids=()
+objs=()
+for s in "${SRCS[@]}"; do
+  o="$OBJ/$(echo "$s" | tr '/' '_' | sed 's/\.cpp$/.o/')"
+  objs+=("$o")
+  if [ ! -f "$o" ] || [ "$REF/$s" -nt "$o" ]; then
+    $CXX $BASE ${EXTRA[$s]:-} $INC -c "$REF/$s" -o "$o" &
+    pids+=($!)
+  fi
+done
+for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
+
+$CXX $BASE $INC -c "$HERE/ref_shim.cpp" -o "$OBJ/ref_shim.o"
+$CXX -shared -o "$OUT/libsrsran_ref.so" "$OBJ/ref_shim.o" "${objs[@]}" -lpthread
+echo "built $OUT/libsrsran_ref.so"

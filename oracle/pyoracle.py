@@ -1,0 +1,155 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes access to the CPU oracle (libpdc_oracle.so) and, when present, to the compiled
+reference (oracle/_ref/libsrsran_ref.so).  Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may
+import this module; nothing under srsran_project_b200/ does.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "libpdc_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libsrsran_ref.so")
+
+FLAVOUR_GENERIC, FLAVOUR_AVX2, FLAVOUR_AVX512 = 0, 1, 2
+CRC_NONE, CRC16, CRC24A, CRC24B = 0, 1, 2, 3
+
+_c_i8p = ctypes.POINTER(ctypes.c_int8)
+_c_u8p = ctypes.POINTER(ctypes.c_uint8)
+
+
+def _i8(a):
+    return a.ctypes.data_as(_c_i8p)
+
+
+def _u8(a):
+    return a.ctypes.data_as(_c_u8p)
+
+
+def build_oracle():
+    """Compiles the C restatement (seconds). Building the checker is not using it."""
+    if not os.path.exists(ORACLE_SO) or any(
+        os.path.getmtime(os.path.join(HERE, f)) > os.path.getmtime(ORACLE_SO)
+        for f in ("pdc_oracle.c", "pdc_oracle_decode.c", "pdc_oracle_tx.c", "pdc_oracle.h")
+    ):
+        subprocess.check_call(["make", "-C", HERE, os.path.join(HERE, "libpdc_oracle.so")], stdout=subprocess.DEVNULL)
+
+
+def kb_of(bg):
+    return 22 if bg == 1 else 10
+
+
+def nshort_of(bg):
+    return 66 if bg == 1 else 50
+
+
+class Oracle:
+    """The plain-C restatement."""
+
+    def __init__(self):
+        build_oracle()
+        self.lib = ctypes.CDLL(ORACLE_SO)
+        self.lib.orc_crc_bits.restype = ctypes.c_uint32
+
+    def crc(self, crc_id, packed, nbits):
+        packed = np.ascontiguousarray(packed, dtype=np.uint8)
+        return int(self.lib.orc_crc_bits(crc_id, _u8(packed), int(nbits)))
+
+    def rate_dematch(self, flavour, buf, llrs, new_data, rv, Qm, Nref, nof_filler):
+        assert buf.dtype == np.int8 and buf.flags.c_contiguous
+        llrs = np.ascontiguousarray(llrs, dtype=np.int8)
+        return self.lib.orc_rate_dematch(flavour, _i8(buf), buf.size, _i8(llrs), llrs.size, int(new_data), rv, Qm,
+                                         Nref, nof_filler)
+
+    def decode(self, flavour, bg, Z, llrs, nof_filler=0, max_iter=6, crc_id=CRC_NONE, force_decoding=False):
+        llrs = np.ascontiguousarray(llrs, dtype=np.int8)
+        K = kb_of(bg) * Z
+        out = np.zeros((K + 7) // 8, np.uint8)
+        it = self.lib.orc_ldpc_decode(flavour, bg, Z, nof_filler, max_iter, crc_id, int(force_decoding), _i8(llrs),
+                                      llrs.size, _u8(out))
+        return it, out
+
+    def codeblock_decode(self, flavour, bg, Z, buf, llrs, new_data, rv, Qm, Nref, nof_filler, crc_id, max_iter=6,
+                         early_stop=True, force_decoding=False):
+        llrs = np.ascontiguousarray(llrs, dtype=np.int8)
+        K = kb_of(bg) * Z
+        out = np.zeros((K + 7) // 8, np.uint8)
+        it = self.lib.orc_codeblock_decode(flavour, bg, Z, _i8(buf), _i8(llrs), llrs.size, int(new_data), rv, Qm,
+                                           Nref, nof_filler, crc_id, max_iter, int(early_stop), int(force_decoding),
+                                           _u8(out))
+        return it, out
+
+    def encode(self, bg, Z, msg_bits):
+        msg_bits = np.ascontiguousarray(msg_bits, dtype=np.uint8)
+        cb = np.zeros(nshort_of(bg) * Z, np.uint8)
+        assert self.lib.orc_ldpc_encode(bg, Z, _u8(msg_bits), _u8(cb)) == 0
+        return cb
+
+    def rate_match(self, bg, Z, cb_bits, rv, Qm, Nref, nof_filler, E):
+        cb_bits = np.ascontiguousarray(cb_bits, dtype=np.uint8)
+        out = np.zeros(E, np.uint8)
+        assert self.lib.orc_rate_match(bg, Z, _u8(cb_bits), rv, Qm, Nref, nof_filler, E, _u8(out)) == 0
+        return out
+
+
+def ref_available():
+    return os.path.exists(REF_SO)
+
+
+class Reference:
+    """The UNMODIFIED srsRAN classes behind oracle/ref_shim.cpp."""
+
+    def __init__(self, flavour=FLAVOUR_AVX512):
+        self.lib = ctypes.CDLL(REF_SO)
+        self.lib.ref_create.restype = ctypes.c_void_p
+        self.lib.ref_crc.restype = ctypes.c_uint32
+        self.flavour = flavour
+        self.h = ctypes.c_void_p(self.lib.ref_create(flavour))
+
+    def __del__(self):
+        try:
+            self.lib.ref_destroy(self.h)
+        except Exception:
+            pass
+
+    def crc(self, impl, crc_id, packed, nbits):
+        packed = np.ascontiguousarray(packed, dtype=np.uint8)
+        return int(self.lib.ref_crc(impl, crc_id, _u8(packed), int(nbits)))
+
+    def rate_dematch(self, buf, llrs, new_data, bg, Z, rv, Qm, Nref, nof_filler):
+        llrs = np.ascontiguousarray(llrs, dtype=np.int8)
+        self.lib.ref_rate_dematch(self.h, _i8(buf), buf.size, _i8(llrs), llrs.size, int(new_data), bg, Z, rv, Qm, Nref,
+                                  nof_filler)
+
+    def decode(self, bg, Z, llrs, nof_filler=0, max_iter=6, crc_id=CRC_NONE, force_decoding=False, nof_crc_bits=None):
+        llrs = np.ascontiguousarray(llrs, dtype=np.int8)
+        K = kb_of(bg) * Z
+        out = np.zeros((K + 7) // 8, np.uint8)
+        if nof_crc_bits is None:
+            nof_crc_bits = 16 if crc_id in (CRC_NONE, CRC16) else 24
+        it = self.lib.ref_ldpc_decode(self.h, bg, Z, nof_filler, nof_crc_bits, max_iter, crc_id, int(force_decoding),
+                                      _i8(llrs), llrs.size, _u8(out))
+        return it, out
+
+    def encode(self, bg, Z, msg_bits):
+        packed = np.packbits(np.ascontiguousarray(msg_bits, dtype=np.uint8))
+        cb = np.zeros(nshort_of(bg) * Z, np.uint8)
+        self.lib.ref_ldpc_encode(self.h, bg, Z, _u8(packed), _u8(cb))
+        return cb
+
+    def encode_rm(self, bg, Z, msg_bits, rv, Qm, Nref, nof_filler, E):
+        packed = np.packbits(np.ascontiguousarray(msg_bits, dtype=np.uint8))
+        out = np.zeros(E, np.uint8)
+        self.lib.ref_ldpc_encode_rm(self.h, bg, Z, _u8(packed), rv, Qm, Nref, nof_filler, E, _u8(out))
+        return out
+
+    def segment_rx(self, bg, rv, Qm, Nref, nof_layers, nof_llrs, tbs_bits):
+        arrs = [np.zeros(152, np.uint32) for _ in range(6)]
+        n = self.lib.ref_segment_rx(bg, rv, Qm, Nref, nof_layers, nof_llrs, tbs_bits,
+                                    *[a.ctypes.data_as(ctypes.c_void_p) for a in arrs])
+        keys = ("Z", "full_length", "rm_length", "nof_filler", "cw_offset", "nof_crc_bits")
+        return [{k: int(a[i]) for k, a in zip(keys, arrs)} for i in range(n)]
+
+
+LIFTING_SIZES = sorted(a * 2 ** j for a in (2, 3, 5, 7, 9, 11, 13, 15) for j in range(8) if a * 2 ** j <= 384)
