@@ -1,0 +1,136 @@
+/*
+ * pusch_dec_cuda.h — C ABI of the B200-native PUSCH code-block decode chain (libpuschdec_cuda.so).
+ *
+ * One code block (CB) = LDPC rate dematching with HARQ soft combining -> layered normalised min-sum LDPC decoding
+ * (BG1/BG2, every lifting size) -> CB CRC with early stop, executed by one CUDA thread block on an sm_100a device.
+ * The entry points are what the reference's C++ operator interfaces for this path bind to (see INTEGRATION.md for
+ * the adapter classes):
+ *
+ *   srsran::ldpc_decoder::decode                 include/srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h:37-73
+ *   srsran::ldpc_rate_dematcher::rate_dematch    include/srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h:35-57
+ *   srsran::crc_calculator (CB CRC, early stop)  include/srsran/phy/upper/channel_coding/crc_calculator.h:31-87
+ *   srsran::pusch_codeblock_decoder::decode      lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp:35-74
+ *   srsran::hal::hw_accelerator_pusch_dec        include/srsran/hal/phy/upper/channel_processors/pusch/
+ *                                                hw_accelerator_pusch_dec.h:83-115 (enqueue/dequeue/read_outputs/HARQ)
+ *
+ * Conventions: plain pointers and sizes only; every function returns a pdc_status (0 = ok) and never throws or
+ * aborts; a context is thread-safe; there is NO CPU fallback — without a CUDA device pdc_create fails.
+ */
+#ifndef PUSCH_DEC_CUDA_H
+#define PUSCH_DEC_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDC_ABI_VERSION 1
+
+typedef enum {
+  PDC_OK               = 0,
+  PDC_ERR_INVALID_ARG  = 1, /* a contract the reference guards with srsran_assert was violated */
+  PDC_ERR_NO_DEVICE    = 2,
+  PDC_ERR_CUDA         = 3, /* see pdc_last_error() */
+  PDC_ERR_CAPACITY     = 4, /* batch larger than the context was created for / no free ticket */
+  PDC_ERR_NOT_READY    = 5, /* pdc_poll only */
+  PDC_ERR_BAD_TICKET   = 6
+} pdc_status;
+
+/* CB CRC selection (crc_calculator_generic_impl.cpp:31-56). */
+#define PDC_CRC_NONE 0 /* ldpc_decoder::decode(crc = nullptr): run max_iter iterations, no early stop */
+#define PDC_CRC16 1
+#define PDC_CRC24A 2
+#define PDC_CRC24B 3
+
+/* pdc_cb_desc.flags */
+#define PDC_F_NEW_DATA 0x01u       /* first HARQ transmission: copy (not combine) the first lap (rate_dematch new_data) */
+#define PDC_F_EARLY_STOP 0x02u     /* check the CB CRC after every iteration (pusch_codeblock_decoder use_early_stop) */
+#define PDC_F_FORCE_DECODING 0x04u /* ldpc_decoder_factory_configuration::force_decoding (semantics as implemented) */
+#define PDC_F_GENERIC 0x08u        /* arithmetic of ldpc_decoder_generic (scale = round(0.8f x)); default AVX2/AVX512 */
+#define PDC_F_DECODE_ONLY 0x10u    /* ldpc_decoder::decode: llrs are the E = N_in de-matched soft bits, no HARQ buffer */
+#define PDC_F_DEMATCH_ONLY 0x20u   /* ldpc_rate_dematcher::rate_dematch only (CB already decoded: combine, no decode) */
+
+/* One code block. Mirrors codeblock_metadata (include/srsran/phy/upper/codeblock_metadata.h:41-100) plus
+ * ldpc_decoder::configuration (ldpc_decoder.h:44-55) and hw_pusch_decoder_configuration
+ * (hw_accelerator_pusch_dec.h:39-72). */
+typedef struct {
+  uint8_t  bg;         /* 1 | 2 */
+  uint8_t  Qm;         /* 1, 2, 4, 6, 8 */
+  uint8_t  rv;         /* 0..3 */
+  uint8_t  crc_type;   /* PDC_CRC_* */
+  uint8_t  max_iter;   /* > 0 */
+  uint8_t  flags;      /* PDC_F_* */
+  uint16_t Z;          /* lifting size */
+  uint32_t E;          /* rate-matched length in LLRs (decode-only: number of input soft bits, multiple of Z) */
+  uint32_t Nref;       /* limited-buffer rate matching length, 0 = none */
+  uint32_t nof_filler; /* filler bits F */
+  int32_t  harq_slot;  /* >= 0: soft buffer lives in the device arena slot (external HARQ); -1: exchanged with host */
+  uint64_t llr_offset; /* byte offset of this CB's LLRs in the llrs buffer */
+  uint64_t soft_offset;/* byte offset of this CB's N-entry soft buffer in the soft buffers (harq_slot < 0 only) */
+  uint64_t out_offset; /* byte offset of this CB's packed hard bits (ceil(K/8) bytes, MSB first) in the bits buffer;
+                          must be a multiple of 4 */
+} pdc_cb_desc;
+
+/* Per-CB outcome: hw_pusch_decoder_outputs (hw_accelerator_pusch_dec.h:75-80) / optional<unsigned> of decode(). */
+typedef struct {
+  int32_t  iterations; /* 1-based iteration at which the CRC matched; max_iter if it matched only at the end (no
+                          early stop); -1 = reference's std::nullopt (CRC failed, or crc_type NONE) */
+  uint8_t  crc_pass;   /* 1 iff iterations > 0 */
+  uint8_t  status;     /* 0 ok; 1 = descriptor rejected (PDC_ERR_INVALID_ARG for this CB only) */
+  uint16_t nof_layers; /* base-graph check nodes actually processed (ldpc_decoder_impl.cpp:115), 0 if not decoded */
+} pdc_cb_result;
+
+typedef struct pdc_ctx pdc_ctx;
+typedef int64_t        pdc_ticket;
+
+typedef struct {
+  int      device;        /* CUDA device ordinal */
+  uint32_t max_batch_cbs; /* largest number of CBs in one submit */
+  uint64_t max_batch_llrs;/* largest total number of LLR bytes in one submit */
+  uint32_t harq_slots;    /* device HARQ arena capacity in CBs (each slot = 25344 B = 66 * 384) */
+  uint32_t nof_tickets;   /* submits that may be in flight at once (each owns pinned + device staging) */
+} pdc_config;
+
+/* --- lifetime ---------------------------------------------------------------------------------------------------- */
+pdc_status  pdc_create(const pdc_config* cfg, pdc_ctx** out);
+void        pdc_destroy(pdc_ctx* ctx);
+const char* pdc_last_error(const pdc_ctx* ctx); /* static or context-owned string; "" if none */
+int         pdc_abi_version(void);
+
+/* --- host-buffer path (what the srsRAN adapters call): H2D copy, kernel, D2H copy on one stream ---------------- */
+/* Queues n CBs. llrs: host buffer holding every CB's LLRs (desc.llr_offset). soft_in: host soft buffers for CBs with
+ * harq_slot < 0 (NULL allowed when every CB has PDC_F_NEW_DATA|harq_slot>=0|DECODE_ONLY). Copies into pinned staging,
+ * so the caller's memory may be reused as soon as the call returns. */
+pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
+                      const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket);
+/* PDC_OK when the batch has completed, PDC_ERR_NOT_READY otherwise. */
+pdc_status pdc_poll(pdc_ctx* ctx, pdc_ticket ticket);
+/* Blocks until done, then scatters the packed bits to bits + desc.out_offset, the results to res[0..n) and, for CBs
+ * with harq_slot < 0 (and not DECODE_ONLY), the updated soft buffers to soft_out + desc.soft_offset (NULL = skip). */
+pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits_bytes, pdc_cb_result* res,
+                     int8_t* soft_out, size_t soft_bytes);
+
+/* --- device-resident path (inputs and outputs already in HBM; used for kernel-only measurements and by callers that
+ *     produce LLRs on the GPU). All pointers are device pointers; stream is a cudaStream_t (NULL = default). ------- */
+pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32_t n, const int8_t* d_llrs,
+                             int8_t* d_soft, uint8_t* d_bits, pdc_cb_result* d_res, void* stream);
+
+/* --- HARQ arena (ext_harq_buffer_context_repository.h:36-107 / free_harq_context_entry) --------------------------- */
+pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot);                               /* zero-fills the slot */
+pdc_status pdc_harq_read(pdc_ctx* ctx, int32_t slot, int8_t* host_dst, size_t n);   /* test / debug access */
+pdc_status pdc_harq_write(pdc_ctx* ctx, int32_t slot, const int8_t* host_src, size_t n);
+
+/* --- introspection ------------------------------------------------------------------------------------------------ */
+uint64_t pdc_kernel_launches(const pdc_ctx* ctx); /* CUDA kernels launched by this context so far */
+/* Geometry helpers mirroring ldpc.h: K = Kb*Z, N = 66Z | 50Z; 0 if (bg, Z) is invalid. */
+uint32_t pdc_cb_message_bits(int bg, int Z);
+uint32_t pdc_cb_buffer_len(int bg, int Z);
+/* Upper bound on the base-graph layers the decoder will process for this descriptor (sizes shared memory). */
+uint32_t pdc_cb_max_layers(const pdc_cb_desc* d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PUSCH_DEC_CUDA_H */

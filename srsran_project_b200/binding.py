@@ -1,0 +1,188 @@
+"""ctypes binding of include/pusch_dec_cuda.h (test / benchmark glue; the product is the shared library)."""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+PDC_CRC_NONE, PDC_CRC16, PDC_CRC24A, PDC_CRC24B = 0, 1, 2, 3
+PDC_F_NEW_DATA = 0x01
+PDC_F_EARLY_STOP = 0x02
+PDC_F_FORCE_DECODING = 0x04
+PDC_F_GENERIC = 0x08
+PDC_F_DECODE_ONLY = 0x10
+PDC_F_DEMATCH_ONLY = 0x20
+
+PDC_OK, PDC_ERR_INVALID_ARG, PDC_ERR_NO_DEVICE, PDC_ERR_CUDA, PDC_ERR_CAPACITY, PDC_ERR_NOT_READY, PDC_ERR_BAD_TICKET = range(7)
+_STATUS_NAMES = ["PDC_OK", "PDC_ERR_INVALID_ARG", "PDC_ERR_NO_DEVICE", "PDC_ERR_CUDA", "PDC_ERR_CAPACITY",
+                 "PDC_ERR_NOT_READY", "PDC_ERR_BAD_TICKET"]
+
+
+class CbDesc(ctypes.Structure):
+    """pdc_cb_desc."""
+    _fields_ = [("bg", ctypes.c_uint8), ("Qm", ctypes.c_uint8), ("rv", ctypes.c_uint8), ("crc_type", ctypes.c_uint8),
+                ("max_iter", ctypes.c_uint8), ("flags", ctypes.c_uint8), ("Z", ctypes.c_uint16),
+                ("E", ctypes.c_uint32), ("Nref", ctypes.c_uint32), ("nof_filler", ctypes.c_uint32),
+                ("harq_slot", ctypes.c_int32), ("llr_offset", ctypes.c_uint64), ("soft_offset", ctypes.c_uint64),
+                ("out_offset", ctypes.c_uint64)]
+
+
+class CbResult(ctypes.Structure):
+    """pdc_cb_result."""
+    _fields_ = [("iterations", ctypes.c_int32), ("crc_pass", ctypes.c_uint8), ("status", ctypes.c_uint8),
+                ("nof_layers", ctypes.c_uint16)]
+
+
+class PdcConfig(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int), ("max_batch_cbs", ctypes.c_uint32), ("max_batch_llrs", ctypes.c_uint64),
+                ("harq_slots", ctypes.c_uint32), ("nof_tickets", ctypes.c_uint32)]
+
+
+RESULT_DTYPE = np.dtype([("iterations", np.int32), ("crc_pass", np.uint8), ("status", np.uint8),
+                         ("nof_layers", np.uint16)])
+DESC_DTYPE = np.dtype([("bg", np.uint8), ("Qm", np.uint8), ("rv", np.uint8), ("crc_type", np.uint8),
+                       ("max_iter", np.uint8), ("flags", np.uint8), ("Z", np.uint16), ("E", np.uint32),
+                       ("Nref", np.uint32), ("nof_filler", np.uint32), ("harq_slot", np.int32),
+                       ("llr_offset", np.uint64), ("soft_offset", np.uint64), ("out_offset", np.uint64)])
+assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
+assert RESULT_DTYPE.itemsize == ctypes.sizeof(CbResult) == 8
+
+
+class PdcError(RuntimeError):
+    def __init__(self, status, msg=""):
+        self.status = status
+        name = _STATUS_NAMES[status] if 0 <= status < len(_STATUS_NAMES) else str(status)
+        super().__init__(f"{name}: {msg}" if msg else name)
+
+
+def library_path():
+    return os.path.join(HERE, "libpuschdec_cuda.so")
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libpuschdec_cuda.so; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = library_path()
+    if not os.path.exists(path):
+        raise PdcError(PDC_ERR_NO_DEVICE, f"{path} not built: run `make -C srsran_project_b200/csrc`")
+    lib = ctypes.CDLL(path)
+    vp, u8p, i8p = ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint8), ctypes.POINTER(ctypes.c_int8)
+    lib.pdc_create.argtypes = [ctypes.POINTER(PdcConfig), ctypes.POINTER(vp)]
+    lib.pdc_destroy.argtypes = [vp]
+    lib.pdc_destroy.restype = None
+    lib.pdc_last_error.argtypes = [vp]
+    lib.pdc_last_error.restype = ctypes.c_char_p
+    lib.pdc_submit.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t,
+                               ctypes.POINTER(ctypes.c_int64)]
+    lib.pdc_poll.argtypes = [vp, ctypes.c_int64]
+    lib.pdc_fetch.argtypes = [vp, ctypes.c_int64, vp, ctypes.c_size_t, vp, vp, ctypes.c_size_t]
+    lib.pdc_decode_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp, vp, vp]
+    lib.pdc_harq_free.argtypes = [vp, ctypes.c_int32]
+    lib.pdc_harq_read.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
+    lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
+    lib.pdc_kernel_launches.argtypes = [vp]
+    lib.pdc_kernel_launches.restype = ctypes.c_uint64
+    lib.pdc_cb_message_bits.restype = ctypes.c_uint32
+    lib.pdc_cb_buffer_len.restype = ctypes.c_uint32
+    lib.pdc_cb_max_layers.argtypes = [vp]
+    lib.pdc_cb_max_layers.restype = ctypes.c_uint32
+    _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
+                    "pdc_fetch", "pdc_decode_device", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
+                    "pdc_kernel_launches", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
+
+
+def make_descs(n):
+    """Zero-initialised numpy array of pdc_cb_desc with harq_slot = -1."""
+    d = np.zeros(n, DESC_DTYPE)
+    d["harq_slot"] = -1
+    return d
+
+
+class PuschDecCuda:
+    """One accelerator context (one GPU)."""
+
+    def __init__(self, device=0, max_batch_cbs=1024, max_batch_llrs=64 << 20, harq_slots=0, nof_tickets=2):
+        self.lib = load_library()
+        cfg = PdcConfig(device, max_batch_cbs, max_batch_llrs, harq_slots, nof_tickets)
+        h = ctypes.c_void_p()
+        st = self.lib.pdc_create(ctypes.byref(cfg), ctypes.byref(h))
+        if st != PDC_OK:
+            raise PdcError(st, self.lib.pdc_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pdc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st):
+        if st != PDC_OK:
+            raise PdcError(st, self.lib.pdc_last_error(self.h).decode())
+
+    # --- host-buffer path ------------------------------------------------------------------------------------------
+    def submit(self, descs, llrs, soft_in=None):
+        assert descs.dtype == DESC_DTYPE and descs.flags.c_contiguous
+        assert llrs.dtype == np.int8 and llrs.flags.c_contiguous
+        t = ctypes.c_int64()
+        sp, sn = (None, 0) if soft_in is None else (soft_in.ctypes.data, soft_in.nbytes)
+        self._check(self.lib.pdc_submit(self.h, descs.ctypes.data, descs.size, llrs.ctypes.data, llrs.nbytes, sp, sn,
+                                        ctypes.byref(t)))
+        return t.value
+
+    def poll(self, ticket):
+        st = self.lib.pdc_poll(self.h, ticket)
+        if st == PDC_ERR_NOT_READY:
+            return False
+        self._check(st)
+        return True
+
+    def fetch(self, ticket, n, bits, soft_out=None):
+        res = np.zeros(n, RESULT_DTYPE)
+        sp, sn = (None, 0) if soft_out is None else (soft_out.ctypes.data, soft_out.nbytes)
+        self._check(self.lib.pdc_fetch(self.h, ticket, bits.ctypes.data, bits.nbytes, res.ctypes.data, sp, sn))
+        return res
+
+    def run(self, descs, llrs, bits_bytes, soft=None):
+        """submit + fetch. ``soft`` (int8 array) is updated in place when given."""
+        bits = np.zeros(bits_bytes, np.uint8)
+        t = self.submit(descs, llrs, soft)
+        res = self.fetch(t, descs.size, bits, soft)
+        return res, bits
+
+    # --- device path -----------------------------------------------------------------------------------------------
+    def decode_device(self, descs, d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, stream_ptr=None):
+        self._check(self.lib.pdc_decode_device(self.h, descs.ctypes.data, descs.size, d_llrs_ptr, d_soft_ptr,
+                                               d_bits_ptr, d_res_ptr, stream_ptr))
+
+    # --- HARQ arena ------------------------------------------------------------------------------------------------
+    def harq_free(self, slot):
+        self._check(self.lib.pdc_harq_free(self.h, slot))
+
+    def harq_read(self, slot, n):
+        out = np.zeros(n, np.int8)
+        self._check(self.lib.pdc_harq_read(self.h, slot, out.ctypes.data, n))
+        return out
+
+    def harq_write(self, slot, data):
+        data = np.ascontiguousarray(data, np.int8)
+        self._check(self.lib.pdc_harq_write(self.h, slot, data.ctypes.data, data.size))
+
+    def kernel_launches(self):
+        return int(self.lib.pdc_kernel_launches(self.h))

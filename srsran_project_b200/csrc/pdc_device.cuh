@@ -1,0 +1,154 @@
+// Device-side building blocks shared by the code-block kernels: LLR arithmetic, the position-parallel rate dematcher
+// and the bit-parallel CRC.
+//
+// Arithmetic contract (reference file:line):
+//   HARQ combine             ldpc_rate_dematcher_avx512_impl.cpp:29-62 (vector body) / log_likelihood_ratio.cpp:40-73 (tail)
+//   variable-to-check        ldpc_decoder_avx512.cpp:86-126
+//   min / second min / sign  ldpc_decoder_avx512.cpp:128-170, scale avx512_support.h:65-107, generic ldpc_decoder_generic.cpp:70-79
+//   soft-bit update          ldpc_decoder_avx512.cpp:229-270 (promotion to +-127)
+//   CRC                      crc_calculator_generic_impl.cpp:31-56,111-133
+#pragma once
+#include "pdc_common.h"
+#include <cuda_runtime.h>
+
+#define PDC_CRC_TABLE_LEN (PDC_MAX_K + 32) /* x^j mod P for j < K + order */
+
+struct pdc_launch_params {
+  const pdc_dev_cb* cbs;
+  const uint32_t*   graphs;  // [2 * 51][PDC_GRAPH_STRIDE]: col | (shift mod Z) << 8, rows concatenated
+  const uint32_t*   crc_pow; // [3][PDC_CRC_TABLE_LEN]: x^j mod P for CRC16, CRC24A, CRC24B
+  const uint32_t*   order;   // optional permutation of CB indices (nullptr = identity)
+  int               n;
+};
+
+// Row structure of the two base graphs (degrees and prefix sums), uploaded once per process.
+struct pdc_bg_rows {
+  uint16_t start[2][48];
+  uint8_t  deg[2][48];
+};
+#if defined(PDC_KERNEL_TU)
+__constant__ pdc_bg_rows c_bg_rows; // defined once, in pdc_kernels.cu
+#endif
+
+#define PDC_MAX_DYN_SMEM (200 * 1024) /* opt-in dynamic shared memory per CTA */
+
+__device__ __forceinline__ int pdc_clamp(int x, int lo, int hi)
+{
+  return max(lo, min(x, hi));
+}
+
+// log_likelihood_ratio::operator+ (saturating sum with the +-infinity special cases).
+__device__ __forceinline__ int pdc_llr_add_generic(int a, int b)
+{
+  if (a == -b) {
+    return 0;
+  }
+  if (a == PDC_LLR_INF || a == -PDC_LLR_INF) {
+    return a;
+  }
+  if (b == PDC_LLR_INF || b == -PDC_LLR_INF) {
+    return b;
+  }
+  return pdc_clamp(a + b, -PDC_LLR_MAX, PDC_LLR_MAX);
+}
+
+// _mm512_adds_epi8 then clamp to +-120.
+__device__ __forceinline__ int pdc_llr_add_simd(int a, int b)
+{
+  return pdc_clamp(pdc_clamp(a + b, -128, 127), -PDC_LLR_MAX, PDC_LLR_MAX);
+}
+
+__device__ __forceinline__ int pdc_v2c(int soft, int c2v)
+{
+  int v = pdc_clamp(soft - c2v, -PDC_LLR_MAX, PDC_LLR_MAX);
+  return (soft >= PDC_LLR_INF || soft <= -PDC_LLR_INF) ? soft : v;
+}
+
+__device__ __forceinline__ int pdc_soft_update(int v2c, int c2v)
+{
+  int t = v2c + c2v;
+  t     = (t > PDC_LLR_MAX) ? PDC_LLR_INF : ((t < -PDC_LLR_MAX) ? -PDC_LLR_INF : t);
+  return (v2c >= PDC_LLR_INF || v2c <= -PDC_LLR_INF) ? v2c : t;
+}
+
+// Normalisation of a (non-negative, <= 120) minimum. AVX2/AVX512: (x * 52428) >> 16; generic: round(0.8f * x), which
+// for integers 0..120 equals (8x + 5) / 10 (0.8x is never half-way between two integers).
+__device__ __forceinline__ int pdc_scale(int x, bool generic)
+{
+  return generic ? ((8 * x + 5) / 10) : ((x * 52428) >> 16);
+}
+
+// Rate dematching + HARQ combining of one code block, one buffer position per thread and step. Every position's final
+// value depends only on its old value and on the LLRs that land on it, in round order, so positions are independent.
+__device__ __forceinline__ void pdc_dematch(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
+                                            int8_t* __restrict__ buf, bool generic, int tid, int nth)
+{
+  const int F      = pl.n_sys - pl.n_info;
+  const int Kq     = pl.E / pl.Qm;
+  const int zero_to = pl.new_data ? ((pl.k0 < pl.n_info) ? pl.k0 : pl.n_info) : 0;
+  const int fz_from = pl.final_zero ? (pl.N - (pl.Ncb - pl.end_idx)) : pl.N;
+  const int simd_w  = generic ? 0 : 64;
+  for (int p = tid; p < pl.N; p += nth) {
+    int  v       = buf[p];
+    bool in_fill = (p >= pl.n_info) && (p < pl.n_sys);
+    if (p < zero_to) {
+      v = 0;
+    }
+    if (pl.new_data && in_fill) {
+      v = PDC_LLR_INF;
+    }
+    if (!in_fill && p < pl.Ncb) {
+      int gp = (p < pl.n_info) ? p : (p - F);
+      for (int r = 0; r < pl.rounds; ++r) {
+        int start = (r == 0) ? pl.p0 : 0;
+        if (p < start) {
+          continue;
+        }
+        int base = (r == 0) ? 0 : (pl.n0 + (r - 1) * pl.W);
+        int gs   = (start < pl.n_info) ? start : (start - F);
+        int t    = base + gp - gs;
+        if (t >= pl.E) {
+          break;
+        }
+        int x = (pl.Qm == 1) ? in[t] : in[(t % Kq) * pl.Qm + t / Kq];
+        if (pl.new_data && r == 0) {
+          v = x;
+        } else {
+          // Which combine_softbits() call covers this position, and where in it (vector body or scalar tail).
+          int left    = pl.E - base;
+          int sys_len = (start < pl.n_info) ? min(pl.n_info - start, left) : 0;
+          int cs, cl;
+          if (p < pl.n_info) {
+            cs = start, cl = sys_len;
+          } else {
+            cs = max(start, pl.n_sys);
+            cl = min(pl.Ncb - cs, left - sys_len);
+          }
+          bool vec = (simd_w != 0) && ((p - cs) < (cl / simd_w) * simd_w);
+          v        = vec ? pdc_llr_add_simd(v, x) : pdc_llr_add_generic(v, x);
+        }
+      }
+    }
+    if (p >= fz_from) {
+      v = 0;
+    }
+    buf[p] = (int8_t)v;
+  }
+}
+
+// Block-wide XOR of one 32-bit value per thread; result valid in every thread. scratch: >= 32 words of shared memory.
+__device__ __forceinline__ uint32_t pdc_block_xor(uint32_t x, uint32_t* scratch, int tid, int nth)
+{
+  x        = __reduce_xor_sync(0xffffffffu, x);
+  int warp = tid >> 5, nw = (nth + 31) >> 5;
+  __syncthreads();
+  if ((tid & 31) == 0) {
+    scratch[warp] = x;
+  }
+  __syncthreads();
+  uint32_t r = 0;
+  for (int w = 0; w < nw; ++w) {
+    r ^= scratch[w];
+  }
+  return r;
+}

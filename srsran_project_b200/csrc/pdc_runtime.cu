@@ -1,0 +1,443 @@
+// C ABI entry points of libpuschdec_cuda.so (declared in include/pusch_dec_cuda.h). See pdc_runtime_internal.cuh for
+// the context layout and the batch planner.
+#include "pdc_runtime_internal.cuh"
+
+static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
+{
+  const pdc_config& c = ctx->cfg;
+  CK(cudaStreamCreateWithFlags(&t.stream, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&t.done, cudaEventDisableTiming));
+  size_t bits_bytes = (size_t)c.max_batch_cbs * (PDC_MAX_K / 8);
+  CK(cudaHostAlloc((void**)&t.h_cbs, sizeof(pdc_dev_cb) * c.max_batch_cbs, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&t.h_order, sizeof(uint32_t) * c.max_batch_cbs, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&t.h_llrs, c.max_batch_llrs, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&t.h_bits, bits_bytes, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&t.h_res, sizeof(pdc_cb_result) * c.max_batch_cbs, cudaHostAllocDefault));
+  CK(cudaMalloc((void**)&t.d_cbs, sizeof(pdc_dev_cb) * c.max_batch_cbs));
+  CK(cudaMalloc((void**)&t.d_order, sizeof(uint32_t) * c.max_batch_cbs));
+  CK(cudaMalloc((void**)&t.d_llrs, c.max_batch_llrs));
+  CK(cudaMalloc((void**)&t.d_bits, bits_bytes));
+  CK(cudaMalloc((void**)&t.d_res, sizeof(pdc_cb_result) * c.max_batch_cbs));
+  return PDC_OK;
+}
+
+static void free_ticket(ticket_t& t)
+{
+  if (t.stream) {
+    cudaStreamSynchronize(t.stream);
+  }
+  cudaFreeHost(t.h_cbs), cudaFreeHost(t.h_order), cudaFreeHost(t.h_llrs), cudaFreeHost(t.h_bits);
+  cudaFreeHost(t.h_res), cudaFreeHost(t.h_soft);
+  cudaFree(t.d_cbs), cudaFree(t.d_order), cudaFree(t.d_llrs), cudaFree(t.d_bits), cudaFree(t.d_res);
+  cudaFree(t.d_soft);
+  if (t.done) {
+    cudaEventDestroy(t.done);
+  }
+  if (t.stream) {
+    cudaStreamDestroy(t.stream);
+  }
+}
+
+// Grows the (rarely used) host-exchanged soft-buffer staging of a ticket.
+static pdc_status ensure_soft(pdc_ctx* ctx, ticket_t& t, size_t bytes)
+{
+  if (bytes <= t.soft_cap) {
+    return PDC_OK;
+  }
+  cudaFreeHost(t.h_soft), cudaFree(t.d_soft);
+  t.h_soft = nullptr, t.d_soft = nullptr, t.soft_cap = 0;
+  CK(cudaHostAlloc((void**)&t.h_soft, bytes, cudaHostAllocDefault));
+  CK(cudaMalloc((void**)&t.d_soft, bytes));
+  t.soft_cap = bytes;
+  return PDC_OK;
+}
+
+extern "C" {
+
+int pdc_abi_version(void)
+{
+  return PDC_ABI_VERSION;
+}
+
+const char* pdc_last_error(const pdc_ctx* ctx)
+{
+  return ctx ? ctx->err.c_str() : g_static_err;
+}
+
+pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
+{
+  if (!cfg || !out || cfg->max_batch_cbs == 0 || cfg->max_batch_llrs == 0 || cfg->nof_tickets == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  *out      = nullptr;
+  int ndev  = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+    g_static_err = "no CUDA device: this library has no CPU fallback";
+    return PDC_ERR_NO_DEVICE;
+  }
+  pdc_ctx* ctx = new pdc_ctx;
+  ctx->cfg     = *cfg;
+  auto fail    = [&](pdc_status s) {
+    static std::string keep;
+    keep         = ctx->err;
+    g_static_err = keep.c_str();
+    pdc_destroy(ctx);
+    return s;
+  };
+  if (!cuda_ok(ctx, cudaSetDevice(cfg->device), "cudaSetDevice")) {
+    return fail(PDC_ERR_CUDA);
+  }
+  std::vector<uint32_t> graphs, crc;
+  pdc_bg_rows           rows;
+  build_graph_tables(graphs, rows);
+  build_crc_tables(crc);
+  if (!cuda_ok(ctx, pdc_kernels_init_device(&rows), "pdc_kernels_init_device") ||
+      !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_graphs, graphs.size() * 4), "cudaMalloc graphs") ||
+      !cuda_ok(ctx, cudaMemcpy(ctx->d_graphs, graphs.data(), graphs.size() * 4, cudaMemcpyHostToDevice), "copy") ||
+      !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_crc, crc.size() * 4), "cudaMalloc crc") ||
+      !cuda_ok(ctx, cudaMemcpy(ctx->d_crc, crc.data(), crc.size() * 4, cudaMemcpyHostToDevice), "copy")) {
+    return fail(PDC_ERR_CUDA);
+  }
+  if (cfg->harq_slots != 0) {
+    size_t bytes = (size_t)cfg->harq_slots * PDC_MAX_N;
+    if (!cuda_ok(ctx, cudaMalloc((void**)&ctx->d_harq, bytes), "cudaMalloc harq arena") ||
+        !cuda_ok(ctx, cudaMemset(ctx->d_harq, 0, bytes), "cudaMemset harq arena")) {
+      return fail(PDC_ERR_CUDA);
+    }
+  }
+  ctx->tickets.resize(cfg->nof_tickets);
+  for (ticket_t& t : ctx->tickets) {
+    if (alloc_ticket(ctx, t) != PDC_OK) {
+      return fail(PDC_ERR_CUDA);
+    }
+  }
+  *out = ctx;
+  return PDC_OK;
+}
+
+void pdc_destroy(pdc_ctx* ctx)
+{
+  if (!ctx) {
+    return;
+  }
+  cudaSetDevice(ctx->cfg.device);
+  for (ticket_t& t : ctx->tickets) {
+    free_ticket(t);
+  }
+  cudaFree(ctx->d_graphs), cudaFree(ctx->d_crc), cudaFree(ctx->d_harq);
+  delete ctx;
+}
+
+pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
+                      const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket)
+{
+  if (!ctx || !descs || !llrs || !ticket || n == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  if (n > ctx->cfg.max_batch_cbs || llr_bytes > ctx->cfg.max_batch_llrs) {
+    return PDC_ERR_CAPACITY;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  CK(cudaSetDevice(ctx->cfg.device));
+  ticket_t* t = nullptr;
+  for (ticket_t& c : ctx->tickets) {
+    if (!c.in_use) {
+      t = &c;
+      break;
+    }
+  }
+  if (!t) {
+    return PDC_ERR_CAPACITY;
+  }
+  batch_plan bp;
+  pdc_status st = plan_batch(descs, n, t->h_cbs, t->h_order, bp);
+  if (st != PDC_OK) {
+    return st;
+  }
+  // Layout of the exchanged buffers: LLRs as given, bits at out_offset, host soft buffers at soft_offset.
+  size_t bits_need = 0, soft_need = 0;
+  bool   any_host_soft = false;
+  for (uint32_t i = 0; i != n; ++i) {
+    const pdc_cb_desc& d = descs[i];
+    pdc_geom           g;
+    pdc_geom_init(g, d.bg, d.Z);
+    size_t llr_end = d.llr_offset + d.E;
+    if (llr_end > llr_bytes) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    size_t be = d.out_offset + (size_t)((g.K + 31) / 32) * 4;
+    bits_need = be > bits_need ? be : bits_need;
+    if (!(d.flags & PDC_F_DECODE_ONLY)) {
+      if (d.harq_slot >= 0) {
+        if ((uint32_t)d.harq_slot >= ctx->cfg.harq_slots) {
+          return PDC_ERR_INVALID_ARG;
+        }
+      } else {
+        any_host_soft = true;
+        size_t se     = d.soft_offset + (size_t)g.N;
+        soft_need     = se > soft_need ? se : soft_need;
+      }
+    }
+  }
+  if (bits_need > (size_t)ctx->cfg.max_batch_cbs * (PDC_MAX_K / 8)) {
+    return PDC_ERR_CAPACITY;
+  }
+  if (any_host_soft) {
+    if (soft_in && soft_bytes < soft_need) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    st = ensure_soft(ctx, *t, soft_need);
+    if (st != PDC_OK) {
+      return st;
+    }
+  }
+  for (uint32_t i = 0; i != n; ++i) {
+    const pdc_cb_desc& d = descs[i];
+    pdc_dev_cb&        c = t->h_cbs[i];
+    c.llrs               = t->d_llrs + d.llr_offset;
+    c.out                = t->d_bits + d.out_offset;
+    c.res                = t->d_res + i;
+    c.soft               = nullptr;
+    if (!(d.flags & PDC_F_DECODE_ONLY)) {
+      c.soft = (d.harq_slot >= 0) ? (ctx->d_harq + (size_t)d.harq_slot * PDC_MAX_N) : (t->d_soft + d.soft_offset);
+    }
+  }
+  // Stage and go. LLRs already in pinned memory are sent from where they lie.
+  const int8_t*         src = llrs;
+  cudaPointerAttributes attr;
+  bool                  pinned = (cudaPointerGetAttributes(&attr, llrs) == cudaSuccess) &&
+                (attr.type == cudaMemoryTypeHost);
+  cudaGetLastError(); // pageable pointers make the query set an error on some runtimes
+  if (!pinned) {
+    memcpy(t->h_llrs, llrs, llr_bytes);
+    src = t->h_llrs;
+  }
+  CK(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
+  CK(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, t->stream));
+  CK(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
+  if (any_host_soft) {
+    if (soft_in) {
+      memcpy(t->h_soft, soft_in, soft_need);
+      CK(cudaMemcpyAsync(t->d_soft, t->h_soft, soft_need, cudaMemcpyHostToDevice, t->stream));
+    } else {
+      CK(cudaMemsetAsync(t->d_soft, 0, soft_need, t->stream));
+    }
+  }
+  st = launch_batch(ctx, bp, t->d_cbs, t->d_order, t->stream);
+  if (st != PDC_OK) {
+    return st;
+  }
+  CK(cudaMemcpyAsync(t->h_bits, t->d_bits, bits_need, cudaMemcpyDeviceToHost, t->stream));
+  CK(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n, cudaMemcpyDeviceToHost, t->stream));
+  if (any_host_soft) {
+    CK(cudaMemcpyAsync(t->h_soft, t->d_soft, soft_need, cudaMemcpyDeviceToHost, t->stream));
+  }
+  CK(cudaEventRecord(t->done, t->stream));
+  t->in_use     = true;
+  t->id         = ctx->next_id++;
+  t->n          = n;
+  t->bits_bytes = bits_need;
+  t->soft_bytes = soft_need;
+  t->soft_back  = any_host_soft;
+  t->descs.assign(descs, descs + n);
+  *ticket = t->id;
+  return PDC_OK;
+}
+
+static ticket_t* find_ticket(pdc_ctx* ctx, pdc_ticket id)
+{
+  for (ticket_t& c : ctx->tickets) {
+    if (c.in_use && c.id == id) {
+      return &c;
+    }
+  }
+  return nullptr;
+}
+
+pdc_status pdc_poll(pdc_ctx* ctx, pdc_ticket ticket)
+{
+  if (!ctx) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  ticket_t*                   t = find_ticket(ctx, ticket);
+  if (!t) {
+    return PDC_ERR_BAD_TICKET;
+  }
+  cudaError_t e = cudaEventQuery(t->done);
+  if (e == cudaErrorNotReady) {
+    return PDC_ERR_NOT_READY;
+  }
+  CK(e);
+  return PDC_OK;
+}
+
+pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits_bytes, pdc_cb_result* res,
+                     int8_t* soft_out, size_t soft_bytes)
+{
+  if (!ctx || !res) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  ticket_t* t;
+  {
+    std::lock_guard<std::mutex> lock(ctx->mtx);
+    t = find_ticket(ctx, ticket);
+    if (!t) {
+      return PDC_ERR_BAD_TICKET;
+    }
+  }
+  cudaError_t e = cudaEventSynchronize(t->done); // outside the lock: other threads keep submitting
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  if (!cuda_ok(ctx, e, "cudaEventSynchronize")) {
+    t->in_use = false;
+    return PDC_ERR_CUDA;
+  }
+  pdc_status st = PDC_OK;
+  for (uint32_t i = 0; i != t->n; ++i) {
+    const pdc_cb_desc& d = t->descs[i];
+    pdc_geom           g;
+    pdc_geom_init(g, d.bg, d.Z);
+    res[i] = t->h_res[i];
+    // status 2: "not enough soft bits" with a CRC object — the reference leaves the output untouched.
+    if (bits && res[i].status == 0 && !(d.flags & PDC_F_DEMATCH_ONLY)) {
+      size_t nb = (size_t)(g.K + 7) / 8;
+      if (d.out_offset + nb > bits_bytes) {
+        st = PDC_ERR_INVALID_ARG;
+      } else {
+        memcpy(bits + d.out_offset, t->h_bits + d.out_offset, nb);
+      }
+    }
+    if (soft_out && d.harq_slot < 0 && !(d.flags & PDC_F_DECODE_ONLY)) {
+      if (d.soft_offset + (size_t)g.N > soft_bytes) {
+        st = PDC_ERR_INVALID_ARG;
+      } else {
+        memcpy(soft_out + d.soft_offset, t->h_soft + d.soft_offset, (size_t)g.N);
+      }
+    }
+  }
+  t->in_use = false;
+  return st;
+}
+
+pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* d_llrs, int8_t* d_soft,
+                             uint8_t* d_bits, pdc_cb_result* d_res, void* stream_v)
+{
+  if (!ctx || !descs || !d_llrs || !d_bits || !d_res || n == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  if (n > ctx->cfg.max_batch_cbs) {
+    return PDC_ERR_CAPACITY;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t stream = (cudaStream_t)stream_v;
+  // Descriptor staging of a free ticket is borrowed for the duration of the launch (stream-ordered).
+  ticket_t* t = nullptr;
+  for (ticket_t& c : ctx->tickets) {
+    if (!c.in_use) {
+      t = &c;
+      break;
+    }
+  }
+  if (!t) {
+    return PDC_ERR_CAPACITY;
+  }
+  // The pinned descriptor staging may still be read by a previous asynchronous copy on `stream`.
+  CK(cudaStreamSynchronize(t->stream));
+  batch_plan bp;
+  pdc_status st = plan_batch(descs, n, t->h_cbs, t->h_order, bp);
+  if (st != PDC_OK) {
+    return st;
+  }
+  for (uint32_t i = 0; i != n; ++i) {
+    const pdc_cb_desc& d = descs[i];
+    pdc_dev_cb&        c = t->h_cbs[i];
+    c.llrs               = d_llrs + d.llr_offset;
+    c.out                = d_bits + d.out_offset;
+    c.res                = d_res + i;
+    c.soft               = nullptr;
+    if (!(d.flags & PDC_F_DECODE_ONLY)) {
+      if (d.harq_slot >= 0) {
+        if ((uint32_t)d.harq_slot >= ctx->cfg.harq_slots) {
+          return PDC_ERR_INVALID_ARG;
+        }
+        c.soft = ctx->d_harq + (size_t)d.harq_slot * PDC_MAX_N;
+      } else {
+        if (!d_soft) {
+          return PDC_ERR_INVALID_ARG;
+        }
+        c.soft = d_soft + d.soft_offset;
+      }
+    }
+  }
+  CK(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
+  CK(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
+  // The pinned staging is free again once the descriptor copies have been consumed; order that on the ticket's stream.
+  CK(cudaEventRecord(t->done, stream));
+  CK(cudaStreamWaitEvent(t->stream, t->done, 0));
+  return launch_batch(ctx, bp, t->d_cbs, t->d_order, stream);
+}
+
+pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot)
+{
+  if (!ctx || slot < 0 || (uint32_t)slot >= ctx->cfg.harq_slots) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaMemset(ctx->d_harq + (size_t)slot * PDC_MAX_N, 0, PDC_MAX_N));
+  return PDC_OK;
+}
+
+pdc_status pdc_harq_read(pdc_ctx* ctx, int32_t slot, int8_t* host_dst, size_t n)
+{
+  if (!ctx || !host_dst || slot < 0 || (uint32_t)slot >= ctx->cfg.harq_slots || n > PDC_MAX_N) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(host_dst, ctx->d_harq + (size_t)slot * PDC_MAX_N, n, cudaMemcpyDeviceToHost));
+  return PDC_OK;
+}
+
+pdc_status pdc_harq_write(pdc_ctx* ctx, int32_t slot, const int8_t* host_src, size_t n)
+{
+  if (!ctx || !host_src || slot < 0 || (uint32_t)slot >= ctx->cfg.harq_slots || n > PDC_MAX_N) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(ctx->d_harq + (size_t)slot * PDC_MAX_N, host_src, n, cudaMemcpyHostToDevice));
+  return PDC_OK;
+}
+
+uint64_t pdc_kernel_launches(const pdc_ctx* ctx)
+{
+  return ctx ? ctx->launches.load() : 0;
+}
+
+uint32_t pdc_cb_message_bits(int bg, int Z)
+{
+  pdc_geom g;
+  return (pdc_geom_init(g, bg, Z) && pdc_lifting_pos(Z) >= 0) ? (uint32_t)g.K : 0;
+}
+
+uint32_t pdc_cb_buffer_len(int bg, int Z)
+{
+  pdc_geom g;
+  return (pdc_geom_init(g, bg, Z) && pdc_lifting_pos(Z) >= 0) ? (uint32_t)g.N : 0;
+}
+
+uint32_t pdc_cb_max_layers(const pdc_cb_desc* d)
+{
+  pdc_geom g;
+  int      ml = 0;
+  if (!d || !validate_desc(*d, g, ml)) {
+    return 0;
+  }
+  return (uint32_t)ml;
+}
+
+} // extern "C"

@@ -1,0 +1,267 @@
+// Host runtime behind the C ABI of include/pusch_dec_cuda.h: one context per GPU with a small ring of "tickets"
+// (stream + event + pinned staging + device staging), the device-resident HARQ soft-buffer arena, and the constant
+// tables (lifted base graphs, CRC powers). No CPU fallback: without a CUDA device pdc_create fails.
+//
+// Role in the reference's terms: this is what a bbdev-style accelerator driver is to
+// lib/hal/phy/upper/channel_processors/pusch (enqueue = pdc_submit, dequeue = pdc_poll/pdc_fetch, HARQ context =
+// arena slots; hw_accelerator_pusch_dec.h:83-115, ext_harq_buffer_context_repository.h:36-107).
+#include "ldpc_bg_tables.h"
+#include "pdc_device.cuh"
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int n_cbs, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows);
+extern "C" int         pdc_h2_supported(int bg, int Z);
+extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
+
+namespace {
+
+struct ticket_t {
+  cudaStream_t stream   = nullptr;
+  cudaEvent_t  done     = nullptr;
+  bool         in_use   = false;
+  int64_t      id       = -1;
+  uint32_t     n        = 0;
+  // pinned host staging
+  pdc_dev_cb*    h_cbs  = nullptr;
+  int8_t*        h_llrs = nullptr;
+  uint8_t*       h_bits = nullptr;
+  pdc_cb_result* h_res  = nullptr;
+  int8_t*        h_soft = nullptr;
+  uint32_t*      h_order = nullptr;
+  size_t         soft_cap = 0;
+  // device staging
+  pdc_dev_cb*    d_cbs  = nullptr;
+  int8_t*        d_llrs = nullptr;
+  uint8_t*       d_bits = nullptr;
+  pdc_cb_result* d_res  = nullptr;
+  int8_t*        d_soft = nullptr;
+  uint32_t*      d_order = nullptr;
+  // what to hand back
+  std::vector<pdc_cb_desc> descs;
+  size_t                   bits_bytes = 0, soft_bytes = 0;
+  bool                     soft_back  = false;
+};
+
+} // namespace
+
+struct pdc_ctx {
+  pdc_config            cfg;
+  std::mutex            mtx;
+  std::string           err;
+  std::vector<ticket_t> tickets;
+  int64_t               next_id = 1;
+  uint32_t*             d_graphs = nullptr;
+  uint32_t*             d_crc    = nullptr;
+  int8_t*               d_harq   = nullptr;
+  std::atomic<uint64_t> launches{0};
+  size_t                bits_stride_total = 0;
+};
+
+namespace {
+
+const char* g_static_err = "";
+
+bool cuda_ok(pdc_ctx* ctx, cudaError_t e, const char* what)
+{
+  if (e == cudaSuccess) {
+    return true;
+  }
+  char buf[256];
+  snprintf(buf, sizeof(buf), "%s: %s", what, cudaGetErrorString(e));
+  if (ctx) {
+    ctx->err = buf;
+  }
+  return false;
+}
+
+#define CK(call)                                                                                                       \
+  do {                                                                                                                 \
+    if (!cuda_ok(ctx, (call), #call)) {                                                                                \
+      return PDC_ERR_CUDA;                                                                                             \
+    }                                                                                                                  \
+  } while (0)
+
+int lifting_set_index(int Z)
+{
+  static const int base[8] = {2, 3, 5, 7, 9, 11, 13, 15};
+  for (int i = 0; i != 8; ++i) {
+    int z = base[i];
+    while (z < Z) {
+      z *= 2;
+    }
+    if (z == Z) {
+      return i;
+    }
+  }
+  return -1;
+}
+
+// Lifted graphs for all 2 x 51 (bg, Z): entry = col | (V mod Z) << 8 (ldpc_graph_impl.cpp:29-57 does the same reduction).
+void build_graph_tables(std::vector<uint32_t>& out, pdc_bg_rows& rows)
+{
+  out.assign((size_t)2 * PDC_NOF_LIFTING_SIZES * PDC_GRAPH_STRIDE, 0);
+  memset(&rows, 0, sizeof(rows));
+  static const int sizes[PDC_NOF_LIFTING_SIZES] = {2,   3,   4,   5,   6,   7,   8,   9,   10,  11,  12,  13,  14,
+                                                   15,  16,  18,  20,  22,  24,  26,  28,  30,  32,  36,  40,  44,
+                                                   48,  52,  56,  60,  64,  72,  80,  88,  96,  104, 112, 120, 128,
+                                                   144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384};
+  for (int bg = 0; bg != 2; ++bg) {
+    const uint8_t* deg   = bg ? pdc_bg2_row_deg : pdc_bg1_row_deg;
+    const uint8_t* col   = bg ? pdc_bg2_edge_col : pdc_bg1_edge_col;
+    int            M     = bg ? PDC_BG2_ROWS : PDC_BG1_ROWS;
+    int            E     = bg ? PDC_BG2_EDGES : PDC_BG1_EDGES;
+    int            acc   = 0;
+    for (int m = 0; m != M; ++m) {
+      rows.start[bg][m] = (uint16_t)acc;
+      rows.deg[bg][m]   = deg[m];
+      acc += deg[m];
+    }
+    rows.start[bg][M] = (uint16_t)acc;
+    for (int zi = 0; zi != PDC_NOF_LIFTING_SIZES; ++zi) {
+      int             Z   = sizes[zi];
+      int             ils = lifting_set_index(Z);
+      const uint16_t* sh  = bg ? pdc_bg2_edge_shift[ils] : pdc_bg1_edge_shift[ils];
+      uint32_t*       dst = &out[((size_t)bg * PDC_NOF_LIFTING_SIZES + zi) * PDC_GRAPH_STRIDE];
+      for (int e = 0; e != E; ++e) {
+        dst[e] = (uint32_t)col[e] | ((uint32_t)(sh[e] % Z) << 8);
+      }
+    }
+  }
+}
+
+// x^j mod P for j < PDC_CRC_TABLE_LEN, for CRC16 / CRC24A / CRC24B (crc_calculator_generic_impl.cpp:31-56).
+void build_crc_tables(std::vector<uint32_t>& out)
+{
+  static const uint32_t poly[3]  = {0x11021, 0x1864CFB, 0x1800063};
+  static const int      order[3] = {16, 24, 24};
+  out.assign((size_t)3 * PDC_CRC_TABLE_LEN, 0);
+  for (int c = 0; c != 3; ++c) {
+    uint32_t top = 1u << order[c];
+    uint32_t v   = 1;
+    for (int j = 0; j != PDC_CRC_TABLE_LEN; ++j) {
+      out[(size_t)c * PDC_CRC_TABLE_LEN + j] = v;
+      v <<= 1;
+      if (v & top) {
+        v ^= poly[c];
+      }
+    }
+  }
+}
+
+// Validates one descriptor the way the reference's asserts would and fills the derived fields.
+bool validate_desc(const pdc_cb_desc& d, pdc_geom& g, int& max_layers)
+{
+  if (!pdc_geom_init(g, d.bg, d.Z) || pdc_lifting_pos(d.Z) < 0) {
+    return false;
+  }
+  if (d.max_iter == 0 || d.crc_type > PDC_CRC24B || (d.out_offset & 3) != 0) {
+    return false;
+  }
+  if ((uint64_t)d.nof_filler >= (uint64_t)g.K) {
+    return false;
+  }
+  if (d.flags & PDC_F_DECODE_ONLY) {
+    // ldpc_decoder_impl.cpp:64-80: (Kb + 2) Z <= input <= N_short Z.
+    if ((int)d.E < g.K + 2 * g.Z || (int)d.E > g.N) {
+      return false;
+    }
+    max_layers = pdc_layers_for_nz(g, (int)d.E);
+    return true;
+  }
+  pdc_dematch_plan pl;
+  if (d.E > 35u * PDC_MAX_K || d.Nref > (uint32_t)PDC_MAX_N ||
+      !pdc_dematch_plan_init(pl, g, (int)d.E, d.Qm, d.rv, (int)d.Nref, (int)d.nof_filler,
+                             (d.flags & PDC_F_NEW_DATA) != 0)) {
+    return false;
+  }
+  max_layers = pdc_layers_for_nz(g, pdc_dematch_nz_bound(pl));
+  return true;
+}
+
+size_t lane_smem_bytes(const pdc_geom& g, int max_layers)
+{
+  int bgi   = (g.Kb == 22) ? 0 : 1;
+  int M     = bgi ? PDC_BG2_ROWS : PDC_BG1_ROWS;
+  int L     = max_layers > M ? M : max_layers;
+  int edges = 0;
+  const uint8_t* deg = bgi ? pdc_bg2_row_deg : pdc_bg1_row_deg;
+  for (int m = 0; m != L; ++m) {
+    edges += deg[m];
+  }
+  return (size_t)(((g.Kb + L) * g.Z + 15) / 16 * 16) + (size_t)edges * g.Z;
+}
+
+struct batch_plan {
+  size_t   smem_lane = 0, smem_h2 = 0;
+  int      block_lane = 32;
+  uint32_t n_lane = 0, n_h2 = 0; // h2-capable CBs come first in the order array
+};
+
+// Fills dev[i] (pointers left to the caller) and the launch order; returns PDC_OK or the first invalid descriptor.
+pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, pdc_dev_cb* dev, uint32_t* order, batch_plan& bp)
+{
+  std::vector<uint32_t> lane_list;
+  lane_list.reserve(n);
+  uint32_t nh2 = 0;
+  for (uint32_t i = 0; i != n; ++i) {
+    const pdc_cb_desc& d = descs[i];
+    pdc_geom           g;
+    int                ml = 0;
+    if (!validate_desc(d, g, ml)) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    pdc_dev_cb& c = dev[i];
+    c.E = d.E, c.Nref = d.Nref, c.nof_filler = d.nof_filler, c.Z = d.Z;
+    c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter, c.flags = d.flags;
+    c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
+    c.max_layers = (uint16_t)ml;
+    if (pdc_h2_supported(d.bg, d.Z) && !(d.flags & PDC_F_DEMATCH_ONLY)) {
+      order[nh2++] = i;
+      size_t s     = pdc_h2_smem_bytes(d.bg, d.Z, ml);
+      bp.smem_h2   = s > bp.smem_h2 ? s : bp.smem_h2;
+    } else {
+      lane_list.push_back(i);
+      size_t s     = (d.flags & PDC_F_DEMATCH_ONLY) ? 0 : lane_smem_bytes(g, ml);
+      bp.smem_lane = s > bp.smem_lane ? s : bp.smem_lane;
+      int blk      = (d.Z + 31) / 32 * 32;
+      bp.block_lane = blk > bp.block_lane ? blk : bp.block_lane;
+    }
+  }
+  bp.n_h2   = nh2;
+  bp.n_lane = (uint32_t)lane_list.size();
+  for (uint32_t k = 0; k != bp.n_lane; ++k) {
+    order[nh2 + k] = lane_list[k];
+  }
+  return PDC_OK;
+}
+
+pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_cbs, const uint32_t* d_order,
+                        cudaStream_t stream)
+{
+  pdc_launch_params prm;
+  prm.cbs     = d_cbs;
+  prm.graphs  = ctx->d_graphs;
+  prm.crc_pow = ctx->d_crc;
+  if (bp.n_h2 != 0) {
+    prm.order = d_order;
+    prm.n     = (int)bp.n_h2;
+    CK(pdc_launch_h2(prm, (int)bp.n_h2, bp.smem_h2, stream));
+    ctx->launches++;
+  }
+  if (bp.n_lane != 0) {
+    prm.order = d_order + bp.n_h2;
+    prm.n     = (int)bp.n_lane;
+    CK(pdc_launch_lane(prm, bp.block_lane, bp.smem_lane, stream));
+    ctx->launches++;
+  }
+  return PDC_OK;
+}
+
+} // namespace
