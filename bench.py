@@ -1,0 +1,469 @@
+#!/usr/bin/env python3
+"""bench.py — decoded info Gbit/s of the PUSCH code-block decode chain (rate dematch + HARQ combine -> layered min-sum
+LDPC -> CB CRC with early stop), BG1 Z=384, on N B200s (default arm) or on the host cores with the reference's own
+CPU implementation (--impl reference).
+
+Workload (BASELINE.json configs[1]): 100 MHz / 273 PRB / 4 layers / 256QAM R=948/1024 transport
+blocks (TBS 1 277 992 bits, 152 code blocks of Z=384, E = 8960 | 8992, F = 16, CRC24B, rv 0, new data, 6 iterations max,
+early stop on). One step = one slot of `--tbs-per-step` (default 64) such transport blocks per GPU = 9728 code blocks,
+87 MB of LLRs. LLR population (default "awgn"): valid code words from the stimulus generator (tools/stimulus) through
+an LLR-domain AWGN channel, amplitude 8, sigma 2.2 (every CB decodes, 3.7 iterations on average); "random" is the
++-10 pattern of pusch_decoder_hwacc_benchmark.cpp:384-388 (no CB decodes: 6 iterations each, the worst case).
+
+Contract: `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0 (torchrun for N > 1; ranks
+are independent — code blocks are sharded by transport block, there is no collective on the data path).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BG1_DEG = [19, 19, 19, 19, 3, 8, 9, 7, 10, 9, 7, 8, 7, 6, 7, 7, 6, 6, 6, 6, 6, 6, 5, 5, 6, 5, 5, 4, 5, 5, 5, 5, 5, 5, 5,
+           5, 5, 4, 5, 5, 4, 5, 4, 5, 5, 4]
+MAX_ITER = 6
+N_SOFT = 25344  # 66 * 384
+OUT_STRIDE = 1056  # 8448 / 8
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--population", default="awgn", choices=["awgn", "random"])
+    ap.add_argument("--sigma", type=float, default=2.2)
+    ap.add_argument("--tbs-per-step", type=int, default=64)
+    ap.add_argument("--input-sets", type=int, default=2, help="distinct LLR sets rotated between steps (> L2 in total)")
+    ap.add_argument("--chunk-tbs", type=int, default=8, help="transport blocks per submit on the end-to-end path")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target wall time of the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Workload
+# ---------------------------------------------------------------------------------------------------------------------
+def build_workload(args, rank):
+    """Returns dict(seg, Es, msgs[n_cbs, K] or None, llr_sets[list of int8 arrays], llr_offsets, n_cbs, info_bits)."""
+    from tools import stimulus as S
+
+    c = S.CONFIG2
+    seg = S.segmentation(c["bg"], c["tbs"])
+    Es = S.rm_lengths(seg["C"], c["G"], c["nof_layers"], c["Qm"])
+    n_tbs = args.tbs_per_step
+    n_cbs = n_tbs * seg["C"]
+    offs = np.zeros(n_cbs, np.uint64)
+    o = 0
+    for i in range(n_cbs):
+        offs[i] = o
+        o += (Es[i % seg["C"]] + 15) // 16 * 16
+    total = o
+    llr_sets = [np.zeros(total, np.int8) for _ in range(args.input_sets)]
+    msgs = None
+    if args.population == "awgn":
+        msgs = np.zeros((n_cbs, seg["K"]), np.uint8)
+        for t in range(n_tbs):
+            rng = np.random.default_rng(1000 * rank + 100 + t)
+            tb = rng.integers(0, 2, c["tbs"], dtype=np.uint8)
+            _, bits, m = S.tb_encode(c["bg"], c["tbs"], tb, c["rv"], c["Qm"], 0, c["nof_layers"], c["G"])
+            msgs[t * seg["C"]:(t + 1) * seg["C"]] = m
+            for s in range(args.input_sets):
+                llrs = S.awgn_llrs(bits, 8.0, args.sigma, 7919 * (1000 * rank + t) + s + 1)
+                p = 0
+                for r in range(seg["C"]):
+                    i = t * seg["C"] + r
+                    llr_sets[s][int(offs[i]):int(offs[i]) + Es[r]] = llrs[p:p + Es[r]]
+                    p += Es[r]
+    else:
+        for s in range(args.input_sets):
+            rng = np.random.default_rng(1000 * rank + 10 + s)
+            llr_sets[s][:] = (rng.integers(0, 2, total, dtype=np.int8) * 20 - 10)
+    return dict(seg=seg, Es=Es, msgs=msgs, llr_sets=llr_sets, offs=offs, n_cbs=n_cbs, n_tbs=n_tbs,
+                info_bits=n_tbs * c["tbs"], cfg=c)
+
+
+def make_descs(wl, lo, hi, use_arena=True):
+    """pdc_cb_desc array for code blocks [lo, hi) with offsets relative to code block lo."""
+    from srsran_project_b200 import binding as B
+
+    n = hi - lo
+    d = B.make_descs(n)
+    seg, Es = wl["seg"], wl["Es"]
+    d["bg"], d["Z"], d["Qm"], d["rv"] = 1, seg["Z"], wl["cfg"]["Qm"], wl["cfg"]["rv"]
+    d["crc_type"], d["max_iter"] = B.PDC_CRC24B, MAX_ITER
+    d["flags"] = B.PDC_F_NEW_DATA | B.PDC_F_EARLY_STOP
+    d["E"] = [Es[i % seg["C"]] for i in range(lo, hi)]
+    d["nof_filler"] = seg["F"]
+    d["harq_slot"] = np.arange(lo, hi) if use_arena else -1
+    d["llr_offset"] = wl["offs"][lo:hi] - wl["offs"][lo]
+    d["soft_offset"] = np.arange(n, dtype=np.uint64) * N_SOFT
+    d["out_offset"] = np.arange(n, dtype=np.uint64) * OUT_STRIDE
+    return d
+
+
+def ops_per_cb(iterations, layers, Z=384):
+    """ops = I * Z * (8 * sum_{m<L} deg(m) + 2 L) int8 lane-operations."""
+    cs = np.concatenate([[0], np.cumsum(BG1_DEG)])
+    it = np.where(iterations > 0, iterations, MAX_ITER).astype(np.float64)
+    L = layers.astype(np.int64)
+    return it * Z * (8.0 * cs[L] + 2.0 * L)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Clock sampling (B200_PROFILING.md "clocks DURING the timed region")
+# ---------------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
+                                          "50", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])), mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU arms (the reference's own implementation compiled into oracle/_ref, else the C port under oracle/)
+# ---------------------------------------------------------------------------------------------------------------------
+def cpu_run(wl, n_sample_cbs, reps, nthreads, llr_set=0):
+    """Runs code blocks [0, n_sample_cbs) of the workload `reps` times on the host. Returns dict(sec, iters, bits, kind,
+    cores, flavour)."""
+    from oracle import pyoracle as O
+
+    seg, Es = wl["seg"], wl["Es"]
+    n = n_sample_cbs
+    llrs = wl["llr_sets"][llr_set]
+    if O.ref_available():
+        dec, dem = O.ref_best_flavours()
+        d = np.zeros(n, O.REF_CB_DTYPE)
+        d["bg"], d["Z"], d["Qm"], d["rv"], d["crc_id"], d["max_iter"] = 1, seg["Z"], 8, 0, O.CRC24B, MAX_ITER
+        d["new_data"], d["early_stop"] = 1, 1
+        d["E"] = [Es[i % seg["C"]] for i in range(n)]
+        d["nof_filler"], d["nof_crc_bits"] = seg["F"], 24
+        d["llr_offset"] = wl["offs"][:n]
+        d["soft_offset"] = np.arange(n, dtype=np.uint64) * N_SOFT
+        d["out_offset"] = np.arange(n, dtype=np.uint64) * OUT_STRIDE
+        soft = np.zeros(n * N_SOFT, np.int8)
+        bits = np.zeros(n * OUT_STRIDE, np.uint8)
+        sec, iters = O.ref_chain_run(dec, dem, nthreads, d, llrs, soft, bits, reps)
+        names = {0: "generic", 1: "avx2", 2: "avx512"}
+        return dict(sec=sec, iters=iters, bits=bits, kind="reference", cores=nthreads,
+                    flavour=f"ldpc_decoder_{names[dec]}+ldpc_rate_dematcher_{names[dem]}")
+    orc = O.Oracle()
+    iters = np.zeros(n, np.int32)
+    bits = np.zeros(n * OUT_STRIDE, np.uint8)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        for i in range(n):
+            buf = np.zeros(N_SOFT, np.int8)
+            o = int(wl["offs"][i])
+            it, b = orc.codeblock_decode(O.FLAVOUR_AVX512, 1, seg["Z"], buf, llrs[o:o + Es[i % seg["C"]]], True, 0, 8, 0,
+                                         seg["F"], O.CRC24B, MAX_ITER, True)
+            iters[i] = it
+            bits[i * OUT_STRIDE:(i + 1) * OUT_STRIDE] = b
+    return dict(sec=time.perf_counter() - t0, iters=iters, bits=bits, kind="port", cores=1, flavour="C port (scalar)")
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = build_workload(args, 0)
+    nthreads = host_threads()
+    n = wl["n_cbs"]
+    tbs = wl["cfg"]["tbs"]
+    for _ in range(max(args.warmup, 0)):
+        cpu_run(wl, n, 1, nthreads)
+    t = 0.0
+    res = None
+    for k in range(args.steps):
+        res = cpu_run(wl, n, 1, nthreads, llr_set=k % len(wl["llr_sets"]))
+        t += res["sec"]
+    gbps = args.steps * wl["info_bits"] / t / 1e9
+    sample = f"{args.steps} steps x {wl['n_tbs']} TBs ({n} CBs) per step, {res['flavour']}, {nthreads} host threads"
+    line = {"impl": "reference", "metric": "decoded info Gbit/s, PUSCH LDPC BG1 Z=384", "value": gbps, "unit": "Gbit/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": workload_config(args, wl),
+            "cpu_baseline": {"value": gbps, "unit": "Gbit/s", "cores": res["cores"], "kind": res["kind"],
+                             "sample": sample},
+            "e2e": {"value": gbps, "unit": "Gbit/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "tb_bits": tbs}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, wl):
+    return {"workload": f"pusch_decoder 273PRB 4-layer 256QAM R=948/1024 TB (TBS {wl['cfg']['tbs']}, 152 CBs, BG1 Z=384, "
+                        f"E=8960|8992, CRC24B, rv0, max 6 iterations, early stop) x {wl['n_tbs']} TBs per step per GPU",
+            "cbs_per_step_per_gpu": wl["n_cbs"], "population": args.population,
+            "sigma": args.sigma if args.population == "awgn" else None,
+            "l2_policy": f"{len(wl['llr_sets'])} distinct LLR sets of {wl['llr_sets'][0].nbytes >> 20} MiB rotated between "
+                         f"steps + {wl['n_cbs'] * N_SOFT >> 20} MiB of soft buffers rewritten every step (> 126 MB L2)",
+            "sharding": "by transport block, no collective"}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CUDA arm
+# ---------------------------------------------------------------------------------------------------------------------
+def run_cuda_arm(args):
+    import torch
+
+    import srsran_project_b200 as pdc
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("no CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    wl = build_workload(args, rank)
+    n, nsets = wl["n_cbs"], len(wl["llr_sets"])
+    C = wl["seg"]["C"]
+    chunk_cbs = args.chunk_tbs * C
+    n_chunks = (n + chunk_cbs - 1) // chunk_cbs
+    chunk_llr_bytes = max(int((wl["offs"][min(n, (k + 1) * chunk_cbs) - 1] + 9008) - wl["offs"][k * chunk_cbs])
+                          for k in range(n_chunks))
+    nof_tickets = 4
+    ctx = pdc.PuschDecCuda(device=local, max_batch_cbs=max(n, chunk_cbs), max_batch_llrs=chunk_llr_bytes + 64,
+                           harq_slots=n, nof_tickets=nof_tickets)
+
+    # ---- device-resident leg ("value"): inputs already in HBM ---------------------------------------------------------
+    d_llrs = [torch.from_numpy(s).cuda() for s in wl["llr_sets"]]
+    d_bits = torch.zeros(n * OUT_STRIDE, dtype=torch.uint8, device="cuda")
+    d_res = torch.zeros(n * 8, dtype=torch.uint8, device="cuda")
+    descs = make_descs(wl, 0, n)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def device_step(k):
+        ctx.decode_device(descs, d_llrs[k % nsets].data_ptr(), None, d_bits.data_ptr(), d_res.data_ptr(), stream)
+
+    for k in range(args.warmup):
+        device_step(k)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.kernel_launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for k in range(args.steps):
+        device_step(k)
+    ev1.record()
+    barrier()
+    launches = ctx.kernel_launches() - l0
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    clocks = sampler.stop() if rank == 0 else None
+
+    from srsran_project_b200 import binding as B
+
+    # Results of the last step (set (steps-1) % nsets) for the roofline's operation count and the self-check.
+    res = d_res.cpu().numpy().view(B.RESULT_DTYPE)
+    bits_last = d_bits.cpu().numpy()
+    last_set = (args.steps - 1) % nsets
+    ok = res["crc_pass"] == 1
+    if wl["msgs"] is not None:
+        got = np.unpackbits(bits_last.reshape(n, OUT_STRIDE), axis=1)[:, :wl["seg"]["Kp"]]
+        same = (got == wl["msgs"][:, :wl["seg"]["Kp"]]).all(axis=1)
+        wrong = int((ok & ~same).sum())
+        if wrong:
+            raise RuntimeError(f"{wrong} code blocks passed the CRC with bits different from the transmitted ones")
+    ops_step = float(ops_per_cb(res["iterations"], res["nof_layers"]).sum())
+    # The iteration profile differs slightly between LLR sets; the operation count of the timed region is taken as
+    # steps x the last step's count (sets are draws of the same distribution).
+    total_info = sum_over_ranks(float(args.steps * wl["info_bits"]))
+    value = total_info / (dev_ms * 1e-3) / 1e9
+
+    # ---- end-to-end leg: host buffers, H2D + kernel + D2H inside the timed region, through the public C ABI ------------
+    h_llrs = []
+    for s in wl["llr_sets"]:
+        t = torch.empty(s.size + 16384, dtype=torch.int8).pin_memory()
+        t[:s.size] = torch.from_numpy(s)
+        h_llrs.append(t.numpy())
+    h_bits = np.zeros(n * OUT_STRIDE, np.uint8)
+    chunk_descs = [make_descs(wl, k * chunk_cbs, min(n, (k + 1) * chunk_cbs)) for k in range(n_chunks)]
+    chunk_span = []
+    for k in range(n_chunks):
+        lo, hi = k * chunk_cbs, min(n, (k + 1) * chunk_cbs)
+        b0 = int(wl["offs"][lo])
+        b1 = int(wl["offs"][hi - 1]) + (wl["Es"][(hi - 1) % C] + 15) // 16 * 16
+        chunk_span.append((lo, hi, b0, b1))
+
+    def e2e_step(k):
+        src = h_llrs[k % nsets]
+        inflight = []
+        all_res = []
+        for c in range(n_chunks):
+            lo, hi, b0, b1 = chunk_span[c]
+            if len(inflight) == nof_tickets:
+                t, (plo, phi) = inflight.pop(0)
+                all_res.append(ctx.fetch(t, phi - plo, h_bits[plo * OUT_STRIDE:phi * OUT_STRIDE]))
+            inflight.append((ctx.submit(chunk_descs[c], src[b0:b1]), (lo, hi)))
+        for t, (plo, phi) in inflight:
+            all_res.append(ctx.fetch(t, phi - plo, h_bits[plo * OUT_STRIDE:phi * OUT_STRIDE]))
+        return all_res
+
+    for k in range(args.warmup):
+        e2e_step(k)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        e2e_res = e2e_step(k)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = total_info / e2e_s / 1e9
+    e2e_res = np.concatenate(e2e_res)
+    if not ((e2e_res["iterations"] == res["iterations"]).all() and (h_bits == bits_last).all()):
+        raise RuntimeError("end-to-end path and device-resident path disagree")
+    h2d = int(sum(b1 - b0 for (_, _, b0, b1) in chunk_span)) + n * 60  # LLRs + device descriptors and launch order
+    d2h = n * OUT_STRIDE + n * 8
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline: integer / half2 ALU issue rate measured on this device in this run ------------------------------------
+    probe = {m: ctx.probe_issue_rate(i) for i, m in enumerate(["lop3", "imad", "lop3+imad", "hmnmx2+hfma2",
+                                                               "vimnmx16x2+viadd16x2"])}
+    kernel_ms = ev0.elapsed_time(ev1) / args.steps
+    achieved = ops_step / (kernel_ms * 1e-3)
+    peak = probe["lop3+imad"]
+    alg_bytes = float(sum(wl["Es"][i % C] for i in range(n))) + n * (N_SOFT + OUT_STRIDE + 8)
+    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak, hbm_src = 6650.0, "fallback"
+    if os.path.exists(peaks_file):
+        try:
+            hbm_peak, hbm_src = float(json.load(open(peaks_file))["hbm_gbs"]), "measured"
+        except (ValueError, KeyError):
+            pass
+    roofline = {"bound": "alu", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tops/s (int8 lane-ops)",
+                "frac": achieved / peak, "traffic": None,
+                "ops_per_step": ops_step, "ops_model": "I*Z*(8*sum_deg(L)+2L) per CB (SURVEY 8d)",
+                "peak_source": "measured in this run: LOP3+IMAD dual-pipe issue rate, 32-bit lanes (pack=1)",
+                "probe_Tinst_per_s": {k: v / 1e12 for k, v in probe.items()},
+                "kernel_ms": kernel_ms,
+                "hbm": {"achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "peak_source": hbm_src,
+                        "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
+                        "algorithmic_bytes_per_step": alg_bytes}}
+
+    # ---- CPU baseline (reference's own AVX512/AVX2 chain on the host cores), bounded sample ------------------------------
+    cpu = None
+    parity = None
+    if world == 1 and not args.no_cpu_baseline:
+        nthreads = host_threads()
+        n_s = min(n, 8 * C)
+        r1 = cpu_run(wl, n_s, 1, nthreads, llr_set=last_set)
+        reps = max(1, int(args.cpu_seconds / max(r1["sec"], 1e-4)))
+        r = cpu_run(wl, n_s, reps, nthreads, llr_set=last_set)
+        cpu_gbps = reps * (n_s // C) * wl["cfg"]["tbs"] / r["sec"] / 1e9
+        cpu = {"value": cpu_gbps, "unit": "Gbit/s", "cores": r["cores"], "kind": r["kind"],
+               "sample": f"{n_s // C} TBs ({n_s} CBs) of LLR set {last_set} x {reps} repetitions, {r['flavour']}, "
+                         f"{r['sec']:.1f} s wall"}
+        it_ok = (r["iters"] == res["iterations"][:n_s]).all()
+        bits_ok = (r["bits"] == bits_last[:n_s * OUT_STRIDE]).all()
+        parity = {"cbs_checked": int(n_s), "iterations_equal": bool(it_ok), "bits_equal": bool(bits_ok)}
+        if not (it_ok and bits_ok):
+            raise RuntimeError(f"GPU results differ from the CPU {r['kind']} on the sample: {parity}")
+
+    cfg = workload_config(args, wl)
+    cfg["avg_iterations"] = float(np.where(res["iterations"] > 0, res["iterations"], MAX_ITER).mean())
+    cfg["cb_crc_pass_fraction"] = float(ok.mean())
+    cfg["parity_sample"] = parity
+    line = {"metric": "decoded info Gbit/s, PUSCH LDPC BG1 Z=384", "value": value, "unit": "Gbit/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic", "config": cfg,
+            "e2e": {"value": e2e_value, "unit": "Gbit/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1e3 * e2e_s / args.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_cuda_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -124,6 +124,10 @@ pdc_status pdc_harq_write(pdc_ctx* ctx, int32_t slot, const int8_t* host_src, si
 
 /* --- introspection ------------------------------------------------------------------------------------------------ */
 uint64_t pdc_kernel_launches(const pdc_ctx* ctx); /* CUDA kernels launched by this context so far */
+/* Measures the device's instruction issue rate (thread-level instructions per second) for the instruction classes
+ * the decoder uses; mode: 0 LOP3, 1 IMAD, 2 LOP3+IMAD, 3 HMNMX2+HFMA2, 4 VIMNMX.S16x2+VIADD.16x2. This is the
+ * roofline denominator reported by bench.py (the path is integer-ALU bound). */
+pdc_status pdc_probe_issue_rate(pdc_ctx* ctx, int mode, double* thread_inst_per_s);
 /* Geometry helpers mirroring ldpc.h: K = Kb*Z, N = 66Z | 50Z; 0 if (bg, Z) is invalid. */
 uint32_t pdc_cb_message_bits(int bg, int Z);
 uint32_t pdc_cb_buffer_len(int bg, int Z);

@@ -16,7 +16,7 @@ if [ ! -d "$REF/lib/phy/upper/channel_coding/ldpc" ]; then
 fi
 mkdir -p "$OBJ"
 CXX=${CXX:-g++}
-INC="-I$REF/include -I$REF/external/fmt/include -I$REF/external -I$REF/lib -I$REF/lib/phy/upper/channel_coding"
+INC="-I$REF/include -I$REF/external/fmt/include -I$REF/external -I$REF/lib -I$REF/lib/phy/upper/channel_coding -I$REF/lib/phy/upper/channel_processors/pusch"
 BASE="-std=c++17 -O3 -fPIC -march=x86-64-v3 -mtune=generic -fno-trapping-math -fno-math-errno -DFMT_HEADER_ONLY -DASSERTS_ENABLED -w"
 
 CC_DIR=lib/phy/upper/channel_coding
@@ -49,6 +49,7 @@ SRCS=(
   lib/phy/upper/log_likelihood_ratio.cpp
   lib/srsvec/compare.cpp
   lib/srsvec/bit.cpp
+  lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp
 )
 # Extra reference units may be appended by the caller (e.g. the whole pusch_decoder for the TB-level harness).
 SRCS+=(${REF_EXTRA_SRCS:-})

@@ -36,10 +36,6 @@ int orc_ldpc_decode(int flavour, int bg, int Z, int nof_filler, int max_iter, in
 int orc_codeblock_decode(int flavour, int bg, int Z, int8_t* buf, const int8_t* in, int E, int new_data, int rv,
                          int Qm, int Nref, int nof_filler, int crc_id, int max_iter, int use_early_stop,
                          int force_decoding, uint8_t* out_packed);
-/* Stimulus (transmit side). */
-int orc_ldpc_encode(int bg, int Z, const uint8_t* msg_bits, uint8_t* cb_bits);
-int orc_rate_match(int bg, int Z, const uint8_t* cb_bits, int rv, int Qm, int Nref, int nof_filler, int E,
-                   uint8_t* out_bits);
 
 #ifdef __cplusplus
 }

@@ -31,7 +31,7 @@ def build_oracle():
     """Compiles the C restatement (seconds). Building the checker is not using it."""
     if not os.path.exists(ORACLE_SO) or any(
         os.path.getmtime(os.path.join(HERE, f)) > os.path.getmtime(ORACLE_SO)
-        for f in ("pdc_oracle.c", "pdc_oracle_decode.c", "pdc_oracle_tx.c", "pdc_oracle.h")
+        for f in ("pdc_oracle.c", "pdc_oracle_decode.c", "pdc_oracle.h")
     ):
         subprocess.check_call(["make", "-C", HERE, os.path.join(HERE, "libpdc_oracle.so")], stdout=subprocess.DEVNULL)
 
@@ -80,17 +80,16 @@ class Oracle:
                                            _u8(out))
         return it, out
 
+    # Stimulus (transmit side) lives in tools/stimulus; kept here as thin forwards so that tests read naturally.
     def encode(self, bg, Z, msg_bits):
-        msg_bits = np.ascontiguousarray(msg_bits, dtype=np.uint8)
-        cb = np.zeros(nshort_of(bg) * Z, np.uint8)
-        assert self.lib.orc_ldpc_encode(bg, Z, _u8(msg_bits), _u8(cb)) == 0
-        return cb
+        from tools import stimulus
+
+        return stimulus.encode(bg, Z, msg_bits)
 
     def rate_match(self, bg, Z, cb_bits, rv, Qm, Nref, nof_filler, E):
-        cb_bits = np.ascontiguousarray(cb_bits, dtype=np.uint8)
-        out = np.zeros(E, np.uint8)
-        assert self.lib.orc_rate_match(bg, Z, _u8(cb_bits), rv, Qm, Nref, nof_filler, E, _u8(out)) == 0
-        return out
+        from tools import stimulus
+
+        return stimulus.rate_match(bg, Z, cb_bits, rv, Qm, Nref, nof_filler, E)
 
 
 def ref_available():
@@ -150,6 +149,42 @@ class Reference:
                                     *[a.ctypes.data_as(ctypes.c_void_p) for a in arrs])
         keys = ("Z", "full_length", "rm_length", "nof_filler", "cw_offset", "nof_crc_bits")
         return [{k: int(a[i]) for k, a in zip(keys, arrs)} for i in range(n)]
+
+
+REF_CB_DTYPE = np.dtype([("bg", np.int32), ("Z", np.int32), ("Qm", np.int32), ("rv", np.int32), ("crc_id", np.int32),
+                         ("max_iter", np.int32), ("new_data", np.int32), ("early_stop", np.int32), ("E", np.uint32),
+                         ("Nref", np.uint32), ("nof_filler", np.uint32), ("nof_crc_bits", np.uint32),
+                         ("llr_offset", np.uint64), ("soft_offset", np.uint64), ("out_offset", np.uint64),
+                         ("decode_only", np.int32), ("pad", np.int32)])
+
+
+def ref_cpu_flags():
+    """Bit 0 AVX2, bit 1 AVX512F+BW, bit 2 AVX512VBMI, bit 3 PCLMUL on THIS host (oracle/_ref must exist)."""
+    lib = ctypes.CDLL(REF_SO)
+    return int(lib.ref_cpu_flags())
+
+
+def ref_best_flavours():
+    """(decoder flavour, dematcher flavour) the reference's "auto" factories would pick on this host
+    (channel_coding_factories.cpp:114-137, 284-320)."""
+    f = ref_cpu_flags()
+    dec = FLAVOUR_AVX512 if f & 2 else (FLAVOUR_AVX2 if f & 1 else FLAVOUR_GENERIC)
+    dem = FLAVOUR_AVX512 if (f & 2 and f & 4) else (FLAVOUR_AVX2 if f & 1 else FLAVOUR_GENERIC)
+    return dec, dem
+
+
+def ref_chain_run(dec_flavour, dem_flavour, nthreads, descs, llrs, soft, bits, reps=1):
+    """Runs the UNMODIFIED reference pusch_codeblock_decoder chain over descs (REF_CB_DTYPE) on nthreads host threads.
+    Returns (seconds, iterations[int32])."""
+    assert descs.dtype == REF_CB_DTYPE and descs.flags.c_contiguous
+    lib = ctypes.CDLL(REF_SO)
+    lib.ref_chain_run.restype = ctypes.c_double
+    iters = np.zeros(descs.size, np.int32)
+    vp = ctypes.c_void_p
+    sec = lib.ref_chain_run(int(dec_flavour), int(dem_flavour), int(nthreads), int(descs.size), vp(descs.ctypes.data),
+                            vp(llrs.ctypes.data), vp(soft.ctypes.data), vp(bits.ctypes.data), vp(iters.ctypes.data),
+                            int(reps))
+    return float(sec), iters
 
 
 LIFTING_SIZES = sorted(a * 2 ** j for a in (2, 3, 5, 7, 9, 11, 13, 15) for j in range(8) if a * 2 ** j <= 384)

@@ -24,11 +24,15 @@
 #include "ldpc/ldpc_rate_dematcher_impl.h"
 #include "ldpc/ldpc_rate_matcher_impl.h"
 #include "ldpc/ldpc_segmenter_rx_impl.h"
+#include "pusch_codeblock_decoder.h"
 #include "srsran/phy/upper/channel_coding/ldpc/ldpc.h"
 #include "srsran/ran/sch/modulation_scheme.h"
 #include <cstdint>
 #include <cstring>
 #include <memory>
+#include <atomic>
+#include <chrono>
+#include <thread>
 #include <vector>
 
 using namespace srsran;
@@ -326,6 +330,117 @@ int ref_segment_rx(int       bg,
     nof_crc_bits[i]              = md.cb_specific.nof_crc_bits;
   }
   return cbs.size();
+}
+
+// ---- CPU baseline driver (bench.py --impl reference / cpu_baseline) ---------------------------------------------------
+
+// Bit 0: AVX2, bit 1: AVX512F+BW (ldpc_decoder_avx512), bit 2: AVX512VBMI (ldpc_rate_dematcher_avx512_impl),
+// bit 3: PCLMUL. The caller picks the widest flavour the host supports (channel_coding_factories.cpp:114-137 "auto").
+int ref_cpu_flags()
+{
+  __builtin_cpu_init();
+  int f = 0;
+  f |= __builtin_cpu_supports("avx2") ? 1 : 0;
+  f |= (__builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw")) ? 2 : 0;
+  f |= __builtin_cpu_supports("avx512vbmi") ? 4 : 0;
+  f |= __builtin_cpu_supports("pclmul") ? 8 : 0;
+  return f;
+}
+
+struct ref_cb_desc {
+  int32_t  bg, Z, Qm, rv, crc_id, max_iter, new_data, early_stop;
+  uint32_t E, Nref, nof_filler, nof_crc_bits;
+  uint64_t llr_offset, soft_offset, out_offset;
+  int32_t  decode_only, pad;
+};
+
+// Runs n code blocks `reps` times through the UNMODIFIED reference chain on `nthreads` host threads, each thread owning
+// one pusch_codeblock_decoder (rate dematcher + LDPC decoder + CRC calculators), exactly like the reference's pool of
+// nof_pusch_decoder_threads instances (lib/phy/upper/channel_processors/pusch/factories.cpp:82-94). Code blocks are
+// handed out dynamically. decode_only != 0 runs ldpc_decoder::decode alone on llrs (ldpc_decoder_benchmark.cpp:193).
+// dec_flavour / dem_flavour: 0 generic, 1 AVX2, 2 AVX512. Returns the wall-clock seconds of the parallel region.
+double ref_chain_run(int                dec_flavour,
+                     int                dem_flavour,
+                     int                nthreads,
+                     int                n,
+                     const ref_cb_desc* cbs,
+                     const int8_t*      llrs,
+                     int8_t*            soft,
+                     uint8_t*           bits,
+                     int32_t*           iters,
+                     int                reps)
+{
+  std::atomic<int>         next{0};
+  std::atomic<int>         ready{0};
+  std::atomic<bool>        go{false};
+  std::vector<std::thread> pool;
+  int                      total = n * reps;
+  auto                     body  = [&]() {
+    pusch_codeblock_decoder::sch_crc crcs;
+    int crc_impl = (dec_flavour == FLAVOUR_GENERIC) ? 1 : 2;
+    crcs.crc16   = make_crc(crc_impl, crc_generator_poly::CRC16);
+    crcs.crc24A  = make_crc(crc_impl, crc_generator_poly::CRC24A);
+    crcs.crc24B  = make_crc(crc_impl, crc_generator_poly::CRC24B);
+    pusch_codeblock_decoder       chain(make_dematcher(dem_flavour), make_decoder(dec_flavour, false), crcs);
+    std::unique_ptr<ldpc_decoder> dec = make_decoder(dec_flavour, false);
+    std::unique_ptr<crc_calculator> crc_alone[4];
+    for (int id = 1; id <= 3; ++id) {
+      crc_alone[id] = make_crc(crc_impl, poly_from_id(id));
+    }
+    ready++;
+    while (!go.load()) {
+      std::this_thread::yield();
+    }
+    for (;;) {
+      int k = next.fetch_add(1);
+      if (k >= total) {
+        break;
+      }
+      const ref_cb_desc& d = cbs[k % n];
+      unsigned           K = ((d.bg == 1) ? 22 : 10) * d.Z;
+      unsigned           N = ((d.bg == 1) ? 66 : 50) * d.Z;
+      bit_buffer out = bit_buffer::from_bytes(span<uint8_t>(bits + d.out_offset, (K + 7) / 8)).first(K);
+      std::optional<unsigned> r;
+      if (d.decode_only) {
+        ldpc_decoder::configuration cfg;
+        cfg.base_graph      = (d.bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+        cfg.lifting_size    = static_cast<ldpc::lifting_size_t>(d.Z);
+        cfg.nof_filler_bits = d.nof_filler;
+        cfg.nof_crc_bits    = d.nof_crc_bits;
+        cfg.max_iterations  = d.max_iter;
+        span<const log_likelihood_ratio> in(reinterpret_cast<const log_likelihood_ratio*>(llrs + d.llr_offset), d.E);
+        r = dec->decode(out, in, d.crc_id ? crc_alone[d.crc_id].get() : nullptr, cfg);
+      } else {
+        codeblock_metadata md;
+        md.tb_common.base_graph        = (d.bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+        md.tb_common.lifting_size      = static_cast<ldpc::lifting_size_t>(d.Z);
+        md.tb_common.rv                = d.rv;
+        md.tb_common.mod               = mod_from_qm(d.Qm);
+        md.tb_common.Nref              = d.Nref;
+        md.cb_specific.nof_filler_bits = d.nof_filler;
+        md.cb_specific.nof_crc_bits    = d.nof_crc_bits;
+        md.cb_specific.full_length     = N;
+        md.cb_specific.rm_length       = d.E;
+        span<log_likelihood_ratio> buf(reinterpret_cast<log_likelihood_ratio*>(soft + d.soft_offset), N);
+        span<const log_likelihood_ratio> in(reinterpret_cast<const log_likelihood_ratio*>(llrs + d.llr_offset), d.E);
+        r = chain.decode(out, buf, in, d.new_data != 0, poly_from_id(d.crc_id), d.early_stop != 0, d.max_iter, false, md);
+      }
+      iters[k % n] = r.has_value() ? static_cast<int>(*r) : -1;
+    }
+  };
+  for (int t = 0; t != nthreads; ++t) {
+    pool.emplace_back(body);
+  }
+  while (ready.load() != nthreads) {
+    std::this_thread::yield();
+  }
+  auto t0 = std::chrono::steady_clock::now();
+  go.store(true);
+  for (auto& th : pool) {
+    th.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  return std::chrono::duration<double>(t1 - t0).count();
 }
 
 } // extern "C"

@@ -88,6 +88,7 @@ def load_library():
     lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_kernel_launches.argtypes = [vp]
     lib.pdc_kernel_launches.restype = ctypes.c_uint64
+    lib.pdc_probe_issue_rate.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
     lib.pdc_cb_message_bits.restype = ctypes.c_uint32
     lib.pdc_cb_buffer_len.restype = ctypes.c_uint32
     lib.pdc_cb_max_layers.argtypes = [vp]
@@ -98,7 +99,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
-                    "pdc_kernel_launches", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
+                    "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
 
 
 def make_descs(n):
@@ -183,6 +184,12 @@ class PuschDecCuda:
     def harq_write(self, slot, data):
         data = np.ascontiguousarray(data, np.int8)
         self._check(self.lib.pdc_harq_write(self.h, slot, data.ctypes.data, data.size))
+
+    def probe_issue_rate(self, mode):
+        """Thread-level instructions per second of the probe `mode` (see pdc_probe_issue_rate)."""
+        v = ctypes.c_double()
+        self._check(self.lib.pdc_probe_issue_rate(self.h, mode, ctypes.byref(v)))
+        return v.value
 
     def kernel_launches(self):
         return int(self.lib.pdc_kernel_launches(self.h))

@@ -4,6 +4,7 @@
 #include "pdc_device.cuh"
 #include "pdc_kernel_lane.cuh"
 #include "pdc_kernel_h2.cuh"
+#include "pdc_probe.cuh"
 
 extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream)
 {
@@ -23,4 +24,34 @@ extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows)
     return e;
   }
   return pdc_h2_init_device();
+}
+
+// Times one issue-rate probe (see pdc_probe.cuh) on `stream`; reports thread-level instructions per second.
+extern "C" cudaError_t pdc_probe_run(int mode, int sm_count, cudaStream_t stream, double* thread_inst_per_s)
+{
+  uint32_t*   d_out = nullptr;
+  cudaError_t e     = cudaMalloc((void**)&d_out, sizeof(uint32_t) * 256 * (size_t)sm_count * 8);
+  if (e != cudaSuccess) {
+    return e;
+  }
+  cudaEvent_t t0, t1;
+  cudaEventCreate(&t0), cudaEventCreate(&t1);
+  double winst = 0;
+  const int blocks = sm_count * 8, iters = 2000;
+  e = pdc_probe_launch(mode, blocks, 50, d_out, stream, &winst); // warm-up
+  double best = 0;
+  for (int rep = 0; rep < 3 && e == cudaSuccess; ++rep) {
+    cudaEventRecord(t0, stream);
+    e = pdc_probe_launch(mode, blocks, iters, d_out, stream, &winst);
+    cudaEventRecord(t1, stream);
+    cudaEventSynchronize(t1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, t0, t1);
+    double rate = winst * 32.0 / (ms * 1e-3);
+    best        = rate > best ? rate : best;
+  }
+  cudaEventDestroy(t0), cudaEventDestroy(t1);
+  cudaFree(d_out);
+  *thread_inst_per_s = best;
+  return e;
 }

@@ -418,6 +418,20 @@ uint64_t pdc_kernel_launches(const pdc_ctx* ctx)
   return ctx ? ctx->launches.load() : 0;
 }
 
+pdc_status pdc_probe_issue_rate(pdc_ctx* ctx, int mode, double* thread_inst_per_s)
+{
+  if (!ctx || !thread_inst_per_s) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, ctx->cfg.device));
+  CK(pdc_probe_run(mode, prop.multiProcessorCount, ctx->tickets[0].stream, thread_inst_per_s));
+  ctx->launches += 4;
+  return PDC_OK;
+}
+
 uint32_t pdc_cb_message_bits(int bg, int Z)
 {
   pdc_geom g;

@@ -17,6 +17,7 @@
 extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int n_cbs, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows);
+extern "C" cudaError_t pdc_probe_run(int mode, int sm_count, cudaStream_t stream, double* thread_inst_per_s);
 extern "C" int         pdc_h2_supported(int bg, int Z);
 extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
 
