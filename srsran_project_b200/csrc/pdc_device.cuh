@@ -136,6 +136,103 @@ __device__ __forceinline__ void pdc_dematch(const pdc_dematch_plan& pl, const in
   }
 }
 
+// First transmission that fits the circular buffer in one lap (new_data, rounds == 1): every written position receives
+// exactly one LLR, so the walk of allot_llrs (:134-195) is a pure scatter. Input-major: a thread reads whole Qm-byte
+// symbols (one vector load) and scatters them to the Qm de-interleaved streams; for a fixed stream neighbouring threads
+// write neighbouring bytes. Same write set as pdc_dematch(): zero [0, min(k0, n_info)), fillers = +127, the LLRs, and the
+// reference's final zero of the last (Ncb - end) entries of the N-long buffer.
+template <int QM>
+__device__ __forceinline__ void pdc_dematch_scatter(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
+                                                    int8_t* __restrict__ buf, int tid, int nth)
+{
+  const int  F   = pl.n_sys - pl.n_info;
+  const int  Kq  = pl.E / QM;
+  const int  gs0 = (pl.p0 < pl.n_info) ? pl.p0 : (pl.p0 - F);
+  const bool vec = (QM == 1) || ((reinterpret_cast<uintptr_t>(in) & (uintptr_t)((QM == 6) ? 1 : (QM - 1))) == 0);
+  for (int i = tid; i < Kq; i += nth) {
+    int8_t x[QM];
+    if (vec && QM == 8) {
+      const int2 w = *reinterpret_cast<const int2*>(in + (size_t)i * 8);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        x[j]     = (int8_t)(w.x >> (8 * j));
+        x[4 + j] = (int8_t)(w.y >> (8 * j));
+      }
+    } else if (vec && QM == 4) {
+      const int w = *reinterpret_cast<const int*>(in + (size_t)i * 4);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        x[j] = (int8_t)(w >> (8 * j));
+      }
+    } else if (vec && (QM == 2 || QM == 6)) {
+#pragma unroll
+      for (int j = 0; j < QM; j += 2) {
+        const short w = *reinterpret_cast<const short*>(in + (size_t)i * QM + j);
+        x[j]          = (int8_t)w;
+        x[j + 1]      = (int8_t)(w >> 8);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < QM; ++j) {
+        x[j] = in[(size_t)i * QM + j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < QM; ++j) {
+      const int gidx = gs0 + j * Kq + i;
+      const int p    = (gidx < pl.n_info) ? gidx : (gidx + F);
+      buf[p]         = x[j];
+    }
+  }
+}
+
+__device__ __forceinline__ void pdc_dematch_first_tx(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
+                                                     int8_t* __restrict__ buf, int tid, int nth)
+{
+  const int zero_to = (pl.k0 < pl.n_info) ? pl.k0 : pl.n_info;
+  const int fz_from = pl.final_zero ? (pl.N - (pl.Ncb - pl.end_idx)) : pl.N;
+  for (int p = tid; p < zero_to; p += nth) {
+    buf[p] = 0;
+  }
+  for (int p = pl.n_info + tid; p < pl.n_sys && p < fz_from; p += nth) {
+    buf[p] = PDC_LLR_INF;
+  }
+  // Final zero region [fz_from, N): bytes up to the first 16-byte boundary, then whole vectors, then the tail.
+  {
+    const uintptr_t a0   = reinterpret_cast<uintptr_t>(buf + fz_from);
+    int             head = (int)((16 - (a0 & 15)) & 15);
+    head                 = min(head, pl.N - fz_from);
+    const int nvec       = (pl.N - fz_from - head) >> 4;
+    for (int p = tid; p < head; p += nth) {
+      buf[fz_from + p] = 0;
+    }
+    int4* v = reinterpret_cast<int4*>(buf + fz_from + head);
+    for (int k = tid; k < nvec; k += nth) {
+      v[k] = make_int4(0, 0, 0, 0);
+    }
+    for (int p = fz_from + head + 16 * nvec + tid; p < pl.N; p += nth) {
+      buf[p] = 0;
+    }
+  }
+  switch (pl.Qm) {
+    case 1:
+      pdc_dematch_scatter<1>(pl, in, buf, tid, nth);
+      break;
+    case 2:
+      pdc_dematch_scatter<2>(pl, in, buf, tid, nth);
+      break;
+    case 4:
+      pdc_dematch_scatter<4>(pl, in, buf, tid, nth);
+      break;
+    case 6:
+      pdc_dematch_scatter<6>(pl, in, buf, tid, nth);
+      break;
+    default:
+      pdc_dematch_scatter<8>(pl, in, buf, tid, nth);
+      break;
+  }
+}
+
 // Block-wide XOR of one 32-bit value per thread; result valid in every thread. scratch: >= 32 words of shared memory.
 __device__ __forceinline__ uint32_t pdc_block_xor(uint32_t x, uint32_t* scratch, int tid, int nth)
 {

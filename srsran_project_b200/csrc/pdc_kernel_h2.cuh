@@ -1,21 +1,477 @@
-// Packed fp16x2 code-block kernel (placeholder until the real kernel lands: reports "unsupported" for every size so
-// that the lane kernel takes every code block).
+// Code-block kernel for high-rate code blocks: packed half2 arithmetic, check-to-variable messages in registers.
+//
+// Scope: code blocks whose decode touches only the four core rows of the base graph (nof_layers == 4, i.e. the code rate
+// is high enough that no extension row carries received LLRs: ldpc_decoder_impl.cpp:106-115) and whose lifting size is a
+// multiple of 32. That is the operating point of the metric (100 MHz / 256QAM PUSCH: BG1, Z = 384, E = 8960 | 8992).
+// Everything else is decoded by the lane kernel (pdc_kernel_lane.cuh).
+//
+// Mapping. One CTA per code block, Z/2 threads; thread t owns check lanes (2t, 2t+1) of EVERY row, packed as one half2.
+//   * Soft bits live in shared memory as IEEE halves. Integers up to 2048 are exact in a half, and the reference's
+//     "+-127 means infinity" (log_likelihood_ratio.h:250-255) becomes a real +-inf, so saturation, promotion and the
+//     sticky infinities of ldpc_decoder_avx512.cpp:86-126,229-270 each cost one or two half2 instructions instead of
+//     byte-wise emulation (sm_100a has no native byte SIMD except VABSDIFF4).
+//   * The 76 (BG1) / 36 (BG2) check-to-variable messages of a lane pair stay in REGISTERS for the whole decode: they are
+//     only ever touched by the thread that owns the check lane, so they never travel through shared memory.
+//   * Circulant shifts: every column is stored in the lane order of the row that wrote it last ("lazy rotation"), twice
+//     back to back, so that the next row reads its rotated view as a plain offset (the same idea as the reference's
+//     doubled node buffer, ldpc_decoder_impl.h:95-98) and always writes whole aligned words. An odd relative shift costs
+//     one PRMT to realign the pair. The relative shifts are computed on the host per (base graph, Z) and sit in constant
+//     memory.
+//   * The instruction mix is split over both issue pipes on purpose: min / max / logic on the ALU pipe, add / promotion /
+//     scaling as HFMA2 on the FMA pipe (see the pipe utilisation in profiles/).
+//
+// Arithmetic (bit-exact with ldpc_decoder_avx512 / ldpc_decoder_generic; model and proof-by-test in tests/h2_model.py):
+//   u   = S - c_old                                     v2c, unclamped; +-inf stays +-inf
+//   m1, m2 = two smallest |u| capped at 120; par = xor of signs
+//   s1, s2 = scale(m1), scale(m2)                       HFMA2 tricks, exact for 0..120 (tests/test_h2_model.py)
+//   c_new = +-( |u| == m1 ? s2 : s1 ), sign = par ^ sign(u)   (ties make s1 == s2, so no argmin is needed)
+//   t   = clamp(u, +-120) + c_new
+//   S'  = t * (1 + 65504 * sat(max(|t|, |u| - 216) - 120))    |t| > 120 or u infinite  ->  overflow to +-inf
 #pragma once
+#include "ldpc_bg_tables.h"
 #include "pdc_device.cuh"
+#include <utility>
 
-extern "C" int pdc_h2_supported(int, int)
+#define PDC_H2_TAB_STRIDE 104 /* u32 per (bg, Z): 76 edge entries (offset | PRMT selector << 16) + 26 column alignments */
+#define PDC_H2_SIGMA_OFF 76
+#if defined(PDC_KERNEL_TU)
+__constant__ uint32_t c_h2_tab[2 * PDC_NOF_LIFTING_SIZES][PDC_H2_TAB_STRIDE];
+#endif
+
+// ---- half2 instructions on raw 32-bit registers ------------------------------------------------------------------------
+#define PDC_H2_OP2(name, ptx)                                                                                          \
+  __device__ __forceinline__ uint32_t name(uint32_t a, uint32_t b)                                                     \
+  {                                                                                                                    \
+    uint32_t d;                                                                                                        \
+    asm(ptx " %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));                                                                \
+    return d;                                                                                                          \
+  }
+PDC_H2_OP2(h2_add, "add.f16x2")
+PDC_H2_OP2(h2_sub, "sub.f16x2")
+PDC_H2_OP2(h2_mul, "mul.f16x2")
+PDC_H2_OP2(h2_min, "min.f16x2")
+PDC_H2_OP2(h2_max, "max.f16x2")
+PDC_H2_OP2(h2_eq_mask, "set.eq.u32.f16x2")
+PDC_H2_OP2(h2_le_mask, "set.le.u32.f16x2")
+__device__ __forceinline__ uint32_t h2_abs(uint32_t a)
 {
-  return 0;
+  uint32_t d;
+  asm("abs.f16x2 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
 }
-extern "C" size_t pdc_h2_smem_bytes(int, int, int)
+__device__ __forceinline__ uint32_t h2_fma(uint32_t a, uint32_t b, uint32_t c)
 {
-  return 0;
+  uint32_t d;
+  asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
 }
-extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params&, int, size_t, cudaStream_t)
+__device__ __forceinline__ uint32_t h2_fma_sat(uint32_t a, uint32_t b, uint32_t c)
 {
-  return cudaErrorNotSupported;
+  uint32_t d;
+  asm("fma.rn.sat.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
 }
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v)
+{
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v));
+}
+
+static constexpr uint32_t H2_120 = 0x57805780u, H2_N120 = 0xD780D780u, H2_64 = 0x54005400u, H2_N64 = 0xD400D400u;
+static constexpr uint32_t H2_N216 = 0xDAC0DAC0u, H2_65504 = 0x7BFF7BFFu, H2_ONE = 0x3C003C00u, H2_1024 = 0x64006400u;
+static constexpr uint32_t H2_N1024 = 0xE400E400u, H2_1023_5 = 0x63FF63FFu, H2_0_8 = 0x3A663A66u, H2_N1152 = 0xE480E480u;
+static constexpr uint32_t H2_SIGN = 0x80008000u;
+
+// Normalisation of a non-negative integer <= 120 held in both halves: (x * 52428) >> 16 (AVX2 / AVX512) or
+// round(0.8f * x) (generic). One fused multiply-add whose single rounding lands on the integer we want.
+__device__ __forceinline__ uint32_t h2_scale(uint32_t m, bool generic)
+{
+  if (generic) {
+    return h2_add(h2_fma(m, H2_0_8, H2_1024), H2_N1024);
+  }
+  return h2_add(h2_max(h2_fma(m, H2_0_8, H2_1023_5), H2_1024), H2_N1024);
+}
+
+// ---- compile-time structure of the four core rows -------------------------------------------------------------------------
+template <int BG>
+struct h2_graph;
+template <>
+struct h2_graph<1> {
+  static constexpr int KB = 22, NCOL = 26, NEDGE = 76;
+  __host__ __device__ static constexpr int deg(int m) { return pdc_bg1_row_deg[m]; }
+  __host__ __device__ static constexpr int col(int e) { return pdc_bg1_edge_col[e]; }
+};
+template <>
+struct h2_graph<2> {
+  static constexpr int KB = 10, NCOL = 14, NEDGE = 36;
+  __host__ __device__ static constexpr int deg(int m) { return pdc_bg2_row_deg[m]; }
+  __host__ __device__ static constexpr int col(int e) { return pdc_bg2_edge_col[e]; }
+};
+template <int BG>
+__host__ __device__ constexpr int h2_row_start(int m)
+{
+  int s = 0;
+  for (int i = 0; i < m; ++i) {
+    s += h2_graph<BG>::deg(i);
+  }
+  return s;
+}
+
+template <class F, int... I>
+__device__ __forceinline__ void h2_static_for_impl(F&& f, std::integer_sequence<int, I...>)
+{
+  (f(std::integral_constant<int, I>{}), ...);
+}
+template <int N, class F>
+__device__ __forceinline__ void h2_static_for(F&& f)
+{
+  h2_static_for_impl(static_cast<F&&>(f), std::make_integer_sequence<int, N>{});
+}
+
+// 16 bits -> 32 bits with a zero between neighbours.
+__device__ __forceinline__ uint32_t h2_spread16(uint32_t x)
+{
+  x = (x | (x << 8)) & 0x00ff00ffu;
+  x = (x | (x << 4)) & 0x0f0f0f0fu;
+  x = (x | (x << 2)) & 0x33333333u;
+  x = (x | (x << 1)) & 0x55555555u;
+  return x;
+}
+
+// One row (layer) of the decode for the lane pair of this thread. c2v: the thread's message registers of this row.
+template <int BG, int M>
+__device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], const uint32_t* __restrict__ tab,
+                                       uint32_t soft_t, uint32_t row_bytes, bool active, bool generic)
+{
+  using G            = h2_graph<BG>;
+  constexpr int DEG  = G::deg(M);
+  constexpr int E0   = h2_row_start<BG>(M);
+  uint32_t      u[DEG];
+  uint32_t      m1 = H2_120, m2 = H2_120, par = 0;
+  // ---- pass 1: variable-to-check messages, two smallest magnitudes, sign parity ------------------------------------------
+  h2_static_for<DEG>([&](auto k_) {
+    constexpr int k   = decltype(k_)::value;
+    const uint32_t ent = tab[E0 + k];
+    const uint32_t adr = soft_t + (ent & 0xffffu);
+    const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+    const uint32_t S  = __byte_perm(w0, w1, ent >> 16);
+    u[k]              = h2_sub(S, c2v[E0 + k]);
+    const uint32_t a  = h2_abs(u[k]);
+    m2                = h2_min(m2, h2_max(m1, a));
+    m1                = h2_min(m1, a);
+    par ^= u[k];
+  });
+  const uint32_t s1  = h2_scale(m1, generic);
+  const uint32_t s2  = h2_scale(m2, generic);
+  const uint32_t d   = s1 ^ s2;
+  const uint32_t s1p = s1 | (par & H2_SIGN);
+  __syncthreads(); // every thread has read this row's columns; they may now be overwritten
+  // ---- pass 2: new check-to-variable messages and soft bits ------------------------------------------------------------------
+  h2_static_for<DEG>([&](auto k_) {
+    constexpr int k   = decltype(k_)::value;
+    constexpr int col = G::col(E0 + k);
+    const uint32_t a  = h2_abs(u[k]);
+    const uint32_t eq = h2_eq_mask(a, m1);
+    const uint32_t cn = (s1p ^ (d & eq)) ^ (u[k] & H2_SIGN);
+    const uint32_t v  = h2_max(h2_min(u[k], H2_120), H2_N120);
+    const uint32_t t  = h2_add(v, cn);
+    const uint32_t x  = h2_max(h2_abs(t), h2_add(a, H2_N216));
+    const uint32_t q  = h2_fma_sat(x, H2_ONE, H2_N120);
+    const uint32_t g  = h2_fma(q, H2_65504, H2_ONE);
+    const uint32_t Sn = h2_mul(t, g);
+    c2v[E0 + k]       = cn;
+    if (active) {
+      const uint32_t adr = soft_t + col * row_bytes;
+      sts32(adr, Sn);
+      sts32(adr + (row_bytes >> 1), Sn);
+    }
+  });
+  __syncthreads();
+}
+
+template <int BG>
+__global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm)
+{
+  using G = h2_graph<BG>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t s_crc_tab[256];
+  __shared__ uint32_t s_ballot[G::KB][6][2]; // [column][warp][even | odd stored positions]
+  __shared__ uint32_t s_sbits[G::KB][12];    // hard bits of a column in stored order
+  __shared__ uint32_t s_flag[2];
+
+  const int        tid = threadIdx.x, nth = blockDim.x;
+  const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
+  const pdc_dev_cb cb  = prm.cbs[cbi];
+  if (cb.bg != BG) {
+    return; // the host launches one grid per base graph; a mismatch is a host bug and leaves status untouched
+  }
+  pdc_geom g;
+  pdc_geom_init(g, cb.bg, cb.Z);
+  const int       Z = g.Z, W = Z >> 1, K = g.K, nw = Z >> 5;
+  const bool      active  = tid < W;
+  const bool      generic = (cb.flags & PDC_F_GENERIC) != 0;
+  const uint32_t* tab     = c_h2_tab[cb.graph_idx];
+
+  pdc_cb_result res;
+  res.iterations = -1, res.crc_pass = 0, res.status = 0, res.nof_layers = 4;
+
+  // ---- prologue 1: rate dematching + HARQ combining into the soft buffer in HBM ------------------------------------------------
+  const int8_t* dec_in;
+  int           n_in;
+  if (cb.flags & PDC_F_DECODE_ONLY) {
+    dec_in = cb.llrs;
+    n_in   = (int)cb.E;
+  } else {
+    pdc_dematch_plan pl;
+    pdc_dematch_plan_init(pl, g, (int)cb.E, cb.Qm, cb.rv, (int)cb.Nref, (int)cb.nof_filler,
+                          (cb.flags & PDC_F_NEW_DATA) != 0);
+    if (pl.new_data && pl.rounds == 1) {
+      pdc_dematch_first_tx(pl, cb.llrs, cb.soft, tid, nth);
+    } else {
+      pdc_dematch(pl, cb.llrs, cb.soft, generic, tid, nth);
+    }
+    dec_in = cb.soft;
+    n_in   = g.N;
+  }
+  // CRC byte table of the selected polynomial: tab[b] = b(x) * x^order mod P.
+  const int      crc_order = (cb.crc_type == PDC_CRC16) ? 16 : 24;
+  const uint32_t crc_poly  = (cb.crc_type == PDC_CRC16) ? 0x11021u : ((cb.crc_type == PDC_CRC24A) ? 0x1864CFBu : 0x1800063u);
+  const uint32_t crc_mask  = (1u << crc_order) - 1u;
+  for (int b = tid; b < 256; b += nth) {
+    uint32_t r = (uint32_t)b << (crc_order - 8);
+    for (int k = 0; k < 8; ++k) {
+      r <<= 1;
+      r ^= (r >> crc_order) & 1u ? crc_poly : 0u;
+    }
+    s_crc_tab[b] = r & crc_mask;
+  }
+  __syncthreads(); // orders the dematcher's global writes before the reads below (same CTA)
+
+  // ---- prologue 2: load_soft_bits (ldpc_decoder_impl.cpp:150-191) into the rotated, doubled half rows --------------------------
+  const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+  const uint32_t row_bytes = 4u * (uint32_t)Z; // one column: 2 copies x Z halves
+  const uint32_t soft_t    = smem_base + 4u * (uint32_t)(active ? tid : 0); // idle lanes read lane 0's words
+  if (active) {
+    sts32(soft_t, 0u), sts32(soft_t + 2u * Z, 0u); // the two punctured columns
+    sts32(soft_t + row_bytes, 0u), sts32(soft_t + row_bytes + 2u * Z, 0u);
+    for (int c = 2; c < G::NCOL; ++c) {
+      const int sigma = (int)tab[PDC_H2_SIGMA_OFF + c];
+      int       la    = 2 * tid + sigma;
+      la -= (la >= Z) ? Z : 0;
+      int lb = la + 1;
+      lb -= (lb >= Z) ? Z : 0;
+      const int pa = (c - 2) * Z + la, pb = (c - 2) * Z + lb;
+      int       xa = (pa < n_in) ? (int)dec_in[pa] : 0;
+      int       xb = (pb < n_in) ? (int)dec_in[pb] : 0;
+      xa           = max(-64, min(64, xa));
+      xb           = max(-64, min(64, xb));
+      // int16x2 -> half2: 0x6400 | (x + 128) is the half 1024 + 128 + x.
+      const uint32_t packed = ((uint32_t)(xa + 0x6480) & 0xffffu) | ((uint32_t)(xb + 0x6480) << 16);
+      const uint32_t S      = h2_add(packed, H2_N1152);
+      sts32(soft_t + c * row_bytes, S);
+      sts32(soft_t + c * row_bytes + 2u * Z, S);
+    }
+  }
+  __syncthreads();
+
+  const uint32_t* crc_pow  = (cb.crc_type != PDC_CRC_NONE) ? prm.crc_pow + (cb.crc_type - 1) * PDC_CRC_TABLE_LEN : nullptr;
+  const int       n_sig    = K - (int)cb.nof_filler;
+  const bool      has_crc  = cb.crc_type != PDC_CRC_NONE;
+  const bool      early    = (cb.flags & PDC_F_EARLY_STOP) && has_crc;
+  const int       max_iter = cb.max_iter;
+  const int       nwords   = K >> 5;
+  uint32_t*       out_words = reinterpret_cast<uint32_t*>(smem_raw + G::NCOL * row_bytes); // [K / 32], output byte order
+
+  uint32_t c2v[G::NEDGE];
+#pragma unroll
+  for (int e = 0; e < G::NEDGE; ++e) {
+    c2v[e] = 0u;
+  }
+
+  int  it_done = 0;
+  bool success = false;
+  for (int it = 0; it < max_iter && !success; ++it) {
+    h2_row<BG, 0>(c2v, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 1>(c2v, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 2>(c2v, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 3>(c2v, tab, soft_t, row_bytes, active, generic);
+    it_done = it + 1;
+    const bool last = (it_done == max_iter);
+    if (!early && !last) {
+      continue;
+    }
+    // ---- hard decision (log_likelihood_ratio.cpp:350-376): bit = soft <= 0; a zero soft bit refuses the early stop ----------
+    uint32_t amin = H2_ONE;
+#pragma unroll
+    for (int c = 0; c < G::KB; ++c) {
+      const uint32_t S  = active ? lds32(soft_t + c * row_bytes) : H2_ONE;
+      const uint32_t le = h2_le_mask(S, 0u);
+      amin              = h2_min(amin, h2_abs(S));
+      const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
+      const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
+      if ((tid & 31) == 0) {
+        s_ballot[c][tid >> 5][0] = be;
+        s_ballot[c][tid >> 5][1] = bo;
+      }
+    }
+    const int bad = __syncthreads_or(((amin & 0x7fffu) == 0) || ((amin & 0x7fff0000u) == 0));
+    // Stored-order bit strings: interleave the even / odd ballots.
+    for (int idx = tid; idx < G::KB * nw; idx += nth) {
+      const int      c = idx / nw, k = idx - c * nw;
+      const uint32_t e16 = (s_ballot[c][k >> 1][0] >> (16 * (k & 1))) & 0xffffu;
+      const uint32_t o16 = (s_ballot[c][k >> 1][1] >> (16 * (k & 1))) & 0xffffu;
+      s_sbits[c][k]      = h2_spread16(e16) | (h2_spread16(o16) << 1);
+    }
+    __syncthreads();
+    // Natural order: lane l of column c sits at stored position (l - sigma_c) mod Z. Output bytes are MSB first.
+    for (int idx = tid; idx < nwords; idx += nth) {
+      const int c = idx / nw, k = idx - c * nw;
+      int       j0 = 32 * k - (int)tab[PDC_H2_SIGMA_OFF + c];
+      j0 += (j0 < 0) ? Z : 0;
+      const int      a = j0 >> 5, b = j0 & 31;
+      const uint32_t lo = s_sbits[c][a], hi = s_sbits[c][(a + 1 == nw) ? 0 : a + 1];
+      const uint32_t nat = __funnelshift_r(lo, hi, b);
+      out_words[idx]     = __byte_perm(__brev(nat), 0u, 0x0123);
+    }
+    __syncthreads();
+    if (has_crc) {
+      // ---- CRC of the first n_sig bits by warp 0: byte-table CRC per lane chunk, chunks combined with x^k mod P ----------------
+      if (tid < 32) {
+        const int ch     = (nwords + 31) >> 5; // words per lane
+        const int bit_lo = 32 * ch * tid;
+        int       bit_hi = bit_lo + 32 * ch;
+        bit_hi           = bit_hi < n_sig ? bit_hi : n_sig;
+        uint32_t acc     = 0;
+        if (bit_lo < bit_hi) {
+          const uint8_t* bytes = reinterpret_cast<const uint8_t*>(out_words);
+          uint32_t       r     = 0;
+          const int      nbytes = (bit_hi - bit_lo) >> 3, rem = (bit_hi - bit_lo) & 7;
+          for (int i = 0; i < nbytes; ++i) {
+            const uint32_t byte = bytes[(bit_lo >> 3) + i];
+            r = ((r << 8) ^ s_crc_tab[((r >> (crc_order - 8)) ^ byte) & 0xffu]) & crc_mask;
+          }
+          if (rem) {
+            const uint32_t byte = bytes[(bit_lo >> 3) + nbytes];
+            for (int k = 0; k < rem; ++k) {
+              const uint32_t bit = (byte >> (7 - k)) & 1u;
+              r                  = (r << 1) ^ (bit << crc_order);
+              r ^= (r >> crc_order) & 1u ? crc_poly : 0u;
+              r &= crc_mask;
+            }
+          }
+          // Shift past the bits that follow this chunk: r(x) * x^kk mod P = xor of x^(kk + b) over the set bits b of r.
+          const int kk = n_sig - bit_hi;
+          for (int b = 0; b < crc_order; ++b) {
+            acc ^= ((r >> b) & 1u) ? crc_pow[kk + b] : 0u;
+          }
+        }
+        acc = __reduce_xor_sync(0xffffffffu, acc);
+        if (tid == 0) {
+          s_flag[0] = (acc == 0u) ? 1u : 0u;
+        }
+      }
+      __syncthreads();
+      const bool crc_ok = s_flag[0] != 0u;
+      if (early) {
+        success = crc_ok && !bad;
+      } else {
+        success = crc_ok; // pusch_codeblock_decoder.cpp:62-73: one CRC after the last iteration, zero soft bits allowed
+      }
+    }
+  }
+
+  for (int w = tid; w < nwords; w += nth) {
+    reinterpret_cast<uint32_t*>(cb.out)[w] = out_words[w];
+  }
+  if (success) {
+    res.iterations = early ? it_done : max_iter;
+    res.crc_pass   = 1;
+  }
+  if (tid == 0) {
+    *cb.res = res;
+  }
+}
+
+extern "C" int pdc_h2_supported(int bg, int Z)
+{
+  return (bg == 1 || bg == 2) && (Z % 32 == 0) && Z >= 32 && Z <= PDC_MAX_Z;
+}
+extern "C" size_t pdc_h2_smem_bytes(int bg, int Z, int)
+{
+  const int ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
+  return (size_t)ncol * 4 * Z + (size_t)kb * Z / 8;
+}
+extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream)
+{
+  if (bg == 1) {
+    pdc_cb_kernel_h2<1><<<prm.n, block, smem, stream>>>(prm);
+  } else {
+    pdc_cb_kernel_h2<2><<<prm.n, block, smem, stream>>>(prm);
+  }
+  return cudaGetLastError();
+}
+
+// Relative shifts of the lazily rotated columns, for all 2 x 51 (bg, Z); uploaded once per device.
 static cudaError_t pdc_h2_init_device()
 {
-  return cudaSuccess;
+  static uint32_t host_tab[2 * PDC_NOF_LIFTING_SIZES][PDC_H2_TAB_STRIDE];
+  static const int sizes[PDC_NOF_LIFTING_SIZES] = {2,   3,   4,   5,   6,   7,   8,   9,   10,  11,  12,  13,  14,
+                                                   15,  16,  18,  20,  22,  24,  26,  28,  30,  32,  36,  40,  44,
+                                                   48,  52,  56,  60,  64,  72,  80,  88,  96,  104, 112, 120, 128,
+                                                   144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384};
+  static const int base[8] = {2, 3, 5, 7, 9, 11, 13, 15};
+  for (int bg = 0; bg != 2; ++bg) {
+    const uint8_t* deg  = bg ? pdc_bg2_row_deg : pdc_bg1_row_deg;
+    const uint8_t* cols = bg ? pdc_bg2_edge_col : pdc_bg1_edge_col;
+    const int      ncol = bg ? 14 : 26;
+    for (int zi = 0; zi != PDC_NOF_LIFTING_SIZES; ++zi) {
+      const int Z   = sizes[zi];
+      int       ils = 0;
+      for (int i = 0; i != 8; ++i) {
+        int z = base[i];
+        while (z < Z) {
+          z *= 2;
+        }
+        ils = (z == Z) ? i : ils;
+      }
+      const uint16_t* sh  = bg ? pdc_bg2_edge_shift[ils] : pdc_bg1_edge_shift[ils];
+      uint32_t*       dst = host_tab[bg * PDC_NOF_LIFTING_SIZES + zi];
+      int             row_of[80], ne = 0;
+      for (int m = 0; m != 4; ++m) {
+        for (int k = 0; k != deg[m]; ++k) {
+          row_of[ne++] = m;
+        }
+      }
+      // Alignment of a column after a full iteration = shift of the last core row that holds it.
+      int sigma[26];
+      for (int c = 0; c != ncol; ++c) {
+        sigma[c] = 0;
+        for (int e = 0; e != ne; ++e) {
+          if (cols[e] == c) {
+            sigma[c] = sh[e] % Z;
+          }
+        }
+        dst[PDC_H2_SIGMA_OFF + c] = (uint32_t)sigma[c];
+      }
+      for (int e = 0; e != ne; ++e) {
+        // Previous writer of this column: the nearest earlier row holding it, cyclically (previous iteration included).
+        int prev = sigma[cols[e]];
+        for (int e2 = 0; e2 != e; ++e2) {
+          if (cols[e2] == cols[e] && row_of[e2] < row_of[e]) {
+            prev = sh[e2] % Z;
+          }
+        }
+        const int rel = ((sh[e] % Z) - prev + Z) % Z;
+        const uint32_t off = (uint32_t)cols[e] * 4u * (uint32_t)Z + 4u * (uint32_t)(rel >> 1);
+        const uint32_t sel = (rel & 1) ? 0x5432u : 0x3210u;
+        dst[e]             = off | (sel << 16);
+      }
+    }
+  }
+  return cudaMemcpyToSymbol(c_h2_tab, host_tab, sizeof(host_tab));
 }

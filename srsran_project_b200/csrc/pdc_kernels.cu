@@ -23,6 +23,14 @@ extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows)
   if (e != cudaSuccess) {
     return e;
   }
+  e = cudaFuncSetAttribute(pdc_cb_kernel_h2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+  if (e != cudaSuccess) {
+    return e;
+  }
+  e = cudaFuncSetAttribute(pdc_cb_kernel_h2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+  if (e != cudaSuccess) {
+    return e;
+  }
   return pdc_h2_init_device();
 }
 

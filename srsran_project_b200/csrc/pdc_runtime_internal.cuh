@@ -15,7 +15,7 @@
 #include <vector>
 
 extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream);
-extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int n_cbs, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows);
 extern "C" cudaError_t pdc_probe_run(int mode, int sm_count, cudaStream_t stream, double* thread_inst_per_s);
 extern "C" int         pdc_h2_supported(int bg, int Z);
@@ -200,17 +200,33 @@ size_t lane_smem_bytes(const pdc_geom& g, int max_layers)
 }
 
 struct batch_plan {
-  size_t   smem_lane = 0, smem_h2 = 0;
-  int      block_lane = 32;
-  uint32_t n_lane = 0, n_h2 = 0; // h2-capable CBs come first in the order array
+  size_t   smem_lane = 0, smem_h2[2] = {0, 0};
+  int      block_lane = 32, block_h2[2] = {32, 32};
+  uint32_t n_lane = 0, n_h2[2] = {0, 0}; // order array: packed-kernel CBs of BG1, then of BG2, then lane-kernel CBs
 };
+
+// Which code blocks the packed half2 kernel takes: the four core rows only, Z a multiple of 32 (pdc_kernel_h2.cuh).
+bool takes_h2(const pdc_cb_desc& d, int max_layers)
+{
+  if (!pdc_h2_supported(d.bg, d.Z) || max_layers != 4) {
+    return false;
+  }
+  if (d.flags & (PDC_F_DEMATCH_ONLY | PDC_F_FORCE_DECODING)) {
+    return false;
+  }
+  if ((d.flags & PDC_F_DECODE_ONLY) && (d.E % d.Z) != 0) {
+    return false;
+  }
+  return true;
+}
 
 // Fills dev[i] (pointers left to the caller) and the launch order; returns PDC_OK or the first invalid descriptor.
 pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, pdc_dev_cb* dev, uint32_t* order, batch_plan& bp)
 {
-  std::vector<uint32_t> lane_list;
-  lane_list.reserve(n);
-  uint32_t nh2 = 0;
+  std::vector<uint32_t> lists[3];
+  for (auto& l : lists) {
+    l.reserve(n);
+  }
   for (uint32_t i = 0; i != n; ++i) {
     const pdc_cb_desc& d = descs[i];
     pdc_geom           g;
@@ -223,22 +239,29 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, pdc_dev_cb* dev, uin
     c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter, c.flags = d.flags;
     c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
     c.max_layers = (uint16_t)ml;
-    if (pdc_h2_supported(d.bg, d.Z) && !(d.flags & PDC_F_DEMATCH_ONLY)) {
-      order[nh2++] = i;
-      size_t s     = pdc_h2_smem_bytes(d.bg, d.Z, ml);
-      bp.smem_h2   = s > bp.smem_h2 ? s : bp.smem_h2;
+    if (takes_h2(d, ml)) {
+      int k = d.bg - 1;
+      lists[k].push_back(i);
+      size_t s      = pdc_h2_smem_bytes(d.bg, d.Z, ml);
+      bp.smem_h2[k] = s > bp.smem_h2[k] ? s : bp.smem_h2[k];
+      int blk       = (d.Z / 2 + 31) / 32 * 32;
+      bp.block_h2[k] = blk > bp.block_h2[k] ? blk : bp.block_h2[k];
     } else {
-      lane_list.push_back(i);
+      lists[2].push_back(i);
       size_t s     = (d.flags & PDC_F_DEMATCH_ONLY) ? 0 : lane_smem_bytes(g, ml);
       bp.smem_lane = s > bp.smem_lane ? s : bp.smem_lane;
       int blk      = (d.Z + 31) / 32 * 32;
       bp.block_lane = blk > bp.block_lane ? blk : bp.block_lane;
     }
   }
-  bp.n_h2   = nh2;
-  bp.n_lane = (uint32_t)lane_list.size();
-  for (uint32_t k = 0; k != bp.n_lane; ++k) {
-    order[nh2 + k] = lane_list[k];
+  bp.n_h2[0] = (uint32_t)lists[0].size();
+  bp.n_h2[1] = (uint32_t)lists[1].size();
+  bp.n_lane  = (uint32_t)lists[2].size();
+  uint32_t k = 0;
+  for (auto& l : lists) {
+    for (uint32_t i : l) {
+      order[k++] = i;
+    }
   }
   return PDC_OK;
 }
@@ -250,14 +273,18 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
   prm.cbs     = d_cbs;
   prm.graphs  = ctx->d_graphs;
   prm.crc_pow = ctx->d_crc;
-  if (bp.n_h2 != 0) {
-    prm.order = d_order;
-    prm.n     = (int)bp.n_h2;
-    CK(pdc_launch_h2(prm, (int)bp.n_h2, bp.smem_h2, stream));
-    ctx->launches++;
+  uint32_t off = 0;
+  for (int k = 0; k != 2; ++k) {
+    if (bp.n_h2[k] != 0) {
+      prm.order = d_order + off;
+      prm.n     = (int)bp.n_h2[k];
+      CK(pdc_launch_h2(prm, k + 1, bp.block_h2[k], bp.smem_h2[k], stream));
+      ctx->launches++;
+      off += bp.n_h2[k];
+    }
   }
   if (bp.n_lane != 0) {
-    prm.order = d_order + bp.n_h2;
+    prm.order = d_order + off;
     prm.n     = (int)bp.n_lane;
     CK(pdc_launch_lane(prm, bp.block_lane, bp.smem_lane, stream));
     ctx->launches++;

@@ -249,3 +249,74 @@ def test_chain_heavy_repetition_and_tiny_inputs(acc, oracle):
                          (1, 384, 2, 60000), (2, 384, 4, 2048)):
         cases.append(chain_case(rng, oracle, bg, Z, Qm, E, min(4, Z - 1), 0, CRC16, (6.0, 6.0), (0, 1)))
     run_chain(acc, oracle, cases, FLAVOUR_AVX512)
+
+
+# ---- packed half2 kernel (pdc_kernel_h2.cuh): high-rate code blocks, four core rows, Z a multiple of 32 -----------------
+H2_SIZES = [Z for Z in LIFTING_SIZES if Z % 32 == 0]
+
+
+def high_rate_E(bg, Z, F, Qm, frac):
+    """Largest E (multiple of Qm) that keeps nof_layers == 4: nz = E + F <= (Kb + 2) Z, scaled by frac."""
+    kb = kb_of(bg)
+    lo = (kb - 2) * Z - F + 8  # at least a few parity bits
+    hi = (kb + 2) * Z - F
+    return max(Qm, int(lo + frac * (hi - lo)) // Qm * Qm)
+
+
+@pytest.mark.parametrize("flavour", [FLAVOUR_AVX512, FLAVOUR_GENERIC])
+def test_h2_chain_high_rate_all_sizes(acc, oracle, flavour):
+    rng = np.random.default_rng(71 + flavour)
+    cases = []
+    for bg in (1, 2):
+        for zi, Z in enumerate(H2_SIZES):
+            K = kb_of(bg) * Z
+            for trial in range(6):
+                Qm = (8, 6, 4, 2, 1, 8)[trial]
+                F = (0, 16, Z - 1, 5, 0, 2 * Z - 3)[trial]
+                crc_id = (CRC24B, CRC24A, CRC16, CRC24B, CRC16, CRC24B)[(trial + zi) % 6]
+                E = high_rate_E(bg, Z, F, Qm, (1.0, 0.9, 0.5, 1.0, 0.2, 0.97)[trial])
+                # Noise from "decodes at once" to "never decodes"; amplitude up to the LLR range to exercise promotion.
+                sigma = (1.0, 2.0, 2.6, 3.5, 8.0, 2.3)[(trial + zi) % 6]
+                c = chain_case(rng, oracle, bg, Z, Qm, E, F, 0, crc_id, (sigma, sigma), (0, 0), garbage=(trial % 2 == 0))
+                cases.append(c)
+    order = rng.permutation(len(cases))
+    run_chain(acc, oracle, [cases[i] for i in order], flavour)
+
+
+def test_h2_chain_strong_llrs_and_no_early_stop(acc, oracle):
+    # Large amplitudes drive soft bits into the +-127 "infinity" states (promotion, sticky infinities).
+    rng = np.random.default_rng(83)
+    cases = []
+    for bg, Z in ((1, 384), (1, 352), (2, 384), (2, 64), (1, 32), (2, 32), (1, 96)):
+        for amp, sigma in ((40.0, 30.0), (100.0, 60.0), (8.0, 2.2), (20.0, 14.0)):
+            K = kb_of(bg) * Z
+            F = 16 if Z > 16 else 0
+            E = high_rate_E(bg, Z, F, 8, 1.0)
+            msg = message_with_crc(oracle, rng, K, F, CRC24B)
+            cb = oracle.encode(bg, Z, msg)
+            txs = []
+            for rv in (0, 0):
+                bits = oracle.rate_match(bg, Z, cb, rv, 8, 0, F, E)
+                txs.append((rv, awgn_llrs(rng, bits, sigma, amp)))
+            cases.append(dict(bg=bg, Z=Z, Qm=8, E=E, F=F, Nref=0, crc_id=CRC24B, txs=txs,
+                              soft0=np.zeros(nshort_of(bg) * Z, np.int8), msg=msg))
+    run_chain(acc, oracle, cases, FLAVOUR_AVX512)
+    run_chain(acc, oracle, cases, FLAVOUR_AVX512, early_stop=False, max_iter=4)
+    run_chain(acc, oracle, cases, FLAVOUR_GENERIC, early_stop=False, max_iter=2)
+
+
+def test_h2_decode_only_high_rate(acc, oracle):
+    rng = np.random.default_rng(97)
+    cases = []
+    for bg in (1, 2):
+        kb = kb_of(bg)
+        for Z in H2_SIZES:
+            K = kb * Z
+            for trial in range(3):
+                n = (kb + 2) * Z
+                msg = message_with_crc(oracle, rng, K, 0, CRC24B if trial else CRC16)
+                cb = oracle.encode(bg, Z, msg)
+                llrs = awgn_llrs(rng, cb[:n], (2.0, 3.0, 6.0)[trial])
+                for crc_id, max_iter in ((CRC_NONE, 6), (CRC24B if trial else CRC16, 6), (CRC24A, 1)):
+                    cases.append(dict(bg=bg, Z=Z, llrs=llrs, F=0, max_iter=max_iter, crc_id=crc_id))
+    run_decode_only_batch(acc, oracle, cases, FLAVOUR_AVX512)
