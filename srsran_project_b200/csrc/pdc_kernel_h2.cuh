@@ -32,8 +32,10 @@
 #include "pdc_device.cuh"
 #include <utility>
 
-#define PDC_H2_TAB_STRIDE 104 /* u32 per (bg, Z): 76 edge entries (offset | PRMT selector << 16) + 26 column alignments */
+#define PDC_H2_TAB_STRIDE 128 /* u32 per (bg, Z): 76 edge entries (offset | PRMT selector << 16), 26 column alignments,
+                                 26 natural-order views (offset | selector) */
 #define PDC_H2_SIGMA_OFF 76
+#define PDC_H2_NAT_OFF 102
 #if defined(PDC_KERNEL_TU)
 __constant__ uint32_t c_h2_tab[2 * PDC_NOF_LIFTING_SIZES][PDC_H2_TAB_STRIDE];
 #endif
@@ -80,6 +82,31 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr)
 __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v)
 {
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v));
+}
+
+// Split-phase barriers on shared-memory mbarriers: a warp announces "our reads (or writes) of this phase are done" with
+// arrive and only blocks, with wait, right before its first access that depends on the other warps. The arithmetic in
+// between overlaps with the slower warps instead of idling at a __syncthreads. One arrival per warp (lane 0 after a
+// __syncwarp); arrive has release and wait has acquire semantics at CTA scope, which orders the shared-memory traffic.
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_warp(uint32_t bar)
+{
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(bar) : "memory");
+  }
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+  asm volatile("{ .reg .pred p;\n"
+               "MBAR_WAIT: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+               "@p bra MBAR_DONE;\n"
+               "bra MBAR_WAIT;\n"
+               "MBAR_DONE: }" ::"r"(bar), "r"(parity)
+               : "memory");
 }
 
 static constexpr uint32_t H2_120 = 0x57805780u, H2_N120 = 0xD780D780u, H2_64 = 0x54005400u, H2_N64 = 0xD400D400u;
@@ -146,13 +173,16 @@ __device__ __forceinline__ uint32_t h2_spread16(uint32_t x)
 // One row (layer) of the decode for the lane pair of this thread. c2v: the thread's message registers of this row.
 template <int BG, int M>
 __device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], const uint32_t* __restrict__ tab,
-                                       uint32_t soft_t, uint32_t row_bytes, bool active, bool generic)
+                                       uint32_t soft_t, uint32_t row_bytes, bool active, bool generic, uint32_t bar_reads,
+                                       uint32_t bar_writes, uint32_t& phase_reads, uint32_t& phase_writes)
 {
   using G            = h2_graph<BG>;
   constexpr int DEG  = G::deg(M);
   constexpr int E0   = h2_row_start<BG>(M);
   uint32_t      u[DEG];
   uint32_t      m1 = H2_120, m2 = H2_120, par = 0;
+  mbar_wait(bar_writes, phase_writes & 1u); // the previous row (or the loader) has stored its soft bits
+  ++phase_writes;
   // ---- pass 1: variable-to-check messages, two smallest magnitudes, sign parity ------------------------------------------
   h2_static_for<DEG>([&](auto k_) {
     constexpr int k   = decltype(k_)::value;
@@ -170,11 +200,10 @@ __device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], con
   const uint32_t s2  = h2_scale(m2, generic);
   const uint32_t d   = s1 ^ s2;
   const uint32_t s1p = s1 | (par & H2_SIGN);
-  __syncthreads(); // every thread has read this row's columns; they may now be overwritten
-  // ---- pass 2: new check-to-variable messages and soft bits ------------------------------------------------------------------
+  mbar_arrive_warp(bar_reads); // this warp has consumed the row's soft bits: they may be overwritten once all have
+  // ---- pass 2: new check-to-variable messages and soft bits (kept in u[] until every thread has read the old ones) ---------
   h2_static_for<DEG>([&](auto k_) {
     constexpr int k   = decltype(k_)::value;
-    constexpr int col = G::col(E0 + k);
     const uint32_t a  = h2_abs(u[k]);
     const uint32_t eq = h2_eq_mask(a, m1);
     const uint32_t cn = (s1p ^ (d & eq)) ^ (u[k] & H2_SIGN);
@@ -183,15 +212,85 @@ __device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], con
     const uint32_t x  = h2_max(h2_abs(t), h2_add(a, H2_N216));
     const uint32_t q  = h2_fma_sat(x, H2_ONE, H2_N120);
     const uint32_t g  = h2_fma(q, H2_65504, H2_ONE);
-    const uint32_t Sn = h2_mul(t, g);
     c2v[E0 + k]       = cn;
-    if (active) {
-      const uint32_t adr = soft_t + col * row_bytes;
-      sts32(adr, Sn);
-      sts32(adr + (row_bytes >> 1), Sn);
-    }
+    u[k]              = h2_mul(t, g);
   });
-  __syncthreads();
+  mbar_wait(bar_reads, phase_reads & 1u);
+  ++phase_reads;
+  if (active) {
+    h2_static_for<DEG>([&](auto k_) {
+      constexpr int k   = decltype(k_)::value;
+      constexpr int col = G::col(E0 + k);
+      const uint32_t adr = soft_t + col * row_bytes;
+      sts32(adr, u[k]);
+      sts32(adr + (row_bytes >> 1), u[k]);
+    });
+  }
+  mbar_arrive_warp(bar_writes);
+}
+
+// Scatter of a first transmission (see pdc_dematch_first_tx) that also fills the natural-order int8 staging copy in
+// shared memory from which the soft rows are loaded. Up to U symbols per thread are in flight before the first store.
+template <int QM>
+__device__ __forceinline__ void h2_dematch_scatter(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
+                                                   int8_t* __restrict__ buf, int8_t* __restrict__ stg, int nstage,
+                                                   int tid, int nth)
+{
+  constexpr int U   = 6;
+  const int     F   = pl.n_sys - pl.n_info;
+  const int     Kq  = pl.E / QM;
+  const int     gs0 = (pl.p0 < pl.n_info) ? pl.p0 : (pl.p0 - F);
+  const bool    vec = (QM == 1) || ((reinterpret_cast<uintptr_t>(in) & (uintptr_t)((QM == 6) ? 1 : (QM - 1))) == 0);
+  for (int i0 = tid; i0 < Kq; i0 += U * nth) {
+    int8_t x[U][QM];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * nth;
+      if (i < Kq) {
+        if (vec && QM == 8) {
+          const int2 w = *reinterpret_cast<const int2*>(in + (size_t)i * 8);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            x[u][j]     = (int8_t)(w.x >> (8 * j));
+            x[u][4 + j] = (int8_t)(w.y >> (8 * j));
+          }
+        } else if (vec && QM == 4) {
+          const int w = *reinterpret_cast<const int*>(in + (size_t)i * 4);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            x[u][j] = (int8_t)(w >> (8 * j));
+          }
+        } else if (vec && (QM == 2 || QM == 6)) {
+#pragma unroll
+          for (int j = 0; j < QM; j += 2) {
+            const short w = *reinterpret_cast<const short*>(in + (size_t)i * QM + j);
+            x[u][j]       = (int8_t)w;
+            x[u][j + 1]   = (int8_t)(w >> 8);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < QM; ++j) {
+            x[u][j] = in[(size_t)i * QM + j];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * nth;
+      if (i < Kq) {
+#pragma unroll
+        for (int j = 0; j < QM; ++j) {
+          const int gidx = gs0 + j * Kq + i;
+          const int pos  = (gidx < pl.n_info) ? gidx : (gidx + F);
+          buf[pos]       = x[u][j];
+          if (pos < nstage) {
+            stg[pos] = x[u][j];
+          }
+        }
+      }
+    }
+  }
 }
 
 template <int BG>
@@ -199,10 +298,8 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
 {
   using G = h2_graph<BG>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ uint32_t s_crc_tab[256];
-  __shared__ uint32_t s_ballot[G::KB][6][2]; // [column][warp][even | odd stored positions]
-  __shared__ uint32_t s_sbits[G::KB][12];    // hard bits of a column in stored order
-  __shared__ uint32_t s_flag[2];
+  __shared__ uint32_t s_red[8];
+  __shared__ __align__(8) uint64_t s_mbar[2]; // [0] reads of a row done, [1] writes of a row done
 
   const int        tid = threadIdx.x, nth = blockDim.x;
   const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
@@ -212,7 +309,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   }
   pdc_geom g;
   pdc_geom_init(g, cb.bg, cb.Z);
-  const int       Z = g.Z, W = Z >> 1, K = g.K, nw = Z >> 5;
+  const int       Z = g.Z, W = Z >> 1, K = g.K;
   const bool      active  = tid < W;
   const bool      generic = (cb.flags & PDC_F_GENERIC) != 0;
   const uint32_t* tab     = c_h2_tab[cb.graph_idx];
@@ -220,45 +317,108 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   pdc_cb_result res;
   res.iterations = -1, res.crc_pass = 0, res.status = 0, res.nof_layers = 4;
 
+  const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+  const uint32_t row_bytes = 4u * (uint32_t)Z; // one column: 2 copies x Z halves
+  const uint32_t soft_t    = smem_base + 4u * (uint32_t)(active ? tid : 0); // idle lanes read lane 0's words
+  // After the soft rows: the natural-order int8 staging copy (prologue) / the packed output words (epilogue).
+  unsigned char* aux       = smem_raw + G::NCOL * row_bytes;
+  const int      nstage    = (G::NCOL - 2) * Z;
+
+  const uint32_t bar_reads  = (uint32_t)__cvta_generic_to_shared(&s_mbar[0]);
+  const uint32_t bar_writes = (uint32_t)__cvta_generic_to_shared(&s_mbar[1]);
+  uint32_t       phase_reads = 0, phase_writes = 0;
+  if (tid == 0) {
+    mbar_init(bar_reads, (uint32_t)nth >> 5);
+    mbar_init(bar_writes, (uint32_t)nth >> 5);
+  }
+
   // ---- prologue 1: rate dematching + HARQ combining into the soft buffer in HBM ------------------------------------------------
-  const int8_t* dec_in;
+  const int8_t* dec_in;       // where load_soft_bits reads from
   int           n_in;
+  bool          from_smem = false;
   if (cb.flags & PDC_F_DECODE_ONLY) {
     dec_in = cb.llrs;
     n_in   = (int)cb.E;
+    __syncthreads();
   } else {
     pdc_dematch_plan pl;
     pdc_dematch_plan_init(pl, g, (int)cb.E, cb.Qm, cb.rv, (int)cb.Nref, (int)cb.nof_filler,
                           (cb.flags & PDC_F_NEW_DATA) != 0);
-    if (pl.new_data && pl.rounds == 1) {
-      pdc_dematch_first_tx(pl, cb.llrs, cb.soft, tid, nth);
+    n_in = g.N;
+    if (pl.new_data && pl.rounds == 1 && pl.Ncb == pl.N && pl.k0 == 0 && pl.E >= pl.n_info) {
+      // First transmission from the start of the buffer, one lap, reaching past the systematic part: every position is a
+      // zero, a filler or exactly one LLR (a shorter one leaves [E, n_info) untouched, i.e. holding whatever the buffer
+      // held before: allot_llrs :134-195). The scatter goes to HBM (HARQ state) and to a natural-order staging copy in
+      // shared memory at the same time.
+      int8_t* stg = reinterpret_cast<int8_t*>(aux);
+      for (int k = tid; k < (nstage >> 4); k += nth) {
+        reinterpret_cast<int4*>(stg)[k] = make_int4(0, 0, 0, 0);
+      }
+      __syncthreads();
+      const int zero_to = (pl.k0 < pl.n_info) ? pl.k0 : pl.n_info;
+      const int fz_from = pl.final_zero ? pl.end_idx : pl.N;
+      for (int q = tid; q < zero_to; q += nth) {
+        cb.soft[q] = 0;
+      }
+      for (int q = pl.n_info + tid; q < pl.n_sys; q += nth) {
+        if (q < fz_from) {
+          cb.soft[q] = PDC_LLR_INF;
+          if (q < nstage) {
+            stg[q] = PDC_LLR_INF;
+          }
+        }
+      }
+      {
+        const uintptr_t a0   = reinterpret_cast<uintptr_t>(cb.soft + fz_from);
+        int             head = (int)((16 - (a0 & 15)) & 15);
+        head                 = min(head, pl.N - fz_from);
+        const int nvec       = (pl.N - fz_from - head) >> 4;
+        for (int q = tid; q < head; q += nth) {
+          cb.soft[fz_from + q] = 0;
+        }
+        int4* v = reinterpret_cast<int4*>(cb.soft + fz_from + head);
+        for (int k = tid; k < nvec; k += nth) {
+          v[k] = make_int4(0, 0, 0, 0);
+        }
+        for (int q = fz_from + head + 16 * nvec + tid; q < pl.N; q += nth) {
+          cb.soft[q] = 0;
+        }
+      }
+      switch (pl.Qm) {
+        case 1:
+          h2_dematch_scatter<1>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          break;
+        case 2:
+          h2_dematch_scatter<2>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          break;
+        case 4:
+          h2_dematch_scatter<4>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          break;
+        case 6:
+          h2_dematch_scatter<6>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          break;
+        default:
+          h2_dematch_scatter<8>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          break;
+      }
+      dec_in    = stg;
+      from_smem = true;
     } else {
-      pdc_dematch(pl, cb.llrs, cb.soft, generic, tid, nth);
+      if (pl.new_data && pl.rounds == 1) {
+        pdc_dematch_first_tx(pl, cb.llrs, cb.soft, tid, nth);
+      } else {
+        pdc_dematch(pl, cb.llrs, cb.soft, generic, tid, nth);
+      }
+      dec_in = cb.soft;
     }
-    dec_in = cb.soft;
-    n_in   = g.N;
+    __syncthreads(); // orders the dematcher's writes before the reads below (same CTA)
   }
-  // CRC byte table of the selected polynomial: tab[b] = b(x) * x^order mod P.
-  const int      crc_order = (cb.crc_type == PDC_CRC16) ? 16 : 24;
-  const uint32_t crc_poly  = (cb.crc_type == PDC_CRC16) ? 0x11021u : ((cb.crc_type == PDC_CRC24A) ? 0x1864CFBu : 0x1800063u);
-  const uint32_t crc_mask  = (1u << crc_order) - 1u;
-  for (int b = tid; b < 256; b += nth) {
-    uint32_t r = (uint32_t)b << (crc_order - 8);
-    for (int k = 0; k < 8; ++k) {
-      r <<= 1;
-      r ^= (r >> crc_order) & 1u ? crc_poly : 0u;
-    }
-    s_crc_tab[b] = r & crc_mask;
-  }
-  __syncthreads(); // orders the dematcher's global writes before the reads below (same CTA)
 
   // ---- prologue 2: load_soft_bits (ldpc_decoder_impl.cpp:150-191) into the rotated, doubled half rows --------------------------
-  const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
-  const uint32_t row_bytes = 4u * (uint32_t)Z; // one column: 2 copies x Z halves
-  const uint32_t soft_t    = smem_base + 4u * (uint32_t)(active ? tid : 0); // idle lanes read lane 0's words
   if (active) {
     sts32(soft_t, 0u), sts32(soft_t + 2u * Z, 0u); // the two punctured columns
     sts32(soft_t + row_bytes, 0u), sts32(soft_t + row_bytes + 2u * Z, 0u);
+#pragma unroll 4
     for (int c = 2; c < G::NCOL; ++c) {
       const int sigma = (int)tab[PDC_H2_SIGMA_OFF + c];
       int       la    = 2 * tid + sigma;
@@ -266,10 +426,16 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
       int lb = la + 1;
       lb -= (lb >= Z) ? Z : 0;
       const int pa = (c - 2) * Z + la, pb = (c - 2) * Z + lb;
-      int       xa = (pa < n_in) ? (int)dec_in[pa] : 0;
-      int       xb = (pb < n_in) ? (int)dec_in[pb] : 0;
-      xa           = max(-64, min(64, xa));
-      xb           = max(-64, min(64, xb));
+      int       xa, xb;
+      if (from_smem) {
+        xa = (int)reinterpret_cast<const int8_t*>(aux)[pa];
+        xb = (int)reinterpret_cast<const int8_t*>(aux)[pb];
+      } else {
+        xa = (pa < n_in) ? (int)dec_in[pa] : 0;
+        xb = (pb < n_in) ? (int)dec_in[pb] : 0;
+      }
+      xa = max(-64, min(64, xa));
+      xb = max(-64, min(64, xb));
       // int16x2 -> half2: 0x6400 | (x + 128) is the half 1024 + 128 + x.
       const uint32_t packed = ((uint32_t)(xa + 0x6480) & 0xffffu) | ((uint32_t)(xb + 0x6480) << 16);
       const uint32_t S      = h2_add(packed, H2_N1152);
@@ -277,15 +443,17 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
       sts32(soft_t + c * row_bytes + 2u * Z, S);
     }
   }
-  __syncthreads();
+  mbar_arrive_warp(bar_writes);
 
-  const uint32_t* crc_pow  = (cb.crc_type != PDC_CRC_NONE) ? prm.crc_pow + (cb.crc_type - 1) * PDC_CRC_TABLE_LEN : nullptr;
   const int       n_sig    = K - (int)cb.nof_filler;
   const bool      has_crc  = cb.crc_type != PDC_CRC_NONE;
   const bool      early    = (cb.flags & PDC_F_EARLY_STOP) && has_crc;
   const int       max_iter = cb.max_iter;
-  const int       nwords   = K >> 5;
-  uint32_t*       out_words = reinterpret_cast<uint32_t*>(smem_raw + G::NCOL * row_bytes); // [K / 32], output byte order
+  const int       crc_order = (cb.crc_type == PDC_CRC16) ? 16 : 24;
+  // x^j mod P table, zero for exponents below the CRC order (filler positions), padded in front: see build_crc_tables().
+  const uint32_t* crc_bit = has_crc ? prm.crc_bit + (cb.crc_type - 1) * PDC_CRC_BIT_TABLE_LEN +
+                                          (PDC_CRC_BIT_PAD + n_sig - 1 + crc_order - 2 * tid)
+                                    : nullptr;
 
   uint32_t c2v[G::NEDGE];
 #pragma unroll
@@ -296,97 +464,76 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   int  it_done = 0;
   bool success = false;
   for (int it = 0; it < max_iter && !success; ++it) {
-    h2_row<BG, 0>(c2v, tab, soft_t, row_bytes, active, generic);
-    h2_row<BG, 1>(c2v, tab, soft_t, row_bytes, active, generic);
-    h2_row<BG, 2>(c2v, tab, soft_t, row_bytes, active, generic);
-    h2_row<BG, 3>(c2v, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 0>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, 1>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, 2>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, 3>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
     it_done = it + 1;
     const bool last = (it_done == max_iter);
-    if (!early && !last) {
+    if (!has_crc || (!early && !last)) {
       continue;
     }
-    // ---- hard decision (log_likelihood_ratio.cpp:350-376): bit = soft <= 0; a zero soft bit refuses the early stop ----------
-    uint32_t amin = H2_ONE;
+    // ---- hard decision + CRC (ldpc_decoder_impl.cpp:127-135, log_likelihood_ratio.cpp:350-376). The CRC is linear: it is
+    //      the xor of x^(n_sig - 1 - n + order) mod P over the set bits n, so every thread folds its own lane pairs, in
+    //      natural order, straight from the soft rows; a zero soft bit among the K systematic ones refuses the early stop.
+    mbar_wait(bar_writes, phase_writes & 1u); // row 3 has stored its soft bits
+    ++phase_writes;
+    uint32_t amin = H2_ONE, acc = 0;
+    if (active) {
 #pragma unroll
-    for (int c = 0; c < G::KB; ++c) {
-      const uint32_t S  = active ? lds32(soft_t + c * row_bytes) : H2_ONE;
-      const uint32_t le = h2_le_mask(S, 0u);
-      amin              = h2_min(amin, h2_abs(S));
-      const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
-      const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
-      if ((tid & 31) == 0) {
-        s_ballot[c][tid >> 5][0] = be;
-        s_ballot[c][tid >> 5][1] = bo;
+      for (int c = 0; c < G::KB; ++c) {
+        const uint32_t ent = tab[PDC_H2_NAT_OFF + c];
+        const uint32_t adr = soft_t + (ent & 0xffffu);
+        const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+        const uint32_t S  = __byte_perm(w0, w1, ent >> 16); // natural lanes (2 tid, 2 tid + 1) of column c
+        amin              = h2_min(amin, h2_abs(S));
+        const uint32_t t_lo = crc_bit[-c * Z], t_hi = crc_bit[-c * Z - 1];
+        asm("{ .reg .pred p, q;\n"
+            "setp.le.f16x2 p|q, %1, %2;\n"
+            "@p xor.b32 %0, %0, %3;\n"
+            "@q xor.b32 %0, %0, %4; }"
+            : "+r"(acc)
+            : "r"(S), "r"(0u), "r"(t_lo), "r"(t_hi));
       }
+    }
+    acc = __reduce_xor_sync(0xffffffffu, acc);
+    if ((tid & 31) == 0) {
+      s_red[tid >> 5] = acc;
     }
     const int bad = __syncthreads_or(((amin & 0x7fffu) == 0) || ((amin & 0x7fff0000u) == 0));
-    // Stored-order bit strings: interleave the even / odd ballots.
-    for (int idx = tid; idx < G::KB * nw; idx += nth) {
-      const int      c = idx / nw, k = idx - c * nw;
-      const uint32_t e16 = (s_ballot[c][k >> 1][0] >> (16 * (k & 1))) & 0xffffu;
-      const uint32_t o16 = (s_ballot[c][k >> 1][1] >> (16 * (k & 1))) & 0xffffu;
-      s_sbits[c][k]      = h2_spread16(e16) | (h2_spread16(o16) << 1);
+    uint32_t  crc = 0;
+    for (int w = 0; w < (nth >> 5); ++w) {
+      crc ^= s_red[w];
     }
-    __syncthreads();
-    // Natural order: lane l of column c sits at stored position (l - sigma_c) mod Z. Output bytes are MSB first.
-    for (int idx = tid; idx < nwords; idx += nth) {
-      const int c = idx / nw, k = idx - c * nw;
-      int       j0 = 32 * k - (int)tab[PDC_H2_SIGMA_OFF + c];
-      j0 += (j0 < 0) ? Z : 0;
-      const int      a = j0 >> 5, b = j0 & 31;
-      const uint32_t lo = s_sbits[c][a], hi = s_sbits[c][(a + 1 == nw) ? 0 : a + 1];
-      const uint32_t nat = __funnelshift_r(lo, hi, b);
-      out_words[idx]     = __byte_perm(__brev(nat), 0u, 0x0123);
-    }
-    __syncthreads();
-    if (has_crc) {
-      // ---- CRC of the first n_sig bits by warp 0: byte-table CRC per lane chunk, chunks combined with x^k mod P ----------------
-      if (tid < 32) {
-        const int ch     = (nwords + 31) >> 5; // words per lane
-        const int bit_lo = 32 * ch * tid;
-        int       bit_hi = bit_lo + 32 * ch;
-        bit_hi           = bit_hi < n_sig ? bit_hi : n_sig;
-        uint32_t acc     = 0;
-        if (bit_lo < bit_hi) {
-          const uint8_t* bytes = reinterpret_cast<const uint8_t*>(out_words);
-          uint32_t       r     = 0;
-          const int      nbytes = (bit_hi - bit_lo) >> 3, rem = (bit_hi - bit_lo) & 7;
-          for (int i = 0; i < nbytes; ++i) {
-            const uint32_t byte = bytes[(bit_lo >> 3) + i];
-            r = ((r << 8) ^ s_crc_tab[((r >> (crc_order - 8)) ^ byte) & 0xffu]) & crc_mask;
-          }
-          if (rem) {
-            const uint32_t byte = bytes[(bit_lo >> 3) + nbytes];
-            for (int k = 0; k < rem; ++k) {
-              const uint32_t bit = (byte >> (7 - k)) & 1u;
-              r                  = (r << 1) ^ (bit << crc_order);
-              r ^= (r >> crc_order) & 1u ? crc_poly : 0u;
-              r &= crc_mask;
-            }
-          }
-          // Shift past the bits that follow this chunk: r(x) * x^kk mod P = xor of x^(kk + b) over the set bits b of r.
-          const int kk = n_sig - bit_hi;
-          for (int b = 0; b < crc_order; ++b) {
-            acc ^= ((r >> b) & 1u) ? crc_pow[kk + b] : 0u;
-          }
-        }
-        acc = __reduce_xor_sync(0xffffffffu, acc);
-        if (tid == 0) {
-          s_flag[0] = (acc == 0u) ? 1u : 0u;
-        }
-      }
-      __syncthreads();
-      const bool crc_ok = s_flag[0] != 0u;
-      if (early) {
-        success = crc_ok && !bad;
-      } else {
-        success = crc_ok; // pusch_codeblock_decoder.cpp:62-73: one CRC after the last iteration, zero soft bits allowed
-      }
-    }
+    // pusch_codeblock_decoder.cpp:62-73: without early stop there is one CRC after the last iteration and zero soft bits
+    // do not matter.
+    success = (crc == 0u) && (early ? !bad : true);
+    mbar_arrive_warp(bar_writes); // pairs with the wait at the top of the next iteration's first row
   }
 
-  for (int w = tid; w < nwords; w += nth) {
-    reinterpret_cast<uint32_t*>(cb.out)[w] = out_words[w];
+  // ---- output: K hard bits in natural order, MSB first (bit_buffer.h:106-136). Lane l of column c sits at half index
+  //      l + (Z - sigma_c) of the doubled row; a warp ballot packs 32 consecutive lanes. -----------------------------------------
+  if (!(has_crc && (early || it_done == max_iter))) {
+    mbar_wait(bar_writes, phase_writes & 1u);
+  }
+  __syncthreads();
+  {
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
+    for (int c = 0; c < G::KB; ++c) {
+      const int      sigma = (int)tab[PDC_H2_SIGMA_OFF + c];
+      const uint32_t base  = smem_base + c * row_bytes + 2u * (uint32_t)((sigma == 0) ? 0 : (Z - sigma));
+      for (int l0 = 0; l0 < Z; l0 += nth) {
+        const int l = l0 + tid;
+        int       h = 1; // positive: bit 0
+        if (l < Z) {
+          asm volatile("ld.shared.s16 %0, [%1];" : "=r"(h) : "r"(base + 2u * (uint32_t)l));
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, h <= 0); // +0 is 0x0000, negatives have the sign bit: h <= 0 as int
+        if ((tid & 31) == 0 && (l0 + (tid & ~31)) < Z) {
+          out32[(c * Z + l0 + (tid & ~31)) >> 5] = __byte_perm(__brev(word), 0u, 0x0123);
+        }
+      }
+    }
   }
   if (success) {
     res.iterations = early ? it_done : max_iter;
@@ -403,8 +550,8 @@ extern "C" int pdc_h2_supported(int bg, int Z)
 }
 extern "C" size_t pdc_h2_smem_bytes(int bg, int Z, int)
 {
-  const int ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
-  return (size_t)ncol * 4 * Z + (size_t)kb * Z / 8;
+  const int ncol = (bg == 1) ? 26 : 14;
+  return (size_t)ncol * 4 * Z + (size_t)(ncol - 2) * Z; // soft rows + staging copy
 }
 extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream)
 {
@@ -457,6 +604,10 @@ static cudaError_t pdc_h2_init_device()
           }
         }
         dst[PDC_H2_SIGMA_OFF + c] = (uint32_t)sigma[c];
+        // Natural order seen through the doubled row: lane l sits at half index l + (Z - sigma) mod Z.
+        const int      nat = (Z - sigma[c]) % Z;
+        const uint32_t no  = (uint32_t)c * 4u * (uint32_t)Z + 4u * (uint32_t)(nat >> 1);
+        dst[PDC_H2_NAT_OFF + c] = no | (((nat & 1) ? 0x5432u : 0x3210u) << 16);
       }
       for (int e = 0; e != ne; ++e) {
         // Previous writer of this column: the nearest earlier row holding it, cyclically (previous iteration included).

@@ -87,15 +87,18 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   if (!cuda_ok(ctx, cudaSetDevice(cfg->device), "cudaSetDevice")) {
     return fail(PDC_ERR_CUDA);
   }
-  std::vector<uint32_t> graphs, crc;
+  std::vector<uint32_t> graphs, crc, crc_bit;
   pdc_bg_rows           rows;
   build_graph_tables(graphs, rows);
   build_crc_tables(crc);
+  build_crc_bit_tables(crc, crc_bit);
   if (!cuda_ok(ctx, pdc_kernels_init_device(&rows), "pdc_kernels_init_device") ||
       !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_graphs, graphs.size() * 4), "cudaMalloc graphs") ||
       !cuda_ok(ctx, cudaMemcpy(ctx->d_graphs, graphs.data(), graphs.size() * 4, cudaMemcpyHostToDevice), "copy") ||
       !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_crc, crc.size() * 4), "cudaMalloc crc") ||
-      !cuda_ok(ctx, cudaMemcpy(ctx->d_crc, crc.data(), crc.size() * 4, cudaMemcpyHostToDevice), "copy")) {
+      !cuda_ok(ctx, cudaMemcpy(ctx->d_crc, crc.data(), crc.size() * 4, cudaMemcpyHostToDevice), "copy") ||
+      !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_crc_bit, crc_bit.size() * 4), "cudaMalloc crc bit table") ||
+      !cuda_ok(ctx, cudaMemcpy(ctx->d_crc_bit, crc_bit.data(), crc_bit.size() * 4, cudaMemcpyHostToDevice), "copy")) {
     return fail(PDC_ERR_CUDA);
   }
   if (cfg->harq_slots != 0) {
@@ -124,7 +127,7 @@ void pdc_destroy(pdc_ctx* ctx)
   for (ticket_t& t : ctx->tickets) {
     free_ticket(t);
   }
-  cudaFree(ctx->d_graphs), cudaFree(ctx->d_crc), cudaFree(ctx->d_harq);
+  cudaFree(ctx->d_graphs), cudaFree(ctx->d_crc), cudaFree(ctx->d_crc_bit), cudaFree(ctx->d_harq);
   delete ctx;
 }
 

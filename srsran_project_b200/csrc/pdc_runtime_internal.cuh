@@ -60,6 +60,7 @@ struct pdc_ctx {
   int64_t               next_id = 1;
   uint32_t*             d_graphs = nullptr;
   uint32_t*             d_crc    = nullptr;
+  uint32_t*             d_crc_bit = nullptr;
   int8_t*               d_harq   = nullptr;
   std::atomic<uint64_t> launches{0};
   size_t                bits_stride_total = 0;
@@ -156,6 +157,19 @@ void build_crc_tables(std::vector<uint32_t>& out)
   }
 }
 
+// Per-bit CRC table of the packed kernel: entry PAD + j = x^j mod P for j >= order and 0 below, so that the bit at
+// position n of an n_sig-bit message adds entry PAD + (n_sig - 1 - n + order) and filler positions (n >= n_sig) add 0.
+void build_crc_bit_tables(const std::vector<uint32_t>& pow, std::vector<uint32_t>& out)
+{
+  static const int order[3] = {16, 24, 24};
+  out.assign((size_t)3 * PDC_CRC_BIT_TABLE_LEN, 0);
+  for (int c = 0; c != 3; ++c) {
+    for (int j = order[c]; j < PDC_CRC_TABLE_LEN; ++j) {
+      out[(size_t)c * PDC_CRC_BIT_TABLE_LEN + PDC_CRC_BIT_PAD + j] = pow[(size_t)c * PDC_CRC_TABLE_LEN + j];
+    }
+  }
+}
+
 // Validates one descriptor the way the reference's asserts would and fills the derived fields.
 bool validate_desc(const pdc_cb_desc& d, pdc_geom& g, int& max_layers)
 {
@@ -208,7 +222,7 @@ struct batch_plan {
 // Which code blocks the packed half2 kernel takes: the four core rows only, Z a multiple of 32 (pdc_kernel_h2.cuh).
 bool takes_h2(const pdc_cb_desc& d, int max_layers)
 {
-  if (!pdc_h2_supported(d.bg, d.Z) || max_layers != 4) {
+  if (!pdc_h2_supported(d.bg, d.Z) || max_layers != 4 || d.nof_filler > PDC_CRC_BIT_PAD - 32) {
     return false;
   }
   if (d.flags & (PDC_F_DEMATCH_ONLY | PDC_F_FORCE_DECODING)) {
@@ -273,6 +287,7 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
   prm.cbs     = d_cbs;
   prm.graphs  = ctx->d_graphs;
   prm.crc_pow = ctx->d_crc;
+  prm.crc_bit = ctx->d_crc_bit;
   uint32_t off = 0;
   for (int k = 0; k != 2; ++k) {
     if (bp.n_h2[k] != 0) {
