@@ -511,28 +511,38 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
     mbar_arrive_warp(bar_writes); // pairs with the wait at the top of the next iteration's first row
   }
 
-  // ---- output: K hard bits in natural order, MSB first (bit_buffer.h:106-136). Lane l of column c sits at half index
-  //      l + (Z - sigma_c) of the doubled row; a warp ballot packs 32 consecutive lanes. -----------------------------------------
+  // ---- output: K hard bits in natural order, MSB first (bit_buffer.h:106-136). Every thread reads its natural lane pair
+  //      of each column (as the CRC pass does); two warp ballots give the even and the odd lanes of 64 consecutive bits,
+  //      which are then interleaved, bit-reversed per byte and stored with coalesced words. -------------------------------------
   if (!(has_crc && (early || it_done == max_iter))) {
     mbar_wait(bar_writes, phase_writes & 1u);
   }
   __syncthreads();
   {
-    uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
+    uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]
+#pragma unroll
     for (int c = 0; c < G::KB; ++c) {
-      const int      sigma = (int)tab[PDC_H2_SIGMA_OFF + c];
-      const uint32_t base  = smem_base + c * row_bytes + 2u * (uint32_t)((sigma == 0) ? 0 : (Z - sigma));
-      for (int l0 = 0; l0 < Z; l0 += nth) {
-        const int l = l0 + tid;
-        int       h = 1; // positive: bit 0
-        if (l < Z) {
-          asm volatile("ld.shared.s16 %0, [%1];" : "=r"(h) : "r"(base + 2u * (uint32_t)l));
-        }
-        const uint32_t word = __ballot_sync(0xffffffffu, h <= 0); // +0 is 0x0000, negatives have the sign bit: h <= 0 as int
-        if ((tid & 31) == 0 && (l0 + (tid & ~31)) < Z) {
-          out32[(c * Z + l0 + (tid & ~31)) >> 5] = __byte_perm(__brev(word), 0u, 0x0123);
-        }
+      const uint32_t ent = tab[PDC_H2_NAT_OFF + c];
+      const uint32_t adr = soft_t + (ent & 0xffffu);
+      const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+      const uint32_t S  = __byte_perm(w0, w1, ent >> 16);
+      const uint32_t le = active ? h2_le_mask(S, 0u) : 0u;
+      const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
+      const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
+      if ((tid & 31) == 0) {
+        s_bal[(c * 6 + (tid >> 5)) * 2 + 0] = be;
+        s_bal[(c * 6 + (tid >> 5)) * 2 + 1] = bo;
       }
+    }
+    __syncthreads();
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
+    const int nw    = Z >> 5;
+    for (int idx = tid; idx < (K >> 5); idx += nth) {
+      const int      c = idx / nw, k = idx - c * nw;
+      const uint32_t e16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 0] >> (16 * (k & 1))) & 0xffffu;
+      const uint32_t o16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 1] >> (16 * (k & 1))) & 0xffffu;
+      const uint32_t nat = h2_spread16(e16) | (h2_spread16(o16) << 1);
+      out32[idx]         = __byte_perm(__brev(nat), 0u, 0x0123);
     }
   }
   if (success) {
@@ -550,8 +560,9 @@ extern "C" int pdc_h2_supported(int bg, int Z)
 }
 extern "C" size_t pdc_h2_smem_bytes(int bg, int Z, int)
 {
-  const int ncol = (bg == 1) ? 26 : 14;
-  return (size_t)ncol * 4 * Z + (size_t)(ncol - 2) * Z; // soft rows + staging copy
+  const int    ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
+  const size_t aux  = (size_t)(ncol - 2) * Z > (size_t)kb * 48 ? (size_t)(ncol - 2) * Z : (size_t)kb * 48;
+  return (size_t)ncol * 4 * Z + aux; // soft rows + (staging copy of the prologue | ballot words of the output)
 }
 extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream)
 {
