@@ -15,7 +15,9 @@ if [ ! -d "$REF/lib/phy/upper/channel_coding/ldpc" ]; then
   exit 0
 fi
 mkdir -p "$OBJ"
-CXX=${CXX:-g++}
+# The environment's CXX may be a wrapper that links libstdc++ statically; several private copies of libstdc++ in one
+# process (this library, the adapters, numpy) corrupt each other's locale facets. Use the system compiler, shared runtime.
+CXX=${PDC_CXX:-/usr/bin/g++}
 INC="-I$REF/include -I$REF/external/fmt/include -I$REF/external -I$REF/lib -I$REF/lib/phy/upper/channel_coding -I$REF/lib/phy/upper/channel_processors/pusch"
 BASE="-std=c++17 -O3 -fPIC -march=x86-64-v3 -mtune=generic -fno-trapping-math -fno-math-errno -DFMT_HEADER_ONLY -DASSERTS_ENABLED -w"
 

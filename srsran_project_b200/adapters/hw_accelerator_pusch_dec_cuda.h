@@ -1,0 +1,33 @@
+// CUDA implementation of the reference's hardware-accelerated PUSCH decoder HAL interface
+// (include/srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec.h:83-115), the drop-in that
+// pusch_decoder_hw_impl (lib/phy/upper/channel_processors/pusch/pusch_decoder_hw_impl.cpp:149-364) drives in place of the
+// bbdev / ACC100 accelerator (whose implementation is not part of the open-source tree:
+// lib/hal/phy/upper/channel_processors/pusch/hw_accelerator_factories.cpp:28-36 returns nullptr).
+#pragma once
+
+#include "cuda_pusch_dec_context.h"
+#include "srsran/hal/phy/upper/channel_processors/pusch/hw_accelerator_pusch_dec_factory.h"
+
+namespace srsran {
+namespace hal {
+
+/// Configuration of the CUDA PUSCH decoder accelerator factory (the counterpart of
+/// bbdev_hwacc_pusch_dec_factory_configuration, hw_accelerator_factories.h:33-45).
+struct cuda_hwacc_pusch_dec_factory_configuration {
+  /// Shared accelerator context (one per GPU); created on device 0 with defaults when empty.
+  std::shared_ptr<cuda::pusch_dec_context> context;
+  /// Keeps the HARQ soft buffers in the device arena, keyed by the absolute code-block identifier (the reference's
+  /// "external HARQ" mode, ext_harq_buffer_context_repository.h:36-107). When false the soft buffer travels from and to
+  /// the host with every operation, as with force_local_harq of the bbdev factory.
+  bool external_harq = true;
+  /// Reproduce ldpc_decoder_generic instead of ldpc_decoder_avx512 / _avx2.
+  bool generic_arithmetic = false;
+};
+
+/// \brief Creates a CUDA PUSCH decoder hardware accelerator factory.
+/// \return A valid factory. Throws std::runtime_error if no CUDA device is usable (there is no CPU fallback).
+std::shared_ptr<hw_accelerator_pusch_dec_factory>
+create_cuda_pusch_dec_acc_factory(const cuda_hwacc_pusch_dec_factory_configuration& accelerator_config);
+
+} // namespace hal
+} // namespace srsran

@@ -1,0 +1,230 @@
+// TEST INFRASTRUCTURE ONLY. Boundary test harness: the UNMODIFIED reference transport-block decoders
+// (pusch_decoder_impl and pusch_decoder_hw_impl, compiled from /root/reference by tests/adapters/build.sh) driving
+//   mode 0: the reference's own software operators (ldpc_decoder_avx512 | avx2 | generic + matching dematcher) — the oracle,
+//   mode 1: the CUDA ldpc_decoder + ldpc_rate_dematcher (srsran_project_b200/adapters/channel_coding_factories_cuda.h)
+//           inside the reference's pusch_codeblock_decoder / pusch_decoder_impl (drop-in boundary 1),
+//   mode 2: the CUDA hal::hw_accelerator_pusch_dec inside the reference's pusch_decoder_hw_impl (drop-in boundary 2).
+// Driven from Python (tests/test_adapters.py) through a small C ABI; the stimulus comes from tools/stimulus.
+#include "../../srsran_project_b200/adapters/channel_coding_factories_cuda.h"
+#include "../../srsran_project_b200/adapters/hw_accelerator_pusch_dec_cuda.h"
+#include "crc_calculator_clmul_impl.h"
+#include "crc_calculator_lut_impl.h"
+#include "ldpc/ldpc_decoder_avx2.h"
+#include "ldpc/ldpc_decoder_avx512.h"
+#include "ldpc/ldpc_decoder_generic.h"
+#include "ldpc/ldpc_rate_dematcher_avx2_impl.h"
+#include "ldpc/ldpc_rate_dematcher_avx512_impl.h"
+#include "ldpc/ldpc_rate_dematcher_impl.h"
+#include "ldpc/ldpc_segmenter_rx_impl.h"
+#include "pusch_codeblock_decoder.h"
+#include "pusch_decoder_hw_impl.h"
+#include "pusch_decoder_impl.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_notifier.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_result.h"
+#include "srsran/phy/upper/rx_buffer_pool.h"
+#include "srsran/phy/upper/unique_rx_buffer.h"
+#include <cstring>
+#include <memory>
+#include <vector>
+
+using namespace srsran;
+
+namespace {
+
+struct notifier_capture : public pusch_decoder_notifier {
+  pusch_decoder_result last;
+  bool                 called = false;
+  void                 on_sch_data(const pusch_decoder_result& result) override
+  {
+    last   = result;
+    called = true;
+  }
+};
+
+std::unique_ptr<crc_calculator> make_crc(crc_generator_poly poly)
+{
+  if (__builtin_cpu_supports("pclmul")) {
+    return std::make_unique<crc_calculator_clmul_impl>(poly);
+  }
+  return std::make_unique<crc_calculator_lut_impl>(poly);
+}
+
+std::unique_ptr<ldpc_decoder> make_sw_decoder(int flavour)
+{
+  if (flavour == 2) {
+    return std::make_unique<ldpc_decoder_avx512>(false);
+  }
+  if (flavour == 1) {
+    return std::make_unique<ldpc_decoder_avx2>(false);
+  }
+  return std::make_unique<ldpc_decoder_generic>(false);
+}
+
+std::unique_ptr<ldpc_rate_dematcher> make_sw_dematcher(int flavour)
+{
+  if (flavour == 2) {
+    return std::make_unique<ldpc_rate_dematcher_avx512_impl>();
+  }
+  if (flavour == 1) {
+    return std::make_unique<ldpc_rate_dematcher_avx2_impl>();
+  }
+  return std::make_unique<ldpc_rate_dematcher_impl>();
+}
+
+struct harness {
+  std::shared_ptr<cuda::pusch_dec_context>   context;
+  std::unique_ptr<rx_buffer_pool_controller> pool;
+  std::unique_ptr<pusch_decoder>             decoder;
+  unsigned                                   pool_codeblocks = 0;
+};
+
+} // namespace
+
+extern "C" {
+
+// mode: see the header comment. dec_flavour / dem_flavour (mode 0): 0 generic, 1 AVX2, 2 AVX512. cuda_generic (modes 1, 2):
+// reproduce the generic decoder instead of the AVX one. external_harq (mode 2): soft buffers live in the device arena.
+void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, int external_harq, unsigned nof_buffers,
+                 unsigned nof_codeblocks)
+{
+  __builtin_cpu_init();
+  auto h             = std::make_unique<harness>();
+  h->pool_codeblocks = nof_codeblocks;
+
+  rx_buffer_pool_config pool_cfg = {};
+  pool_cfg.max_codeblock_size   = ldpc::MAX_CODEBLOCK_SIZE;
+  pool_cfg.nof_buffers          = nof_buffers;
+  pool_cfg.nof_codeblocks       = nof_codeblocks;
+  pool_cfg.expire_timeout_slots = 100000;
+  pool_cfg.external_soft_bits   = (mode == 2) && (external_harq != 0);
+  h->pool                       = create_rx_buffer_pool(pool_cfg);
+
+  if (mode != 0) {
+    cuda::pusch_dec_context_config ccfg;
+    ccfg.max_batch_cbs   = 152;
+    ccfg.max_batch_llrs  = 4u << 20;
+    ccfg.harq_codeblocks = nof_codeblocks;
+    ccfg.nof_instances   = 4;
+    h->context           = std::make_shared<cuda::pusch_dec_context>(ccfg);
+  }
+  ldpc_decoder_cuda_flavour fl = cuda_generic ? ldpc_decoder_cuda_flavour::generic : ldpc_decoder_cuda_flavour::avx512;
+
+  if (mode == 2) {
+    hal::cuda_hwacc_pusch_dec_factory_configuration acfg;
+    acfg.context            = h->context;
+    acfg.external_harq      = external_harq != 0;
+    acfg.generic_arithmetic = cuda_generic != 0;
+    auto acc_factory        = hal::create_cuda_pusch_dec_acc_factory(acfg);
+    std::vector<std::unique_ptr<hal::hw_accelerator_pusch_dec>> accs;
+    for (unsigned i = 0; i != 2; ++i) {
+      accs.push_back(acc_factory->create());
+    }
+    auto hw_pool = std::make_shared<pusch_decoder_hw_impl::hw_decoder_pool>(accs);
+    pusch_decoder_hw_impl::sch_crc crcs = {make_crc(crc_generator_poly::CRC16),
+                                           make_crc(crc_generator_poly::CRC24A),
+                                           make_crc(crc_generator_poly::CRC24B)};
+    h->decoder = std::make_unique<pusch_decoder_hw_impl>(std::make_unique<ldpc_segmenter_rx_impl>(), crcs, hw_pool, nullptr);
+  } else {
+    std::shared_ptr<ldpc_decoder_factory>        dec_factory;
+    std::shared_ptr<ldpc_rate_dematcher_factory> dem_factory;
+    if (mode == 1) {
+      dec_factory = create_ldpc_decoder_factory_cuda({false}, h->context, fl);
+      dem_factory = create_ldpc_rate_dematcher_factory_cuda(h->context, fl);
+    }
+    std::vector<std::unique_ptr<pusch_codeblock_decoder>> cb_decoders;
+    for (unsigned i = 0; i != 2; ++i) {
+      pusch_codeblock_decoder::sch_crc crcs = {make_crc(crc_generator_poly::CRC16),
+                                               make_crc(crc_generator_poly::CRC24A),
+                                               make_crc(crc_generator_poly::CRC24B)};
+      cb_decoders.push_back(std::make_unique<pusch_codeblock_decoder>(
+          (mode == 1) ? dem_factory->create() : make_sw_dematcher(dem_flavour),
+          (mode == 1) ? dec_factory->create() : make_sw_decoder(dec_flavour),
+          crcs));
+    }
+    auto cb_pool = std::make_shared<pusch_decoder_impl::codeblock_decoder_pool>(cb_decoders);
+    pusch_decoder_impl::sch_crc crcs = {make_crc(crc_generator_poly::CRC16),
+                                        make_crc(crc_generator_poly::CRC24A),
+                                        make_crc(crc_generator_poly::CRC24B)};
+    h->decoder = std::make_unique<pusch_decoder_impl>(
+        std::make_unique<ldpc_segmenter_rx_impl>(), cb_pool, std::move(crcs), nullptr, MAX_RB, 4);
+  }
+  return h.release();
+}
+
+void adt_destroy(void* handle)
+{
+  auto* h = static_cast<harness*>(handle);
+  if (h) {
+    h->decoder.reset();
+    h->pool->stop();
+    delete h;
+  }
+}
+
+// Decodes one transmission of one transport block (HARQ process harq_id). Returns 0, or a negative value if the soft
+// buffer could not be reserved / the notifier was not called. stats: [tb_crc_ok, nof_codeblocks, nof_observations,
+// min_iterations, max_iterations, mean_iterations * 1000].
+int adt_decode_tb(void*         handle,
+                  unsigned      harq_id,
+                  int           new_data,
+                  unsigned      rv,
+                  int           bg,
+                  unsigned      Qm,
+                  unsigned      nof_layers,
+                  unsigned      Nref,
+                  unsigned      max_iter,
+                  int           early_stop,
+                  unsigned      tbs_bits,
+                  const int8_t* llrs,
+                  unsigned      nof_llrs,
+                  uint8_t*      tb_out,
+                  int64_t*      stats)
+{
+  auto* h = static_cast<harness*>(handle);
+
+  pusch_decoder::configuration cfg = {};
+  cfg.base_graph          = (bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+  cfg.rv                  = rv;
+  cfg.mod                 = static_cast<modulation_scheme>(Qm);
+  cfg.Nref                = Nref;
+  cfg.nof_layers          = nof_layers;
+  cfg.nof_ldpc_iterations = max_iter;
+  cfg.force_decoding      = false;
+  cfg.use_early_stop      = early_stop != 0;
+  cfg.new_data            = new_data != 0;
+
+  unsigned         nof_cbs = ldpc::compute_nof_codeblocks(units::bits(tbs_bits), cfg.base_graph);
+  unique_rx_buffer buffer  = h->pool->get_pool().reserve({}, trx_buffer_identifier(1, harq_id), nof_cbs, new_data != 0);
+  if (!buffer.is_valid()) {
+    return -1;
+  }
+  if (new_data) {
+    buffer.get().reset_codeblocks_crc();
+  }
+
+  std::vector<uint8_t> tb(tbs_bits / 8, 0);
+  notifier_capture     notifier;
+  pusch_decoder_buffer& in = h->decoder->new_data(tb, std::move(buffer), notifier, cfg);
+  span<const log_likelihood_ratio> view(reinterpret_cast<const log_likelihood_ratio*>(llrs), nof_llrs);
+  // Feed the codeword in two chunks with the length announced in between, as pusch_decoder_vectortest.cpp:357-375 does.
+  unsigned first = nof_llrs / 2;
+  in.on_new_softbits(view.first(first));
+  h->decoder->set_nof_softbits(units::bits(nof_llrs));
+  in.on_new_softbits(view.last(nof_llrs - first));
+  in.on_end_softbits();
+  if (!notifier.called) {
+    return -2;
+  }
+  std::memcpy(tb_out, tb.data(), tb.size());
+  const pusch_decoder_result& r = notifier.last;
+  stats[0]                      = r.tb_crc_ok ? 1 : 0;
+  stats[1]                      = r.nof_codeblocks_total;
+  stats[2]                      = r.ldpc_decoder_stats.get_nof_observations();
+  bool any                      = r.ldpc_decoder_stats.get_nof_observations() != 0;
+  stats[3]                      = any ? r.ldpc_decoder_stats.get_min() : 0;
+  stats[4]                      = any ? r.ldpc_decoder_stats.get_max() : 0;
+  stats[5]                      = any ? static_cast<int64_t>(r.ldpc_decoder_stats.get_mean() * 1000.0 + 0.5) : 0;
+  return 0;
+}
+
+} // extern "C"
