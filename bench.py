@@ -73,12 +73,13 @@ def build_workload(args, rank):
     if args.population == "awgn":
         msgs = np.zeros((n_cbs, seg["K"]), np.uint8)
         for t in range(n_tbs):
-            rng = np.random.default_rng(1000 * rank + 100 + t)
+            g = tb_shard(rank, n_tbs)[t]  # global transport-block index: every rank decodes different blocks
+            rng = np.random.default_rng(100 + g)
             tb = rng.integers(0, 2, c["tbs"], dtype=np.uint8)
             _, bits, m = S.tb_encode(c["bg"], c["tbs"], tb, c["rv"], c["Qm"], 0, c["nof_layers"], c["G"])
             msgs[t * seg["C"]:(t + 1) * seg["C"]] = m
             for s in range(args.input_sets):
-                llrs = S.awgn_llrs(bits, 8.0, args.sigma, 7919 * (1000 * rank + t) + s + 1)
+                llrs = S.awgn_llrs(bits, 8.0, args.sigma, 7919 * g + s + 1)
                 p = 0
                 for r in range(seg["C"]):
                     i = t * seg["C"] + r
@@ -253,6 +254,62 @@ def workload_config(args, wl):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# Ranks: one process per GPU, sharded by transport block, NO collective on the data path. torch.distributed only carries
+# the barrier around the timed region and the max / sum over ranks of scalars (timing, decoded bits).
+# ---------------------------------------------------------------------------------------------------------------------
+class Ranks:
+    def __init__(self, backend, device, local=0):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.device = device
+        self.dist = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            if backend == "nccl":
+                dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            else:
+                dist.init_process_group(backend)
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        if self.device == "cuda":
+            import torch
+
+            torch.cuda.synchronize()
+
+    def _reduce(self, x, op):
+        if self.dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max(self, x):
+        return self._reduce(x, self.dist.ReduceOp.MAX if self.dist else None)
+
+    def sum(self, x):
+        return self._reduce(x, self.dist.ReduceOp.SUM if self.dist else None)
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+            self.dist = None
+
+
+def tb_shard(rank, n_tbs_per_rank):
+    """Transport blocks (global indices) decoded by `rank`: weak scaling, a fixed slot of TBs per GPU, TB t of rank r is
+    cell r * n + t of the multi-cell load (BASELINE config 5). A TB's code blocks and HARQ slots stay on one GPU."""
+    return range(rank * n_tbs_per_rank, (rank + 1) * n_tbs_per_rank)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
 # CUDA arm
 # ---------------------------------------------------------------------------------------------------------------------
 def run_cuda_arm(args):
@@ -266,30 +323,8 @@ def run_cuda_arm(args):
     if not torch.cuda.is_available():
         raise RuntimeError("no CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    ranks = Ranks("nccl", "cuda", local)
+    barrier, max_over_ranks, sum_over_ranks = ranks.barrier, ranks.max, ranks.sum
 
     wl = build_workload(args, rank)
     n, nsets = wl["n_cbs"], len(wl["llr_sets"])
@@ -394,8 +429,8 @@ def run_cuda_arm(args):
     d2h = n * OUT_STRIDE + n * 8
 
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
+        ctx.close()
+        ranks.close()
         return
 
     # ---- roofline: integer / half2 ALU issue rate measured on this device in this run ------------------------------------
@@ -453,8 +488,7 @@ def run_cuda_arm(args):
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
     ctx.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    ranks.close()
 
 
 def main():
