@@ -20,6 +20,11 @@
 //   * The instruction mix is split over both issue pipes on purpose: min / max / logic on the ALU pipe, add / promotion /
 //     scaling as HFMA2 on the FMA pipe (see the pipe utilisation in profiles/).
 //
+// Two instantiations per base graph: ZC == 0 takes the lifting size at run time (relative shifts from the constant-memory
+// table below); ZC == 384 is the metric's operating point with every shift, offset and PRMT selector folded into the
+// instruction stream as an immediate (no table loads, no uniform-datapath address arithmetic, and no second load + PRMT
+// for the edges whose relative shift is even).
+//
 // Arithmetic (bit-exact with ldpc_decoder_avx512 / ldpc_decoder_generic; model and proof-by-test in tests/h2_model.py):
 //   u   = S - c_old                                     v2c, unclamped; +-inf stays +-inf
 //   m1, m2 = two smallest |u| capped at 120; par = xor of signs
@@ -83,6 +88,25 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v)
 {
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v));
 }
+// Same with a compile-time byte offset that ends up in the instruction's immediate field.
+template <int OFF>
+__device__ __forceinline__ uint32_t lds32i(uint32_t addr)
+{
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ void sts32i(uint32_t addr, uint32_t v)
+{
+  asm volatile("st.shared.u32 [%0+%1], %2;" ::"r"(addr), "n"(OFF), "r"(v));
+}
+__device__ __forceinline__ uint32_t lds16(uint32_t addr)
+{
+  uint32_t v;
+  asm volatile("{ .reg .b16 t; ld.shared.u16 t, [%1]; cvt.u32.u16 %0, t; }" : "=r"(v) : "r"(addr));
+  return v;
+}
 
 // Split-phase barriers on shared-memory mbarriers: a warp announces "our reads (or writes) of this phase are done" with
 // arrive and only blocks, with wait, right before its first access that depends on the other warps. The arithmetic in
@@ -140,6 +164,51 @@ struct h2_graph<2> {
   __host__ __device__ static constexpr int col(int e) { return pdc_bg2_edge_col[e]; }
 };
 template <int BG>
+__host__ __device__ constexpr int h2_shift(int ils, int e)
+{
+  return (BG == 1) ? pdc_bg1_edge_shift[ils][e] : pdc_bg2_edge_shift[ils][e];
+}
+__host__ __device__ constexpr int h2_set_index(int Z)
+{
+  const int base[8] = {2, 3, 5, 7, 9, 11, 13, 15};
+  int       ils     = 0;
+  for (int i = 0; i != 8; ++i) {
+    int z = base[i];
+    while (z < Z) {
+      z *= 2;
+    }
+    ils = (z == Z) ? i : ils;
+  }
+  return ils;
+}
+// Alignment of column c after a full iteration = shift of the last core-row edge that holds it (0 if none does).
+template <int BG>
+__host__ __device__ constexpr int h2_sigma(int Z, int c)
+{
+  const int ils = h2_set_index(Z);
+  int       sg  = 0;
+  for (int e = 0; e != h2_graph<BG>::NEDGE; ++e) {
+    if (h2_graph<BG>::col(e) == c) {
+      sg = h2_shift<BG>(ils, e) % Z;
+    }
+  }
+  return sg;
+}
+// Rotation of edge e's view relative to how its column was stored by the previous writer (the nearest earlier edge on the
+// same column, cyclically: the previous iteration's last writer for the first edge of a column).
+template <int BG>
+__host__ __device__ constexpr int h2_rel(int Z, int e)
+{
+  const int ils  = h2_set_index(Z);
+  int       prev = h2_sigma<BG>(Z, h2_graph<BG>::col(e));
+  for (int e2 = 0; e2 != e; ++e2) {
+    if (h2_graph<BG>::col(e2) == h2_graph<BG>::col(e)) {
+      prev = h2_shift<BG>(ils, e2) % Z; // edges are listed row by row: a later match is a later row
+    }
+  }
+  return ((h2_shift<BG>(ils, e) % Z) - prev + Z) % Z;
+}
+template <int BG>
 __host__ __device__ constexpr int h2_row_start(int m)
 {
   int s = 0;
@@ -170,8 +239,63 @@ __device__ __forceinline__ uint32_t h2_spread16(uint32_t x)
   return x;
 }
 
+// The rotated view of edge E (absolute edge index) of the thread's lane pair: compile-time offsets for ZC > 0, else the
+// (offset | PRMT selector << 16) entry of the constant-memory table.
+template <int BG, int ZC, int E>
+__device__ __forceinline__ uint32_t h2_read_edge(const uint32_t* __restrict__ tab, uint32_t soft_t)
+{
+  if constexpr (ZC > 0) {
+    constexpr int rel = h2_rel<BG>(ZC, E);
+    constexpr int off = h2_graph<BG>::col(E) * 4 * ZC + 4 * (rel >> 1);
+    if constexpr ((rel & 1) == 0) {
+      return lds32i<off>(soft_t);
+    } else {
+      const uint32_t w0 = lds32i<off>(soft_t), w1 = lds32i<off + 4>(soft_t);
+      return __byte_perm(w0, w1, 0x5432);
+    }
+  } else {
+    const uint32_t ent = tab[E];
+    const uint32_t adr = soft_t + (ent & 0xffffu);
+    const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+    return __byte_perm(w0, w1, ent >> 16);
+  }
+}
+// Natural-order view (lanes 2 tid, 2 tid + 1) of column C.
+template <int BG, int ZC, int C>
+__device__ __forceinline__ uint32_t h2_read_natural(const uint32_t* __restrict__ tab, uint32_t soft_t)
+{
+  if constexpr (ZC > 0) {
+    constexpr int nat = (ZC - h2_sigma<BG>(ZC, C)) % ZC;
+    constexpr int off = C * 4 * ZC + 4 * (nat >> 1);
+    if constexpr ((nat & 1) == 0) {
+      return lds32i<off>(soft_t);
+    } else {
+      const uint32_t w0 = lds32i<off>(soft_t), w1 = lds32i<off + 4>(soft_t);
+      return __byte_perm(w0, w1, 0x5432);
+    }
+  } else {
+    const uint32_t ent = tab[PDC_H2_NAT_OFF + C];
+    const uint32_t adr = soft_t + (ent & 0xffffu);
+    const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+    return __byte_perm(w0, w1, ent >> 16);
+  }
+}
+// Both copies of the thread's word of column C.
+template <int ZC, int C>
+__device__ __forceinline__ void h2_write_col(uint32_t soft_t, uint32_t row_bytes, uint32_t v)
+{
+  if constexpr (ZC > 0) {
+    sts32i<C * 4 * ZC>(soft_t, v);
+    sts32i<C * 4 * ZC + 2 * ZC>(soft_t, v);
+  } else {
+    const uint32_t adr = soft_t + C * row_bytes;
+    sts32(adr, v);
+    sts32(adr + (row_bytes >> 1), v);
+  }
+}
+
 // One row (layer) of the decode for the lane pair of this thread. c2v: the thread's message registers of this row.
-template <int BG, int M>
+template <int BG, int ZC, int M>
 __device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], const uint32_t* __restrict__ tab,
                                        uint32_t soft_t, uint32_t row_bytes, bool active, bool generic, uint32_t bar_reads,
                                        uint32_t bar_writes, uint32_t& phase_reads, uint32_t& phase_writes)
@@ -186,10 +310,7 @@ __device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], con
   // ---- pass 1: variable-to-check messages, two smallest magnitudes, sign parity ------------------------------------------
   h2_static_for<DEG>([&](auto k_) {
     constexpr int k   = decltype(k_)::value;
-    const uint32_t ent = tab[E0 + k];
-    const uint32_t adr = soft_t + (ent & 0xffffu);
-    const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
-    const uint32_t S  = __byte_perm(w0, w1, ent >> 16);
+    const uint32_t S  = h2_read_edge<BG, ZC, E0 + k>(tab, soft_t);
     u[k]              = h2_sub(S, c2v[E0 + k]);
     const uint32_t a  = h2_abs(u[k]);
     m2                = h2_min(m2, h2_max(m1, a));
@@ -217,83 +338,142 @@ __device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], con
   });
   mbar_wait(bar_reads, phase_reads & 1u);
   ++phase_reads;
-  if (active) {
+  if (ZC > 0 || active) {
     h2_static_for<DEG>([&](auto k_) {
-      constexpr int k   = decltype(k_)::value;
-      constexpr int col = G::col(E0 + k);
-      const uint32_t adr = soft_t + col * row_bytes;
-      sts32(adr, u[k]);
-      sts32(adr + (row_bytes >> 1), u[k]);
+      constexpr int k = decltype(k_)::value;
+      h2_write_col<ZC, G::col(E0 + k)>(soft_t, row_bytes, u[k]);
     });
   }
   mbar_arrive_warp(bar_writes);
 }
 
-// Scatter of a first transmission (see pdc_dematch_first_tx) that also fills the natural-order int8 staging copy in
-// shared memory from which the soft rows are loaded. Up to U symbols per thread are in flight before the first store.
-template <int QM>
-__device__ __forceinline__ void h2_dematch_scatter(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
-                                                   int8_t* __restrict__ buf, int8_t* __restrict__ stg, int nstage,
-                                                   int tid, int nth)
+// ---- prologue of a first transmission: deinterleaver into a natural-order int8 staging tile in shared memory ------------
+// deinterleave (ldpc_rate_dematcher_impl.cpp:203-257): x[(E/Qm) j + i] = in[i Qm + j]; the walk over the circular buffer
+// then skips the filler window (allot_llrs :128-201), i.e. stream index g lands at g (g < n_info) or g + F.
+//
+// Vector variant: one task = 4 consecutive symbols = 4 Qm bytes loaded with 64/128-bit loads; a byte transposition in
+// registers (PRMT) turns them into Qm words of 4 consecutive stream positions each, stored with 32-bit stores.
+// Needs Kq % 4 == 0, F % 4 == 0 and an 8-byte (Qm = 8, 4: 16-byte) aligned input; the caller checks.
+__device__ __forceinline__ void h2_transpose4(uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t (&o)[4])
 {
-  constexpr int U   = 6;
-  const int     F   = pl.n_sys - pl.n_info;
-  const int     Kq  = pl.E / QM;
-  const int     gs0 = (pl.p0 < pl.n_info) ? pl.p0 : (pl.p0 - F);
-  const bool    vec = (QM == 1) || ((reinterpret_cast<uintptr_t>(in) & (uintptr_t)((QM == 6) ? 1 : (QM - 1))) == 0);
-  for (int i0 = tid; i0 < Kq; i0 += U * nth) {
-    int8_t x[U][QM];
+  const uint32_t t0 = __byte_perm(a, b, 0x5140), t1 = __byte_perm(a, b, 0x7362);
+  const uint32_t t2 = __byte_perm(c, d, 0x5140), t3 = __byte_perm(c, d, 0x7362);
+  o[0] = __byte_perm(t0, t2, 0x5410), o[1] = __byte_perm(t0, t2, 0x7632);
+  o[2] = __byte_perm(t1, t3, 0x5410), o[3] = __byte_perm(t1, t3, 0x7632);
+}
+template <int QM>
+__device__ __forceinline__ void h2_task_words(const int8_t* __restrict__ src, uint32_t (&w)[QM])
+{
+  if constexpr (QM == 8 || QM == 4) {
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = i0 + u * nth;
-      if (i < Kq) {
-        if (vec && QM == 8) {
-          const int2 w = *reinterpret_cast<const int2*>(in + (size_t)i * 8);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            x[u][j]     = (int8_t)(w.x >> (8 * j));
-            x[u][4 + j] = (int8_t)(w.y >> (8 * j));
-          }
-        } else if (vec && QM == 4) {
-          const int w = *reinterpret_cast<const int*>(in + (size_t)i * 4);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            x[u][j] = (int8_t)(w >> (8 * j));
-          }
-        } else if (vec && (QM == 2 || QM == 6)) {
-#pragma unroll
-          for (int j = 0; j < QM; j += 2) {
-            const short w = *reinterpret_cast<const short*>(in + (size_t)i * QM + j);
-            x[u][j]       = (int8_t)w;
-            x[u][j + 1]   = (int8_t)(w >> 8);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < QM; ++j) {
-            x[u][j] = in[(size_t)i * QM + j];
-          }
-        }
-      }
+    for (int r = 0; r < QM / 4; ++r) {
+      const int4 v = __ldg(reinterpret_cast<const int4*>(src) + r);
+      w[4 * r] = (uint32_t)v.x, w[4 * r + 1] = (uint32_t)v.y, w[4 * r + 2] = (uint32_t)v.z, w[4 * r + 3] = (uint32_t)v.w;
     }
+  } else {
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = i0 + u * nth;
-      if (i < Kq) {
+    for (int r = 0; r < QM / 2; ++r) {
+      const int2 v = __ldg(reinterpret_cast<const int2*>(src) + r);
+      w[2 * r] = (uint32_t)v.x, w[2 * r + 1] = (uint32_t)v.y;
+    }
+  }
+}
+// Byte k of the 4 Qm-byte chunk held in w[].
+template <int QM, int K0, int K1>
+__device__ __forceinline__ uint32_t h2_pick2(const uint32_t (&w)[QM])
+{
+  return __byte_perm(w[K0 / 4], w[K1 / 4], (K0 % 4) | ((4 + K1 % 4) << 4));
+}
+template <int QM>
+__device__ __forceinline__ void h2_task_transpose(const uint32_t (&w)[QM], uint32_t (&o)[QM])
+{
+  if constexpr (QM == 8) {
+    uint32_t lo[4], hi[4];
+    h2_transpose4(w[0], w[2], w[4], w[6], lo);
+    h2_transpose4(w[1], w[3], w[5], w[7], hi);
 #pragma unroll
-        for (int j = 0; j < QM; ++j) {
-          const int gidx = gs0 + j * Kq + i;
-          const int pos  = (gidx < pl.n_info) ? gidx : (gidx + F);
-          buf[pos]       = x[u][j];
-          if (pos < nstage) {
-            stg[pos] = x[u][j];
-          }
-        }
+    for (int j = 0; j < 4; ++j) {
+      o[j] = lo[j], o[4 + j] = hi[j];
+    }
+  } else if constexpr (QM == 4) {
+    h2_transpose4(w[0], w[1], w[2], w[3], o);
+  } else if constexpr (QM == 2) {
+    o[0] = __byte_perm(w[0], w[1], 0x6420), o[1] = __byte_perm(w[0], w[1], 0x7531);
+  } else {
+    h2_static_for<QM>([&](auto j_) {
+      constexpr int j = decltype(j_)::value;
+      o[j] = __byte_perm(h2_pick2<QM, j, QM + j>(w), h2_pick2<QM, 2 * QM + j, 3 * QM + j>(w), 0x5410);
+    });
+  }
+}
+template <int QM>
+__device__ __forceinline__ void h2_deinterleave_vec(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
+                                                    uint32_t stg_addr, int tid, int nth)
+{
+  const int F = pl.n_sys - pl.n_info, Kq = pl.E / QM, ntask = Kq >> 2;
+  for (int k0 = tid; k0 < ntask; k0 += 2 * nth) { // two tasks in flight per thread
+    const int k1   = k0 + nth;
+    const bool has1 = k1 < ntask;
+    uint32_t   w0[QM], w1[QM], o[QM];
+    h2_task_words<QM>(in + (size_t)k0 * 4 * QM, w0);
+    if (has1) {
+      h2_task_words<QM>(in + (size_t)k1 * 4 * QM, w1);
+    }
+    h2_task_transpose<QM>(w0, o);
+#pragma unroll
+    for (int j = 0; j < QM; ++j) {
+      const int g = j * Kq + 4 * k0;
+      sts32(stg_addr + (uint32_t)((g < pl.n_info) ? g : (g + F)), o[j]);
+    }
+    if (has1) {
+      h2_task_transpose<QM>(w1, o);
+#pragma unroll
+      for (int j = 0; j < QM; ++j) {
+        const int g = j * Kq + 4 * k1;
+        sts32(stg_addr + (uint32_t)((g < pl.n_info) ? g : (g + F)), o[j]);
       }
     }
   }
 }
+// Byte variant for inputs that miss the alignment conditions (odd fillers, Kq not a multiple of 4, Qm = 1).
+template <int QM>
+__device__ __forceinline__ void h2_deinterleave_bytes(const pdc_dematch_plan& pl, const int8_t* __restrict__ in,
+                                                      int8_t* __restrict__ stg, int tid, int nth)
+{
+  const int F = pl.n_sys - pl.n_info, Kq = pl.E / QM;
+  for (int i = tid; i < Kq; i += nth) {
+#pragma unroll
+    for (int j = 0; j < QM; ++j) {
+      const int g                        = j * Kq + i;
+      stg[(g < pl.n_info) ? g : (g + F)] = in[(size_t)i * QM + j];
+    }
+  }
+}
+template <int QM>
+__device__ __forceinline__ void h2_deinterleave(const pdc_dematch_plan& pl, const int8_t* __restrict__ in, int8_t* stg,
+                                                uint32_t stg_addr, int tid, int nth)
+{
+  if constexpr (QM == 1) {
+    h2_deinterleave_bytes<1>(pl, in, stg, tid, nth);
+  } else {
+    const int       F     = pl.n_sys - pl.n_info, Kq = pl.E / QM;
+    const uintptr_t align = (QM == 8 || QM == 4) ? 15 : 7;
+    if (((Kq | F) & 3) == 0 && (reinterpret_cast<uintptr_t>(in) & align) == 0) {
+      h2_deinterleave_vec<QM>(pl, in, stg_addr, tid, nth);
+    } else {
+      h2_deinterleave_bytes<QM>(pl, in, stg, tid, nth);
+    }
+  }
+}
 
-template <int BG>
+// int8 pair (low two bytes of w) -> clamped half2 soft bits: offset binary, 0x6400 | (x + 128) is the half 1024 + 128 + x.
+__device__ __forceinline__ uint32_t h2_soft_from_bytes(uint32_t w)
+{
+  const uint32_t p = __byte_perm(w ^ 0x8080u, 0x64646464u, 0x4140);
+  return h2_max(h2_min(h2_add(p, H2_N1152), H2_64), H2_N64);
+}
+
+template <int BG, int ZC>
 __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm)
 {
   using G = h2_graph<BG>;
@@ -304,13 +484,13 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   const int        tid = threadIdx.x, nth = blockDim.x;
   const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
   const pdc_dev_cb cb  = prm.cbs[cbi];
-  if (cb.bg != BG) {
-    return; // the host launches one grid per base graph; a mismatch is a host bug and leaves status untouched
+  if (cb.bg != BG || (ZC > 0 && (cb.Z != ZC || nth != ZC / 2))) {
+    return; // the host launches one grid per (base graph, specialisation); a mismatch is a host bug: status stays untouched
   }
   pdc_geom g;
   pdc_geom_init(g, cb.bg, cb.Z);
-  const int       Z = g.Z, W = Z >> 1, K = g.K;
-  const bool      active  = tid < W;
+  const int       Z = (ZC > 0) ? ZC : g.Z, W = Z >> 1, K = G::KB * Z;
+  const bool      active  = (ZC > 0) || (tid < W);
   const bool      generic = (cb.flags & PDC_F_GENERIC) != 0;
   const uint32_t* tab     = c_h2_tab[cb.graph_idx];
 
@@ -320,8 +500,9 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
   const uint32_t row_bytes = 4u * (uint32_t)Z; // one column: 2 copies x Z halves
   const uint32_t soft_t    = smem_base + 4u * (uint32_t)(active ? tid : 0); // idle lanes read lane 0's words
-  // After the soft rows: the natural-order int8 staging copy (prologue) / the packed output words (epilogue).
+  // After the soft rows: the natural-order int8 staging copy (prologue) / the ballot words (output).
   unsigned char* aux       = smem_raw + G::NCOL * row_bytes;
+  const uint32_t aux_addr  = smem_base + G::NCOL * row_bytes;
   const int      nstage    = (G::NCOL - 2) * Z;
 
   const uint32_t bar_reads  = (uint32_t)__cvta_generic_to_shared(&s_mbar[0]);
@@ -333,8 +514,8 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   }
 
   // ---- prologue 1: rate dematching + HARQ combining into the soft buffer in HBM ------------------------------------------------
-  const int8_t* dec_in;       // where load_soft_bits reads from
-  int           n_in;
+  const int8_t* dec_in = nullptr; // where load_soft_bits reads from (global memory), unless the staging tile holds it
+  int           n_in   = 0;
   bool          from_smem = false;
   if (cb.flags & PDC_F_DECODE_ONLY) {
     dec_in = cb.llrs;
@@ -345,63 +526,57 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
     pdc_dematch_plan_init(pl, g, (int)cb.E, cb.Qm, cb.rv, (int)cb.Nref, (int)cb.nof_filler,
                           (cb.flags & PDC_F_NEW_DATA) != 0);
     n_in = g.N;
-    if (pl.new_data && pl.rounds == 1 && pl.Ncb == pl.N && pl.k0 == 0 && pl.E >= pl.n_info) {
-      // First transmission from the start of the buffer, one lap, reaching past the systematic part: every position is a
-      // zero, a filler or exactly one LLR (a shorter one leaves [E, n_info) untouched, i.e. holding whatever the buffer
-      // held before: allot_llrs :134-195). The scatter goes to HBM (HARQ state) and to a natural-order staging copy in
-      // shared memory at the same time.
+    const int end_pos = pl.final_zero ? pl.end_idx : pl.N;
+    if (pl.new_data && pl.rounds == 1 && pl.Ncb == pl.N && pl.k0 == 0 && pl.E >= pl.n_info && end_pos <= nstage) {
+      // First transmission from the start of the buffer, one lap, reaching past the systematic part: every position of the
+      // N-entry soft buffer is a zero, a filler or exactly one LLR (a shorter one leaves [E, n_info) untouched, i.e. holding
+      // whatever the buffer held before: allot_llrs :134-195), and everything that is not zero lies in the first nstage
+      // entries. Build them in the natural-order staging tile, then stream tile + zeros to HBM (the HARQ state) with
+      // 16-byte stores while the soft rows are loaded from the tile.
       int8_t* stg = reinterpret_cast<int8_t*>(aux);
-      for (int k = tid; k < (nstage >> 4); k += nth) {
-        reinterpret_cast<int4*>(stg)[k] = make_int4(0, 0, 0, 0);
-      }
-      __syncthreads();
-      const int zero_to = (pl.k0 < pl.n_info) ? pl.k0 : pl.n_info;
-      const int fz_from = pl.final_zero ? pl.end_idx : pl.N;
-      for (int q = tid; q < zero_to; q += nth) {
-        cb.soft[q] = 0;
-      }
       for (int q = pl.n_info + tid; q < pl.n_sys; q += nth) {
-        if (q < fz_from) {
-          cb.soft[q] = PDC_LLR_INF;
-          if (q < nstage) {
-            stg[q] = PDC_LLR_INF;
-          }
+        if (q < end_pos) {
+          stg[q] = PDC_LLR_INF; // filler bits (:162-166)
         }
       }
-      {
-        const uintptr_t a0   = reinterpret_cast<uintptr_t>(cb.soft + fz_from);
-        int             head = (int)((16 - (a0 & 15)) & 15);
-        head                 = min(head, pl.N - fz_from);
-        const int nvec       = (pl.N - fz_from - head) >> 4;
-        for (int q = tid; q < head; q += nth) {
-          cb.soft[fz_from + q] = 0;
-        }
-        int4* v = reinterpret_cast<int4*>(cb.soft + fz_from + head);
-        for (int k = tid; k < nvec; k += nth) {
-          v[k] = make_int4(0, 0, 0, 0);
-        }
-        for (int q = fz_from + head + 16 * nvec + tid; q < pl.N; q += nth) {
-          cb.soft[q] = 0;
-        }
+      for (int q = end_pos + tid; q < nstage; q += nth) {
+        stg[q] = 0; // final zero (:198-200)
       }
       switch (pl.Qm) {
         case 1:
-          h2_dematch_scatter<1>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          h2_deinterleave<1>(pl, cb.llrs, stg, aux_addr, tid, nth);
           break;
         case 2:
-          h2_dematch_scatter<2>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          h2_deinterleave<2>(pl, cb.llrs, stg, aux_addr, tid, nth);
           break;
         case 4:
-          h2_dematch_scatter<4>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          h2_deinterleave<4>(pl, cb.llrs, stg, aux_addr, tid, nth);
           break;
         case 6:
-          h2_dematch_scatter<6>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          h2_deinterleave<6>(pl, cb.llrs, stg, aux_addr, tid, nth);
           break;
         default:
-          h2_dematch_scatter<8>(pl, cb.llrs, cb.soft, stg, nstage, tid, nth);
+          h2_deinterleave<8>(pl, cb.llrs, stg, aux_addr, tid, nth);
           break;
       }
-      dec_in    = stg;
+      __syncthreads();
+      if ((reinterpret_cast<uintptr_t>(cb.soft) & 15) == 0) {
+        int4*     dst = reinterpret_cast<int4*>(cb.soft);
+        const int n16 = nstage >> 4, N16 = pl.N >> 4; // Z is a multiple of 32
+        for (int q = tid; q < n16; q += nth) {
+          dst[q] = reinterpret_cast<const int4*>(stg)[q];
+        }
+        for (int q = n16 + tid; q < N16; q += nth) {
+          dst[q] = make_int4(0, 0, 0, 0);
+        }
+      } else {
+        for (int q = tid; q < nstage; q += nth) {
+          cb.soft[q] = stg[q];
+        }
+        for (int q = nstage + tid; q < pl.N; q += nth) {
+          cb.soft[q] = 0;
+        }
+      }
       from_smem = true;
     } else {
       if (pl.new_data && pl.rounds == 1) {
@@ -410,37 +585,55 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
         pdc_dematch(pl, cb.llrs, cb.soft, generic, tid, nth);
       }
       dec_in = cb.soft;
+      __syncthreads(); // orders the dematcher's writes before the reads below (same CTA)
     }
-    __syncthreads(); // orders the dematcher's writes before the reads below (same CTA)
   }
 
   // ---- prologue 2: load_soft_bits (ldpc_decoder_impl.cpp:150-191) into the rotated, doubled half rows --------------------------
   if (active) {
     sts32(soft_t, 0u), sts32(soft_t + 2u * Z, 0u); // the two punctured columns
     sts32(soft_t + row_bytes, 0u), sts32(soft_t + row_bytes + 2u * Z, 0u);
+    if (ZC > 0 && from_smem) {
+      // Staging tile -> rows with every rotation known at compile time: lanes (2 tid + sigma, + 1) mod Z of column c.
+      h2_static_for<G::NCOL - 2>([&](auto c_) {
+        constexpr int c     = decltype(c_)::value + 2;
+        constexpr int sigma = (ZC > 0) ? h2_sigma<BG>(ZC > 0 ? ZC : 32, c) : 0;
+        constexpr int Zc    = (ZC > 0) ? ZC : 32;
+        const uint32_t base = aux_addr + (uint32_t)((c - 2) * Zc);
+        uint32_t       w;
+        if constexpr ((sigma & 1) == 0) {
+          int la = 2 * tid + sigma;
+          la -= (la >= Zc) ? Zc : 0;
+          w = lds16(base + la);
+        } else {
+          int la = 2 * tid + sigma; // odd
+          la -= (la >= Zc) ? Zc : 0;
+          int lb = la + 1;          // even
+          lb -= (lb >= Zc) ? Zc : 0;
+          w = __byte_perm(lds16(base + la - 1), lds16(base + lb), 0x0041);
+        }
+        h2_write_col<ZC, c>(soft_t, row_bytes, h2_soft_from_bytes(w));
+      });
+    } else {
 #pragma unroll 4
-    for (int c = 2; c < G::NCOL; ++c) {
-      const int sigma = (int)tab[PDC_H2_SIGMA_OFF + c];
-      int       la    = 2 * tid + sigma;
-      la -= (la >= Z) ? Z : 0;
-      int lb = la + 1;
-      lb -= (lb >= Z) ? Z : 0;
-      const int pa = (c - 2) * Z + la, pb = (c - 2) * Z + lb;
-      int       xa, xb;
-      if (from_smem) {
-        xa = (int)reinterpret_cast<const int8_t*>(aux)[pa];
-        xb = (int)reinterpret_cast<const int8_t*>(aux)[pb];
-      } else {
-        xa = (pa < n_in) ? (int)dec_in[pa] : 0;
-        xb = (pb < n_in) ? (int)dec_in[pb] : 0;
+      for (int c = 2; c < G::NCOL; ++c) {
+        const int sigma = (int)tab[PDC_H2_SIGMA_OFF + c];
+        int       la    = 2 * tid + sigma;
+        la -= (la >= Z) ? Z : 0;
+        int lb = la + 1;
+        lb -= (lb >= Z) ? Z : 0;
+        const int pa = (c - 2) * Z + la, pb = (c - 2) * Z + lb;
+        uint32_t  xa, xb;
+        if (from_smem) {
+          xa = aux[pa], xb = aux[pb];
+        } else {
+          xa = (pa < n_in) ? (uint8_t)dec_in[pa] : 0u;
+          xb = (pb < n_in) ? (uint8_t)dec_in[pb] : 0u;
+        }
+        const uint32_t S = h2_soft_from_bytes(xa | (xb << 8));
+        sts32(soft_t + c * row_bytes, S);
+        sts32(soft_t + c * row_bytes + 2u * Z, S);
       }
-      xa = max(-64, min(64, xa));
-      xb = max(-64, min(64, xb));
-      // int16x2 -> half2: 0x6400 | (x + 128) is the half 1024 + 128 + x.
-      const uint32_t packed = ((uint32_t)(xa + 0x6480) & 0xffffu) | ((uint32_t)(xb + 0x6480) << 16);
-      const uint32_t S      = h2_add(packed, H2_N1152);
-      sts32(soft_t + c * row_bytes, S);
-      sts32(soft_t + c * row_bytes + 2u * Z, S);
     }
   }
   mbar_arrive_warp(bar_writes);
@@ -464,10 +657,10 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   int  it_done = 0;
   bool success = false;
   for (int it = 0; it < max_iter && !success; ++it) {
-    h2_row<BG, 0>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, 1>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, 2>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, 3>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 0>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 1>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 2>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 3>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
     it_done = it + 1;
     const bool last = (it_done == max_iter);
     if (!has_crc || (!early && !last)) {
@@ -480,12 +673,9 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
     ++phase_writes;
     uint32_t amin = H2_ONE, acc = 0;
     if (active) {
-#pragma unroll
-      for (int c = 0; c < G::KB; ++c) {
-        const uint32_t ent = tab[PDC_H2_NAT_OFF + c];
-        const uint32_t adr = soft_t + (ent & 0xffffu);
-        const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
-        const uint32_t S  = __byte_perm(w0, w1, ent >> 16); // natural lanes (2 tid, 2 tid + 1) of column c
+      h2_static_for<G::KB>([&](auto c_) {
+        constexpr int  c  = decltype(c_)::value;
+        const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t); // natural lanes (2 tid, 2 tid + 1) of column c
         amin              = h2_min(amin, h2_abs(S));
         const uint32_t t_lo = crc_bit[-c * Z], t_hi = crc_bit[-c * Z - 1];
         asm("{ .reg .pred p, q;\n"
@@ -494,7 +684,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
             "@q xor.b32 %0, %0, %4; }"
             : "+r"(acc)
             : "r"(S), "r"(0u), "r"(t_lo), "r"(t_hi));
-      }
+      });
     }
     acc = __reduce_xor_sync(0xffffffffu, acc);
     if ((tid & 31) == 0) {
@@ -520,12 +710,9 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
   __syncthreads();
   {
     uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]
-#pragma unroll
-    for (int c = 0; c < G::KB; ++c) {
-      const uint32_t ent = tab[PDC_H2_NAT_OFF + c];
-      const uint32_t adr = soft_t + (ent & 0xffffu);
-      const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
-      const uint32_t S  = __byte_perm(w0, w1, ent >> 16);
+    h2_static_for<G::KB>([&](auto c_) {
+      constexpr int  c  = decltype(c_)::value;
+      const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t);
       const uint32_t le = active ? h2_le_mask(S, 0u) : 0u;
       const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
       const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
@@ -533,7 +720,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
         s_bal[(c * 6 + (tid >> 5)) * 2 + 0] = be;
         s_bal[(c * 6 + (tid >> 5)) * 2 + 1] = bo;
       }
-    }
+    });
     __syncthreads();
     uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
     const int nw    = Z >> 5;
@@ -564,12 +751,25 @@ extern "C" size_t pdc_h2_smem_bytes(int bg, int Z, int)
   const size_t aux  = (size_t)(ncol - 2) * Z > (size_t)kb * 48 ? (size_t)(ncol - 2) * Z : (size_t)kb * 48;
   return (size_t)ncol * 4 * Z + aux; // soft rows + (staging copy of the prologue | ballot words of the output)
 }
-extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream)
+// zc: 0 = lifting sizes taken at run time (mixed list), 384 = every code block of the list has Z = 384.
+extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int zc, int block, size_t smem,
+                                     cudaStream_t stream)
 {
+  if (zc == 384 && block != 192) {
+    return cudaErrorInvalidValue;
+  }
   if (bg == 1) {
-    pdc_cb_kernel_h2<1><<<prm.n, block, smem, stream>>>(prm);
+    if (zc == 384) {
+      pdc_cb_kernel_h2<1, 384><<<prm.n, block, smem, stream>>>(prm);
+    } else {
+      pdc_cb_kernel_h2<1, 0><<<prm.n, block, smem, stream>>>(prm);
+    }
   } else {
-    pdc_cb_kernel_h2<2><<<prm.n, block, smem, stream>>>(prm);
+    if (zc == 384) {
+      pdc_cb_kernel_h2<2, 384><<<prm.n, block, smem, stream>>>(prm);
+    } else {
+      pdc_cb_kernel_h2<2, 0><<<prm.n, block, smem, stream>>>(prm);
+    }
   }
   return cudaGetLastError();
 }

@@ -23,13 +23,13 @@ extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows)
   if (e != cudaSuccess) {
     return e;
   }
-  e = cudaFuncSetAttribute(pdc_cb_kernel_h2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-  if (e != cudaSuccess) {
-    return e;
-  }
-  e = cudaFuncSetAttribute(pdc_cb_kernel_h2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-  if (e != cudaSuccess) {
-    return e;
+  const void* h2_kernels[4] = {(const void*)pdc_cb_kernel_h2<1, 0>, (const void*)pdc_cb_kernel_h2<2, 0>,
+                               (const void*)pdc_cb_kernel_h2<1, 384>, (const void*)pdc_cb_kernel_h2<2, 384>};
+  for (const void* k : h2_kernels) {
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e != cudaSuccess) {
+      return e;
+    }
   }
   return pdc_h2_init_device();
 }

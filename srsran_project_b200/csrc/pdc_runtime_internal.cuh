@@ -15,7 +15,8 @@
 #include <vector>
 
 extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream);
-extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_launch_h2(const pdc_launch_params& prm, int bg, int zc, int block, size_t smem,
+                                     cudaStream_t stream);
 extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows);
 extern "C" cudaError_t pdc_probe_run(int mode, int sm_count, cudaStream_t stream, double* thread_inst_per_s);
 extern "C" int         pdc_h2_supported(int bg, int Z);
@@ -214,9 +215,10 @@ size_t lane_smem_bytes(const pdc_geom& g, int max_layers)
 }
 
 struct batch_plan {
-  size_t   smem_lane = 0, smem_h2[2] = {0, 0};
-  int      block_lane = 32, block_h2[2] = {32, 32};
-  uint32_t n_lane = 0, n_h2[2] = {0, 0}; // order array: packed-kernel CBs of BG1, then of BG2, then lane-kernel CBs
+  // Packed-kernel lists: [0] BG1 any Z, [1] BG2 any Z, [2] BG1 Z = 384, [3] BG2 Z = 384 (compile-time specialisations).
+  size_t   smem_lane = 0, smem_h2[4] = {0, 0, 0, 0};
+  int      block_lane = 32, block_h2[4] = {32, 32, 32, 32};
+  uint32_t n_lane = 0, n_h2[4] = {0, 0, 0, 0}; // order array: the four packed-kernel lists, then the lane-kernel CBs
 };
 
 // Which code blocks the packed half2 kernel takes: the four core rows only, Z a multiple of 32 (pdc_kernel_h2.cuh).
@@ -237,7 +239,7 @@ bool takes_h2(const pdc_cb_desc& d, int max_layers)
 // Fills dev[i] (pointers left to the caller) and the launch order; returns PDC_OK or the first invalid descriptor.
 pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, pdc_dev_cb* dev, uint32_t* order, batch_plan& bp)
 {
-  std::vector<uint32_t> lists[3];
+  std::vector<uint32_t> lists[5];
   for (auto& l : lists) {
     l.reserve(n);
   }
@@ -254,23 +256,24 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, pdc_dev_cb* dev, uin
     c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
     c.max_layers = (uint16_t)ml;
     if (takes_h2(d, ml)) {
-      int k = d.bg - 1;
+      int k = (d.bg - 1) + ((d.Z == 384) ? 2 : 0);
       lists[k].push_back(i);
       size_t s      = pdc_h2_smem_bytes(d.bg, d.Z, ml);
       bp.smem_h2[k] = s > bp.smem_h2[k] ? s : bp.smem_h2[k];
       int blk       = (d.Z / 2 + 31) / 32 * 32;
       bp.block_h2[k] = blk > bp.block_h2[k] ? blk : bp.block_h2[k];
     } else {
-      lists[2].push_back(i);
+      lists[4].push_back(i);
       size_t s     = (d.flags & PDC_F_DEMATCH_ONLY) ? 0 : lane_smem_bytes(g, ml);
       bp.smem_lane = s > bp.smem_lane ? s : bp.smem_lane;
       int blk      = (d.Z + 31) / 32 * 32;
       bp.block_lane = blk > bp.block_lane ? blk : bp.block_lane;
     }
   }
-  bp.n_h2[0] = (uint32_t)lists[0].size();
-  bp.n_h2[1] = (uint32_t)lists[1].size();
-  bp.n_lane  = (uint32_t)lists[2].size();
+  for (int k = 0; k != 4; ++k) {
+    bp.n_h2[k] = (uint32_t)lists[k].size();
+  }
+  bp.n_lane = (uint32_t)lists[4].size();
   uint32_t k = 0;
   for (auto& l : lists) {
     for (uint32_t i : l) {
@@ -289,11 +292,11 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
   prm.crc_pow = ctx->d_crc;
   prm.crc_bit = ctx->d_crc_bit;
   uint32_t off = 0;
-  for (int k = 0; k != 2; ++k) {
+  for (int k = 0; k != 4; ++k) {
     if (bp.n_h2[k] != 0) {
       prm.order = d_order + off;
       prm.n     = (int)bp.n_h2[k];
-      CK(pdc_launch_h2(prm, k + 1, bp.block_h2[k], bp.smem_h2[k], stream));
+      CK(pdc_launch_h2(prm, (k & 1) + 1, (k & 2) ? 384 : 0, bp.block_h2[k], bp.smem_h2[k], stream));
       ctx->launches++;
       off += bp.n_h2[k];
     }
