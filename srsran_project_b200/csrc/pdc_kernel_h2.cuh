@@ -78,6 +78,12 @@ __device__ __forceinline__ uint32_t h2_fma_sat(uint32_t a, uint32_t b, uint32_t 
   asm("fma.rn.sat.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
   return d;
 }
+__device__ __forceinline__ uint32_t h2_add_sat(uint32_t a, uint32_t b)
+{
+  uint32_t d;
+  asm("add.rn.sat.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t addr)
 {
   uint32_t v;
@@ -137,6 +143,10 @@ static constexpr uint32_t H2_120 = 0x57805780u, H2_N120 = 0xD780D780u, H2_64 = 0
 static constexpr uint32_t H2_N216 = 0xDAC0DAC0u, H2_65504 = 0x7BFF7BFFu, H2_ONE = 0x3C003C00u, H2_1024 = 0x64006400u;
 static constexpr uint32_t H2_N1024 = 0xE400E400u, H2_1023_5 = 0x63FF63FFu, H2_0_8 = 0x3A663A66u, H2_N1152 = 0xE480E480u;
 static constexpr uint32_t H2_SIGN = 0x80008000u;
+// Soft bits sit in shared memory with a bias of 1152 = 1024 + 128: the half 1152 + x is the bit pattern 0x6400 | (x + 128)
+// for every int8 x, which is what makes packing / unpacking int8 <-> half a single PRMT (see h2_row).
+static constexpr uint32_t H2_BIAS = 0x64806480u, H2_BIAS_P64 = 0x64C064C0u, H2_BIAS_N64 = 0x64406440u;
+static constexpr uint32_t H2_N336 = 0xDD40DD40u;
 
 // Normalisation of a non-negative integer <= 120 held in both halves: (x * 52428) >> 16 (AVX2 / AVX512) or
 // round(0.8f * x) (generic). One fused multiply-add whose single rounding lands on the integer we want.
@@ -294,47 +304,116 @@ __device__ __forceinline__ void h2_write_col(uint32_t soft_t, uint32_t row_bytes
   }
 }
 
-// One row (layer) of the decode for the lane pair of this thread. c2v: the thread's message registers of this row.
+// ---- check-to-variable messages: int8 pairs, two edges per register ---------------------------------------------------------
+// A message is an integer in [-96, 96]; stored as the byte c + 128, edge k of a row in register k / 2, bytes (2 (k % 2),
+// 2 (k % 2) + 1) = (lane 2 tid, lane 2 tid + 1). PRMT with the constant 0x64 turns the two bytes into the half2
+// (1152 + c, 1152 + c) without arithmetic; because the soft bits carry the same bias, S_biased - that = S - c.
+template <int BG>
+__host__ __device__ constexpr int h2_pack_start(int m)
+{
+  int s = 0;
+  for (int i = 0; i < m; ++i) {
+    s += (h2_graph<BG>::deg(i) + 1) / 2;
+  }
+  return s;
+}
+template <int BG>
+struct h2_pack {
+  static constexpr int NREG = h2_pack_start<BG>(4);
+};
+
+// Two smallest of the node list (lo[i] <= hi[i]); pairs of nodes merge with min / max / min3.
+template <int N>
+__device__ __forceinline__ void h2_min2_tree(const uint32_t (&lo)[N], const uint32_t (&hi)[N], uint32_t& m1, uint32_t& m2)
+{
+  if constexpr (N == 1) {
+    m1 = lo[0], m2 = hi[0];
+  } else {
+    constexpr int H = (N + 1) / 2;
+    uint32_t      l2[H], h2[H];
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) {
+      l2[i] = h2_min(lo[2 * i], lo[2 * i + 1]);
+      h2[i] = h2_min(h2_min(h2_max(lo[2 * i], lo[2 * i + 1]), hi[2 * i]), hi[2 * i + 1]);
+    }
+    if constexpr ((N & 1) != 0) {
+      l2[H - 1] = lo[N - 1], h2[H - 1] = hi[N - 1];
+    }
+    h2_min2_tree<H>(l2, h2, m1, m2);
+  }
+}
+
+// One row (layer) of the decode for the lane pair of this thread. cp: the thread's packed message registers.
+//
+// Arithmetic of pass 2 in sign-normalised form (sg = sign of u as +-1, everything else is computed on magnitudes, so the
+// work is spread over both issue pipes: 4 ALU-pipe and 8 FMA-pipe instructions per edge):
+//   ms = (|u| == m1 ? s2 : s1) with the sign of the row parity          (magnitude of the new message, sign-normalised)
+//   w  = min(|u|, 120) + ms                                             (sign-normalised soft value: t = sg w)
+//   g  = 1, or 65504 (+ 65504) when w > 120 or u is infinite            (qb, qa)
+//   S' = (sg w) g + 0 [+ bias]     overflow = promotion to +-inf; the + 0 turns a -0 product into the reference's +0
+//   c' = sg ms                     stored as the byte c' + 128
 template <int BG, int ZC, int M>
-__device__ __forceinline__ void h2_row(uint32_t (&c2v)[h2_graph<BG>::NEDGE], const uint32_t* __restrict__ tab,
+__device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const uint32_t* __restrict__ tab,
                                        uint32_t soft_t, uint32_t row_bytes, bool active, bool generic, uint32_t bar_reads,
                                        uint32_t bar_writes, uint32_t& phase_reads, uint32_t& phase_writes)
 {
-  using G            = h2_graph<BG>;
-  constexpr int DEG  = G::deg(M);
-  constexpr int E0   = h2_row_start<BG>(M);
+  using G             = h2_graph<BG>;
+  constexpr int DEG   = G::deg(M);
+  constexpr int E0    = h2_row_start<BG>(M);
+  constexpr int P0    = h2_pack_start<BG>(M);
+  constexpr int NLEAF = DEG / 2 + 1; // pairs of edges, plus (last edge | 120, 120): caps both minima at 120
   uint32_t      u[DEG];
-  uint32_t      m1 = H2_120, m2 = H2_120, par = 0;
+  uint32_t      lo[NLEAF], hi[NLEAF];
+  uint32_t      par = 0;
   mbar_wait(bar_writes, phase_writes & 1u); // the previous row (or the loader) has stored its soft bits
   ++phase_writes;
   // ---- pass 1: variable-to-check messages, two smallest magnitudes, sign parity ------------------------------------------
   h2_static_for<DEG>([&](auto k_) {
-    constexpr int k   = decltype(k_)::value;
-    const uint32_t S  = h2_read_edge<BG, ZC, E0 + k>(tab, soft_t);
-    u[k]              = h2_sub(S, c2v[E0 + k]);
-    const uint32_t a  = h2_abs(u[k]);
-    m2                = h2_min(m2, h2_max(m1, a));
-    m1                = h2_min(m1, a);
+    constexpr int  k = decltype(k_)::value;
+    const uint32_t S = h2_read_edge<BG, ZC, E0 + k>(tab, soft_t);
+    const uint32_t x = __byte_perm(cp[P0 + k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+    u[k]             = h2_sub(S, x);
     par ^= u[k];
   });
+  h2_static_for<DEG / 2>([&](auto i_) {
+    constexpr int  i = decltype(i_)::value;
+    const uint32_t a = h2_abs(u[2 * i]), b = h2_abs(u[2 * i + 1]);
+    lo[i] = h2_min(a, b), hi[i] = h2_max(a, b);
+  });
+  if constexpr ((DEG & 1) != 0) {
+    lo[NLEAF - 1] = h2_min(h2_abs(u[DEG - 1]), H2_120), hi[NLEAF - 1] = H2_120;
+  } else {
+    lo[NLEAF - 1] = H2_120, hi[NLEAF - 1] = H2_120;
+  }
+  uint32_t m1, m2;
+  h2_min2_tree<NLEAF>(lo, hi, m1, m2);
   const uint32_t s1  = h2_scale(m1, generic);
   const uint32_t s2  = h2_scale(m2, generic);
   const uint32_t d   = s1 ^ s2;
   const uint32_t s1p = s1 | (par & H2_SIGN);
   mbar_arrive_warp(bar_reads); // this warp has consumed the row's soft bits: they may be overwritten once all have
   // ---- pass 2: new check-to-variable messages and soft bits (kept in u[] until every thread has read the old ones) ---------
+  uint32_t y[DEG];
   h2_static_for<DEG>([&](auto k_) {
-    constexpr int k   = decltype(k_)::value;
+    constexpr int  k  = decltype(k_)::value;
     const uint32_t a  = h2_abs(u[k]);
     const uint32_t eq = h2_eq_mask(a, m1);
-    const uint32_t cn = (s1p ^ (d & eq)) ^ (u[k] & H2_SIGN);
-    const uint32_t v  = h2_max(h2_min(u[k], H2_120), H2_N120);
-    const uint32_t t  = h2_add(v, cn);
-    const uint32_t x  = h2_max(h2_abs(t), h2_add(a, H2_N216));
-    const uint32_t q  = h2_fma_sat(x, H2_ONE, H2_N120);
-    const uint32_t g  = h2_fma(q, H2_65504, H2_ONE);
-    c2v[E0 + k]       = cn;
-    u[k]              = h2_mul(t, g);
+    const uint32_t ms = s1p ^ (d & eq);
+    const uint32_t sg = (u[k] & H2_SIGN) | H2_ONE;
+    const uint32_t w  = h2_add(h2_min(a, H2_120), ms);
+    const uint32_t qa = h2_add_sat(a, H2_N336);
+    const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);
+    const uint32_t g  = h2_fma(qa, H2_65504, h2_fma(qb, H2_65504, H2_ONE));
+    y[k]              = h2_fma(ms, sg, H2_BIAS);
+    u[k]              = h2_fma(h2_mul(w, sg), g, H2_BIAS);
+  });
+  h2_static_for<(DEG + 1) / 2>([&](auto i_) {
+    constexpr int i = decltype(i_)::value;
+    if constexpr (2 * i + 1 < DEG) {
+      cp[P0 + i] = __byte_perm(y[2 * i], y[2 * i + 1], 0x6420);
+    } else {
+      cp[P0 + i] = __byte_perm(y[2 * i], 0u, 0x4420);
+    }
   });
   mbar_wait(bar_reads, phase_reads & 1u);
   ++phase_reads;
@@ -466,15 +545,16 @@ __device__ __forceinline__ void h2_deinterleave(const pdc_dematch_plan& pl, cons
   }
 }
 
-// int8 pair (low two bytes of w) -> clamped half2 soft bits: offset binary, 0x6400 | (x + 128) is the half 1024 + 128 + x.
+// int8 pair (low two bytes of w) -> clamped, biased half2 soft bits: 0x6400 | (x + 128) is the half 1152 + x; the clamp to
+// +-64 of load_soft_bits (ldpc_decoder_impl.cpp:162-181) is applied on the biased value.
 __device__ __forceinline__ uint32_t h2_soft_from_bytes(uint32_t w)
 {
   const uint32_t p = __byte_perm(w ^ 0x8080u, 0x64646464u, 0x4140);
-  return h2_max(h2_min(h2_add(p, H2_N1152), H2_64), H2_N64);
+  return h2_max(h2_min(p, H2_BIAS_P64), H2_BIAS_N64);
 }
 
 template <int BG, int ZC>
-__global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm)
+__global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_launch_params prm)
 {
   using G = h2_graph<BG>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -591,8 +671,8 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
 
   // ---- prologue 2: load_soft_bits (ldpc_decoder_impl.cpp:150-191) into the rotated, doubled half rows --------------------------
   if (active) {
-    sts32(soft_t, 0u), sts32(soft_t + 2u * Z, 0u); // the two punctured columns
-    sts32(soft_t + row_bytes, 0u), sts32(soft_t + row_bytes + 2u * Z, 0u);
+    sts32(soft_t, H2_BIAS), sts32(soft_t + 2u * Z, H2_BIAS); // the two punctured columns: zero
+    sts32(soft_t + row_bytes, H2_BIAS), sts32(soft_t + row_bytes + 2u * Z, H2_BIAS);
     if (ZC > 0 && from_smem) {
       // Staging tile -> rows with every rotation known at compile time: lanes (2 tid + sigma, + 1) mod Z of column c.
       h2_static_for<G::NCOL - 2>([&](auto c_) {
@@ -648,19 +728,19 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
                                           (PDC_CRC_BIT_PAD + n_sig - 1 + crc_order - 2 * tid)
                                     : nullptr;
 
-  uint32_t c2v[G::NEDGE];
+  uint32_t cp[h2_pack<BG>::NREG]; // check-to-variable messages, all zero (byte 128) before the first iteration
 #pragma unroll
-  for (int e = 0; e < G::NEDGE; ++e) {
-    c2v[e] = 0u;
+  for (int e = 0; e < h2_pack<BG>::NREG; ++e) {
+    cp[e] = 0x80808080u;
   }
 
   int  it_done = 0;
   bool success = false;
   for (int it = 0; it < max_iter && !success; ++it) {
-    h2_row<BG, ZC, 0>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, ZC, 1>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, ZC, 2>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, ZC, 3>(c2v, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 0>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 1>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 2>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 3>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
     it_done = it + 1;
     const bool last = (it_done == max_iter);
     if (!has_crc || (!early && !last)) {
@@ -676,14 +756,14 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
       h2_static_for<G::KB>([&](auto c_) {
         constexpr int  c  = decltype(c_)::value;
         const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t); // natural lanes (2 tid, 2 tid + 1) of column c
-        amin              = h2_min(amin, h2_abs(S));
+        amin              = h2_min(amin, h2_abs(h2_sub(S, H2_BIAS)));
         const uint32_t t_lo = crc_bit[-c * Z], t_hi = crc_bit[-c * Z - 1];
         asm("{ .reg .pred p, q;\n"
             "setp.le.f16x2 p|q, %1, %2;\n"
             "@p xor.b32 %0, %0, %3;\n"
             "@q xor.b32 %0, %0, %4; }"
             : "+r"(acc)
-            : "r"(S), "r"(0u), "r"(t_lo), "r"(t_hi));
+            : "r"(S), "r"(H2_BIAS), "r"(t_lo), "r"(t_hi));
       });
     }
     acc = __reduce_xor_sync(0xffffffffu, acc);
@@ -713,7 +793,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2(pdc_launch_params prm
     h2_static_for<G::KB>([&](auto c_) {
       constexpr int  c  = decltype(c_)::value;
       const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t);
-      const uint32_t le = active ? h2_le_mask(S, 0u) : 0u;
+      const uint32_t le = active ? h2_le_mask(S, H2_BIAS) : 0u;
       const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
       const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
       if ((tid & 31) == 0) {
