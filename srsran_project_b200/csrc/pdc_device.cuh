@@ -14,12 +14,15 @@
 #define PDC_CRC_TABLE_LEN (PDC_MAX_K + 32) /* x^j mod P for j < K + order */
 #define PDC_CRC_BIT_PAD 800                 /* zeros in front of the bit table: filler positions index below the order */
 #define PDC_CRC_BIT_TABLE_LEN (PDC_CRC_BIT_PAD + PDC_MAX_K + 32)
+/* Two copies per CRC type, the second one shifted by one entry, so that the pair of entries a thread needs for two
+   neighbouring bits is an aligned 64-bit load whatever the parity of the number of filler bits. */
+#define PDC_CRC_BIT_STRIDE (PDC_CRC_BIT_TABLE_LEN + 2)
 
 struct pdc_launch_params {
   const pdc_dev_cb* cbs;
   const uint32_t*   graphs;  // [2 * 51][PDC_GRAPH_STRIDE]: col | (shift mod Z) << 8, rows concatenated
   const uint32_t*   crc_pow; // [3][PDC_CRC_TABLE_LEN]: x^j mod P for CRC16, CRC24A, CRC24B
-  const uint32_t*   crc_bit; // [3][PDC_CRC_BIT_TABLE_LEN]: entry PAD + j = x^j mod P for j >= order, 0 below
+  const uint32_t*   crc_bit; // [3][2][PDC_CRC_BIT_STRIDE]: copy v, entry v + PAD + j = x^j mod P for j >= order, 0 below
   const uint32_t*   order;   // optional permutation of CB indices (nullptr = identity)
   int               n;
 };

@@ -84,6 +84,20 @@ __device__ __forceinline__ uint32_t h2_add_sat(uint32_t a, uint32_t b)
   asm("add.rn.sat.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
   return d;
 }
+// (a & 0x80008000) | one as ONE LOP3: the 1.0 pair has to live in a register the compiler cannot fold (an instruction takes
+// a single immediate), hence the opaque move.
+__device__ __forceinline__ uint32_t h2_opaque_one()
+{
+  uint32_t r;
+  asm volatile("mov.b32 %0, 0x3C003C00;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t h2_copysign_one(uint32_t a, uint32_t one)
+{
+  uint32_t d;
+  asm("lop3.b32 %0, %1, 0x80008000, %2, 0xEA;" : "=r"(d) : "r"(a), "r"(one));
+  return d;
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t addr)
 {
   uint32_t v;
@@ -365,6 +379,7 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
   uint32_t      u[DEG];
   uint32_t      lo[NLEAF], hi[NLEAF];
   uint32_t      par = 0;
+  const uint32_t one = h2_opaque_one();
   mbar_wait(bar_writes, phase_writes & 1u); // the previous row (or the loader) has stored its soft bits
   ++phase_writes;
   // ---- pass 1: variable-to-check messages, two smallest magnitudes, sign parity ------------------------------------------
@@ -399,7 +414,7 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
     const uint32_t a  = h2_abs(u[k]);
     const uint32_t eq = h2_eq_mask(a, m1);
     const uint32_t ms = s1p ^ (d & eq);
-    const uint32_t sg = (u[k] & H2_SIGN) | H2_ONE;
+    const uint32_t sg = h2_copysign_one(u[k], one);
     const uint32_t w  = h2_add(h2_min(a, H2_120), ms);
     const uint32_t qa = h2_add_sat(a, H2_N336);
     const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);
@@ -723,10 +738,16 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
   const bool      early    = (cb.flags & PDC_F_EARLY_STOP) && has_crc;
   const int       max_iter = cb.max_iter;
   const int       crc_order = (cb.crc_type == PDC_CRC16) ? 16 : 24;
-  // x^j mod P table, zero for exponents below the CRC order (filler positions), padded in front: see build_crc_tables().
-  const uint32_t* crc_bit = has_crc ? prm.crc_bit + (cb.crc_type - 1) * PDC_CRC_BIT_TABLE_LEN +
-                                          (PDC_CRC_BIT_PAD + n_sig - 1 + crc_order - 2 * tid)
-                                    : nullptr;
+  // x^j mod P table, zero for exponents below the CRC order (filler positions), padded in front: see build_crc_bit_tables().
+  // Bit n contributes entry X - n, X = PAD + n_sig - 1 + order; this thread's lanes (2 tid, 2 tid + 1) of column c need
+  // entries X - c Z - 2 tid - 1 and X - c Z - 2 tid: one aligned 64-bit load from the copy whose shift makes X - 1 even.
+  const uint2* crc_pair = nullptr;
+  if (has_crc) {
+    const int X = PDC_CRC_BIT_PAD + n_sig - 1 + crc_order;
+    const int v = (X - 1) & 1;
+    crc_pair    = reinterpret_cast<const uint2*>(prm.crc_bit + (size_t)(2 * (cb.crc_type - 1) + v) * PDC_CRC_BIT_STRIDE +
+                                              (v + X - 1 - 2 * tid));
+  }
 
   uint32_t cp[h2_pack<BG>::NREG]; // check-to-variable messages, all zero (byte 128) before the first iteration
 #pragma unroll
@@ -757,13 +778,13 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
         constexpr int  c  = decltype(c_)::value;
         const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t); // natural lanes (2 tid, 2 tid + 1) of column c
         amin              = h2_min(amin, h2_abs(h2_sub(S, H2_BIAS)));
-        const uint32_t t_lo = crc_bit[-c * Z], t_hi = crc_bit[-c * Z - 1];
+        const uint2 tp = __ldg(crc_pair - c * (Z >> 1)); // .x: lane 2 tid + 1, .y: lane 2 tid
         asm("{ .reg .pred p, q;\n"
             "setp.le.f16x2 p|q, %1, %2;\n"
             "@p xor.b32 %0, %0, %3;\n"
             "@q xor.b32 %0, %0, %4; }"
             : "+r"(acc)
-            : "r"(S), "r"(H2_BIAS), "r"(t_lo), "r"(t_hi));
+            : "r"(S), "r"(H2_BIAS), "r"(tp.y), "r"(tp.x));
       });
     }
     acc = __reduce_xor_sync(0xffffffffu, acc);

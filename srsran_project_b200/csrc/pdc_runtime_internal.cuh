@@ -163,10 +163,12 @@ void build_crc_tables(std::vector<uint32_t>& out)
 void build_crc_bit_tables(const std::vector<uint32_t>& pow, std::vector<uint32_t>& out)
 {
   static const int order[3] = {16, 24, 24};
-  out.assign((size_t)3 * PDC_CRC_BIT_TABLE_LEN, 0);
+  out.assign((size_t)3 * 2 * PDC_CRC_BIT_STRIDE, 0);
   for (int c = 0; c != 3; ++c) {
-    for (int j = order[c]; j < PDC_CRC_TABLE_LEN; ++j) {
-      out[(size_t)c * PDC_CRC_BIT_TABLE_LEN + PDC_CRC_BIT_PAD + j] = pow[(size_t)c * PDC_CRC_TABLE_LEN + j];
+    for (int v = 0; v != 2; ++v) {
+      for (int j = order[c]; j < PDC_CRC_TABLE_LEN; ++j) {
+        out[(size_t)(2 * c + v) * PDC_CRC_BIT_STRIDE + v + PDC_CRC_BIT_PAD + j] = pow[(size_t)c * PDC_CRC_TABLE_LEN + j];
+      }
     }
   }
 }

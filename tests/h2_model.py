@@ -46,27 +46,28 @@ def decode(graph_rows, Z, llrs, K, n_layers, max_iter, generic=False, check=None
                 with np.errstate(invalid="ignore"):
                     u[k] = S - c2v[m][k]
             a = np.abs(u)
-            m1 = np.full(Z, 120.0, F16)
-            m2 = np.full(Z, 120.0, F16)
+            # two smallest magnitudes capped at 120 (the kernel finds them with a min / max tree; same multiset result)
+            srt = np.sort(np.vstack([a.astype(np.float32), np.full((2, Z), 120.0, np.float32)]), axis=0)
+            m1, m2 = srt[0].astype(F16), srt[1].astype(F16)
             par = np.zeros(Z, bool)
             for k in range(len(row)):
-                m2 = np.minimum(m2, np.maximum(m1, a[k]))
-                m1 = np.minimum(m1, a[k])
                 par ^= sign(u[k])
             s1 = scale_generic(m1) if generic else scale_simd(m1)
             s2 = scale_generic(m2) if generic else scale_simd(m2)
             for k, (c, s) in enumerate(row):
+                # sign-normalised form of pdc_kernel_h2.cuh::h2_row pass 2
                 mag = np.where(a[k] == m1, s2, s1)
-                neg = par ^ sign(u[k])
-                cn = np.where(neg, -mag, mag).astype(F16)  # may be -0: harmless
-                v = np.maximum(np.minimum(u[k], F16(120.0)), F16(-120.0))
-                t = (v + cn).astype(F16)
+                ms = np.where(par, -mag, mag).astype(F16)                       # magnitude of the new message, row-parity sign
+                sg = np.where(sign(u[k]), F16(-1.0), F16(1.0)).astype(F16)       # copysign(1, u)
+                w = (np.minimum(a[k], F16(120.0)) + ms).astype(F16)
                 with np.errstate(invalid="ignore"):
-                    xx = np.maximum(np.abs(t), (a[k].astype(np.float64) - 216.0).astype(F16))
-                q = np.clip(xx.astype(np.float64) - 120.0, 0.0, 1.0).astype(F16)
-                G = fma16(q, F16(65504.0), 1.0)
+                    qa = np.clip(a[k].astype(np.float64) - 336.0, 0.0, 1.0).astype(F16)  # 1 iff u is infinite
+                qb = np.clip(w.astype(np.float64) - 120.0, 0.0, 1.0).astype(F16)          # 1 iff w > 120
+                G = fma16(qa, F16(65504.0), fma16(qb, F16(65504.0), 1.0))
+                cn = (ms.astype(np.float64) * sg.astype(np.float64)).astype(F16)          # may be -0: harmless
+                t = (w.astype(np.float64) * sg.astype(np.float64)).astype(F16)
                 with np.errstate(over="ignore"):
-                    Snew = (t.astype(np.float64) * G.astype(np.float64)).astype(F16)
+                    Snew = (t.astype(np.float64) * G.astype(np.float64) + 0.0).astype(F16)  # + 0: a -0 product becomes +0
                 c2v[m][k] = cn
                 soft[c] = np.roll(Snew, s)
         if check is not None and check(it + 1, soft):
