@@ -271,7 +271,19 @@ class Ranks:
 
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             if backend == "nccl":
-                dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+                # NCCL prints its version banner on stdout when the first communicator comes up; stdout carries exactly
+                # one JSON line, so the banner is sent to stderr (fd level: the print comes from native code).
+                sys.stdout.flush()
+                saved = os.dup(1)
+                os.dup2(2, 1)
+                try:
+                    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+                    dist.barrier()
+                    torch.cuda.synchronize()
+                finally:
+                    sys.stdout.flush()
+                    os.dup2(saved, 1)
+                    os.close(saved)
             else:
                 dist.init_process_group(backend)
             self.dist = dist
