@@ -320,3 +320,56 @@ def test_h2_decode_only_high_rate(acc, oracle):
                 for crc_id, max_iter in ((CRC_NONE, 6), (CRC24B if trial else CRC16, 6), (CRC24A, 1)):
                     cases.append(dict(bg=bg, Z=Z, llrs=llrs, F=0, max_iter=max_iter, crc_id=crc_id))
     run_decode_only_batch(acc, oracle, cases, FLAVOUR_AVX512)
+
+
+def test_h2_unaligned_buffers_and_byte_paths(acc, oracle):
+    """The packed kernel's vector paths need aligned LLRs / soft buffers and Kq, F multiples of 4; everything else takes the
+    byte paths. Same results either way: odd LLR and soft-buffer offsets, every Qm, fillers of every residue."""
+    from srsran_project_b200 import binding as B
+
+    rng = np.random.default_rng(131)
+    cases = []
+    for bg, Z in ((1, 384), (2, 384), (1, 64), (2, 96)):
+        for k, (Qm, F) in enumerate(((8, 16), (8, 17), (6, 12), (6, 3), (4, 8), (4, 6), (2, 4), (2, 1), (1, 0), (8, 0))):
+            E = high_rate_E(bg, Z, F, Qm, (1.0, 0.93, 0.8)[k % 3])
+            if k == 9:
+                E = E // (4 * Qm) * (4 * Qm) + Qm  # Kq not a multiple of 4
+            cases.append(chain_case(rng, oracle, bg, Z, Qm, E, F, 0, CRC24B, (2.4,), (0,)))
+    for shift_llr, shift_soft in ((0, 0), (1, 0), (8, 4), (3, 7), (16, 16)):
+        n = len(cases)
+        descs = B.make_descs(n)
+        lo = so = oo = 0
+        soft_off, out_off = [], []
+        for i, c in enumerate(cases):
+            d = descs[i]
+            d["bg"], d["Z"], d["Qm"], d["rv"], d["crc_type"], d["max_iter"] = c["bg"], c["Z"], c["Qm"], 0, c["crc_id"], 6
+            d["flags"], d["E"], d["nof_filler"], d["harq_slot"] = B.PDC_F_NEW_DATA | B.PDC_F_EARLY_STOP, c["E"], c["F"], -1
+            lo = (lo + 15) // 16 * 16 + shift_llr
+            so = (so + 15) // 16 * 16 + shift_soft
+            d["llr_offset"], d["soft_offset"], d["out_offset"] = lo, so, oo
+            soft_off.append(so), out_off.append(oo)
+            lo += c["E"]
+            so += nshort_of(c["bg"]) * c["Z"]
+            oo += out_stride(kb_of(c["bg"]) * c["Z"])
+        llrs = np.zeros(lo + 16, np.int8)
+        soft = rng.integers(-120, 121, so + 16).astype(np.int8)
+        soft_before = soft.copy()
+        for i, c in enumerate(cases):
+            o = int(descs[i]["llr_offset"])
+            llrs[o:o + c["E"]] = c["txs"][0][1]
+        res, bits = acc.run(descs, llrs, oo, soft)
+        for i, c in enumerate(cases):
+            K, N = kb_of(c["bg"]) * c["Z"], nshort_of(c["bg"]) * c["Z"]
+            want_soft = soft_before[soft_off[i]:soft_off[i] + N].copy()
+            it, want = oracle.codeblock_decode(FLAVOUR_AVX512, c["bg"], c["Z"], want_soft, c["txs"][0][1], True, 0, c["Qm"],
+                                               0, c["F"], c["crc_id"], 6, True)
+            tag = (shift_llr, shift_soft, i, c["bg"], c["Z"], c["Qm"], c["E"], c["F"])
+            assert (soft[soft_off[i]:soft_off[i] + N] == want_soft).all(), ("soft", tag)
+            assert res[i]["iterations"] == it, ("iterations", tag)
+            got = np.unpackbits(bits[out_off[i]:out_off[i] + (K + 7) // 8])[:K]
+            assert (got == np.unpackbits(want)[:K]).all(), ("bits", tag)
+        # nothing outside the code blocks' own soft buffers was written
+        mask = np.ones(soft.size, bool)
+        for i, c in enumerate(cases):
+            mask[soft_off[i]:soft_off[i] + nshort_of(c["bg"]) * c["Z"]] = False
+        assert (soft[mask] == soft_before[mask]).all()
