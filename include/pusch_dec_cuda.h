@@ -70,7 +70,7 @@ typedef struct {
   uint64_t llr_offset; /* byte offset of this CB's LLRs in the llrs buffer */
   uint64_t soft_offset;/* byte offset of this CB's N-entry soft buffer in the soft buffers (harq_slot < 0 only) */
   uint64_t out_offset; /* byte offset of this CB's packed hard bits (ceil(K/8) bytes, MSB first) in the bits buffer;
-                          must be a multiple of 4 */
+                          must be a multiple of 4; the bytes up to the next multiple of 4 belong to the CB as padding */
 } pdc_cb_desc;
 
 /* Per-CB outcome: hw_pusch_decoder_outputs (hw_accelerator_pusch_dec.h:75-80) / optional<unsigned> of decode(). */

@@ -131,6 +131,35 @@ void pdc_destroy(pdc_ctx* ctx)
   delete ctx;
 }
 
+// Takes a free ticket (marks it in use) or returns nullptr. The planning and the CUDA calls of a submission then run
+// WITHOUT the context lock: tickets own their stream and staging, so several host threads submit concurrently.
+static ticket_t* reserve_ticket(pdc_ctx* ctx)
+{
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  for (ticket_t& c : ctx->tickets) {
+    if (!c.in_use) {
+      c.in_use = true;
+      c.id     = ctx->next_id++;
+      return &c;
+    }
+  }
+  return nullptr;
+}
+
+static pdc_status release_ticket(pdc_ctx* ctx, ticket_t* t, pdc_status st)
+{
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  t->in_use = false;
+  return st;
+}
+
+#define CKT(call)                                                                                                      \
+  do {                                                                                                                 \
+    if (!cuda_ok(ctx, (call), #call)) {                                                                                \
+      return release_ticket(ctx, t, PDC_ERR_CUDA);                                                                     \
+    }                                                                                                                  \
+  } while (0)
+
 pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
                       const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket)
 {
@@ -140,69 +169,44 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
   if (n > ctx->cfg.max_batch_cbs || llr_bytes > ctx->cfg.max_batch_llrs) {
     return PDC_ERR_CAPACITY;
   }
-  std::lock_guard<std::mutex> lock(ctx->mtx);
-  CK(cudaSetDevice(ctx->cfg.device));
-  ticket_t* t = nullptr;
-  for (ticket_t& c : ctx->tickets) {
-    if (!c.in_use) {
-      t = &c;
-      break;
-    }
-  }
+  ticket_t* t = reserve_ticket(ctx);
   if (!t) {
     return PDC_ERR_CAPACITY;
   }
+  CKT(cudaSetDevice(ctx->cfg.device));
+  if (t->borrowed) {
+    CKT(cudaStreamSynchronize(t->stream)); // pdc_decode_device's descriptor copy out of this staging has to be over
+    t->borrowed = false;
+  }
+  batch_buffers buf;
+  buf.d_llrs = t->d_llrs, buf.d_soft = t->d_soft, buf.d_bits = t->d_bits, buf.d_res = t->d_res;
+  buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots, buf.llr_bytes = llr_bytes;
   batch_plan bp;
-  pdc_status st = plan_batch(descs, n, t->h_cbs, t->h_order, bp);
+  t->lst.resize(n);
+  pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
   if (st != PDC_OK) {
-    return st;
+    return release_ticket(ctx, t, st);
   }
-  // Layout of the exchanged buffers: LLRs as given, bits at out_offset, host soft buffers at soft_offset.
-  size_t bits_need = 0, soft_need = 0;
-  bool   any_host_soft = false;
-  for (uint32_t i = 0; i != n; ++i) {
-    const pdc_cb_desc& d = descs[i];
-    pdc_geom           g;
-    pdc_geom_init(g, d.bg, d.Z);
-    size_t llr_end = d.llr_offset + d.E;
-    if (llr_end > llr_bytes) {
-      return PDC_ERR_INVALID_ARG;
+  if (bp.bits_end > (size_t)ctx->cfg.max_batch_cbs * (PDC_MAX_K / 8)) {
+    return release_ticket(ctx, t, PDC_ERR_CAPACITY);
+  }
+  if (bp.any_host_soft) {
+    if (soft_in && soft_bytes < bp.soft_end) {
+      return release_ticket(ctx, t, PDC_ERR_INVALID_ARG);
     }
-    size_t be = d.out_offset + (size_t)((g.K + 31) / 32) * 4;
-    bits_need = be > bits_need ? be : bits_need;
-    if (!(d.flags & PDC_F_DECODE_ONLY)) {
-      if (d.harq_slot >= 0) {
-        if ((uint32_t)d.harq_slot >= ctx->cfg.harq_slots) {
-          return PDC_ERR_INVALID_ARG;
-        }
-      } else {
-        any_host_soft = true;
-        size_t se     = d.soft_offset + (size_t)g.N;
-        soft_need     = se > soft_need ? se : soft_need;
+    if (bp.soft_end > t->soft_cap) {
+      // The staging grows (rare): the device pointers planned above are stale, plan again on the new buffers.
+      st = ensure_soft(ctx, *t, bp.soft_end);
+      if (st != PDC_OK) {
+        return release_ticket(ctx, t, st);
       }
-    }
-  }
-  if (bits_need > (size_t)ctx->cfg.max_batch_cbs * (PDC_MAX_K / 8)) {
-    return PDC_ERR_CAPACITY;
-  }
-  if (any_host_soft) {
-    if (soft_in && soft_bytes < soft_need) {
-      return PDC_ERR_INVALID_ARG;
-    }
-    st = ensure_soft(ctx, *t, soft_need);
-    if (st != PDC_OK) {
-      return st;
-    }
-  }
-  for (uint32_t i = 0; i != n; ++i) {
-    const pdc_cb_desc& d = descs[i];
-    pdc_dev_cb&        c = t->h_cbs[i];
-    c.llrs               = t->d_llrs + d.llr_offset;
-    c.out                = t->d_bits + d.out_offset;
-    c.res                = t->d_res + i;
-    c.soft               = nullptr;
-    if (!(d.flags & PDC_F_DECODE_ONLY)) {
-      c.soft = (d.harq_slot >= 0) ? (ctx->d_harq + (size_t)d.harq_slot * PDC_MAX_N) : (t->d_soft + d.soft_offset);
+      buf.d_soft = t->d_soft;
+      batch_plan again;
+      st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), again);
+      if (st != PDC_OK) {
+        return release_ticket(ctx, t, st);
+      }
+      bp = again;
     }
   }
   // Stage and go. LLRs already in pinned memory are sent from where they lie.
@@ -215,33 +219,34 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
     memcpy(t->h_llrs, llrs, llr_bytes);
     src = t->h_llrs;
   }
-  CK(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
-  CK(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, t->stream));
-  CK(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
-  if (any_host_soft) {
+  CKT(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
+  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, t->stream));
+  if (!bp.identity) {
+    CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
+  }
+  if (bp.any_host_soft) {
     if (soft_in) {
-      memcpy(t->h_soft, soft_in, soft_need);
-      CK(cudaMemcpyAsync(t->d_soft, t->h_soft, soft_need, cudaMemcpyHostToDevice, t->stream));
+      memcpy(t->h_soft, soft_in, bp.soft_end);
+      CKT(cudaMemcpyAsync(t->d_soft, t->h_soft, bp.soft_end, cudaMemcpyHostToDevice, t->stream));
     } else {
-      CK(cudaMemsetAsync(t->d_soft, 0, soft_need, t->stream));
+      CKT(cudaMemsetAsync(t->d_soft, 0, bp.soft_end, t->stream));
     }
   }
   st = launch_batch(ctx, bp, t->d_cbs, t->d_order, t->stream);
   if (st != PDC_OK) {
-    return st;
+    return release_ticket(ctx, t, st);
   }
-  CK(cudaMemcpyAsync(t->h_bits, t->d_bits, bits_need, cudaMemcpyDeviceToHost, t->stream));
-  CK(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n, cudaMemcpyDeviceToHost, t->stream));
-  if (any_host_soft) {
-    CK(cudaMemcpyAsync(t->h_soft, t->d_soft, soft_need, cudaMemcpyDeviceToHost, t->stream));
+  CKT(cudaMemcpyAsync(t->h_bits, t->d_bits, bp.bits_end, cudaMemcpyDeviceToHost, t->stream));
+  CKT(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n, cudaMemcpyDeviceToHost, t->stream));
+  if (bp.any_host_soft) {
+    CKT(cudaMemcpyAsync(t->h_soft, t->d_soft, bp.soft_end, cudaMemcpyDeviceToHost, t->stream));
   }
-  CK(cudaEventRecord(t->done, t->stream));
-  t->in_use     = true;
-  t->id         = ctx->next_id++;
+  CKT(cudaEventRecord(t->done, t->stream));
   t->n          = n;
-  t->bits_bytes = bits_need;
-  t->soft_bytes = soft_need;
-  t->soft_back  = any_host_soft;
+  t->bits_bytes = bp.bits_end;
+  t->bits_dense = bp.bits_dense;
+  t->soft_bytes = bp.soft_end;
+  t->soft_back  = bp.any_host_soft;
   t->descs.assign(descs, descs + n);
   *ticket = t->id;
   return PDC_OK;
@@ -290,36 +295,47 @@ pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits
     }
   }
   cudaError_t e = cudaEventSynchronize(t->done); // outside the lock: other threads keep submitting
-  std::lock_guard<std::mutex> lock(ctx->mtx);
   if (!cuda_ok(ctx, e, "cudaEventSynchronize")) {
-    t->in_use = false;
-    return PDC_ERR_CUDA;
+    return release_ticket(ctx, t, PDC_ERR_CUDA);
   }
   pdc_status st = PDC_OK;
+  memcpy(res, t->h_res, sizeof(pdc_cb_result) * t->n);
+  bool all_written = true; // status 2: "not enough soft bits" with a CRC object — the reference leaves the output untouched
   for (uint32_t i = 0; i != t->n; ++i) {
-    const pdc_cb_desc& d = t->descs[i];
-    pdc_geom           g;
-    pdc_geom_init(g, d.bg, d.Z);
-    res[i] = t->h_res[i];
-    // status 2: "not enough soft bits" with a CRC object — the reference leaves the output untouched.
-    if (bits && res[i].status == 0 && !(d.flags & PDC_F_DEMATCH_ONLY)) {
-      size_t nb = (size_t)(g.K + 7) / 8;
+    all_written &= (t->h_res[i].status == 0);
+  }
+  if (bits && all_written && t->bits_dense && t->bits_bytes <= bits_bytes) {
+    memcpy(bits, t->h_bits, t->bits_bytes); // the outputs tile the range: one copy (words are whole: K is a multiple of 8
+                                            // only up to the word padding each code block owns anyway)
+  } else if (bits) {
+    for (uint32_t i = 0; i != t->n; ++i) {
+      const pdc_cb_desc& d = t->descs[i];
+      if (res[i].status != 0 || (d.flags & PDC_F_DEMATCH_ONLY)) {
+        continue;
+      }
+      size_t nb = ((size_t)pdc_cb_message_bits(d.bg, d.Z) + 7) / 8;
       if (d.out_offset + nb > bits_bytes) {
         st = PDC_ERR_INVALID_ARG;
       } else {
         memcpy(bits + d.out_offset, t->h_bits + d.out_offset, nb);
       }
     }
-    if (soft_out && d.harq_slot < 0 && !(d.flags & PDC_F_DECODE_ONLY)) {
-      if (d.soft_offset + (size_t)g.N > soft_bytes) {
+  }
+  if (soft_out && t->soft_back) {
+    for (uint32_t i = 0; i != t->n; ++i) {
+      const pdc_cb_desc& d = t->descs[i];
+      if (d.harq_slot >= 0 || (d.flags & PDC_F_DECODE_ONLY)) {
+        continue;
+      }
+      size_t N = pdc_cb_buffer_len(d.bg, d.Z);
+      if (d.soft_offset + N > soft_bytes) {
         st = PDC_ERR_INVALID_ARG;
       } else {
-        memcpy(soft_out + d.soft_offset, t->h_soft + d.soft_offset, (size_t)g.N);
+        memcpy(soft_out + d.soft_offset, t->h_soft + d.soft_offset, N);
       }
     }
   }
-  t->in_use = false;
-  return st;
+  return release_ticket(ctx, t, st);
 }
 
 pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* d_llrs, int8_t* d_soft,
@@ -331,54 +347,39 @@ pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n,
   if (n > ctx->cfg.max_batch_cbs) {
     return PDC_ERR_CAPACITY;
   }
-  std::lock_guard<std::mutex> lock(ctx->mtx);
-  CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t stream = (cudaStream_t)stream_v;
-  // Descriptor staging of a free ticket is borrowed for the duration of the launch (stream-ordered).
-  ticket_t* t = nullptr;
-  for (ticket_t& c : ctx->tickets) {
-    if (!c.in_use) {
-      t = &c;
-      break;
-    }
-  }
+  // The descriptor staging of a free ticket is borrowed for the duration of the launch (stream-ordered).
+  ticket_t* t = reserve_ticket(ctx);
   if (!t) {
     return PDC_ERR_CAPACITY;
   }
-  // The pinned descriptor staging may still be read by a previous asynchronous copy on `stream`.
-  CK(cudaStreamSynchronize(t->stream));
+  CKT(cudaSetDevice(ctx->cfg.device));
+  // The pinned descriptor staging may still be read by a previous asynchronous copy on the caller's stream.
+  if (t->borrowed) {
+    CKT(cudaStreamSynchronize(t->stream));
+  }
+  t->borrowed = true;
+  batch_buffers buf;
+  buf.d_llrs = d_llrs, buf.d_soft = d_soft, buf.d_bits = d_bits, buf.d_res = d_res;
+  buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots;
   batch_plan bp;
-  pdc_status st = plan_batch(descs, n, t->h_cbs, t->h_order, bp);
+  t->lst.resize(n);
+  pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
+  if (st == PDC_OK && bp.any_host_soft && !d_soft) {
+    st = PDC_ERR_INVALID_ARG;
+  }
   if (st != PDC_OK) {
-    return st;
+    return release_ticket(ctx, t, st);
   }
-  for (uint32_t i = 0; i != n; ++i) {
-    const pdc_cb_desc& d = descs[i];
-    pdc_dev_cb&        c = t->h_cbs[i];
-    c.llrs               = d_llrs + d.llr_offset;
-    c.out                = d_bits + d.out_offset;
-    c.res                = d_res + i;
-    c.soft               = nullptr;
-    if (!(d.flags & PDC_F_DECODE_ONLY)) {
-      if (d.harq_slot >= 0) {
-        if ((uint32_t)d.harq_slot >= ctx->cfg.harq_slots) {
-          return PDC_ERR_INVALID_ARG;
-        }
-        c.soft = ctx->d_harq + (size_t)d.harq_slot * PDC_MAX_N;
-      } else {
-        if (!d_soft) {
-          return PDC_ERR_INVALID_ARG;
-        }
-        c.soft = d_soft + d.soft_offset;
-      }
-    }
+  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
+  if (!bp.identity) {
+    CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
   }
-  CK(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
-  CK(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
   // The pinned staging is free again once the descriptor copies have been consumed; order that on the ticket's stream.
-  CK(cudaEventRecord(t->done, stream));
-  CK(cudaStreamWaitEvent(t->stream, t->done, 0));
-  return launch_batch(ctx, bp, t->d_cbs, t->d_order, stream);
+  CKT(cudaEventRecord(t->done, stream));
+  CKT(cudaStreamWaitEvent(t->stream, t->done, 0));
+  st = launch_batch(ctx, bp, t->d_cbs, t->d_order, stream);
+  return release_ticket(ctx, t, st);
 }
 
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot)

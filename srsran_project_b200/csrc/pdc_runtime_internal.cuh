@@ -8,6 +8,7 @@
 #include "ldpc_bg_tables.h"
 #include "pdc_device.cuh"
 #include <atomic>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -47,8 +48,10 @@ struct ticket_t {
   uint32_t*      d_order = nullptr;
   // what to hand back
   std::vector<pdc_cb_desc> descs;
+  std::vector<uint8_t>     lst; // kernel list of every code block (planner scratch)
   size_t                   bits_bytes = 0, soft_bytes = 0;
-  bool                     soft_back  = false;
+  bool                     soft_back  = false, bits_dense = false;
+  bool                     borrowed   = false; // staging lent to pdc_decode_device: its copy may still be in flight
 };
 
 } // namespace
@@ -179,7 +182,7 @@ bool validate_desc(const pdc_cb_desc& d, pdc_geom& g, int& max_layers)
   if (!pdc_geom_init(g, d.bg, d.Z) || pdc_lifting_pos(d.Z) < 0) {
     return false;
   }
-  if (d.max_iter == 0 || d.crc_type > PDC_CRC24B || (d.out_offset & 3) != 0) {
+  if (d.max_iter == 0 || d.crc_type > PDC_CRC24B) {
     return false;
   }
   if ((uint64_t)d.nof_filler >= (uint64_t)g.K) {
@@ -221,6 +224,9 @@ struct batch_plan {
   size_t   smem_lane = 0, smem_h2[4] = {0, 0, 0, 0};
   int      block_lane = 32, block_h2[4] = {32, 32, 32, 32};
   uint32_t n_lane = 0, n_h2[4] = {0, 0, 0, 0}; // order array: the four packed-kernel lists, then the lane-kernel CBs
+  bool     identity = false;                   // one list holds every code block: launch without the order array
+  size_t   bits_end = 0, soft_end = 0;         // extent of the packed bits / host-exchanged soft buffers
+  bool     bits_dense = false, any_host_soft = false;
 };
 
 // Which code blocks the packed half2 kernel takes: the four core rows only, Z a multiple of 32 (pdc_kernel_h2.cuh).
@@ -238,48 +244,134 @@ bool takes_h2(const pdc_cb_desc& d, int max_layers)
   return true;
 }
 
-// Fills dev[i] (pointers left to the caller) and the launch order; returns PDC_OK or the first invalid descriptor.
-pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, pdc_dev_cb* dev, uint32_t* order, batch_plan& bp)
+// Everything that is derived from the first 20 bytes of a descriptor (bg .. nof_filler). The code blocks of a transport
+// block differ only in E (two values), their offsets and their HARQ slot, so the planner recomputes a class only when those
+// 20 bytes change: the per-code-block host cost is a compare and a 56-byte copy.
+struct desc_class {
+  pdc_cb_desc key;
+  pdc_dev_cb  proto; // pointers zero
+  size_t      K_bytes4 = 0; // packed message size rounded up to words
+  uint32_t    N        = 0;
+  int         list     = 0; // 0..3 packed-kernel lists, 4 lane kernel
+  bool        valid    = false;
+};
+
+inline bool same_class(const pdc_cb_desc& a, const pdc_cb_desc& b)
 {
-  std::vector<uint32_t> lists[5];
-  for (auto& l : lists) {
-    l.reserve(n);
+  static_assert(offsetof(pdc_cb_desc, harq_slot) == 20, "class key = the first 20 bytes of pdc_cb_desc");
+  return memcmp(&a, &b, 20) == 0;
+}
+
+bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
+{
+  pdc_geom g;
+  int      ml = 0;
+  cls.valid   = false;
+  if (!validate_desc(d, g, ml)) {
+    return false;
   }
+  cls.key       = d;
+  pdc_dev_cb& c = cls.proto;
+  memset(&c, 0, sizeof(c));
+  c.E = d.E, c.Nref = d.Nref, c.nof_filler = d.nof_filler, c.Z = d.Z;
+  c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter, c.flags = d.flags;
+  c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
+  c.max_layers = (uint16_t)ml;
+  cls.K_bytes4 = (size_t)((g.K + 31) / 32) * 4;
+  cls.N        = (uint32_t)g.N;
+  if (takes_h2(d, ml)) {
+    int k    = (d.bg - 1) + ((d.Z == 384) ? 2 : 0);
+    cls.list = k;
+    size_t s = pdc_h2_smem_bytes(d.bg, d.Z, ml);
+    bp.smem_h2[k]  = s > bp.smem_h2[k] ? s : bp.smem_h2[k];
+    int blk        = (d.Z / 2 + 31) / 32 * 32;
+    bp.block_h2[k] = blk > bp.block_h2[k] ? blk : bp.block_h2[k];
+  } else {
+    cls.list      = 4;
+    size_t s      = (d.flags & PDC_F_DEMATCH_ONLY) ? 0 : lane_smem_bytes(g, ml);
+    bp.smem_lane  = s > bp.smem_lane ? s : bp.smem_lane;
+    int blk       = (d.Z + 31) / 32 * 32;
+    bp.block_lane = blk > bp.block_lane ? blk : bp.block_lane;
+  }
+  cls.valid = true;
+  return true;
+}
+
+// Where the buffers of a batch live on the device (ticket staging for pdc_submit, caller's pointers for pdc_decode_device).
+struct batch_buffers {
+  const int8_t*  d_llrs = nullptr;
+  int8_t*        d_soft = nullptr; // soft buffers exchanged with the host (harq_slot < 0); may be null if none is needed
+  uint8_t*       d_bits = nullptr;
+  pdc_cb_result* d_res  = nullptr;
+  int8_t*        d_harq = nullptr;
+  uint32_t       harq_slots = 0;
+  size_t         llr_bytes  = (size_t)-1; // bound for llr_offset + E
+};
+
+// One pass over the descriptors: validation, device descriptors (dev[i], pointers included), kernel list of every code
+// block (lst[i]) and the launch order. Reports the extent of the bits / host soft buffers the batch touches.
+pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers& buf, pdc_dev_cb* dev, uint32_t* order,
+                      uint8_t* lst, batch_plan& bp)
+{
+  desc_class cls;
+  uint32_t   cnt[5]   = {0, 0, 0, 0, 0};
+  size_t     bits_end = 0, soft_end = 0;
+  bool       any_host_soft = false, dense = true;
   for (uint32_t i = 0; i != n; ++i) {
     const pdc_cb_desc& d = descs[i];
-    pdc_geom           g;
-    int                ml = 0;
-    if (!validate_desc(d, g, ml)) {
+    if (!cls.valid || !same_class(d, cls.key)) {
+      if (!classify(d, cls, bp)) {
+        return PDC_ERR_INVALID_ARG;
+      }
+    }
+    if ((d.out_offset & 3) != 0 || d.llr_offset + d.E > buf.llr_bytes) {
       return PDC_ERR_INVALID_ARG;
     }
     pdc_dev_cb& c = dev[i];
-    c.E = d.E, c.Nref = d.Nref, c.nof_filler = d.nof_filler, c.Z = d.Z;
-    c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter, c.flags = d.flags;
-    c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
-    c.max_layers = (uint16_t)ml;
-    if (takes_h2(d, ml)) {
-      int k = (d.bg - 1) + ((d.Z == 384) ? 2 : 0);
-      lists[k].push_back(i);
-      size_t s      = pdc_h2_smem_bytes(d.bg, d.Z, ml);
-      bp.smem_h2[k] = s > bp.smem_h2[k] ? s : bp.smem_h2[k];
-      int blk       = (d.Z / 2 + 31) / 32 * 32;
-      bp.block_h2[k] = blk > bp.block_h2[k] ? blk : bp.block_h2[k];
-    } else {
-      lists[4].push_back(i);
-      size_t s     = (d.flags & PDC_F_DEMATCH_ONLY) ? 0 : lane_smem_bytes(g, ml);
-      bp.smem_lane = s > bp.smem_lane ? s : bp.smem_lane;
-      int blk      = (d.Z + 31) / 32 * 32;
-      bp.block_lane = blk > bp.block_lane ? blk : bp.block_lane;
+    c             = cls.proto;
+    c.llrs        = buf.d_llrs + d.llr_offset;
+    c.out         = buf.d_bits + d.out_offset;
+    c.res         = buf.d_res + i;
+    dense &= (d.out_offset == bits_end); // outputs back to back from offset 0, in order
+    size_t be     = d.out_offset + cls.K_bytes4;
+    bits_end      = be > bits_end ? be : bits_end;
+    if (!(d.flags & PDC_F_DECODE_ONLY)) {
+      if (d.harq_slot >= 0) {
+        if ((uint32_t)d.harq_slot >= buf.harq_slots) {
+          return PDC_ERR_INVALID_ARG;
+        }
+        c.soft = buf.d_harq + (size_t)d.harq_slot * PDC_MAX_N;
+      } else {
+        any_host_soft = true;
+        c.soft        = buf.d_soft + d.soft_offset; // checked by the caller through bp.soft_end
+        size_t se     = d.soft_offset + (size_t)cls.N;
+        soft_end      = se > soft_end ? se : soft_end;
+      }
     }
+    lst[i] = (uint8_t)cls.list;
+    cnt[cls.list]++;
   }
   for (int k = 0; k != 4; ++k) {
-    bp.n_h2[k] = (uint32_t)lists[k].size();
+    bp.n_h2[k] = cnt[k];
   }
-  bp.n_lane = (uint32_t)lists[4].size();
-  uint32_t k = 0;
-  for (auto& l : lists) {
-    for (uint32_t i : l) {
-      order[k++] = i;
+  bp.n_lane        = cnt[4];
+  bp.bits_end      = bits_end;
+  bp.bits_dense    = dense; // the packed outputs tile [0, bits_end): one copy hands them back
+  bp.soft_end      = soft_end;
+  bp.any_host_soft = any_host_soft;
+  int used         = 0;
+  for (int k = 0; k != 5; ++k) {
+    used += (cnt[k] != 0);
+  }
+  bp.identity = (used == 1); // a single kernel takes the whole batch in the given order: no indirection needed
+  if (!bp.identity) {
+    uint32_t off[5], acc = 0;
+    for (int k = 0; k != 5; ++k) {
+      off[k] = acc;
+      acc += cnt[k];
+    }
+    for (uint32_t i = 0; i != n; ++i) {
+      order[off[lst[i]]++] = i;
     }
   }
   return PDC_OK;
@@ -296,7 +388,7 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
   uint32_t off = 0;
   for (int k = 0; k != 4; ++k) {
     if (bp.n_h2[k] != 0) {
-      prm.order = d_order + off;
+      prm.order = bp.identity ? nullptr : d_order + off;
       prm.n     = (int)bp.n_h2[k];
       CK(pdc_launch_h2(prm, (k & 1) + 1, (k & 2) ? 384 : 0, bp.block_h2[k], bp.smem_h2[k], stream));
       ctx->launches++;
@@ -304,7 +396,7 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
     }
   }
   if (bp.n_lane != 0) {
-    prm.order = d_order + off;
+    prm.order = bp.identity ? nullptr : d_order + off;
     prm.n     = (int)bp.n_lane;
     CK(pdc_launch_lane(prm, bp.block_lane, bp.smem_lane, stream));
     ctx->launches++;
