@@ -357,6 +357,47 @@ __device__ __forceinline__ void h2_min2_tree(const uint32_t (&lo)[N], const uint
   }
 }
 
+// Pass 1, second half: the two smallest magnitudes of u[0..DEG) capped at 120, scaled, and the row's sign parity.
+// Out: m1 (smallest magnitude), s1p (scaled m1 with the parity sign), d (scaled m1 xor scaled m2).
+template <int DEG>
+__device__ __forceinline__ void h2_row_minima(const uint32_t (&u)[DEG], uint32_t par, bool generic, uint32_t& m1,
+                                              uint32_t& s1p, uint32_t& d)
+{
+  constexpr int NLEAF = DEG / 2 + 1; // pairs of edges, plus (last edge | 120, 120): caps both minima at 120
+  uint32_t      lo[NLEAF], hi[NLEAF];
+  h2_static_for<DEG / 2>([&](auto i_) {
+    constexpr int  i = decltype(i_)::value;
+    const uint32_t a = h2_abs(u[2 * i]), b = h2_abs(u[2 * i + 1]);
+    lo[i] = h2_min(a, b), hi[i] = h2_max(a, b);
+  });
+  if constexpr ((DEG & 1) != 0) {
+    lo[NLEAF - 1] = h2_min(h2_abs(u[DEG - 1]), H2_120), hi[NLEAF - 1] = H2_120;
+  } else {
+    lo[NLEAF - 1] = H2_120, hi[NLEAF - 1] = H2_120;
+  }
+  uint32_t m2;
+  h2_min2_tree<NLEAF>(lo, hi, m1, m2);
+  const uint32_t s1 = h2_scale(m1, generic);
+  const uint32_t s2 = h2_scale(m2, generic);
+  d                 = s1 ^ s2;
+  s1p               = s1 | (par & H2_SIGN);
+}
+
+// Pass 2 for one edge: in u = v2c message (S - c_old); out u = new biased soft value, y = new message as 1152 + c.
+__device__ __forceinline__ void h2_edge_update(uint32_t& u, uint32_t& y, uint32_t m1, uint32_t s1p, uint32_t d, uint32_t one)
+{
+  const uint32_t a  = h2_abs(u);
+  const uint32_t eq = h2_eq_mask(a, m1);
+  const uint32_t ms = s1p ^ (d & eq);
+  const uint32_t sg = h2_copysign_one(u, one);
+  const uint32_t w  = h2_add(h2_min(a, H2_120), ms);
+  const uint32_t qa = h2_add_sat(a, H2_N336);
+  const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);
+  const uint32_t g  = h2_fma(qa, H2_65504, h2_fma(qb, H2_65504, H2_ONE));
+  y                 = h2_fma(ms, sg, H2_BIAS);
+  u                 = h2_fma(h2_mul(w, sg), g, H2_BIAS);
+}
+
 // One row (layer) of the decode for the lane pair of this thread. cp: the thread's packed message registers.
 //
 // Arithmetic of pass 2 in sign-normalised form (sg = sign of u as +-1, everything else is computed on magnitudes, so the
@@ -375,9 +416,7 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
   constexpr int DEG   = G::deg(M);
   constexpr int E0    = h2_row_start<BG>(M);
   constexpr int P0    = h2_pack_start<BG>(M);
-  constexpr int NLEAF = DEG / 2 + 1; // pairs of edges, plus (last edge | 120, 120): caps both minima at 120
   uint32_t      u[DEG];
-  uint32_t      lo[NLEAF], hi[NLEAF];
   uint32_t      par = 0;
   const uint32_t one = h2_opaque_one();
   mbar_wait(bar_writes, phase_writes & 1u); // the previous row (or the loader) has stored its soft bits
@@ -390,37 +429,14 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
     u[k]             = h2_sub(S, x);
     par ^= u[k];
   });
-  h2_static_for<DEG / 2>([&](auto i_) {
-    constexpr int  i = decltype(i_)::value;
-    const uint32_t a = h2_abs(u[2 * i]), b = h2_abs(u[2 * i + 1]);
-    lo[i] = h2_min(a, b), hi[i] = h2_max(a, b);
-  });
-  if constexpr ((DEG & 1) != 0) {
-    lo[NLEAF - 1] = h2_min(h2_abs(u[DEG - 1]), H2_120), hi[NLEAF - 1] = H2_120;
-  } else {
-    lo[NLEAF - 1] = H2_120, hi[NLEAF - 1] = H2_120;
-  }
-  uint32_t m1, m2;
-  h2_min2_tree<NLEAF>(lo, hi, m1, m2);
-  const uint32_t s1  = h2_scale(m1, generic);
-  const uint32_t s2  = h2_scale(m2, generic);
-  const uint32_t d   = s1 ^ s2;
-  const uint32_t s1p = s1 | (par & H2_SIGN);
+  uint32_t s1p, d, m1;
+  h2_row_minima<DEG>(u, par, generic, m1, s1p, d);
   mbar_arrive_warp(bar_reads); // this warp has consumed the row's soft bits: they may be overwritten once all have
   // ---- pass 2: new check-to-variable messages and soft bits (kept in u[] until every thread has read the old ones) ---------
   uint32_t y[DEG];
   h2_static_for<DEG>([&](auto k_) {
-    constexpr int  k  = decltype(k_)::value;
-    const uint32_t a  = h2_abs(u[k]);
-    const uint32_t eq = h2_eq_mask(a, m1);
-    const uint32_t ms = s1p ^ (d & eq);
-    const uint32_t sg = h2_copysign_one(u[k], one);
-    const uint32_t w  = h2_add(h2_min(a, H2_120), ms);
-    const uint32_t qa = h2_add_sat(a, H2_N336);
-    const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);
-    const uint32_t g  = h2_fma(qa, H2_65504, h2_fma(qb, H2_65504, H2_ONE));
-    y[k]              = h2_fma(ms, sg, H2_BIAS);
-    u[k]              = h2_fma(h2_mul(w, sg), g, H2_BIAS);
+    constexpr int k = decltype(k_)::value;
+    h2_edge_update(u[k], y[k], m1, s1p, d, one);
   });
   h2_static_for<(DEG + 1) / 2>([&](auto i_) {
     constexpr int i = decltype(i_)::value;

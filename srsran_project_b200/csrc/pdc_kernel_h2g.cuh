@@ -1,0 +1,402 @@
+// Packed half2 code-block kernel for ANY number of layers (4 < L <= 46 | 42): low and medium code rates, retransmissions
+// that filled more of the circular buffer, the rate-1/3 case of ldpc_decoder_benchmark. Lifting sizes that are multiples
+// of 32. Same arithmetic, lane mapping, lazily rotated doubled rows, split-phase barriers, CRC epilogue and output as
+// pdc_kernel_h2.cuh (whose helpers it reuses); what differs:
+//   * the number of layers is known only after the rate dematcher ran (ldpc_decoder_impl.cpp:83-115: it follows from the
+//     index of the last non-zero soft bit), so the relative rotations of the columns — which depend on WHICH rows take
+//     part — are derived per code block, in shared memory, by one thread per column;
+//   * the four core rows keep their messages in registers; the extension rows (degree 3..10, each with one private
+//     degree-1 parity column) keep theirs as the same int8 pairs in shared memory, [word][thread] so that every access is
+//     conflict free, and their parity column as one private word per thread (never rotated, never shared);
+//   * extension rows are a run-time loop over rows with the row degree as a template parameter (8 variants).
+#pragma once
+#include "pdc_kernel_h2.cuh"
+
+#define PDC_H2G_MAX_EDGES 320
+
+template <int DEG>
+__device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstride, uint32_t padr,
+                                            const uint32_t* __restrict__ xr, const uint32_t* __restrict__ xw, uint32_t soft_t,
+                                            uint32_t half_row, bool active, bool generic, uint32_t bar_reads,
+                                            uint32_t bar_writes, uint32_t& phase_reads, uint32_t& phase_writes)
+{
+  constexpr int  NW = (DEG + 1) / 2;
+  uint32_t       u[DEG], cw[NW];
+  uint32_t       par = 0;
+  const uint32_t one = h2_opaque_one();
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    cw[j] = lds32(cadr + j * cstride); // private to the thread: no ordering needed
+  }
+  const uint32_t Sp = lds32(padr);
+  mbar_wait(bar_writes, phase_writes & 1u);
+  ++phase_writes;
+  h2_static_for<DEG>([&](auto k_) {
+    constexpr int k = decltype(k_)::value;
+    uint32_t      S;
+    if constexpr (k + 1 < DEG) {
+      const uint32_t ent = xr[e0 + k];
+      const uint32_t adr = soft_t + (ent & 0xffffu);
+      const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+      S = __byte_perm(w0, w1, ent >> 16);
+    } else {
+      S = Sp; // the row's own parity column (last edge: columns ascend)
+    }
+    const uint32_t x = __byte_perm(cw[k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+    u[k]             = h2_sub(S, x);
+    par ^= u[k];
+  });
+  uint32_t s1p, d, m1;
+  h2_row_minima<DEG>(u, par, generic, m1, s1p, d);
+  mbar_arrive_warp(bar_reads);
+  uint32_t y[DEG];
+  h2_static_for<DEG>([&](auto k_) {
+    constexpr int k = decltype(k_)::value;
+    h2_edge_update(u[k], y[k], m1, s1p, d, one);
+  });
+  if (active) {
+    h2_static_for<NW>([&](auto i_) {
+      constexpr int i = decltype(i_)::value;
+      if constexpr (2 * i + 1 < DEG) {
+        sts32(cadr + i * cstride, __byte_perm(y[2 * i], y[2 * i + 1], 0x6420));
+      } else {
+        sts32(cadr + i * cstride, __byte_perm(y[2 * i], 0u, 0x4420));
+      }
+    });
+    sts32(padr, u[DEG - 1]);
+  }
+  mbar_wait(bar_reads, phase_reads & 1u);
+  ++phase_reads;
+  if (active) {
+    h2_static_for<DEG - 1>([&](auto k_) {
+      constexpr int  k   = decltype(k_)::value;
+      const uint32_t adr = soft_t + xw[e0 + k];
+      sts32(adr, u[k]);
+      sts32(adr + half_row, u[k]);
+    });
+  }
+  mbar_arrive_warp(bar_writes);
+}
+
+template <int BG>
+__global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params prm)
+{
+  using G = h2_graph<BG>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t s_graph[PDC_H2G_MAX_EDGES]; // col | shift << 8 of every edge, rows concatenated
+  __shared__ uint32_t s_tab[PDC_H2_TAB_STRIDE];   // core edges, column alignments, natural views: layout of c_h2_tab
+  __shared__ uint32_t s_xr[PDC_H2G_MAX_EDGES];    // extension edges: read offset | PRMT selector << 16
+  __shared__ uint32_t s_xw[PDC_H2G_MAX_EDGES];    // extension edges: byte offset of the column
+  __shared__ uint16_t s_wstart[48];               // first message word of every extension row
+  __shared__ uint32_t s_red[8];
+  __shared__ int      s_nz;
+  __shared__ __align__(8) uint64_t s_mbar[2];
+
+  const int        tid = threadIdx.x, nth = blockDim.x;
+  const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
+  const pdc_dev_cb cb  = prm.cbs[cbi];
+  if (cb.bg != BG) {
+    return;
+  }
+  pdc_geom g;
+  pdc_geom_init(g, cb.bg, cb.Z);
+  const int  Z = g.Z, W = Z >> 1, K = G::KB * Z, bgi = BG - 1;
+  const bool active  = tid < W;
+  const bool generic = (cb.flags & PDC_F_GENERIC) != 0;
+
+  pdc_cb_result res;
+  res.iterations = -1, res.crc_pass = 0, res.status = 0, res.nof_layers = 0;
+
+  const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+  const uint32_t row_bytes = 4u * (uint32_t)Z;
+  const uint32_t soft_t    = smem_base + 4u * (uint32_t)(active ? tid : 0);
+  const uint32_t bar_reads  = (uint32_t)__cvta_generic_to_shared(&s_mbar[0]);
+  const uint32_t bar_writes = (uint32_t)__cvta_generic_to_shared(&s_mbar[1]);
+  uint32_t       phase_reads = 0, phase_writes = 0;
+  if (tid == 0) {
+    mbar_init(bar_reads, (uint32_t)nth >> 5);
+    mbar_init(bar_writes, (uint32_t)nth >> 5);
+    s_nz = 0;
+  }
+  const uint16_t* row_start = c_bg_rows.start[bgi];
+  const uint8_t*  row_deg   = c_bg_rows.deg[bgi];
+  const int       M_rows    = (BG == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
+  for (int e = tid; e < row_start[M_rows]; e += nth) {
+    s_graph[e] = prm.graphs[(size_t)cb.graph_idx * PDC_GRAPH_STRIDE + e];
+  }
+
+  // ---- prologue 1: rate dematching + HARQ combining into the soft buffer in HBM ------------------------------------------------
+  const int8_t* dec_in;
+  int           n_in;
+  if (cb.flags & PDC_F_DECODE_ONLY) {
+    dec_in = cb.llrs;
+    n_in   = (int)cb.E;
+  } else {
+    pdc_dematch_plan pl;
+    pdc_dematch_plan_init(pl, g, (int)cb.E, cb.Qm, cb.rv, (int)cb.Nref, (int)cb.nof_filler,
+                          (cb.flags & PDC_F_NEW_DATA) != 0);
+    if (pl.new_data && pl.rounds == 1) {
+      pdc_dematch_first_tx(pl, cb.llrs, cb.soft, tid, nth);
+    } else {
+      pdc_dematch(pl, cb.llrs, cb.soft, generic, tid, nth);
+    }
+    dec_in = cb.soft;
+    n_in   = g.N;
+  }
+  __syncthreads(); // orders the dematcher's writes before the reads below (same CTA); s_graph, s_nz, barriers visible
+
+  // ---- number of layers (ldpc_decoder_impl.cpp:83-87,106-115) ------------------------------------------------------------------
+  {
+    int best = 0;
+    for (int n = tid; n < n_in; n += nth) {
+      if (dec_in[n] != 0) {
+        best = n + 1;
+      }
+    }
+    best = __reduce_max_sync(0xffffffffu, best);
+    if ((tid & 31) == 0 && best > 0) {
+      atomicMax(&s_nz, best);
+    }
+  }
+  __syncthreads();
+  const int L = pdc_layers_for_nz(g, s_nz);
+  if (L > (int)cb.max_layers) { // cannot happen unless the host bound is wrong; fail loudly instead of overrunning
+    res.status = 3;
+    if (tid == 0) {
+      *cb.res = res;
+    }
+    return;
+  }
+  res.nof_layers = (uint16_t)L;
+  const int E_L  = row_start[L];
+
+  // ---- relative rotations for THIS set of rows: one thread per core column walks the edge list once -------------------------
+  if (tid < G::NCOL) {
+    const int c    = tid;
+    int       prev = -1, first = -1, first_sh = 0;
+    auto      put  = [&](int e, int rel) {
+      const uint32_t off = (uint32_t)c * row_bytes + 4u * (uint32_t)(rel >> 1);
+      const uint32_t val = off | (((rel & 1) ? 0x5432u : 0x3210u) << 16);
+      if (e < G::NEDGE) {
+        s_tab[e] = val;
+      } else {
+        s_xr[e] = val;
+        s_xw[e] = (uint32_t)c * row_bytes;
+      }
+    };
+    for (int e = 0; e < E_L; ++e) {
+      const uint32_t ge = s_graph[e];
+      if ((int)(ge & 0xffu) == c) {
+        const int sh = (int)(ge >> 8);
+        if (prev < 0) {
+          first = e, first_sh = sh;
+        } else {
+          int rel = sh - prev;
+          rel += (rel < 0) ? Z : 0;
+          put(e, rel);
+        }
+        prev = sh;
+      }
+    }
+    const int sigma = (prev < 0) ? 0 : prev; // alignment after a full iteration = shift of the last row holding the column
+    if (first >= 0) {
+      int rel = first_sh - sigma;
+      rel += (rel < 0) ? Z : 0;
+      put(first, rel);
+    }
+    s_tab[PDC_H2_SIGMA_OFF + c] = (uint32_t)sigma;
+    const int nat               = (Z - sigma) % Z;
+    s_tab[PDC_H2_NAT_OFF + c]   = ((uint32_t)c * row_bytes + 4u * (uint32_t)(nat >> 1)) | (((nat & 1) ? 0x5432u : 0x3210u) << 16);
+  }
+  if (tid == nth - 1) { // a thread without a column to walk (nth >= 32 > NCOL)
+    int acc = 0;
+    for (int m = 4; m < L; ++m) {
+      s_wstart[m] = (uint16_t)acc;
+      acc += (row_deg[m] + 1) >> 1;
+    }
+    s_wstart[L] = (uint16_t)acc;
+  }
+  __syncthreads();
+
+  // Shared-memory map: core columns (doubled rows) | parity columns of the extension rows (one word per thread) |
+  // messages of the extension rows ([word][thread]) | ballot words of the output.
+  const uint32_t ext_base = smem_base + G::NCOL * row_bytes;
+  const uint32_t ext_row  = 4u * (uint32_t)W; // bytes per private word-row
+  const uint32_t c2v_base = ext_base + (uint32_t)(L - 4) * ext_row;
+  const uint32_t priv_t   = 4u * (uint32_t)(active ? tid : 0);
+  unsigned char* aux      = smem_raw + G::NCOL * row_bytes + (size_t)(L - 4) * ext_row + (size_t)s_wstart[L] * ext_row;
+
+  // ---- prologue 2: load_soft_bits (ldpc_decoder_impl.cpp:150-191) -------------------------------------------------------------
+  if (active) {
+    sts32(soft_t, H2_BIAS), sts32(soft_t + 2u * Z, H2_BIAS); // the two punctured columns: zero
+    sts32(soft_t + row_bytes, H2_BIAS), sts32(soft_t + row_bytes + 2u * Z, H2_BIAS);
+    for (int c = 2; c < G::KB + L; ++c) {
+      const int sigma = (c < G::NCOL) ? (int)s_tab[PDC_H2_SIGMA_OFF + c] : 0;
+      int       la    = 2 * tid + sigma;
+      la -= (la >= Z) ? Z : 0;
+      int lb = la + 1;
+      lb -= (lb >= Z) ? Z : 0;
+      const int      pa = (c - 2) * Z + la, pb = (c - 2) * Z + lb;
+      const uint32_t xa = (pa < n_in) ? (uint8_t)dec_in[pa] : 0u;
+      const uint32_t xb = (pb < n_in) ? (uint8_t)dec_in[pb] : 0u;
+      const uint32_t S  = h2_soft_from_bytes(xa | (xb << 8));
+      if (c < G::NCOL) {
+        sts32(soft_t + c * row_bytes, S);
+        sts32(soft_t + c * row_bytes + 2u * Z, S);
+      } else {
+        sts32(ext_base + (uint32_t)(c - G::NCOL) * ext_row + priv_t, S);
+      }
+    }
+    const int nwords = s_wstart[L];
+    for (int w = 0; w < nwords; ++w) {
+      sts32(c2v_base + (uint32_t)w * ext_row + priv_t, 0x80808080u); // all messages zero before the first iteration
+    }
+  }
+  mbar_arrive_warp(bar_writes);
+
+  const int  n_sig     = K - (int)cb.nof_filler;
+  const bool has_crc   = cb.crc_type != PDC_CRC_NONE;
+  const bool early     = (cb.flags & PDC_F_EARLY_STOP) && has_crc;
+  const int  max_iter  = cb.max_iter;
+  const int  crc_order = (cb.crc_type == PDC_CRC16) ? 16 : 24;
+  const uint2* crc_pair = nullptr; // see pdc_kernel_h2.cuh
+  if (has_crc) {
+    const int X = PDC_CRC_BIT_PAD + n_sig - 1 + crc_order;
+    const int v = (X - 1) & 1;
+    crc_pair    = reinterpret_cast<const uint2*>(prm.crc_bit + (size_t)(2 * (cb.crc_type - 1) + v) * PDC_CRC_BIT_STRIDE +
+                                              (v + X - 1 - 2 * (active ? tid : 0)));
+  }
+
+  uint32_t cp[h2_pack<BG>::NREG];
+#pragma unroll
+  for (int e = 0; e < h2_pack<BG>::NREG; ++e) {
+    cp[e] = 0x80808080u;
+  }
+
+  int  it_done = 0;
+  bool success = false;
+  for (int it = 0; it < max_iter && !success; ++it) {
+    h2_row<BG, 0, 0>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, 0, 1>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    for (int m = 4; m < L; ++m) {
+      const int      e0   = row_start[m];
+      const uint32_t cadr = c2v_base + (uint32_t)s_wstart[m] * ext_row + priv_t;
+      const uint32_t padr = ext_base + (uint32_t)(m - 4) * ext_row + priv_t;
+#define PDC_H2G_CASE(D)                                                                                                \
+  case D:                                                                                                              \
+    h2g_ext_row<D>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic, bar_reads, bar_writes,  \
+                   phase_reads, phase_writes);                                                                         \
+    break;
+      switch (row_deg[m]) {
+        PDC_H2G_CASE(3)
+        PDC_H2G_CASE(4)
+        PDC_H2G_CASE(5)
+        PDC_H2G_CASE(6)
+        PDC_H2G_CASE(7)
+        PDC_H2G_CASE(8)
+        PDC_H2G_CASE(9)
+        default:
+          h2g_ext_row<10>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic, bar_reads,
+                          bar_writes, phase_reads, phase_writes);
+          break;
+      }
+#undef PDC_H2G_CASE
+    }
+    it_done = it + 1;
+    const bool last = (it_done == max_iter);
+    if (!has_crc || (!early && !last)) {
+      continue;
+    }
+    // ---- hard decision + CRC, as in pdc_kernel_h2.cuh -------------------------------------------------------------------------
+    mbar_wait(bar_writes, phase_writes & 1u);
+    ++phase_writes;
+    uint32_t amin = H2_ONE, acc = 0;
+    if (active) {
+      h2_static_for<G::KB>([&](auto c_) {
+        constexpr int  c = decltype(c_)::value;
+        const uint32_t S = h2_read_natural<BG, 0, c>(s_tab, soft_t);
+        amin             = h2_min(amin, h2_abs(h2_sub(S, H2_BIAS)));
+        const uint2 tp   = __ldg(crc_pair - c * (Z >> 1));
+        asm("{ .reg .pred p, q;\n"
+            "setp.le.f16x2 p|q, %1, %2;\n"
+            "@p xor.b32 %0, %0, %3;\n"
+            "@q xor.b32 %0, %0, %4; }"
+            : "+r"(acc)
+            : "r"(S), "r"(H2_BIAS), "r"(tp.y), "r"(tp.x));
+      });
+    }
+    acc = __reduce_xor_sync(0xffffffffu, acc);
+    if ((tid & 31) == 0) {
+      s_red[tid >> 5] = acc;
+    }
+    const int bad = __syncthreads_or(((amin & 0x7fffu) == 0) || ((amin & 0x7fff0000u) == 0));
+    uint32_t  crc = 0;
+    for (int w = 0; w < (nth >> 5); ++w) {
+      crc ^= s_red[w];
+    }
+    success = (crc == 0u) && (early ? !bad : true);
+    mbar_arrive_warp(bar_writes);
+  }
+
+  // ---- output (as in pdc_kernel_h2.cuh) -----------------------------------------------------------------------------------------
+  if (!(has_crc && (early || it_done == max_iter))) {
+    mbar_wait(bar_writes, phase_writes & 1u);
+  }
+  __syncthreads();
+  {
+    uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]
+    h2_static_for<G::KB>([&](auto c_) {
+      constexpr int  c  = decltype(c_)::value;
+      const uint32_t S  = h2_read_natural<BG, 0, c>(s_tab, soft_t);
+      const uint32_t le = active ? h2_le_mask(S, H2_BIAS) : 0u;
+      const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
+      const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
+      if ((tid & 31) == 0) {
+        s_bal[(c * 6 + (tid >> 5)) * 2 + 0] = be;
+        s_bal[(c * 6 + (tid >> 5)) * 2 + 1] = bo;
+      }
+    });
+    __syncthreads();
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
+    const int nw    = Z >> 5;
+    for (int idx = tid; idx < (K >> 5); idx += nth) {
+      const int      c = idx / nw, k = idx - c * nw;
+      const uint32_t e16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 0] >> (16 * (k & 1))) & 0xffffu;
+      const uint32_t o16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 1] >> (16 * (k & 1))) & 0xffffu;
+      const uint32_t nat = h2_spread16(e16) | (h2_spread16(o16) << 1);
+      out32[idx]         = __byte_perm(__brev(nat), 0u, 0x0123);
+    }
+  }
+  if (success) {
+    res.iterations = early ? it_done : max_iter;
+    res.crc_pass   = 1;
+  }
+  if (tid == 0) {
+    *cb.res = res;
+  }
+}
+
+// Dynamic shared memory of one code block with at most max_layers layers.
+extern "C" size_t pdc_h2g_smem_bytes(int bg, int Z, int max_layers)
+{
+  const int      ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
+  const int      M    = (bg == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
+  const uint8_t* deg  = (bg == 1) ? pdc_bg1_row_deg : pdc_bg2_row_deg;
+  const int      L    = max_layers > M ? M : max_layers;
+  size_t         words = 0;
+  for (int m = 4; m < L; ++m) {
+    words += (deg[m] + 1) / 2;
+  }
+  return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + words * 2 * Z + (size_t)kb * 48;
+}
+extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream)
+{
+  if (bg == 1) {
+    pdc_cb_kernel_h2g<1><<<prm.n, block, smem, stream>>>(prm);
+  } else {
+    pdc_cb_kernel_h2g<2><<<prm.n, block, smem, stream>>>(prm);
+  }
+  return cudaGetLastError();
+}

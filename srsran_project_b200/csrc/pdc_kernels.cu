@@ -4,6 +4,7 @@
 #include "pdc_device.cuh"
 #include "pdc_kernel_lane.cuh"
 #include "pdc_kernel_h2.cuh"
+#include "pdc_kernel_h2g.cuh"
 #include "pdc_probe.cuh"
 
 extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream)
@@ -29,6 +30,34 @@ extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows)
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     if (e != cudaSuccess) {
       return e;
+    }
+  }
+  const void* h2g_kernels[2] = {(const void*)pdc_cb_kernel_h2g<1>, (const void*)pdc_cb_kernel_h2g<2>};
+  for (const void* k : h2g_kernels) {
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, PDC_MAX_DYN_SMEM);
+    if (e != cudaSuccess) {
+      return e;
+    }
+  }
+  // Structure the general packed kernel relies on: in every extension row the last edge is the row's own degree-1
+  // parity column (Kb + m) and every other edge lies in the core columns.
+  for (int bg = 0; bg != 2; ++bg) {
+    const uint8_t* deg = bg ? pdc_bg2_row_deg : pdc_bg1_row_deg;
+    const uint8_t* col = bg ? pdc_bg2_edge_col : pdc_bg1_edge_col;
+    const int      M = bg ? PDC_BG2_ROWS : PDC_BG1_ROWS, kb = bg ? 10 : 22;
+    int            e0 = 0;
+    for (int m = 0; m != M; ++m) {
+      if (m >= 4) {
+        if (col[e0 + deg[m] - 1] != kb + m || deg[m] < 3 || deg[m] > 10) {
+          return cudaErrorInvalidValue;
+        }
+        for (int k = 0; k + 1 < deg[m]; ++k) {
+          if (col[e0 + k] >= kb + 4) {
+            return cudaErrorInvalidValue;
+          }
+        }
+      }
+      e0 += deg[m];
     }
   }
   return pdc_h2_init_device();

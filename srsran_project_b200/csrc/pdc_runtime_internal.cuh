@@ -22,6 +22,8 @@ extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows);
 extern "C" cudaError_t pdc_probe_run(int mode, int sm_count, cudaStream_t stream, double* thread_inst_per_s);
 extern "C" int         pdc_h2_supported(int bg, int Z);
 extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
+extern "C" size_t      pdc_h2g_smem_bytes(int bg, int Z, int max_layers);
+extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
 
 namespace {
 
@@ -219,20 +221,28 @@ size_t lane_smem_bytes(const pdc_geom& g, int max_layers)
   return (size_t)(((g.Kb + L) * g.Z + 15) / 16 * 16) + (size_t)edges * g.Z;
 }
 
+#define PDC_NOF_PACKED_LISTS 6
+#define PDC_NOF_LISTS (PDC_NOF_PACKED_LISTS + 1)
+
 struct batch_plan {
-  // Packed-kernel lists: [0] BG1 any Z, [1] BG2 any Z, [2] BG1 Z = 384, [3] BG2 Z = 384 (compile-time specialisations).
-  size_t   smem_lane = 0, smem_h2[4] = {0, 0, 0, 0};
-  int      block_lane = 32, block_h2[4] = {32, 32, 32, 32};
-  uint32_t n_lane = 0, n_h2[4] = {0, 0, 0, 0}; // order array: the four packed-kernel lists, then the lane-kernel CBs
+  // Packed-kernel lists, four core rows: [0] BG1 any Z, [1] BG2 any Z, [2] BG1 Z = 384, [3] BG2 Z = 384 (compile-time
+  // specialisations); any number of rows (pdc_kernel_h2g.cuh): [4] BG1, [5] BG2. Then the lane kernel.
+  size_t   smem_lane = 0, smem_h2[PDC_NOF_PACKED_LISTS] = {0, 0, 0, 0, 0, 0};
+  int      block_lane = 32, block_h2[PDC_NOF_PACKED_LISTS] = {32, 32, 32, 32, 32, 32};
+  uint32_t n_lane = 0, n_h2[PDC_NOF_PACKED_LISTS] = {0, 0, 0, 0, 0, 0}; // order array: packed lists, then lane-kernel CBs
   bool     identity = false;                   // one list holds every code block: launch without the order array
   size_t   bits_end = 0, soft_end = 0;         // extent of the packed bits / host-exchanged soft buffers
   bool     bits_dense = false, any_host_soft = false;
 };
 
-// Which code blocks the packed half2 kernel takes: the four core rows only, Z a multiple of 32 (pdc_kernel_h2.cuh).
-bool takes_h2(const pdc_cb_desc& d, int max_layers)
+// Which code blocks the packed half2 kernels take: Z a multiple of 32; the four core rows only (pdc_kernel_h2.cuh) or any
+// number of rows as long as the shared memory fits (pdc_kernel_h2g.cuh).
+bool takes_h2(const pdc_cb_desc& d, int max_layers, bool general)
 {
-  if (!pdc_h2_supported(d.bg, d.Z) || max_layers != 4 || d.nof_filler > PDC_CRC_BIT_PAD - 32) {
+  if (!pdc_h2_supported(d.bg, d.Z) || d.nof_filler > PDC_CRC_BIT_PAD - 32) {
+    return false;
+  }
+  if (general ? (max_layers <= 4 || pdc_h2g_smem_bytes(d.bg, d.Z, max_layers) > (size_t)PDC_MAX_DYN_SMEM) : (max_layers != 4)) {
     return false;
   }
   if (d.flags & (PDC_F_DEMATCH_ONLY | PDC_F_FORCE_DECODING)) {
@@ -252,7 +262,7 @@ struct desc_class {
   pdc_dev_cb  proto; // pointers zero
   size_t      K_bytes4 = 0; // packed message size rounded up to words
   uint32_t    N        = 0;
-  int         list     = 0; // 0..3 packed-kernel lists, 4 lane kernel
+  int         list     = 0; // packed-kernel lists, then PDC_NOF_PACKED_LISTS = lane kernel
   bool        valid    = false;
 };
 
@@ -279,15 +289,16 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
   c.max_layers = (uint16_t)ml;
   cls.K_bytes4 = (size_t)((g.K + 31) / 32) * 4;
   cls.N        = (uint32_t)g.N;
-  if (takes_h2(d, ml)) {
-    int k    = (d.bg - 1) + ((d.Z == 384) ? 2 : 0);
+  const bool core_only = takes_h2(d, ml, false), general = !core_only && takes_h2(d, ml, true);
+  if (core_only || general) {
+    int k    = general ? (4 + (d.bg - 1)) : ((d.bg - 1) + ((d.Z == 384) ? 2 : 0));
     cls.list = k;
-    size_t s = pdc_h2_smem_bytes(d.bg, d.Z, ml);
+    size_t s = general ? pdc_h2g_smem_bytes(d.bg, d.Z, ml) : pdc_h2_smem_bytes(d.bg, d.Z, ml);
     bp.smem_h2[k]  = s > bp.smem_h2[k] ? s : bp.smem_h2[k];
     int blk        = (d.Z / 2 + 31) / 32 * 32;
     bp.block_h2[k] = blk > bp.block_h2[k] ? blk : bp.block_h2[k];
   } else {
-    cls.list      = 4;
+    cls.list      = PDC_NOF_PACKED_LISTS;
     size_t s      = (d.flags & PDC_F_DEMATCH_ONLY) ? 0 : lane_smem_bytes(g, ml);
     bp.smem_lane  = s > bp.smem_lane ? s : bp.smem_lane;
     int blk       = (d.Z + 31) / 32 * 32;
@@ -314,7 +325,7 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
                       uint8_t* lst, batch_plan& bp)
 {
   desc_class cls;
-  uint32_t   cnt[5]   = {0, 0, 0, 0, 0};
+  uint32_t   cnt[PDC_NOF_LISTS] = {0};
   size_t     bits_end = 0, soft_end = 0;
   bool       any_host_soft = false, dense = true;
   for (uint32_t i = 0; i != n; ++i) {
@@ -351,22 +362,22 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
     lst[i] = (uint8_t)cls.list;
     cnt[cls.list]++;
   }
-  for (int k = 0; k != 4; ++k) {
+  for (int k = 0; k != PDC_NOF_PACKED_LISTS; ++k) {
     bp.n_h2[k] = cnt[k];
   }
-  bp.n_lane        = cnt[4];
+  bp.n_lane        = cnt[PDC_NOF_PACKED_LISTS];
   bp.bits_end      = bits_end;
   bp.bits_dense    = dense; // the packed outputs tile [0, bits_end): one copy hands them back
   bp.soft_end      = soft_end;
   bp.any_host_soft = any_host_soft;
   int used         = 0;
-  for (int k = 0; k != 5; ++k) {
+  for (int k = 0; k != PDC_NOF_LISTS; ++k) {
     used += (cnt[k] != 0);
   }
   bp.identity = (used == 1); // a single kernel takes the whole batch in the given order: no indirection needed
   if (!bp.identity) {
-    uint32_t off[5], acc = 0;
-    for (int k = 0; k != 5; ++k) {
+    uint32_t off[PDC_NOF_LISTS], acc = 0;
+    for (int k = 0; k != PDC_NOF_LISTS; ++k) {
       off[k] = acc;
       acc += cnt[k];
     }
@@ -386,11 +397,15 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
   prm.crc_pow = ctx->d_crc;
   prm.crc_bit = ctx->d_crc_bit;
   uint32_t off = 0;
-  for (int k = 0; k != 4; ++k) {
+  for (int k = 0; k != PDC_NOF_PACKED_LISTS; ++k) {
     if (bp.n_h2[k] != 0) {
       prm.order = bp.identity ? nullptr : d_order + off;
       prm.n     = (int)bp.n_h2[k];
-      CK(pdc_launch_h2(prm, (k & 1) + 1, (k & 2) ? 384 : 0, bp.block_h2[k], bp.smem_h2[k], stream));
+      if (k >= 4) {
+        CK(pdc_launch_h2g(prm, (k & 1) + 1, bp.block_h2[k], bp.smem_h2[k], stream));
+      } else {
+        CK(pdc_launch_h2(prm, (k & 1) + 1, (k & 2) ? 384 : 0, bp.block_h2[k], bp.smem_h2[k], stream));
+      }
       ctx->launches++;
       off += bp.n_h2[k];
     }
