@@ -13,6 +13,12 @@
 #include "pdc_kernel_h2.cuh"
 
 #define PDC_H2G_MAX_EDGES 320
+#if defined(PDC_KERNEL_TU)
+// Static structure of the base graphs (filled by pdc_h2g_init_device): previous edge on the same column (0xffff: none) and,
+// per number of layers L, the last edge on every core column among rows < L (0xffff: none).
+__device__ uint16_t d_h2g_prev[2][PDC_H2G_MAX_EDGES];
+__device__ uint16_t d_h2g_last[2][48][26];
+#endif
 
 template <int DEG>
 __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstride, uint32_t padr,
@@ -29,13 +35,18 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
     cw[j] = lds32(cadr + j * cstride); // private to the thread: no ordering needed
   }
   const uint32_t Sp = lds32(padr);
+  uint32_t       ents[DEG - 1];
+#pragma unroll
+  for (int k = 0; k < DEG - 1; ++k) {
+    ents[k] = xr[e0 + k]; // table entries do not depend on the other warps either
+  }
   mbar_wait(bar_writes, phase_writes & 1u);
   ++phase_writes;
   h2_static_for<DEG>([&](auto k_) {
     constexpr int k = decltype(k_)::value;
     uint32_t      S;
     if constexpr (k + 1 < DEG) {
-      const uint32_t ent = xr[e0 + k];
+      const uint32_t ent = ents[k];
       const uint32_t adr = soft_t + (ent & 0xffffu);
       const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
       S = __byte_perm(w0, w1, ent >> 16);
@@ -76,6 +87,23 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
     });
   }
   mbar_arrive_warp(bar_writes);
+}
+
+// Device-side twin of pdc_h2g_smem_bytes (same formula; the row degrees come from constant memory).
+template <int BG>
+__device__ __forceinline__ size_t pdc_h2g_smem_bytes_dev(int Z, int max_layers)
+{
+  constexpr int  ncol = h2_graph<BG>::NCOL, kb = h2_graph<BG>::KB;
+  constexpr int  M    = (BG == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
+  const uint8_t* deg  = c_bg_rows.deg[BG - 1];
+  const int      L    = max_layers > M ? M : max_layers;
+  size_t         words = 0;
+  for (int m = 4; m < L; ++m) {
+    words += (deg[m] + 1) / 2;
+  }
+  const size_t work  = words * 2 * Z + (size_t)kb * 48;
+  const size_t stage = (size_t)(kb + L - 2) * Z + 16;
+  return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + (work > stage ? work : stage);
 }
 
 template <int BG>
@@ -145,11 +173,30 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   }
   __syncthreads(); // orders the dematcher's writes before the reads below (same CTA); s_graph, s_nz, barriers visible
 
-  // ---- number of layers (ldpc_decoder_impl.cpp:83-87,106-115) ------------------------------------------------------------------
+  // ---- the decoder input, staged at the tail of the dynamic shared memory (the host sized it: pdc_h2g_smem_bytes). Only the
+  //      part the host's bound on the number of layers allows to be non-zero is needed. ----------------------------------------
+  const int      n_stage  = min(n_in, (G::KB + (int)cb.max_layers - 2) * Z);
+  const size_t   dyn_size = pdc_h2g_smem_bytes_dev<BG>(Z, (int)cb.max_layers);
+  unsigned char* stage    = smem_raw + dyn_size - (size_t)((n_stage + 15) & ~15);
   {
-    int best = 0;
-    for (int n = tid; n < n_in; n += nth) {
-      if (dec_in[n] != 0) {
+    const bool vec = ((reinterpret_cast<uintptr_t>(dec_in) & 15) == 0);
+    const int  n16 = vec ? (n_stage >> 4) : 0;
+    int        best = 0;
+    for (int q = tid; q < n16; q += nth) {
+      const int4 v = *reinterpret_cast<const int4*>(dec_in + 16 * q);
+      reinterpret_cast<int4*>(stage)[q] = v;
+      const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (w[j] != 0) {
+          best = 16 * q + 4 * j + 4 - (__clz(w[j]) >> 3); // 1 + index of the last non-zero byte of the word
+        }
+      }
+    }
+    for (int n = 16 * n16 + tid; n < n_stage; n += nth) {
+      const int8_t x = dec_in[n];
+      stage[n]       = (unsigned char)x;
+      if (x != 0) {
         best = n + 1;
       }
     }
@@ -170,11 +217,17 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   res.nof_layers = (uint16_t)L;
   const int E_L  = row_start[L];
 
-  // ---- relative rotations for THIS set of rows: one thread per core column walks the edge list once -------------------------
-  if (tid < G::NCOL) {
-    const int c    = tid;
-    int       prev = -1, first = -1, first_sh = 0;
-    auto      put  = [&](int e, int rel) {
+  // ---- relative rotations for THIS set of rows. The previous writer of a column is the nearest earlier edge on the same
+  //      column (static: d_h2g_prev) or, for the first edge of a column, the last edge on it among the L rows that take part
+  //      (d_h2g_last[L]): one thread per edge. -------------------------------------------------------------------------------
+  for (int e = tid; e < E_L; e += nth) {
+    const uint32_t ge = s_graph[e];
+    const int      c  = (int)(ge & 0xffu);
+    if (c < G::NCOL) {
+      int pe = d_h2g_prev[bgi][e];
+      pe     = (pe == 0xffff) ? (int)d_h2g_last[bgi][L][c] : pe;
+      int rel = (int)(ge >> 8) - (int)(s_graph[pe] >> 8);
+      rel += (rel < 0) ? Z : 0;
       const uint32_t off = (uint32_t)c * row_bytes + 4u * (uint32_t)(rel >> 1);
       const uint32_t val = off | (((rel & 1) ? 0x5432u : 0x3210u) << 16);
       if (e < G::NEDGE) {
@@ -183,27 +236,12 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
         s_xr[e] = val;
         s_xw[e] = (uint32_t)c * row_bytes;
       }
-    };
-    for (int e = 0; e < E_L; ++e) {
-      const uint32_t ge = s_graph[e];
-      if ((int)(ge & 0xffu) == c) {
-        const int sh = (int)(ge >> 8);
-        if (prev < 0) {
-          first = e, first_sh = sh;
-        } else {
-          int rel = sh - prev;
-          rel += (rel < 0) ? Z : 0;
-          put(e, rel);
-        }
-        prev = sh;
-      }
     }
-    const int sigma = (prev < 0) ? 0 : prev; // alignment after a full iteration = shift of the last row holding the column
-    if (first >= 0) {
-      int rel = first_sh - sigma;
-      rel += (rel < 0) ? Z : 0;
-      put(first, rel);
-    }
+  }
+  if (tid < G::NCOL) {
+    const int c     = tid;
+    const int le    = d_h2g_last[bgi][L][c];
+    const int sigma = (le == 0xffff) ? 0 : (int)(s_graph[le] >> 8); // alignment after a full iteration
     s_tab[PDC_H2_SIGMA_OFF + c] = (uint32_t)sigma;
     const int nat               = (Z - sigma) % Z;
     s_tab[PDC_H2_NAT_OFF + c]   = ((uint32_t)c * row_bytes + 4u * (uint32_t)(nat >> 1)) | (((nat & 1) ? 0x5432u : 0x3210u) << 16);
@@ -237,8 +275,8 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
       int lb = la + 1;
       lb -= (lb >= Z) ? Z : 0;
       const int      pa = (c - 2) * Z + la, pb = (c - 2) * Z + lb;
-      const uint32_t xa = (pa < n_in) ? (uint8_t)dec_in[pa] : 0u;
-      const uint32_t xb = (pb < n_in) ? (uint8_t)dec_in[pb] : 0u;
+      const uint32_t xa = (pa < n_stage) ? stage[pa] : 0u;
+      const uint32_t xb = (pb < n_stage) ? stage[pb] : 0u;
       const uint32_t S  = h2_soft_from_bytes(xa | (xb << 8));
       if (c < G::NCOL) {
         sts32(soft_t + c * row_bytes, S);
@@ -247,6 +285,9 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
         sts32(ext_base + (uint32_t)(c - G::NCOL) * ext_row + priv_t, S);
       }
     }
+  }
+  __syncthreads(); // the messages below may overlap the staged input
+  if (active) {
     const int nwords = s_wstart[L];
     for (int w = 0; w < nwords; ++w) {
       sts32(c2v_base + (uint32_t)w * ext_row + priv_t, 0x80808080u); // all messages zero before the first iteration
@@ -378,7 +419,8 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   }
 }
 
-// Dynamic shared memory of one code block with at most max_layers layers.
+// Dynamic shared memory of one code block with at most max_layers layers: core columns | parity columns of the extension
+// rows | max(messages + ballot words, staged decoder input).
 extern "C" size_t pdc_h2g_smem_bytes(int bg, int Z, int max_layers)
 {
   const int      ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
@@ -389,7 +431,45 @@ extern "C" size_t pdc_h2g_smem_bytes(int bg, int Z, int max_layers)
   for (int m = 4; m < L; ++m) {
     words += (deg[m] + 1) / 2;
   }
-  return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + words * 2 * Z + (size_t)kb * 48;
+  const size_t work  = words * 2 * Z + (size_t)kb * 48;
+  const size_t stage = (size_t)(kb + L - 2) * Z + 16;
+  return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + (work > stage ? work : stage);
+}
+static cudaError_t pdc_h2g_init_device()
+{
+  static uint16_t prev[2][PDC_H2G_MAX_EDGES];
+  static uint16_t last[2][48][26];
+  for (int bg = 0; bg != 2; ++bg) {
+    const uint8_t* deg = bg ? pdc_bg2_row_deg : pdc_bg1_row_deg;
+    const uint8_t* col = bg ? pdc_bg2_edge_col : pdc_bg1_edge_col;
+    const int      M = bg ? PDC_BG2_ROWS : PDC_BG1_ROWS, ncol = bg ? 14 : 26;
+    int            cur[26];
+    for (int c = 0; c != 26; ++c) {
+      cur[c] = 0xffff;
+    }
+    int e = 0;
+    for (int m = 0; m <= M; ++m) {
+      for (int c = 0; c != 26; ++c) {
+        last[bg][m][c] = (uint16_t)cur[c]; // rows < m
+      }
+      if (m == M) {
+        break;
+      }
+      for (int k = 0; k != deg[m]; ++k, ++e) {
+        if (col[e] < ncol) {
+          prev[bg][e] = (uint16_t)cur[col[e]];
+          cur[col[e]] = e;
+        } else {
+          prev[bg][e] = 0xffff;
+        }
+      }
+    }
+  }
+  cudaError_t err = cudaMemcpyToSymbol(d_h2g_prev, prev, sizeof(prev));
+  if (err != cudaSuccess) {
+    return err;
+  }
+  return cudaMemcpyToSymbol(d_h2g_last, last, sizeof(last));
 }
 extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream)
 {

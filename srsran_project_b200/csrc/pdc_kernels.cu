@@ -60,6 +60,10 @@ extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows)
       e0 += deg[m];
     }
   }
+  e = pdc_h2g_init_device();
+  if (e != cudaSuccess) {
+    return e;
+  }
   return pdc_h2_init_device();
 }
 
