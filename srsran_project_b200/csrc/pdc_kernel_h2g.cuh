@@ -1,6 +1,6 @@
 // Packed half2 code-block kernel for ANY number of layers (4 < L <= 46 | 42): low and medium code rates, retransmissions
 // that filled more of the circular buffer, the rate-1/3 case of ldpc_decoder_benchmark. Lifting sizes that are multiples
-// of 32. Same arithmetic, lane mapping, lazily rotated doubled rows, split-phase barriers, CRC epilogue and output as
+// of 32. Same arithmetic, lane mapping, lazily rotated doubled rows, CRC epilogue and output as
 // pdc_kernel_h2.cuh (whose helpers it reuses); what differs:
 //   * the number of layers is known only after the rate dematcher ran (ldpc_decoder_impl.cpp:83-115: it follows from the
 //     index of the last non-zero soft bit), so the relative rotations of the columns — which depend on WHICH rows take
@@ -23,9 +23,10 @@ __device__ uint16_t d_h2g_last[2][48][26];
 template <int DEG>
 __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstride, uint32_t padr,
                                             const uint32_t* __restrict__ xr, const uint32_t* __restrict__ xw, uint32_t soft_t,
-                                            uint32_t half_row, bool active, bool generic, uint32_t bar_reads,
-                                            uint32_t bar_writes, uint32_t& phase_reads, uint32_t& phase_writes)
+                                            uint32_t half_row, bool active, bool generic)
 {
+  // Extension rows are short (3..10 edges): two CTA-wide hardware barriers per row beat the split-phase mbarriers of the
+  // core rows here (measured +5 %: nothing worth overlapping, and BAR.SYNC wakes up faster than a try_wait loop).
   constexpr int  NW = (DEG + 1) / 2;
   uint32_t       u[DEG], cw[NW];
   uint32_t       par = 0;
@@ -40,8 +41,6 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
   for (int k = 0; k < DEG - 1; ++k) {
     ents[k] = xr[e0 + k]; // table entries do not depend on the other warps either
   }
-  mbar_wait(bar_writes, phase_writes & 1u);
-  ++phase_writes;
   h2_static_for<DEG>([&](auto k_) {
     constexpr int k = decltype(k_)::value;
     uint32_t      S;
@@ -59,7 +58,6 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
   });
   uint32_t s1p, d, m1;
   h2_row_minima<DEG>(u, par, generic, m1, s1p, d);
-  mbar_arrive_warp(bar_reads);
   uint32_t y[DEG];
   h2_static_for<DEG>([&](auto k_) {
     constexpr int k = decltype(k_)::value;
@@ -76,8 +74,7 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
     });
     sts32(padr, u[DEG - 1]);
   }
-  mbar_wait(bar_reads, phase_reads & 1u);
-  ++phase_reads;
+  __syncthreads(); // every warp has read the row's soft bits
   if (active) {
     h2_static_for<DEG - 1>([&](auto k_) {
       constexpr int  k   = decltype(k_)::value;
@@ -86,7 +83,7 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
       sts32(adr + half_row, u[k]);
     });
   }
-  mbar_arrive_warp(bar_writes);
+  __syncthreads(); // ... and written the new ones
 }
 
 // Device-side twin of pdc_h2g_smem_bytes (same formula; the row degrees come from constant memory).
@@ -321,14 +318,17 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
     h2_row<BG, 0, 1>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
     h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
     h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    if (L > 4) {
+      mbar_wait(bar_writes, phase_writes & 1u); // row 3 has stored its soft bits; the extension rows use CTA barriers
+      ++phase_writes;
+    }
     for (int m = 4; m < L; ++m) {
       const int      e0   = row_start[m];
       const uint32_t cadr = c2v_base + (uint32_t)s_wstart[m] * ext_row + priv_t;
       const uint32_t padr = ext_base + (uint32_t)(m - 4) * ext_row + priv_t;
 #define PDC_H2G_CASE(D)                                                                                                \
   case D:                                                                                                              \
-    h2g_ext_row<D>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic, bar_reads, bar_writes,  \
-                   phase_reads, phase_writes);                                                                         \
+    h2g_ext_row<D>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);                       \
     break;
       switch (row_deg[m]) {
         PDC_H2G_CASE(3)
@@ -339,11 +339,13 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
         PDC_H2G_CASE(8)
         PDC_H2G_CASE(9)
         default:
-          h2g_ext_row<10>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic, bar_reads,
-                          bar_writes, phase_reads, phase_writes);
+          h2g_ext_row<10>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);
           break;
       }
 #undef PDC_H2G_CASE
+    }
+    if (L > 4) {
+      mbar_arrive_warp(bar_writes); // hands over to the next consumer of the mbarrier protocol
     }
     it_done = it + 1;
     const bool last = (it_done == max_iter);
