@@ -128,31 +128,6 @@ __device__ __forceinline__ uint32_t lds16(uint32_t addr)
   return v;
 }
 
-// Split-phase barriers on shared-memory mbarriers: a warp announces "our reads (or writes) of this phase are done" with
-// arrive and only blocks, with wait, right before its first access that depends on the other warps. The arithmetic in
-// between overlaps with the slower warps instead of idling at a __syncthreads. One arrival per warp (lane 0 after a
-// __syncwarp); arrive has release and wait has acquire semantics at CTA scope, which orders the shared-memory traffic.
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
-{
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_warp(uint32_t bar)
-{
-  __syncwarp();
-  if ((threadIdx.x & 31) == 0) {
-    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(bar) : "memory");
-  }
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
-{
-  asm volatile("{ .reg .pred p;\n"
-               "MBAR_WAIT: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-               "@p bra MBAR_DONE;\n"
-               "bra MBAR_WAIT;\n"
-               "MBAR_DONE: }" ::"r"(bar), "r"(parity)
-               : "memory");
-}
-
 static constexpr uint32_t H2_120 = 0x57805780u, H2_N120 = 0xD780D780u, H2_64 = 0x54005400u, H2_N64 = 0xD400D400u;
 static constexpr uint32_t H2_N216 = 0xDAC0DAC0u, H2_65504 = 0x7BFF7BFFu, H2_ONE = 0x3C003C00u, H2_1024 = 0x64006400u;
 static constexpr uint32_t H2_N1024 = 0xE400E400u, H2_1023_5 = 0x63FF63FFu, H2_0_8 = 0x3A663A66u, H2_N1152 = 0xE480E480u;
@@ -409,8 +384,7 @@ __device__ __forceinline__ void h2_edge_update(uint32_t& u, uint32_t& y, uint32_
 //   c' = sg ms                     stored as the byte c' + 128
 template <int BG, int ZC, int M>
 __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const uint32_t* __restrict__ tab,
-                                       uint32_t soft_t, uint32_t row_bytes, bool active, bool generic, uint32_t bar_reads,
-                                       uint32_t bar_writes, uint32_t& phase_reads, uint32_t& phase_writes)
+                                       uint32_t soft_t, uint32_t row_bytes, bool active, bool generic)
 {
   using G             = h2_graph<BG>;
   constexpr int DEG   = G::deg(M);
@@ -419,8 +393,6 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
   uint32_t      u[DEG];
   uint32_t      par = 0;
   const uint32_t one = h2_opaque_one();
-  mbar_wait(bar_writes, phase_writes & 1u); // the previous row (or the loader) has stored its soft bits
-  ++phase_writes;
   // ---- pass 1: variable-to-check messages, two smallest magnitudes, sign parity ------------------------------------------
   h2_static_for<DEG>([&](auto k_) {
     constexpr int  k = decltype(k_)::value;
@@ -431,7 +403,6 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
   });
   uint32_t s1p, d, m1;
   h2_row_minima<DEG>(u, par, generic, m1, s1p, d);
-  mbar_arrive_warp(bar_reads); // this warp has consumed the row's soft bits: they may be overwritten once all have
   // ---- pass 2: new check-to-variable messages and soft bits (kept in u[] until every thread has read the old ones) ---------
   uint32_t y[DEG];
   h2_static_for<DEG>([&](auto k_) {
@@ -446,15 +417,14 @@ __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const 
       cp[P0 + i] = __byte_perm(y[2 * i], 0u, 0x4420);
     }
   });
-  mbar_wait(bar_reads, phase_reads & 1u);
-  ++phase_reads;
+  __syncthreads(); // every warp has consumed the row's soft bits: they may be overwritten
   if (ZC > 0 || active) {
     h2_static_for<DEG>([&](auto k_) {
       constexpr int k = decltype(k_)::value;
       h2_write_col<ZC, G::col(E0 + k)>(soft_t, row_bytes, u[k]);
     });
   }
-  mbar_arrive_warp(bar_writes);
+  __syncthreads(); // ... and the next row sees the new ones
 }
 
 // ---- prologue of a first transmission: deinterleaver into a natural-order int8 staging tile in shared memory ------------
@@ -590,7 +560,6 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
   using G = h2_graph<BG>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_red[8];
-  __shared__ __align__(8) uint64_t s_mbar[2]; // [0] reads of a row done, [1] writes of a row done
 
   const int        tid = threadIdx.x, nth = blockDim.x;
   const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
@@ -616,13 +585,6 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
   const uint32_t aux_addr  = smem_base + G::NCOL * row_bytes;
   const int      nstage    = (G::NCOL - 2) * Z;
 
-  const uint32_t bar_reads  = (uint32_t)__cvta_generic_to_shared(&s_mbar[0]);
-  const uint32_t bar_writes = (uint32_t)__cvta_generic_to_shared(&s_mbar[1]);
-  uint32_t       phase_reads = 0, phase_writes = 0;
-  if (tid == 0) {
-    mbar_init(bar_reads, (uint32_t)nth >> 5);
-    mbar_init(bar_writes, (uint32_t)nth >> 5);
-  }
 
   // ---- prologue 1: rate dematching + HARQ combining into the soft buffer in HBM ------------------------------------------------
   const int8_t* dec_in = nullptr; // where load_soft_bits reads from (global memory), unless the staging tile holds it
@@ -747,7 +709,7 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
       }
     }
   }
-  mbar_arrive_warp(bar_writes);
+  __syncthreads();
 
   const int       n_sig    = K - (int)cb.nof_filler;
   const bool      has_crc  = cb.crc_type != PDC_CRC_NONE;
@@ -774,10 +736,10 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
   int  it_done = 0;
   bool success = false;
   for (int it = 0; it < max_iter && !success; ++it) {
-    h2_row<BG, ZC, 0>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, ZC, 1>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, ZC, 2>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, ZC, 3>(cp, tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
+    h2_row<BG, ZC, 0>(cp, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, ZC, 1>(cp, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, ZC, 2>(cp, tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, ZC, 3>(cp, tab, soft_t, row_bytes, active, generic);
     it_done = it + 1;
     const bool last = (it_done == max_iter);
     if (!has_crc || (!early && !last)) {
@@ -786,8 +748,6 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     // ---- hard decision + CRC (ldpc_decoder_impl.cpp:127-135, log_likelihood_ratio.cpp:350-376). The CRC is linear: it is
     //      the xor of x^(n_sig - 1 - n + order) mod P over the set bits n, so every thread folds its own lane pairs, in
     //      natural order, straight from the soft rows; a zero soft bit among the K systematic ones refuses the early stop.
-    mbar_wait(bar_writes, phase_writes & 1u); // row 3 has stored its soft bits
-    ++phase_writes;
     uint32_t amin = H2_ONE, acc = 0;
     if (active) {
       h2_static_for<G::KB>([&](auto c_) {
@@ -815,15 +775,11 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     // pusch_codeblock_decoder.cpp:62-73: without early stop there is one CRC after the last iteration and zero soft bits
     // do not matter.
     success = (crc == 0u) && (early ? !bad : true);
-    mbar_arrive_warp(bar_writes); // pairs with the wait at the top of the next iteration's first row
   }
 
   // ---- output: K hard bits in natural order, MSB first (bit_buffer.h:106-136). Every thread reads its natural lane pair
   //      of each column (as the CRC pass does); two warp ballots give the even and the odd lanes of 64 consecutive bits,
   //      which are then interleaved, bit-reversed per byte and stored with coalesced words. -------------------------------------
-  if (!(has_crc && (early || it_done == max_iter))) {
-    mbar_wait(bar_writes, phase_writes & 1u);
-  }
   __syncthreads();
   {
     uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]

@@ -25,8 +25,6 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
                                             const uint32_t* __restrict__ xr, const uint32_t* __restrict__ xw, uint32_t soft_t,
                                             uint32_t half_row, bool active, bool generic)
 {
-  // Extension rows are short (3..10 edges): two CTA-wide hardware barriers per row beat the split-phase mbarriers of the
-  // core rows here (measured +5 %: nothing worth overlapping, and BAR.SYNC wakes up faster than a try_wait loop).
   constexpr int  NW = (DEG + 1) / 2;
   uint32_t       u[DEG], cw[NW];
   uint32_t       par = 0;
@@ -115,7 +113,6 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   __shared__ uint16_t s_wstart[48];               // first message word of every extension row
   __shared__ uint32_t s_red[8];
   __shared__ int      s_nz;
-  __shared__ __align__(8) uint64_t s_mbar[2];
 
   const int        tid = threadIdx.x, nth = blockDim.x;
   const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
@@ -135,12 +132,7 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
   const uint32_t row_bytes = 4u * (uint32_t)Z;
   const uint32_t soft_t    = smem_base + 4u * (uint32_t)(active ? tid : 0);
-  const uint32_t bar_reads  = (uint32_t)__cvta_generic_to_shared(&s_mbar[0]);
-  const uint32_t bar_writes = (uint32_t)__cvta_generic_to_shared(&s_mbar[1]);
-  uint32_t       phase_reads = 0, phase_writes = 0;
   if (tid == 0) {
-    mbar_init(bar_reads, (uint32_t)nth >> 5);
-    mbar_init(bar_writes, (uint32_t)nth >> 5);
     s_nz = 0;
   }
   const uint16_t* row_start = c_bg_rows.start[bgi];
@@ -290,7 +282,7 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
       sts32(c2v_base + (uint32_t)w * ext_row + priv_t, 0x80808080u); // all messages zero before the first iteration
     }
   }
-  mbar_arrive_warp(bar_writes);
+  __syncthreads();
 
   const int  n_sig     = K - (int)cb.nof_filler;
   const bool has_crc   = cb.crc_type != PDC_CRC_NONE;
@@ -314,14 +306,10 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   int  it_done = 0;
   bool success = false;
   for (int it = 0; it < max_iter && !success; ++it) {
-    h2_row<BG, 0, 0>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, 0, 1>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic, bar_reads, bar_writes, phase_reads, phase_writes);
-    if (L > 4) {
-      mbar_wait(bar_writes, phase_writes & 1u); // row 3 has stored its soft bits; the extension rows use CTA barriers
-      ++phase_writes;
-    }
+    h2_row<BG, 0, 0>(cp, s_tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 0, 1>(cp, s_tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic);
+    h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic);
     for (int m = 4; m < L; ++m) {
       const int      e0   = row_start[m];
       const uint32_t cadr = c2v_base + (uint32_t)s_wstart[m] * ext_row + priv_t;
@@ -344,17 +332,12 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
       }
 #undef PDC_H2G_CASE
     }
-    if (L > 4) {
-      mbar_arrive_warp(bar_writes); // hands over to the next consumer of the mbarrier protocol
-    }
     it_done = it + 1;
     const bool last = (it_done == max_iter);
     if (!has_crc || (!early && !last)) {
       continue;
     }
     // ---- hard decision + CRC, as in pdc_kernel_h2.cuh -------------------------------------------------------------------------
-    mbar_wait(bar_writes, phase_writes & 1u);
-    ++phase_writes;
     uint32_t amin = H2_ONE, acc = 0;
     if (active) {
       h2_static_for<G::KB>([&](auto c_) {
@@ -380,13 +363,9 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
       crc ^= s_red[w];
     }
     success = (crc == 0u) && (early ? !bad : true);
-    mbar_arrive_warp(bar_writes);
   }
 
   // ---- output (as in pdc_kernel_h2.cuh) -----------------------------------------------------------------------------------------
-  if (!(has_crc && (early || it_done == max_iter))) {
-    mbar_wait(bar_writes, phase_writes & 1u);
-  }
   __syncthreads();
   {
     uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]
