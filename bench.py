@@ -516,7 +516,7 @@ def run_cuda_arm(args):
                 "peak_source": f"measured in this run: {best} dual-pipe issue rate x 2 lanes per register (pack=2)",
                 "frac_of_32bit_issue_peak": achieved / probe["lop3+imad"],
                 "probe_Tinst_per_s": {k: v / 1e12 for k, v in probe.items()},
-                "kernel": "pdc_cb_kernel_h2<1>", "kernel_ms": kernel_ms,
+                "kernel": "pdc_cb_kernel_h2<1, 384>", "kernel_ms": kernel_ms,
                 "hbm": {"bound": "hbm", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak,
                         "peak_source": hbm_src, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                         "algorithmic_bytes_per_step": alg_bytes, "traffic": traffic}}
@@ -531,7 +531,9 @@ def run_cuda_arm(args):
         reps = max(1, int(args.cpu_seconds / max(r1["sec"], 1e-4)))
         r = cpu_run(wl, n_s, reps, nthreads, llr_set=last_set)
         cpu_gbps = reps * (n_s // C) * wl["cfg"]["tbs"] / r["sec"] / 1e9
+        r1t = cpu_run(wl, C, max(1, reps // 4), 1, llr_set=last_set)  # one transport block on one pinned-less thread
         cpu = {"value": cpu_gbps, "unit": "Gbit/s", "cores": r["cores"], "kind": r["kind"],
+               "single_thread_value": max(1, reps // 4) * wl["cfg"]["tbs"] / r1t["sec"] / 1e9,
                "sample": f"{n_s // C} TBs ({n_s} CBs) of LLR set {last_set} x {reps} repetitions, {r['flavour']}, "
                          f"{r['sec']:.1f} s wall"}
         it_ok = (r["iters"] == res["iterations"][:n_s]).all()
