@@ -2,7 +2,7 @@
 //
 // Scope: code blocks whose decode touches only the four core rows of the base graph (nof_layers == 4, i.e. the code rate
 // is high enough that no extension row carries received LLRs: ldpc_decoder_impl.cpp:106-115) and whose lifting size is a
-// multiple of 32. That is the operating point of the metric (100 MHz / 256QAM PUSCH: BG1, Z = 384, E = 8960 | 8992).
+// even (44 of the 51 sizes; the odd ones, 3 .. 15, stay with the lane kernel). The operating point of the metric is (100 MHz / 256QAM PUSCH: BG1, Z = 384, E = 8960 | 8992).
 // Everything else is decoded by the lane kernel (pdc_kernel_lane.cuh).
 //
 // Mapping. One CTA per code block, Z/2 threads; thread t owns check lanes (2t, 2t+1) of EVERY row, packed as one half2.
@@ -332,6 +332,39 @@ __device__ __forceinline__ void h2_min2_tree(const uint32_t (&lo)[N], const uint
   }
 }
 
+// ---- output: K hard bits in natural order, MSB first (bit_buffer.h:106-136) -----------------------------------------------
+// s_nat[(c * 6 + w) * 2 + {0, 1}]: the 64 hard bits of lanes 64 w .. 64 w + 63 of column c, natural order, LSB first (built
+// from the two warp ballots of the even and the odd lanes). Word idx of the output holds bits 32 idx .. 32 idx + 31; when Z is
+// a multiple of 32 that is half of one entry, otherwise it is stitched from pieces of up to 32 / Z + 1 columns.
+__device__ __forceinline__ uint32_t h2_output_word(const uint32_t* s_nat, int idx, int Z, int K)
+{
+  uint32_t nat;
+  if ((Z & 31) == 0) {
+    const int nw = Z >> 5, c = idx / nw, k = idx - c * nw;
+    nat          = s_nat[(c * 6 + (k >> 1)) * 2 + (k & 1)];
+  } else {
+    nat        = 0;
+    int n      = 32 * idx;
+    int filled = 0;
+    while (filled < 32 && n < K) {
+      const int c = n / Z, l = n - c * Z;
+      const int cnt = min(32 - filled, Z - l);
+      const int w = l >> 6, o = l & 63;
+      unsigned long long v = ((unsigned long long)s_nat[(c * 6 + w) * 2 + 1] << 32) | s_nat[(c * 6 + w) * 2];
+      v >>= o;
+      if (o != 0 && w + 1 < 6) {
+        const unsigned long long nx = ((unsigned long long)s_nat[(c * 6 + w + 1) * 2 + 1] << 32) | s_nat[(c * 6 + w + 1) * 2];
+        v |= nx << (64 - o);
+      }
+      const uint32_t piece = (uint32_t)v & ((cnt == 32) ? 0xffffffffu : ((1u << cnt) - 1u));
+      nat |= piece << filled;
+      filled += cnt;
+      n += cnt;
+    }
+  }
+  return __byte_perm(__brev(nat), 0u, 0x0123);
+}
+
 // Pass 1, second half: the two smallest magnitudes of u[0..DEG) capped at 120, scaled, and the row's sign parity.
 // Out: m1 (smallest magnitude), s1p (scaled m1 with the parity sign), d (scaled m1 xor scaled m2).
 template <int DEG>
@@ -633,9 +666,9 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
           break;
       }
       __syncthreads();
-      if ((reinterpret_cast<uintptr_t>(cb.soft) & 15) == 0) {
+      if ((reinterpret_cast<uintptr_t>(cb.soft) & 15) == 0 && ((nstage | pl.N) & 15) == 0) {
         int4*     dst = reinterpret_cast<int4*>(cb.soft);
-        const int n16 = nstage >> 4, N16 = pl.N >> 4; // Z is a multiple of 32
+        const int n16 = nstage >> 4, N16 = pl.N >> 4;
         for (int q = tid; q < n16; q += nth) {
           dst[q] = reinterpret_cast<const int4*>(stg)[q];
         }
@@ -777,12 +810,17 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     success = (crc == 0u) && (early ? !bad : true);
   }
 
-  // ---- output: K hard bits in natural order, MSB first (bit_buffer.h:106-136). Every thread reads its natural lane pair
-  //      of each column (as the CRC pass does); two warp ballots give the even and the odd lanes of 64 consecutive bits,
-  //      which are then interleaved, bit-reversed per byte and stored with coalesced words. -------------------------------------
+  // ---- output: every thread reads its natural lane pair of each column (as the CRC pass does); two warp ballots give the
+  //      even and the odd lanes of 64 consecutive bits; lane 0 interleaves them; coalesced word stores. ----------------------
   __syncthreads();
   {
-    uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]
+    uint32_t* s_nat = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][low | high 32 lanes]
+    if (nth < 192) { // warps that do not exist (small Z) hold no bits
+      for (int q = tid; q < 2 * 6 * G::KB; q += nth) {
+        s_nat[q] = 0u;
+      }
+      __syncthreads();
+    }
     h2_static_for<G::KB>([&](auto c_) {
       constexpr int  c  = decltype(c_)::value;
       const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t);
@@ -790,19 +828,14 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
       const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
       const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
       if ((tid & 31) == 0) {
-        s_bal[(c * 6 + (tid >> 5)) * 2 + 0] = be;
-        s_bal[(c * 6 + (tid >> 5)) * 2 + 1] = bo;
+        s_nat[(c * 6 + (tid >> 5)) * 2 + 0] = h2_spread16(be & 0xffffu) | (h2_spread16(bo & 0xffffu) << 1);
+        s_nat[(c * 6 + (tid >> 5)) * 2 + 1] = h2_spread16(be >> 16) | (h2_spread16(bo >> 16) << 1);
       }
     });
     __syncthreads();
     uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
-    const int nw    = Z >> 5;
-    for (int idx = tid; idx < (K >> 5); idx += nth) {
-      const int      c = idx / nw, k = idx - c * nw;
-      const uint32_t e16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 0] >> (16 * (k & 1))) & 0xffffu;
-      const uint32_t o16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 1] >> (16 * (k & 1))) & 0xffffu;
-      const uint32_t nat = h2_spread16(e16) | (h2_spread16(o16) << 1);
-      out32[idx]         = __byte_perm(__brev(nat), 0u, 0x0123);
+    for (int idx = tid; idx < ((K + 31) >> 5); idx += nth) {
+      out32[idx] = h2_output_word(s_nat, idx, Z, K);
     }
   }
   if (success) {
@@ -814,9 +847,10 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
   }
 }
 
+// Every even lifting size: a thread owns the lane pair (2 t, 2 t + 1). The 7 odd sizes (3 .. 15) stay with the lane kernel.
 extern "C" int pdc_h2_supported(int bg, int Z)
 {
-  return (bg == 1 || bg == 2) && (Z % 32 == 0) && Z >= 32 && Z <= PDC_MAX_Z;
+  return (bg == 1 || bg == 2) && (Z % 2 == 0) && Z >= 2 && Z <= PDC_MAX_Z;
 }
 extern "C" size_t pdc_h2_smem_bytes(int bg, int Z, int)
 {

@@ -1,6 +1,6 @@
 // Packed half2 code-block kernel for ANY number of layers (4 < L <= 46 | 42): low and medium code rates, retransmissions
 // that filled more of the circular buffer, the rate-1/3 case of ldpc_decoder_benchmark. Lifting sizes that are multiples
-// of 32. Same arithmetic, lane mapping, lazily rotated doubled rows, CRC epilogue and output as
+// of 2. Same arithmetic, lane mapping, lazily rotated doubled rows, CRC epilogue and output as
 // pdc_kernel_h2.cuh (whose helpers it reuses); what differs:
 //   * the number of layers is known only after the rate dematcher ran (ldpc_decoder_impl.cpp:83-115: it follows from the
 //     index of the last non-zero soft bit), so the relative rotations of the columns — which depend on WHICH rows take
@@ -97,7 +97,7 @@ __device__ __forceinline__ size_t pdc_h2g_smem_bytes_dev(int Z, int max_layers)
     words += (deg[m] + 1) / 2;
   }
   const size_t work  = words * 2 * Z + (size_t)kb * 48;
-  const size_t stage = (size_t)(kb + L - 2) * Z + 16;
+  const size_t stage = (size_t)(kb + L - 2) * Z + 32;
   return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + (work > stage ? work : stage);
 }
 
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   //      part the host's bound on the number of layers allows to be non-zero is needed. ----------------------------------------
   const int      n_stage  = min(n_in, (G::KB + (int)cb.max_layers - 2) * Z);
   const size_t   dyn_size = pdc_h2g_smem_bytes_dev<BG>(Z, (int)cb.max_layers);
-  unsigned char* stage    = smem_raw + dyn_size - (size_t)((n_stage + 15) & ~15);
+  unsigned char* stage    = smem_raw + ((dyn_size - (size_t)((n_stage + 15) & ~15)) & ~(size_t)15);
   {
     const bool vec = ((reinterpret_cast<uintptr_t>(dec_in) & 15) == 0);
     const int  n16 = vec ? (n_stage >> 4) : 0;
@@ -368,7 +368,13 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   // ---- output (as in pdc_kernel_h2.cuh) -----------------------------------------------------------------------------------------
   __syncthreads();
   {
-    uint32_t* s_bal = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][even | odd]
+    uint32_t* s_nat = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][low | high 32 lanes]
+    if (nth < 192) { // warps that do not exist (small Z) hold no bits
+      for (int q = tid; q < 2 * 6 * G::KB; q += nth) {
+        s_nat[q] = 0u;
+      }
+      __syncthreads();
+    }
     h2_static_for<G::KB>([&](auto c_) {
       constexpr int  c  = decltype(c_)::value;
       const uint32_t S  = h2_read_natural<BG, 0, c>(s_tab, soft_t);
@@ -376,19 +382,14 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
       const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
       const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
       if ((tid & 31) == 0) {
-        s_bal[(c * 6 + (tid >> 5)) * 2 + 0] = be;
-        s_bal[(c * 6 + (tid >> 5)) * 2 + 1] = bo;
+        s_nat[(c * 6 + (tid >> 5)) * 2 + 0] = h2_spread16(be & 0xffffu) | (h2_spread16(bo & 0xffffu) << 1);
+        s_nat[(c * 6 + (tid >> 5)) * 2 + 1] = h2_spread16(be >> 16) | (h2_spread16(bo >> 16) << 1);
       }
     });
     __syncthreads();
     uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
-    const int nw    = Z >> 5;
-    for (int idx = tid; idx < (K >> 5); idx += nth) {
-      const int      c = idx / nw, k = idx - c * nw;
-      const uint32_t e16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 0] >> (16 * (k & 1))) & 0xffffu;
-      const uint32_t o16 = (s_bal[(c * 6 + (k >> 1)) * 2 + 1] >> (16 * (k & 1))) & 0xffffu;
-      const uint32_t nat = h2_spread16(e16) | (h2_spread16(o16) << 1);
-      out32[idx]         = __byte_perm(__brev(nat), 0u, 0x0123);
+    for (int idx = tid; idx < ((K + 31) >> 5); idx += nth) {
+      out32[idx] = h2_output_word(s_nat, idx, Z, K);
     }
   }
   if (success) {
@@ -413,7 +414,7 @@ extern "C" size_t pdc_h2g_smem_bytes(int bg, int Z, int max_layers)
     words += (deg[m] + 1) / 2;
   }
   const size_t work  = words * 2 * Z + (size_t)kb * 48;
-  const size_t stage = (size_t)(kb + L - 2) * Z + 16;
+  const size_t stage = (size_t)(kb + L - 2) * Z + 32;
   return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + (work > stage ? work : stage);
 }
 static cudaError_t pdc_h2g_init_device()

@@ -235,7 +235,7 @@ struct batch_plan {
   bool     bits_dense = false, any_host_soft = false;
 };
 
-// Which code blocks the packed half2 kernels take: Z a multiple of 32; the four core rows only (pdc_kernel_h2.cuh) or any
+// Which code blocks the packed half2 kernels take: Z even; the four core rows only (pdc_kernel_h2.cuh) or any
 // number of rows as long as the shared memory fits (pdc_kernel_h2g.cuh).
 bool takes_h2(const pdc_cb_desc& d, int max_layers, bool general)
 {
