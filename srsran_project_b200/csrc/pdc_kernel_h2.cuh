@@ -1,9 +1,9 @@
 // Code-block kernel for high-rate code blocks: packed half2 arithmetic, check-to-variable messages in registers.
 //
 // Scope: code blocks whose decode touches only the four core rows of the base graph (nof_layers == 4, i.e. the code rate
-// is high enough that no extension row carries received LLRs: ldpc_decoder_impl.cpp:106-115) and whose lifting size is a
-// even (44 of the 51 sizes; the odd ones, 3 .. 15, stay with the lane kernel). The operating point of the metric is (100 MHz / 256QAM PUSCH: BG1, Z = 384, E = 8960 | 8992).
-// Everything else is decoded by the lane kernel (pdc_kernel_lane.cuh).
+// is high enough that no extension row carries received LLRs: ldpc_decoder_impl.cpp:106-115) and whose lifting size is
+// even (44 of the 51 sizes). The operating point of the metric is 100 MHz / 256QAM PUSCH: BG1, Z = 384, E = 8960 | 8992.
+// More layers: pdc_kernel_h2g.cuh (which reuses this file's row code); odd lifting sizes: pdc_kernel_lane.cuh.
 //
 // Mapping. One CTA per code block, Z/2 threads; thread t owns check lanes (2t, 2t+1) of EVERY row, packed as one half2.
 //   * Soft bits live in shared memory as IEEE halves. Integers up to 2048 are exact in a half, and the reference's
