@@ -57,7 +57,8 @@ class PdcError(RuntimeError):
 
 
 def library_path():
-    return os.path.join(HERE, "libpuschdec_cuda.so")
+    """PDC_LIBRARY selects another build of the SAME library (kernel A/B runs on one GPU box); never a different backend."""
+    return os.environ.get("PDC_LIBRARY") or os.path.join(HERE, "libpuschdec_cuda.so")
 
 
 _lib = None

@@ -365,6 +365,44 @@ __device__ __forceinline__ uint32_t h2_output_word(const uint32_t* s_nat, int id
   return __byte_perm(__brev(nat), 0u, 0x0123);
 }
 
+// The output phase of a packed kernel. Every thread reads its natural lane pair of each systematic column (as the CRC pass
+// does); two warp ballots give the even and the odd lanes of 64 consecutive bits, which lane 0 stores as they are. Then all
+// threads interleave them into natural-order words (in parallel: a warp instruction with one active lane costs a full issue
+// slot) and store the output with coalesced words.
+template <int BG, int ZC, typename TAB>
+__device__ __forceinline__ void
+h2_emit_bits(TAB tab, uint32_t soft_t, uint32_t* s_nat, bool active, int tid, int nth, int Z, int K, uint32_t* out32)
+{
+  using G = h2_graph<BG>;
+  if (nth < 192) { // warps that do not exist (small Z) hold no bits
+    for (int q = tid; q < 2 * 6 * G::KB; q += nth) {
+      s_nat[q] = 0u;
+    }
+    __syncthreads();
+  }
+  h2_static_for<G::KB>([&](auto c_) {
+    constexpr int  c  = decltype(c_)::value;
+    const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t);
+    const uint32_t le = active ? h2_le_mask(S, H2_BIAS) : 0u;
+    const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
+    const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
+    if ((tid & 31) == 0) {
+      s_nat[(c * 6 + (tid >> 5)) * 2 + 0] = be; // 4-byte accesses: the scratch area is only word aligned for small Z
+      s_nat[(c * 6 + (tid >> 5)) * 2 + 1] = bo;
+    }
+  });
+  __syncthreads();
+  for (int q = tid; q < 6 * G::KB; q += nth) { // one (column, warp) pair of words per task, converted in place
+    const uint32_t be = s_nat[2 * q], bo = s_nat[2 * q + 1];
+    s_nat[2 * q]     = h2_spread16(be & 0xffffu) | (h2_spread16(bo & 0xffffu) << 1);
+    s_nat[2 * q + 1] = h2_spread16(be >> 16) | (h2_spread16(bo >> 16) << 1);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < ((K + 31) >> 5); idx += nth) {
+    out32[idx] = h2_output_word(s_nat, idx, Z, K);
+  }
+}
+
 // Pass 1, second half: the two smallest magnitudes of u[0..DEG) capped at 120, scaled, and the row's sign parity.
 // Out: m1 (smallest magnitude), s1p (scaled m1 with the parity sign), d (scaled m1 xor scaled m2).
 template <int DEG>
@@ -810,34 +848,9 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     success = (crc == 0u) && (early ? !bad : true);
   }
 
-  // ---- output: every thread reads its natural lane pair of each column (as the CRC pass does); two warp ballots give the
-  //      even and the odd lanes of 64 consecutive bits; lane 0 interleaves them; coalesced word stores. ----------------------
+  // ---- output ------------------------------------------------------------------------------------------------------------------
   __syncthreads();
-  {
-    uint32_t* s_nat = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][low | high 32 lanes]
-    if (nth < 192) { // warps that do not exist (small Z) hold no bits
-      for (int q = tid; q < 2 * 6 * G::KB; q += nth) {
-        s_nat[q] = 0u;
-      }
-      __syncthreads();
-    }
-    h2_static_for<G::KB>([&](auto c_) {
-      constexpr int  c  = decltype(c_)::value;
-      const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t);
-      const uint32_t le = active ? h2_le_mask(S, H2_BIAS) : 0u;
-      const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
-      const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
-      if ((tid & 31) == 0) {
-        s_nat[(c * 6 + (tid >> 5)) * 2 + 0] = h2_spread16(be & 0xffffu) | (h2_spread16(bo & 0xffffu) << 1);
-        s_nat[(c * 6 + (tid >> 5)) * 2 + 1] = h2_spread16(be >> 16) | (h2_spread16(bo >> 16) << 1);
-      }
-    });
-    __syncthreads();
-    uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
-    for (int idx = tid; idx < ((K + 31) >> 5); idx += nth) {
-      out32[idx] = h2_output_word(s_nat, idx, Z, K);
-    }
-  }
+  h2_emit_bits<BG, ZC>(tab, soft_t, reinterpret_cast<uint32_t*>(aux), active, tid, nth, Z, K, reinterpret_cast<uint32_t*>(cb.out));
   if (success) {
     res.iterations = early ? it_done : max_iter;
     res.crc_pass   = 1;

@@ -367,31 +367,7 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
 
   // ---- output (as in pdc_kernel_h2.cuh) -----------------------------------------------------------------------------------------
   __syncthreads();
-  {
-    uint32_t* s_nat = reinterpret_cast<uint32_t*>(aux); // [KB][6 warps][low | high 32 lanes]
-    if (nth < 192) { // warps that do not exist (small Z) hold no bits
-      for (int q = tid; q < 2 * 6 * G::KB; q += nth) {
-        s_nat[q] = 0u;
-      }
-      __syncthreads();
-    }
-    h2_static_for<G::KB>([&](auto c_) {
-      constexpr int  c  = decltype(c_)::value;
-      const uint32_t S  = h2_read_natural<BG, 0, c>(s_tab, soft_t);
-      const uint32_t le = active ? h2_le_mask(S, H2_BIAS) : 0u;
-      const uint32_t be = __ballot_sync(0xffffffffu, (le & 0x0000ffffu) != 0);
-      const uint32_t bo = __ballot_sync(0xffffffffu, (le & 0xffff0000u) != 0);
-      if ((tid & 31) == 0) {
-        s_nat[(c * 6 + (tid >> 5)) * 2 + 0] = h2_spread16(be & 0xffffu) | (h2_spread16(bo & 0xffffu) << 1);
-        s_nat[(c * 6 + (tid >> 5)) * 2 + 1] = h2_spread16(be >> 16) | (h2_spread16(bo >> 16) << 1);
-      }
-    });
-    __syncthreads();
-    uint32_t* out32 = reinterpret_cast<uint32_t*>(cb.out);
-    for (int idx = tid; idx < ((K + 31) >> 5); idx += nth) {
-      out32[idx] = h2_output_word(s_nat, idx, Z, K);
-    }
-  }
+  h2_emit_bits<BG, 0>(s_tab, soft_t, reinterpret_cast<uint32_t*>(aux), active, tid, nth, Z, K, reinterpret_cast<uint32_t*>(cb.out));
   if (success) {
     res.iterations = early ? it_done : max_iter;
     res.crc_pass   = 1;
