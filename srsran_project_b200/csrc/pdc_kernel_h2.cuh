@@ -630,7 +630,6 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
 {
   using G = h2_graph<BG>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ uint32_t s_red[8];
 
   const int        tid = threadIdx.x, nth = blockDim.x;
   const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
@@ -654,6 +653,9 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
   // After the soft rows: the natural-order int8 staging copy (prologue) / the ballot words (output).
   unsigned char* aux       = smem_raw + G::NCOL * row_bytes;
   const uint32_t aux_addr  = smem_base + G::NCOL * row_bytes;
+  // Per-warp CRC partials live in the scratch area too (it is idle between the prologue and the output phase): with no static
+  // shared memory four CTAs of Z = 384 need exactly 196 KB, which leaves the SM the larger L1 for the CRC tables.
+  uint32_t* s_red = reinterpret_cast<uint32_t*>(aux);
   const int      nstage    = (G::NCOL - 2) * Z;
 
 
