@@ -12,6 +12,8 @@
  *   srsran::pusch_codeblock_decoder::decode      lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp:35-74
  *   srsran::hal::hw_accelerator_pusch_dec        include/srsran/hal/phy/upper/channel_processors/pusch/
  *                                                hw_accelerator_pusch_dec.h:83-115 (enqueue/dequeue/read_outputs/HARQ)
+ *   srsran::pusch_decoder_impl::join_and_notify  lib/phy/upper/channel_processors/pusch/pusch_decoder_impl.cpp:396-505
+ *     + concatenate_codeblocks                   (transport-block assembly and TB CRC24A: the pdc_*_tbs entry points)
  *
  * Conventions: plain pointers and sizes only; every function returns a pdc_status (0 = ok) and never throws or
  * aborts; a context is thread-safe; there is NO CPU fallback — without a CUDA device pdc_create fails.
@@ -26,7 +28,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 1
+#define PDC_ABI_VERSION 2
 
 typedef enum {
   PDC_OK               = 0,
@@ -51,6 +53,9 @@ typedef enum {
 #define PDC_F_GENERIC 0x08u        /* arithmetic of ldpc_decoder_generic (scale = round(0.8f x)); default AVX2/AVX512 */
 #define PDC_F_DECODE_ONLY 0x10u    /* ldpc_decoder::decode: llrs are the E = N_in de-matched soft bits, no HARQ buffer */
 #define PDC_F_DEMATCH_ONLY 0x20u   /* ldpc_rate_dematcher::rate_dematch only (CB already decoded: combine, no decode) */
+#define PDC_F_DECODED 0x40u        /* pdc_*_tbs only: the CB passed its CRC in an earlier submission and is not enqueued again
+                                      (pusch_decoder_hw_impl.cpp:236-243): no LLRs are read; its bits, kept with the HARQ slot
+                                      (harq_slot >= 0 required), take part in the transport-block assembly */
 
 /* One code block. Mirrors codeblock_metadata (include/srsran/phy/upper/codeblock_metadata.h:41-100) plus
  * ldpc_decoder::configuration (ldpc_decoder.h:44-55) and hw_pusch_decoder_configuration
@@ -82,6 +87,26 @@ typedef struct {
   uint16_t nof_layers; /* base-graph check nodes actually processed (ldpc_decoder_impl.cpp:115), 0 if not decoded */
 } pdc_cb_result;
 
+/* One transport block = C consecutive code blocks of the same submission (pusch_decoder_impl.cpp:396-505). All of them
+ * share bg, Z, nof_filler and crc_type; C == 1: crc_type CRC16 | CRC24A and tbs_bits = K - F - crc bits; C > 1: CRC24B
+ * and tbs_bits + 24 = C * (K - F - 24) (TS 38.212 5.2.2 as ldpc_segmenter_rx_impl.cpp:52-106 derives it). */
+typedef struct {
+  uint32_t first_cb;  /* index of the TB's first code block in descs[] */
+  uint32_t nof_cbs;   /* C >= 1 */
+  uint32_t tbs_bits;  /* transport block size in bits (multiple of 8), TB CRC not included */
+  uint32_t reserved;  /* 0 */
+  uint64_t tb_offset; /* byte offset of the tbs_bits / 8 payload bytes in the TB buffer; multiple of 4 */
+} pdc_tb_desc;
+
+/* pusch_decoder_result (pusch_decoder_result.h) for one TB. A CB counts as passed if its CRC matched in this submission
+ * or it carries PDC_F_DECODED / PDC_F_DEMATCH_ONLY. */
+typedef struct {
+  uint8_t  tb_crc_ok;  /* C == 1: the CB's CRC; C > 1: every CB passed AND CRC24A(payload) equals the 24 bits that follow it */
+  uint8_t  written;    /* 1 iff the payload bytes were written: every CB passed (on a TB CRC mismatch they ARE written and
+                          the caller resets its CB CRC flags: pusch_decoder_impl.cpp:431-437) */
+  uint16_t nof_cbs_ok; /* code blocks of the TB that count as passed */
+} pdc_tb_result;
+
 typedef struct pdc_ctx pdc_ctx;
 typedef int64_t        pdc_ticket;
 
@@ -112,10 +137,27 @@ pdc_status pdc_poll(pdc_ctx* ctx, pdc_ticket ticket);
 pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits_bytes, pdc_cb_result* res,
                      int8_t* soft_out, size_t soft_bytes);
 
+/* --- transport-block path: code blocks decoded AND assembled on the device, one payload per TB comes back ---------------
+ * As pdc_submit, plus ntb transport blocks over those code blocks. Code blocks with harq_slot >= 0 keep their decoded bits
+ * with the HARQ slot, so that a later transmission that re-sends only the failed ones (the others flagged PDC_F_DECODED)
+ * still assembles the whole TB on the device. desc.out_offset is used only by CBs with harq_slot < 0. */
+pdc_status pdc_submit_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
+                          const int8_t* llrs, size_t llr_bytes, const int8_t* soft_in, size_t soft_bytes,
+                          pdc_ticket* ticket);
+/* Blocks until done; TB payloads to tb_bytes + tb.tb_offset (only TBs with written == 1), TB results to tb_res[0..ntb),
+ * per-CB results (iteration statistics) to cb_res[0..n) if not NULL, soft buffers as pdc_fetch. No per-CB bits travel. */
+pdc_status pdc_fetch_tbs(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* tb_bytes, size_t tb_bytes_len, pdc_tb_result* tb_res,
+                         pdc_cb_result* cb_res, int8_t* soft_out, size_t soft_bytes);
+
 /* --- device-resident path (inputs and outputs already in HBM; used for kernel-only measurements and by callers that
  *     produce LLRs on the GPU). All pointers are device pointers; stream is a cudaStream_t (NULL = default). ------- */
 pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32_t n, const int8_t* d_llrs,
                              int8_t* d_soft, uint8_t* d_bits, pdc_cb_result* d_res, void* stream);
+
+/* Device-resident transport-block variant: d_bits may be NULL when every CB has harq_slot >= 0. */
+pdc_status pdc_decode_device_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32_t n, const pdc_tb_desc* tbs_host,
+                                 uint32_t ntb, const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits, pdc_cb_result* d_res,
+                                 uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream);
 
 /* --- HARQ arena (ext_harq_buffer_context_repository.h:36-107 / free_harq_context_entry) --------------------------- */
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot);                               /* zero-fills the slot */

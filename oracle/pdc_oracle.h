@@ -37,6 +37,13 @@ int orc_codeblock_decode(int flavour, int bg, int Z, int8_t* buf, const int8_t* 
                          int Qm, int Nref, int nof_filler, int crc_id, int max_iter, int use_early_stop,
                          int force_decoding, uint8_t* out_packed);
 
+/* pusch_decoder_impl::join_and_notify + concatenate_codeblocks (pusch_decoder_impl.cpp:396-505) for one transport block of
+ * C code blocks with K message bits each (cb_packed: C buffers of cb_stride bytes, MSB first), nof_filler fillers, cb_crc_ok[C].
+ * Writes tbs_bits / 8 bytes to tb_out only where the reference writes its transport_block span; returns tb_crc_ok and sets
+ * *written (payload written) accordingly. */
+int orc_tb_assemble(int C, int K, int nof_filler, const uint8_t* cb_packed, int cb_stride, const uint8_t* cb_crc_ok,
+                    int tbs_bits, uint8_t* tb_out, int* written);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,6 +80,17 @@ class Oracle:
                                            _u8(out))
         return it, out
 
+    def tb_assemble(self, K, nof_filler, cb_packed, cb_crc_ok, tbs_bits, tb_out):
+        """pusch_decoder_impl::join_and_notify for one TB. cb_packed: [C, stride] uint8; tb_out (uint8, tbs_bits / 8) is
+        written where the reference would write. -> (tb_crc_ok, written)"""
+        cb_packed = np.ascontiguousarray(cb_packed, np.uint8)
+        ok = np.ascontiguousarray(cb_crc_ok, np.uint8)
+        assert tb_out.dtype == np.uint8 and tb_out.size == tbs_bits // 8 and tb_out.flags.c_contiguous
+        w = ctypes.c_int(0)
+        r = self.lib.orc_tb_assemble(cb_packed.shape[0], K, nof_filler, _u8(cb_packed), cb_packed.shape[1], _u8(ok),
+                                     tbs_bits, _u8(tb_out), ctypes.byref(w))
+        return bool(r), bool(w.value)
+
     # Stimulus (transmit side) lives in tools/stimulus; kept here as thin forwards so that tests read naturally.
     def encode(self, bg, Z, msg_bits):
         from tools import stimulus

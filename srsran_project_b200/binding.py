@@ -13,6 +13,7 @@ PDC_F_FORCE_DECODING = 0x04
 PDC_F_GENERIC = 0x08
 PDC_F_DECODE_ONLY = 0x10
 PDC_F_DEMATCH_ONLY = 0x20
+PDC_F_DECODED = 0x40
 
 PDC_OK, PDC_ERR_INVALID_ARG, PDC_ERR_NO_DEVICE, PDC_ERR_CUDA, PDC_ERR_CAPACITY, PDC_ERR_NOT_READY, PDC_ERR_BAD_TICKET = range(7)
 _STATUS_NAMES = ["PDC_OK", "PDC_ERR_INVALID_ARG", "PDC_ERR_NO_DEVICE", "PDC_ERR_CUDA", "PDC_ERR_CAPACITY",
@@ -45,7 +46,11 @@ DESC_DTYPE = np.dtype([("bg", np.uint8), ("Qm", np.uint8), ("rv", np.uint8), ("c
                        ("max_iter", np.uint8), ("flags", np.uint8), ("Z", np.uint16), ("E", np.uint32),
                        ("Nref", np.uint32), ("nof_filler", np.uint32), ("harq_slot", np.int32),
                        ("llr_offset", np.uint64), ("soft_offset", np.uint64), ("out_offset", np.uint64)])
+TB_DESC_DTYPE = np.dtype([("first_cb", np.uint32), ("nof_cbs", np.uint32), ("tbs_bits", np.uint32), ("reserved", np.uint32),
+                          ("tb_offset", np.uint64)])  # pdc_tb_desc
+TB_RESULT_DTYPE = np.dtype([("tb_crc_ok", np.uint8), ("written", np.uint8), ("nof_cbs_ok", np.uint16)])  # pdc_tb_result
 assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
+assert TB_DESC_DTYPE.itemsize == 24 and TB_RESULT_DTYPE.itemsize == 4
 assert RESULT_DTYPE.itemsize == ctypes.sizeof(CbResult) == 8
 
 
@@ -84,6 +89,10 @@ def load_library():
     lib.pdc_poll.argtypes = [vp, ctypes.c_int64]
     lib.pdc_fetch.argtypes = [vp, ctypes.c_int64, vp, ctypes.c_size_t, vp, vp, ctypes.c_size_t]
     lib.pdc_decode_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp, vp, vp]
+    lib.pdc_submit_tbs.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t,
+                                   ctypes.POINTER(ctypes.c_int64)]
+    lib.pdc_fetch_tbs.argtypes = [vp, ctypes.c_int64, vp, ctypes.c_size_t, vp, vp, vp, ctypes.c_size_t]
+    lib.pdc_decode_device_tbs.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, vp, vp, vp, vp, vp, vp]
     lib.pdc_harq_free.argtypes = [vp, ctypes.c_int32]
     lib.pdc_harq_read.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
@@ -99,7 +108,7 @@ def load_library():
 
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
-                    "pdc_fetch", "pdc_decode_device", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
+                    "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
                     "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
 
 
@@ -167,6 +176,31 @@ class PuschDecCuda:
         t = self.submit(descs, llrs, soft)
         res = self.fetch(t, descs.size, bits, soft)
         return res, bits
+
+    # --- transport-block path ---------------------------------------------------------------------------------------
+    def submit_tbs(self, descs, tbs, llrs, soft_in=None):
+        assert descs.dtype == DESC_DTYPE and descs.flags.c_contiguous
+        assert tbs.dtype == TB_DESC_DTYPE and tbs.flags.c_contiguous
+        assert llrs.dtype == np.int8 and llrs.flags.c_contiguous
+        t = ctypes.c_int64()
+        sp, sn = (None, 0) if soft_in is None else (soft_in.ctypes.data, soft_in.nbytes)
+        self._check(self.lib.pdc_submit_tbs(self.h, descs.ctypes.data, descs.size, tbs.ctypes.data, tbs.size,
+                                            llrs.ctypes.data if llrs.size else None, llrs.nbytes, sp, sn, ctypes.byref(t)))
+        return t.value
+
+    def fetch_tbs(self, ticket, n, ntb, tb_bytes, soft_out=None):
+        """-> (TB results, CB results); payloads of the written TBs land in ``tb_bytes`` (uint8 array)."""
+        tb_res, cb_res = np.zeros(ntb, TB_RESULT_DTYPE), np.zeros(n, RESULT_DTYPE)
+        sp, sn = (None, 0) if soft_out is None else (soft_out.ctypes.data, soft_out.nbytes)
+        self._check(self.lib.pdc_fetch_tbs(self.h, ticket, tb_bytes.ctypes.data, tb_bytes.nbytes, tb_res.ctypes.data,
+                                           cb_res.ctypes.data, sp, sn))
+        return tb_res, cb_res
+
+    def decode_device_tbs(self, descs, tbs, d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, d_tb_bytes_ptr, d_tb_res_ptr,
+                          stream_ptr=None):
+        self._check(self.lib.pdc_decode_device_tbs(self.h, descs.ctypes.data, descs.size, tbs.ctypes.data, tbs.size,
+                                                   d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, d_tb_bytes_ptr,
+                                                   d_tb_res_ptr, stream_ptr))
 
     # --- device path -----------------------------------------------------------------------------------------------
     def decode_device(self, descs, d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, stream_ptr=None):

@@ -159,6 +159,15 @@ PDC_HD int pdc_layers_for_nz(const pdc_geom& g, int nz)
   return len / g.Z - g.Kb;
 }
 
+// Device-side view of one transport block (built by the host runtime from pdc_tb_desc).
+struct pdc_dev_tb {
+  uint8_t*       out;      // tbs_bits / 8 payload bytes, 4-byte aligned
+  pdc_tb_result* res;
+  uint32_t*      terms;    // [nof_cbs] scratch: every code block's share of the TB CRC remainder
+  uint32_t       first_cb, nof_cbs, tbs_bits;
+  uint32_t       cb_bits;  // C > 1: data bits per code block, K - F - 24 (the last one ends with the 24 TB CRC bits)
+};
+
 // Device-side view of one code block (built by the host runtime from pdc_cb_desc).
 struct pdc_dev_cb {
   const int8_t*  llrs; // E rate-matched LLRs, or the n_in soft bits in decode-only mode

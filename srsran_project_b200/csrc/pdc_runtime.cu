@@ -18,6 +18,14 @@ static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
   CK(cudaMalloc((void**)&t.d_llrs, c.max_batch_llrs));
   CK(cudaMalloc((void**)&t.d_bits, bits_bytes));
   CK(cudaMalloc((void**)&t.d_res, sizeof(pdc_cb_result) * c.max_batch_cbs));
+  // Transport-block path: a TB is never larger than its code blocks together, and there are at most as many TBs as CBs.
+  CK(cudaHostAlloc((void**)&t.h_tbs, sizeof(pdc_dev_tb) * c.max_batch_cbs, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&t.h_tbout, bits_bytes, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&t.h_tbres, sizeof(pdc_tb_result) * c.max_batch_cbs, cudaHostAllocDefault));
+  CK(cudaMalloc((void**)&t.d_tbs, sizeof(pdc_dev_tb) * c.max_batch_cbs));
+  CK(cudaMalloc((void**)&t.d_terms, sizeof(uint32_t) * c.max_batch_cbs));
+  CK(cudaMalloc((void**)&t.d_tbout, bits_bytes));
+  CK(cudaMalloc((void**)&t.d_tbres, sizeof(pdc_tb_result) * c.max_batch_cbs));
   return PDC_OK;
 }
 
@@ -30,6 +38,8 @@ static void free_ticket(ticket_t& t)
   cudaFreeHost(t.h_res), cudaFreeHost(t.h_soft);
   cudaFree(t.d_cbs), cudaFree(t.d_order), cudaFree(t.d_llrs), cudaFree(t.d_bits), cudaFree(t.d_res);
   cudaFree(t.d_soft);
+  cudaFreeHost(t.h_tbs), cudaFreeHost(t.h_tbout), cudaFreeHost(t.h_tbres);
+  cudaFree(t.d_tbs), cudaFree(t.d_terms), cudaFree(t.d_tbout), cudaFree(t.d_tbres);
   if (t.done) {
     cudaEventDestroy(t.done);
   }
@@ -103,8 +113,11 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   }
   if (cfg->harq_slots != 0) {
     size_t bytes = (size_t)cfg->harq_slots * PDC_MAX_N;
+    size_t bits  = (size_t)cfg->harq_slots * PDC_SLOT_BITS;
     if (!cuda_ok(ctx, cudaMalloc((void**)&ctx->d_harq, bytes), "cudaMalloc harq arena") ||
-        !cuda_ok(ctx, cudaMemset(ctx->d_harq, 0, bytes), "cudaMemset harq arena")) {
+        !cuda_ok(ctx, cudaMemset(ctx->d_harq, 0, bytes), "cudaMemset harq arena") ||
+        !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_harq_bits, bits), "cudaMalloc harq bits") ||
+        !cuda_ok(ctx, cudaMemset(ctx->d_harq_bits, 0, bits), "cudaMemset harq bits")) {
       return fail(PDC_ERR_CUDA);
     }
   }
@@ -128,6 +141,7 @@ void pdc_destroy(pdc_ctx* ctx)
     free_ticket(t);
   }
   cudaFree(ctx->d_graphs), cudaFree(ctx->d_crc), cudaFree(ctx->d_crc_bit), cudaFree(ctx->d_harq);
+  cudaFree(ctx->d_harq_bits);
   delete ctx;
 }
 
@@ -160,13 +174,15 @@ static pdc_status release_ticket(pdc_ctx* ctx, ticket_t* t, pdc_status st)
     }                                                                                                                  \
   } while (0)
 
-pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
-                      const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket)
+// pdc_submit (tbs == nullptr) and pdc_submit_tbs.
+static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
+                                const int8_t* llrs, size_t llr_bytes, const int8_t* soft_in, size_t soft_bytes,
+                                pdc_ticket* ticket)
 {
-  if (!ctx || !descs || !llrs || !ticket || n == 0) {
+  if (!ctx || !descs || !ticket || n == 0 || (!llrs && llr_bytes != 0) || (tbs && ntb == 0)) {
     return PDC_ERR_INVALID_ARG;
   }
-  if (n > ctx->cfg.max_batch_cbs || llr_bytes > ctx->cfg.max_batch_llrs) {
+  if (n > ctx->cfg.max_batch_cbs || llr_bytes > ctx->cfg.max_batch_llrs || ntb > ctx->cfg.max_batch_cbs) {
     return PDC_ERR_CAPACITY;
   }
   ticket_t* t = reserve_ticket(ctx);
@@ -181,6 +197,7 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
   batch_buffers buf;
   buf.d_llrs = t->d_llrs, buf.d_soft = t->d_soft, buf.d_bits = t->d_bits, buf.d_res = t->d_res;
   buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots, buf.llr_bytes = llr_bytes;
+  buf.d_slot_bits = tbs ? ctx->d_harq_bits : nullptr;
   batch_plan bp;
   t->lst.resize(n);
   pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
@@ -189,6 +206,16 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
   }
   if (bp.bits_end > (size_t)ctx->cfg.max_batch_cbs * (PDC_MAX_K / 8)) {
     return release_ticket(ctx, t, PDC_ERR_CAPACITY);
+  }
+  tb_plan tp;
+  if (tbs) {
+    st = plan_tbs(tbs, ntb, descs, n, t->d_tbout, t->d_tbres, t->d_terms, t->h_tbs, tp);
+    if (st == PDC_OK && tp.bytes_end > (size_t)ctx->cfg.max_batch_cbs * (PDC_MAX_K / 8)) {
+      st = PDC_ERR_CAPACITY;
+    }
+    if (st != PDC_OK) {
+      return release_ticket(ctx, t, st);
+    }
   }
   if (bp.any_host_soft) {
     if (soft_in && soft_bytes < bp.soft_end) {
@@ -215,11 +242,13 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
   bool                  pinned = (cudaPointerGetAttributes(&attr, llrs) == cudaSuccess) &&
                 (attr.type == cudaMemoryTypeHost);
   cudaGetLastError(); // pageable pointers make the query set an error on some runtimes
-  if (!pinned) {
+  if (!pinned && llr_bytes != 0) {
     memcpy(t->h_llrs, llrs, llr_bytes);
     src = t->h_llrs;
   }
-  CKT(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
+  if (llr_bytes != 0) {
+    CKT(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
+  }
   CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, t->stream));
   if (!bp.identity) {
     CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
@@ -236,7 +265,16 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
   }
-  CKT(cudaMemcpyAsync(t->h_bits, t->d_bits, bp.bits_end, cudaMemcpyDeviceToHost, t->stream));
+  if (tbs) {
+    // Assembly + TB CRC on the device; the payloads and the two result arrays come back, no per-CB bits.
+    CKT(cudaMemcpyAsync(t->d_tbs, t->h_tbs, sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, t->stream));
+    CKT(pdc_launch_tb(t->d_tbs, t->d_cbs, ctx->d_crc, (int)ntb, (int)tp.max_cbs, t->stream));
+    ctx->launches += 2;
+    CKT(cudaMemcpyAsync(t->h_tbout, t->d_tbout, tp.bytes_end, cudaMemcpyDeviceToHost, t->stream));
+    CKT(cudaMemcpyAsync(t->h_tbres, t->d_tbres, sizeof(pdc_tb_result) * ntb, cudaMemcpyDeviceToHost, t->stream));
+  } else {
+    CKT(cudaMemcpyAsync(t->h_bits, t->d_bits, bp.bits_end, cudaMemcpyDeviceToHost, t->stream));
+  }
   CKT(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n, cudaMemcpyDeviceToHost, t->stream));
   if (bp.any_host_soft) {
     CKT(cudaMemcpyAsync(t->h_soft, t->d_soft, bp.soft_end, cudaMemcpyDeviceToHost, t->stream));
@@ -248,8 +286,29 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
   t->soft_bytes = bp.soft_end;
   t->soft_back  = bp.any_host_soft;
   t->descs.assign(descs, descs + n);
+  t->ntb = ntb;
+  t->tbs.assign(tbs, tbs + (tbs ? ntb : 0));
   *ticket = t->id;
   return PDC_OK;
+}
+
+pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
+                      const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket)
+{
+  if (!llrs) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  return submit_common(ctx, descs, n, nullptr, 0, llrs, llr_bytes, soft_in, soft_bytes, ticket);
+}
+
+pdc_status pdc_submit_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
+                          const int8_t* llrs, size_t llr_bytes, const int8_t* soft_in, size_t soft_bytes,
+                          pdc_ticket* ticket)
+{
+  if (!tbs || ntb == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  return submit_common(ctx, descs, n, tbs, ntb, llrs, llr_bytes, soft_in, soft_bytes, ticket);
 }
 
 static ticket_t* find_ticket(pdc_ctx* ctx, pdc_ticket id)
@@ -280,25 +339,92 @@ pdc_status pdc_poll(pdc_ctx* ctx, pdc_ticket ticket)
   return PDC_OK;
 }
 
+// Host-exchanged soft buffers of a finished ticket back to the caller.
+static pdc_status copy_soft_back(ticket_t* t, int8_t* soft_out, size_t soft_bytes)
+{
+  pdc_status st = PDC_OK;
+  if (soft_out && t->soft_back) {
+    for (uint32_t i = 0; i != t->n; ++i) {
+      const pdc_cb_desc& d = t->descs[i];
+      if (d.harq_slot >= 0 || (d.flags & (PDC_F_DECODE_ONLY | PDC_F_DECODED))) {
+        continue;
+      }
+      size_t N = pdc_cb_buffer_len(d.bg, d.Z);
+      if (d.soft_offset + N > soft_bytes) {
+        st = PDC_ERR_INVALID_ARG;
+      } else {
+        memcpy(soft_out + d.soft_offset, t->h_soft + d.soft_offset, N);
+      }
+    }
+  }
+  return st;
+}
+
+// Finds the ticket and waits for it (outside the lock: other threads keep submitting).
+static pdc_status wait_ticket(pdc_ctx* ctx, pdc_ticket ticket, bool want_tbs, ticket_t*& t)
+{
+  {
+    std::lock_guard<std::mutex> lock(ctx->mtx);
+    t = find_ticket(ctx, ticket);
+    if (!t || (t->ntb != 0) != want_tbs) {
+      return PDC_ERR_BAD_TICKET;
+    }
+  }
+  cudaError_t e = cudaEventSynchronize(t->done);
+  if (!cuda_ok(ctx, e, "cudaEventSynchronize")) {
+    return release_ticket(ctx, t, PDC_ERR_CUDA);
+  }
+  return PDC_OK;
+}
+
+pdc_status pdc_fetch_tbs(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* tb_bytes, size_t tb_bytes_len, pdc_tb_result* tb_res,
+                         pdc_cb_result* cb_res, int8_t* soft_out, size_t soft_bytes)
+{
+  if (!ctx || !tb_res) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  ticket_t*  t;
+  pdc_status st = wait_ticket(ctx, ticket, true, t);
+  if (st != PDC_OK) {
+    return st;
+  }
+  memcpy(tb_res, t->h_tbres, sizeof(pdc_tb_result) * t->ntb);
+  if (cb_res) {
+    memcpy(cb_res, t->h_res, sizeof(pdc_cb_result) * t->n);
+    for (uint32_t i = 0; i != t->n; ++i) {
+      if (t->descs[i].flags & PDC_F_DECODED) { // no kernel wrote this entry
+        cb_res[i].iterations = -1, cb_res[i].crc_pass = 1, cb_res[i].status = 0, cb_res[i].nof_layers = 0;
+      }
+    }
+  }
+  if (tb_bytes) {
+    for (uint32_t k = 0; k != t->ntb; ++k) {
+      const pdc_tb_desc& tb = t->tbs[k];
+      if (!tb_res[k].written) {
+        continue; // the caller's transport block buffer stays untouched (pusch_decoder_impl.cpp:425)
+      }
+      if (tb.tb_offset + tb.tbs_bits / 8 > tb_bytes_len) {
+        st = PDC_ERR_INVALID_ARG;
+      } else {
+        memcpy(tb_bytes + tb.tb_offset, t->h_tbout + tb.tb_offset, tb.tbs_bits / 8);
+      }
+    }
+  }
+  pdc_status s2 = copy_soft_back(t, soft_out, soft_bytes);
+  return release_ticket(ctx, t, st != PDC_OK ? st : s2);
+}
+
 pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits_bytes, pdc_cb_result* res,
                      int8_t* soft_out, size_t soft_bytes)
 {
   if (!ctx || !res) {
     return PDC_ERR_INVALID_ARG;
   }
-  ticket_t* t;
-  {
-    std::lock_guard<std::mutex> lock(ctx->mtx);
-    t = find_ticket(ctx, ticket);
-    if (!t) {
-      return PDC_ERR_BAD_TICKET;
-    }
+  ticket_t*  t;
+  pdc_status st = wait_ticket(ctx, ticket, false, t);
+  if (st != PDC_OK) {
+    return st;
   }
-  cudaError_t e = cudaEventSynchronize(t->done); // outside the lock: other threads keep submitting
-  if (!cuda_ok(ctx, e, "cudaEventSynchronize")) {
-    return release_ticket(ctx, t, PDC_ERR_CUDA);
-  }
-  pdc_status st = PDC_OK;
   memcpy(res, t->h_res, sizeof(pdc_cb_result) * t->n);
   bool all_written = true; // status 2: "not enough soft bits" with a CRC object — the reference leaves the output untouched
   for (uint32_t i = 0; i != t->n; ++i) {
@@ -321,30 +447,18 @@ pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits
       }
     }
   }
-  if (soft_out && t->soft_back) {
-    for (uint32_t i = 0; i != t->n; ++i) {
-      const pdc_cb_desc& d = t->descs[i];
-      if (d.harq_slot >= 0 || (d.flags & PDC_F_DECODE_ONLY)) {
-        continue;
-      }
-      size_t N = pdc_cb_buffer_len(d.bg, d.Z);
-      if (d.soft_offset + N > soft_bytes) {
-        st = PDC_ERR_INVALID_ARG;
-      } else {
-        memcpy(soft_out + d.soft_offset, t->h_soft + d.soft_offset, N);
-      }
-    }
-  }
-  return release_ticket(ctx, t, st);
+  pdc_status s2 = copy_soft_back(t, soft_out, soft_bytes);
+  return release_ticket(ctx, t, st != PDC_OK ? st : s2);
 }
 
-pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* d_llrs, int8_t* d_soft,
-                             uint8_t* d_bits, pdc_cb_result* d_res, void* stream_v)
+static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs,
+                                       uint32_t ntb, const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits,
+                                       pdc_cb_result* d_res, uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream_v)
 {
-  if (!ctx || !descs || !d_llrs || !d_bits || !d_res || n == 0) {
+  if (!ctx || !descs || !d_res || n == 0 || (tbs ? (ntb == 0 || !d_tb_bytes || !d_tb_res) : (!d_llrs || !d_bits))) {
     return PDC_ERR_INVALID_ARG;
   }
-  if (n > ctx->cfg.max_batch_cbs) {
+  if (n > ctx->cfg.max_batch_cbs || ntb > ctx->cfg.max_batch_cbs) {
     return PDC_ERR_CAPACITY;
   }
   cudaStream_t stream = (cudaStream_t)stream_v;
@@ -362,14 +476,22 @@ pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n,
   batch_buffers buf;
   buf.d_llrs = d_llrs, buf.d_soft = d_soft, buf.d_bits = d_bits, buf.d_res = d_res;
   buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots;
+  buf.d_slot_bits = tbs ? ctx->d_harq_bits : nullptr;
   batch_plan bp;
   t->lst.resize(n);
   pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
   if (st == PDC_OK && bp.any_host_soft && !d_soft) {
     st = PDC_ERR_INVALID_ARG;
   }
+  tb_plan tp;
+  if (st == PDC_OK && tbs) {
+    st = plan_tbs(tbs, ntb, descs, n, d_tb_bytes, d_tb_res, t->d_terms, t->h_tbs, tp);
+  }
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
+  }
+  if (tbs) {
+    CKT(cudaMemcpyAsync(t->d_tbs, t->h_tbs, sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, stream));
   }
   CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
   if (!bp.identity) {
@@ -379,7 +501,31 @@ pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n,
   CKT(cudaEventRecord(t->done, stream));
   CKT(cudaStreamWaitEvent(t->stream, t->done, 0));
   st = launch_batch(ctx, bp, t->d_cbs, t->d_order, stream);
+  if (st == PDC_OK && tbs) {
+    // d_tbs / d_terms of this ticket are read by these two launches: the next user of the ticket orders itself after them
+    // through the same event (recorded again below), as for the descriptor staging.
+    CKT(pdc_launch_tb(t->d_tbs, t->d_cbs, ctx->d_crc, (int)ntb, (int)tp.max_cbs, stream));
+    ctx->launches += 2;
+    CKT(cudaEventRecord(t->done, stream));
+    CKT(cudaStreamWaitEvent(t->stream, t->done, 0));
+  }
   return release_ticket(ctx, t, st);
+}
+
+pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* d_llrs, int8_t* d_soft,
+                             uint8_t* d_bits, pdc_cb_result* d_res, void* stream)
+{
+  return decode_device_common(ctx, descs, n, nullptr, 0, d_llrs, d_soft, d_bits, d_res, nullptr, nullptr, stream);
+}
+
+pdc_status pdc_decode_device_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
+                                 const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits, pdc_cb_result* d_res,
+                                 uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream)
+{
+  if (!tbs || ntb == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  return decode_device_common(ctx, descs, n, tbs, ntb, d_llrs, d_soft, d_bits, d_res, d_tb_bytes, d_tb_res, stream);
 }
 
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot)

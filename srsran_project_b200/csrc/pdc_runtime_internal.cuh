@@ -24,6 +24,8 @@ extern "C" int         pdc_h2_supported(int bg, int Z);
 extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
 extern "C" size_t      pdc_h2g_smem_bytes(int bg, int Z, int max_layers);
 extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_launch_tb(const pdc_dev_tb* d_tbs, const pdc_dev_cb* d_cbs, const uint32_t* crc_pow, int ntb,
+                                     int max_cbs, cudaStream_t stream);
 
 namespace {
 
@@ -48,6 +50,13 @@ struct ticket_t {
   pdc_cb_result* d_res  = nullptr;
   int8_t*        d_soft = nullptr;
   uint32_t*      d_order = nullptr;
+  // transport-block path (pdc_submit_tbs / pdc_decode_device_tbs)
+  pdc_dev_tb*    h_tbs = nullptr, *d_tbs = nullptr;
+  uint32_t*      d_terms = nullptr;
+  uint8_t*       h_tbout = nullptr, *d_tbout = nullptr;
+  pdc_tb_result* h_tbres = nullptr, *d_tbres = nullptr;
+  uint32_t       ntb = 0;
+  std::vector<pdc_tb_desc> tbs;
   // what to hand back
   std::vector<pdc_cb_desc> descs;
   std::vector<uint8_t>     lst; // kernel list of every code block (planner scratch)
@@ -68,6 +77,7 @@ struct pdc_ctx {
   uint32_t*             d_crc    = nullptr;
   uint32_t*             d_crc_bit = nullptr;
   int8_t*               d_harq   = nullptr;
+  uint8_t*              d_harq_bits = nullptr; // decoded bits kept with every HARQ slot (transport-block path), PDC_MAX_K / 8 each
   std::atomic<uint64_t> launches{0};
   size_t                bits_stride_total = 0;
 };
@@ -223,6 +233,8 @@ size_t lane_smem_bytes(const pdc_geom& g, int max_layers)
 
 #define PDC_NOF_PACKED_LISTS 6
 #define PDC_NOF_LISTS (PDC_NOF_PACKED_LISTS + 1)
+#define PDC_LIST_SKIP 255 /* PDC_F_DECODED: no kernel touches the code block */
+#define PDC_SLOT_BITS (PDC_MAX_K / 8)
 
 struct batch_plan {
   // Packed-kernel lists, four core rows: [0] BG1 any Z, [1] BG2 any Z, [2] BG1 Z = 384, [3] BG2 Z = 384 (compile-time
@@ -277,7 +289,13 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
   pdc_geom g;
   int      ml = 0;
   cls.valid   = false;
-  if (!validate_desc(d, g, ml)) {
+  if (d.flags & PDC_F_DECODED) {
+    // Only the geometry matters: the code block is not processed again.
+    if (!pdc_geom_init(g, d.bg, d.Z) || pdc_lifting_pos(d.Z) < 0 || d.crc_type == PDC_CRC_NONE || d.crc_type > PDC_CRC24B ||
+        (uint64_t)d.nof_filler >= (uint64_t)g.K) {
+      return false;
+    }
+  } else if (!validate_desc(d, g, ml)) {
     return false;
   }
   cls.key       = d;
@@ -290,7 +308,9 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
   cls.K_bytes4 = (size_t)((g.K + 31) / 32) * 4;
   cls.N        = (uint32_t)g.N;
   const bool core_only = takes_h2(d, ml, false), general = !core_only && takes_h2(d, ml, true);
-  if (core_only || general) {
+  if (d.flags & PDC_F_DECODED) {
+    cls.list = PDC_LIST_SKIP;
+  } else if (core_only || general) {
     int k    = general ? (4 + (d.bg - 1)) : ((d.bg - 1) + ((d.Z == 384) ? 2 : 0));
     cls.list = k;
     size_t s = general ? pdc_h2g_smem_bytes(d.bg, d.Z, ml) : pdc_h2_smem_bytes(d.bg, d.Z, ml);
@@ -317,6 +337,7 @@ struct batch_buffers {
   int8_t*        d_harq = nullptr;
   uint32_t       harq_slots = 0;
   size_t         llr_bytes  = (size_t)-1; // bound for llr_offset + E
+  uint8_t*       d_slot_bits = nullptr;   // transport-block path: decoded bits of CBs with a HARQ slot stay with the slot
 };
 
 // One pass over the descriptors: validation, device descriptors (dev[i], pointers included), kernel list of every code
@@ -325,7 +346,7 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
                       uint8_t* lst, batch_plan& bp)
 {
   desc_class cls;
-  uint32_t   cnt[PDC_NOF_LISTS] = {0};
+  uint32_t   cnt[PDC_NOF_LISTS] = {0}, skipped = 0;
   size_t     bits_end = 0, soft_end = 0;
   bool       any_host_soft = false, dense = true;
   for (uint32_t i = 0; i != n; ++i) {
@@ -335,17 +356,36 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
         return PDC_ERR_INVALID_ARG;
       }
     }
+    pdc_dev_cb& c = dev[i];
+    c             = cls.proto;
+    c.res         = buf.d_res + i;
+    const bool slot_bits = buf.d_slot_bits != nullptr && d.harq_slot >= 0 && !(d.flags & PDC_F_DECODE_ONLY);
+    if (cls.list == PDC_LIST_SKIP) {
+      if (!slot_bits || (uint32_t)d.harq_slot >= buf.harq_slots) {
+        return PDC_ERR_INVALID_ARG; // PDC_F_DECODED needs the transport-block path and a HARQ slot that holds the bits
+      }
+      c.out  = buf.d_slot_bits + (size_t)d.harq_slot * PDC_SLOT_BITS;
+      c.soft = buf.d_harq + (size_t)d.harq_slot * PDC_MAX_N;
+      lst[i] = PDC_LIST_SKIP;
+      ++skipped;
+      continue;
+    }
     if ((d.out_offset & 3) != 0 || d.llr_offset + d.E > buf.llr_bytes) {
       return PDC_ERR_INVALID_ARG;
     }
-    pdc_dev_cb& c = dev[i];
-    c             = cls.proto;
-    c.llrs        = buf.d_llrs + d.llr_offset;
-    c.out         = buf.d_bits + d.out_offset;
-    c.res         = buf.d_res + i;
-    dense &= (d.out_offset == bits_end); // outputs back to back from offset 0, in order
-    size_t be     = d.out_offset + cls.K_bytes4;
-    bits_end      = be > bits_end ? be : bits_end;
+    c.llrs = buf.d_llrs + d.llr_offset;
+    if (slot_bits) {
+      c.out = buf.d_slot_bits + (size_t)d.harq_slot * PDC_SLOT_BITS; // range checked with the soft buffer below
+      dense = false;
+    } else {
+      if (!buf.d_bits) {
+        return PDC_ERR_INVALID_ARG;
+      }
+      c.out = buf.d_bits + d.out_offset;
+      dense &= (d.out_offset == bits_end); // outputs back to back from offset 0, in order
+      size_t be = d.out_offset + cls.K_bytes4;
+      bits_end  = be > bits_end ? be : bits_end;
+    }
     if (!(d.flags & PDC_F_DECODE_ONLY)) {
       if (d.harq_slot >= 0) {
         if ((uint32_t)d.harq_slot >= buf.harq_slots) {
@@ -374,7 +414,7 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
   for (int k = 0; k != PDC_NOF_LISTS; ++k) {
     used += (cnt[k] != 0);
   }
-  bp.identity = (used == 1); // a single kernel takes the whole batch in the given order: no indirection needed
+  bp.identity = (used == 1) && skipped == 0; // a single kernel takes the whole batch in the given order: no indirection
   if (!bp.identity) {
     uint32_t off[PDC_NOF_LISTS], acc = 0;
     for (int k = 0; k != PDC_NOF_LISTS; ++k) {
@@ -382,8 +422,63 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
       acc += cnt[k];
     }
     for (uint32_t i = 0; i != n; ++i) {
-      order[off[lst[i]]++] = i;
+      if (lst[i] != PDC_LIST_SKIP) {
+        order[off[lst[i]]++] = i;
+      }
     }
+  }
+  return PDC_OK;
+}
+
+// Transport blocks over a planned batch: validation (pdc_tb_desc contract) and the device descriptors.
+struct tb_plan {
+  uint32_t max_cbs  = 0;
+  size_t   bytes_end = 0; // extent of the TB payload buffer
+};
+
+pdc_status plan_tbs(const pdc_tb_desc* tbs, uint32_t ntb, const pdc_cb_desc* descs, uint32_t n, uint8_t* d_tb_out,
+                    pdc_tb_result* d_tb_res, uint32_t* d_terms, pdc_dev_tb* dev, tb_plan& tp)
+{
+  for (uint32_t t = 0; t != ntb; ++t) {
+    const pdc_tb_desc& tb = tbs[t];
+    if (tb.nof_cbs == 0 || tb.first_cb >= n || tb.nof_cbs > n - tb.first_cb || (tb.tbs_bits & 7) != 0 || tb.tbs_bits == 0 ||
+        (tb.tb_offset & 3) != 0) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    const pdc_cb_desc& d0 = descs[tb.first_cb];
+    pdc_geom           g;
+    if (!pdc_geom_init(g, d0.bg, d0.Z)) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    for (uint32_t c = 0; c != tb.nof_cbs; ++c) {
+      const pdc_cb_desc& d = descs[tb.first_cb + c];
+      if (d.bg != d0.bg || d.Z != d0.Z || d.nof_filler != d0.nof_filler || d.crc_type != d0.crc_type ||
+          (d.flags & PDC_F_DECODE_ONLY)) {
+        return PDC_ERR_INVALID_ARG;
+      }
+    }
+    uint32_t cb_bits = 0;
+    if (tb.nof_cbs == 1) {
+      // pusch_decoder_impl.cpp:35-46: CRC16 up to 3824 bits, CRC24A above; the message is payload || CRC || fillers.
+      const uint32_t ncrc = (d0.crc_type == PDC_CRC16) ? 16 : 24;
+      if ((d0.crc_type != PDC_CRC16 && d0.crc_type != PDC_CRC24A) || tb.tbs_bits + ncrc + d0.nof_filler != (uint32_t)g.K) {
+        return PDC_ERR_INVALID_ARG;
+      }
+    } else {
+      if (d0.crc_type != PDC_CRC24B || (uint32_t)g.K < d0.nof_filler + 24 + 32) {
+        return PDC_ERR_INVALID_ARG;
+      }
+      cb_bits = (uint32_t)g.K - d0.nof_filler - 24;
+      if ((uint64_t)cb_bits * tb.nof_cbs != (uint64_t)tb.tbs_bits + 24) {
+        return PDC_ERR_INVALID_ARG;
+      }
+    }
+    pdc_dev_tb& o = dev[t];
+    o.out = d_tb_out + tb.tb_offset, o.res = d_tb_res + t, o.terms = d_terms + tb.first_cb;
+    o.first_cb = tb.first_cb, o.nof_cbs = tb.nof_cbs, o.tbs_bits = tb.tbs_bits, o.cb_bits = cb_bits;
+    tp.max_cbs   = tb.nof_cbs > tp.max_cbs ? tb.nof_cbs : tp.max_cbs;
+    size_t end   = tb.tb_offset + tb.tbs_bits / 8;
+    tp.bytes_end = end > tp.bytes_end ? end : tp.bytes_end;
   }
   return PDC_OK;
 }
