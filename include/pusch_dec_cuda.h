@@ -89,7 +89,9 @@ typedef struct {
 
 /* One transport block = C consecutive code blocks of the same submission (pusch_decoder_impl.cpp:396-505). All of them
  * share bg, Z, nof_filler and crc_type; C == 1: crc_type CRC16 | CRC24A and tbs_bits = K - F - crc bits; C > 1: CRC24B
- * and tbs_bits + 24 = C * (K - F - 24) (TS 38.212 5.2.2 as ldpc_segmenter_rx_impl.cpp:52-106 derives it). */
+ * and (C - 1) D + 24 < tbs_bits + 24 <= C D with D = K - F - 24 data bits per code block: the payload and its CRC24A fill
+ * the code blocks in order, what is left of the last one is zero padding (TS 38.212 5.2.2 as
+ * ldpc_segmenter_rx_impl.cpp:52-106 derives it; pusch_decoder_impl.cpp:485-487). */
 typedef struct {
   uint32_t first_cb;  /* index of the TB's first code block in descs[] */
   uint32_t nof_cbs;   /* C >= 1 */

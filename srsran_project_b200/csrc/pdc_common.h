@@ -165,7 +165,8 @@ struct pdc_dev_tb {
   pdc_tb_result* res;
   uint32_t*      terms;    // [nof_cbs] scratch: every code block's share of the TB CRC remainder
   uint32_t       first_cb, nof_cbs, tbs_bits;
-  uint32_t       cb_bits;  // C > 1: data bits per code block, K - F - 24 (the last one ends with the 24 TB CRC bits)
+  uint32_t       cb_bits;  // C > 1: data bits per code block D = K - F - 24
+  uint32_t       last_bits; // C > 1: bits of payload || TB CRC in the last code block, tbs + 24 - (C - 1) D (then zero padding)
 };
 
 // Device-side view of one code block (built by the host runtime from pdc_cb_desc).

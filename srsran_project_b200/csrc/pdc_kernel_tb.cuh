@@ -2,14 +2,16 @@
 // concatenate_codeblocks (pusch_decoder_impl.cpp:396-505) do on the host after the code blocks of a TB have been decoded.
 //
 //   C == 1 : tb_crc_ok = the code block's CRC; the first tbs_bits message bits are the payload (:416-424).
-//   C  > 1 : only if EVERY code block passed (:425): the K - F - 24 data bits of each code block are concatenated
-//            (copy_offset, bit granular), the last 24 of them are the TB checksum, and tb_crc_ok = CRC24A(payload) == checksum
-//            (:426-437). The payload is written before the check, i.e. also when the check then fails.
+//   C  > 1 : only if EVERY code block passed (:425): the D = K - F - 24 data bits of each code block are concatenated
+//            (copy_offset, bit granular) up to tbs bits, the next 24 bits of the last code block are the TB checksum (what may
+//            follow is zero padding, :485-487), and tb_crc_ok = CRC24A(payload) == checksum (:426-437). The payload is written
+//            before the check, i.e. also when the check then fails.
 //
 // Two kernels. pdc_tb_assemble_kernel: one CTA per (code block, TB) writes the payload words that START inside its code block
 // (pulling the first bits of the next one where a word straddles) and its share of the CRC: the checksum test is
-// "remainder of payload || checksum == 0", the remainder is linear, so code block r contributes
-// (sum over its set data bits i of x^(D-1-i) ) * x^(D (C-1-r)) mod P. pdc_tb_finish_kernel: one warp per TB xors the shares.
+// "remainder of payload || checksum == 0", the remainder is linear, so code block r < C - 1 contributes
+// (sum over its set data bits i of x^(D-1-i)) * x^(Dl + D (C-2-r)) mod P and the last one the sum over its first Dl bits of
+// x^(Dl-1-i), Dl = tbs + 24 - (C - 1) D. pdc_tb_finish_kernel: one warp per TB xors the shares.
 #pragma once
 #include "pdc_device.cuh"
 
@@ -97,18 +99,19 @@ __global__ void __launch_bounds__(128) pdc_tb_assemble_kernel(const pdc_dev_tb* 
       }
     }
   }
-  // CRC share: sum over the set data bits i < D of x^(D - 1 - i) mod P (crc_pow holds x^j mod P of CRC24A in its second table).
+  // CRC share: sum over the set bits i < Dr of x^(Dr - 1 - i) mod P (crc_pow holds x^j mod P of CRC24A in its second table).
   const uint32_t* pw  = crc_pow + PDC_CRC_TABLE_LEN;
+  const int       Dl = (int)tb.last_bits, Dr = (r == C - 1) ? Dl : D;
   uint32_t        acc = 0;
-  for (int k = tid; 32 * k < D; k += nth) {
+  for (int k = tid; 32 * k < Dr; k += nth) {
     uint32_t v = __byte_perm(cb32[k], 0u, 0x0123);
-    if (D - 32 * k < 32) {
-      v &= ~(0xffffffffu >> (D - 32 * k));
+    if (Dr - 32 * k < 32) {
+      v &= ~(0xffffffffu >> (Dr - 32 * k));
     }
     while (v) {
       const int b = __clz(v);
       v &= ~(0x80000000u >> b);
-      acc ^= __ldg(pw + (D - 1 - (32 * k + b)));
+      acc ^= __ldg(pw + (Dr - 1 - (32 * k + b)));
     }
   }
   __shared__ uint32_t s_part[4];
@@ -122,15 +125,18 @@ __global__ void __launch_bounds__(128) pdc_tb_assemble_kernel(const pdc_dev_tb* 
     for (int w = 0; w < (nth >> 5); ++w) {
       share ^= s_part[w];
     }
-    // times x^(D (C - 1 - r)): square-and-multiply on x^D mod P.
-    uint32_t base = __ldg(pw + D), f = 1u;
-    for (int e = C - 1 - r; e != 0; e >>= 1) {
-      if (e & 1) {
-        f = tb_mulmod(f, base);
+    // times x^(Dl + D (C - 2 - r)) for r < C - 1: square-and-multiply on x^D mod P.
+    if (r != C - 1) {
+      uint32_t base = __ldg(pw + D), f = __ldg(pw + Dl);
+      for (int e = C - 2 - r; e != 0; e >>= 1) {
+        if (e & 1) {
+          f = tb_mulmod(f, base);
+        }
+        base = tb_mulmod(base, base);
       }
-      base = tb_mulmod(base, base);
+      share = tb_mulmod(share, f);
     }
-    tb.terms[r] = tb_mulmod(share, f);
+    tb.terms[r] = share;
   }
 }
 

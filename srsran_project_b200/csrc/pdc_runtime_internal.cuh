@@ -457,7 +457,7 @@ pdc_status plan_tbs(const pdc_tb_desc* tbs, uint32_t ntb, const pdc_cb_desc* des
         return PDC_ERR_INVALID_ARG;
       }
     }
-    uint32_t cb_bits = 0;
+    uint32_t cb_bits = 0, last_bits = 0;
     if (tb.nof_cbs == 1) {
       // pusch_decoder_impl.cpp:35-46: CRC16 up to 3824 bits, CRC24A above; the message is payload || CRC || fillers.
       const uint32_t ncrc = (d0.crc_type == PDC_CRC16) ? 16 : 24;
@@ -468,14 +468,18 @@ pdc_status plan_tbs(const pdc_tb_desc* tbs, uint32_t ntb, const pdc_cb_desc* des
       if (d0.crc_type != PDC_CRC24B || (uint32_t)g.K < d0.nof_filler + 24 + 32) {
         return PDC_ERR_INVALID_ARG;
       }
-      cb_bits = (uint32_t)g.K - d0.nof_filler - 24;
-      if ((uint64_t)cb_bits * tb.nof_cbs != (uint64_t)tb.tbs_bits + 24) {
+      // The payload and its CRC fill the code blocks in order; what is left of the last one is zero padding
+      // (ldpc_segmenter_rx_impl.cpp:52-106: K' = ceil(B' / C); pusch_decoder_impl.cpp:485-487).
+      cb_bits              = (uint32_t)g.K - d0.nof_filler - 24;
+      const uint64_t total = (uint64_t)tb.tbs_bits + 24, before = (uint64_t)cb_bits * (tb.nof_cbs - 1);
+      if (total <= before + 24 || total > before + cb_bits) {
         return PDC_ERR_INVALID_ARG;
       }
+      last_bits = (uint32_t)(total - before);
     }
     pdc_dev_tb& o = dev[t];
     o.out = d_tb_out + tb.tb_offset, o.res = d_tb_res + t, o.terms = d_terms + tb.first_cb;
-    o.first_cb = tb.first_cb, o.nof_cbs = tb.nof_cbs, o.tbs_bits = tb.tbs_bits, o.cb_bits = cb_bits;
+    o.first_cb = tb.first_cb, o.nof_cbs = tb.nof_cbs, o.tbs_bits = tb.tbs_bits, o.cb_bits = cb_bits, o.last_bits = last_bits;
     tp.max_cbs   = tb.nof_cbs > tp.max_cbs ? tb.nof_cbs : tp.max_cbs;
     size_t end   = tb.tb_offset + tb.tbs_bits / 8;
     tp.bytes_end = end > tp.bytes_end ? end : tp.bytes_end;

@@ -3,10 +3,13 @@
 //   mode 0: the reference's own software operators (ldpc_decoder_avx512 | avx2 | generic + matching dematcher) — the oracle,
 //   mode 1: the CUDA ldpc_decoder + ldpc_rate_dematcher (srsran_project_b200/adapters/channel_coding_factories_cuda.h)
 //           inside the reference's pusch_codeblock_decoder / pusch_decoder_impl (drop-in boundary 1),
-//   mode 2: the CUDA hal::hw_accelerator_pusch_dec inside the reference's pusch_decoder_hw_impl (drop-in boundary 2).
+//   mode 2: the CUDA hal::hw_accelerator_pusch_dec inside the reference's pusch_decoder_hw_impl (drop-in boundary 2),
+//   mode 3: the CUDA srsran::pusch_decoder (srsran_project_b200/adapters/pusch_decoder_cuda.h): code blocks AND transport
+//           block assembly + CRC24A on the device, in place of the reference's TB decoders.
 // Driven from Python (tests/test_adapters.py) through a small C ABI; the stimulus comes from tools/stimulus.
 #include "../../srsran_project_b200/adapters/channel_coding_factories_cuda.h"
 #include "../../srsran_project_b200/adapters/hw_accelerator_pusch_dec_cuda.h"
+#include "../../srsran_project_b200/adapters/pusch_decoder_cuda.h"
 #include "crc_calculator_clmul_impl.h"
 #include "crc_calculator_lut_impl.h"
 #include "ldpc/ldpc_decoder_avx2.h"
@@ -71,6 +74,10 @@ std::unique_ptr<ldpc_rate_dematcher> make_sw_dematcher(int flavour)
   return std::make_unique<ldpc_rate_dematcher_impl>();
 }
 
+struct segmenter_factory_local : public ldpc_segmenter_rx_factory {
+  std::unique_ptr<ldpc_segmenter_rx> create() override { return std::make_unique<ldpc_segmenter_rx_impl>(); }
+};
+
 struct harness {
   std::shared_ptr<cuda::pusch_dec_context>   context;
   std::unique_ptr<rx_buffer_pool_controller> pool;
@@ -96,7 +103,7 @@ void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, i
   pool_cfg.nof_buffers          = nof_buffers;
   pool_cfg.nof_codeblocks       = nof_codeblocks;
   pool_cfg.expire_timeout_slots = 100000;
-  pool_cfg.external_soft_bits   = (mode == 2) && (external_harq != 0);
+  pool_cfg.external_soft_bits   = (mode == 3) || ((mode == 2) && (external_harq != 0));
   h->pool                       = create_rx_buffer_pool(pool_cfg);
 
   if (mode != 0) {
@@ -109,7 +116,13 @@ void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, i
   }
   ldpc_decoder_cuda_flavour fl = cuda_generic ? ldpc_decoder_cuda_flavour::generic : ldpc_decoder_cuda_flavour::avx512;
 
-  if (mode == 2) {
+  if (mode == 3) {
+    pusch_decoder_factory_cuda_configuration dcfg;
+    dcfg.segmenter_factory  = std::make_shared<segmenter_factory_local>();
+    dcfg.context            = h->context;
+    dcfg.generic_arithmetic = cuda_generic != 0;
+    h->decoder              = create_pusch_decoder_factory_cuda(dcfg)->create();
+  } else if (mode == 2) {
     hal::cuda_hwacc_pusch_dec_factory_configuration acfg;
     acfg.context            = h->context;
     acfg.external_harq      = external_harq != 0;

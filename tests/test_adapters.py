@@ -1,6 +1,7 @@
 """Drop-in boundary tests: the UNMODIFIED reference transport-block decoders (pusch_decoder_impl, pusch_decoder_hw_impl,
 compiled from the reference sources into tests/adapters/_build/libadapter_harness.so) driving the CUDA adapters of
-srsran_project_b200/adapters/, compared with the same decoders driving the reference's own AVX512 / generic operators.
+srsran_project_b200/adapters/, compared with the same decoders driving the reference's own AVX512 / generic operators; and the CUDA srsran::pusch_decoder
+(code blocks and transport-block assembly + CRC24A on the device) in their place.
 
 Mirrors tests/unittests/phy/upper/channel_processors/pusch/pusch_decoder_vectortest.cpp:286-403 (TB-level HARQ test: feed
 the codeword in two chunks, check tb_crc_ok, the TB bytes, the per-CB statistics and the iteration bounds).
@@ -17,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 HARNESS = os.path.join(HERE, "adapters", "_build", "libadapter_harness.so")
 ADAPTERS = os.path.join(HERE, "..", "srsran_project_b200", "libsrsran_cuda_adapters.so")
 
-MODE_REF, MODE_CUDA_OPERATORS, MODE_CUDA_HAL = 0, 1, 2
+MODE_REF, MODE_CUDA_OPERATORS, MODE_CUDA_HAL, MODE_CUDA_TB = 0, 1, 2, 3
 
 
 def _lib():
@@ -120,19 +121,20 @@ def test_adapter_library_exports():
 
     syms = subprocess.run(["nm", "-D", "--defined-only", "-C", ADAPTERS], capture_output=True, text=True).stdout
     for s in ("srsran::create_ldpc_decoder_factory_cuda", "srsran::create_ldpc_rate_dematcher_factory_cuda",
-              "srsran::hal::create_cuda_pusch_dec_acc_factory"):
+              "srsran::hal::create_cuda_pusch_dec_acc_factory", "srsran::create_pusch_decoder_factory_cuda"):
         assert s in syms, s
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode,external", [(MODE_CUDA_HAL, True), (MODE_CUDA_HAL, False), (MODE_CUDA_OPERATORS, True)])
+@pytest.mark.parametrize("mode,external", [(MODE_CUDA_HAL, True), (MODE_CUDA_HAL, False), (MODE_CUDA_OPERATORS, True),
+                                           (MODE_CUDA_TB, True)])
 @pytest.mark.parametrize("generic", [False, True])
 def test_cuda_adapters_match_reference_decoder(mode, external, generic):
     """Same TB bytes, same tb_crc_ok, same per-CB iteration statistics as the reference decoder on every transmission."""
     ref = Decoder(MODE_REF, ref_generic=generic)
     dut = Decoder(mode, cuda_generic=generic, external_harq=external)
     try:
-        cases = CASES if mode == MODE_CUDA_HAL else CASES[2:]  # 152 synchronous single-CB calls per TB are slow: skip cfg2
+        cases = CASES if mode != MODE_CUDA_OPERATORS else CASES[2:]  # 152 synchronous single-CB calls per TB are slow: skip cfg2
         for i, case in enumerate(cases):
             a = run_case(ref, case, harq_id=i % 4)
             b = run_case(dut, case, harq_id=i % 4)
