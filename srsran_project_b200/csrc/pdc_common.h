@@ -159,6 +159,12 @@ PDC_HD int pdc_layers_for_nz(const pdc_geom& g, int nz)
   return len / g.Z - g.Kb;
 }
 
+// pdc_dev_cb.flags only (never in pdc_cb_desc.flags): the host planner found that this code block is a first transmission from
+// the start of the buffer that fits the packed kernel's staging tile (new data, rv 0, no LBRM, one lap, n_info <= E,
+// E + F <= (Kb + 2) Z): the kernel then needs no dematcher plan (no integer divisions), only n_info = n_sys - F and
+// end = E + F.
+#define PDC_DEVF_FIRST_TX_TILE 0x80u
+
 // Device-side view of one transport block (built by the host runtime from pdc_tb_desc).
 struct pdc_dev_tb {
   uint8_t*       out;      // tbs_bits / 8 payload bytes, 4-byte aligned

@@ -668,12 +668,13 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     n_in   = (int)cb.E;
     __syncthreads();
   } else {
-    pdc_dematch_plan pl;
-    pdc_dematch_plan_init(pl, g, (int)cb.E, cb.Qm, cb.rv, (int)cb.Nref, (int)cb.nof_filler,
-                          (cb.flags & PDC_F_NEW_DATA) != 0);
     n_in = g.N;
-    const int end_pos = pl.final_zero ? pl.end_idx : pl.N;
-    if (pl.new_data && pl.rounds == 1 && pl.Ncb == pl.N && pl.k0 == 0 && pl.E >= pl.n_info && end_pos <= nstage) {
+    if (cb.flags & PDC_DEVF_FIRST_TX_TILE) {
+      // The host planner (classify) established: new data, rv 0, no LBRM, one lap, n_info <= E and E + F <= nstage.
+      pdc_dematch_plan pl;
+      pl.N = ((BG == 1) ? 66 : 50) * Z, pl.n_sys = (G::KB - 2) * Z, pl.n_info = pl.n_sys - (int)cb.nof_filler;
+      pl.E = (int)cb.E, pl.Qm = cb.Qm;
+      const int end_pos = (int)cb.E + (int)cb.nof_filler;
       // First transmission from the start of the buffer, one lap, reaching past the systematic part: every position of the
       // N-entry soft buffer is a zero, a filler or exactly one LLR (a shorter one leaves [E, n_info) untouched, i.e. holding
       // whatever the buffer held before: allot_llrs :134-195), and everything that is not zero lies in the first nstage
@@ -725,6 +726,9 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
       }
       from_smem = true;
     } else {
+      pdc_dematch_plan pl;
+      pdc_dematch_plan_init(pl, g, (int)cb.E, cb.Qm, cb.rv, (int)cb.Nref, (int)cb.nof_filler,
+                            (cb.flags & PDC_F_NEW_DATA) != 0);
       if (pl.new_data && pl.rounds == 1) {
         pdc_dematch_first_tx(pl, cb.llrs, cb.soft, tid, nth);
       } else {

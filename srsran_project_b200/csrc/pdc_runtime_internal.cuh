@@ -302,7 +302,17 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
   pdc_dev_cb& c = cls.proto;
   memset(&c, 0, sizeof(c));
   c.E = d.E, c.Nref = d.Nref, c.nof_filler = d.nof_filler, c.Z = d.Z;
-  c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter, c.flags = d.flags;
+  c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter;
+  c.flags = d.flags & (uint8_t)~PDC_DEVF_FIRST_TX_TILE;
+  if (!(d.flags & (PDC_F_DECODED | PDC_F_DECODE_ONLY | PDC_F_DEMATCH_ONLY))) {
+    pdc_dematch_plan pl;
+    if (pdc_dematch_plan_init(pl, g, (int)d.E, d.Qm, d.rv, (int)d.Nref, (int)d.nof_filler, (d.flags & PDC_F_NEW_DATA) != 0)) {
+      const int end_pos = pl.final_zero ? pl.end_idx : pl.N;
+      if (pl.new_data && pl.rounds == 1 && pl.Ncb == pl.N && pl.k0 == 0 && pl.E >= pl.n_info && end_pos <= (g.Kb + 2) * g.Z) {
+        c.flags |= PDC_DEVF_FIRST_TX_TILE; // then end_pos == E + F (see pdc_dematch_plan_init with k0 = 0, one lap)
+      }
+    }
+  }
   c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
   c.max_layers = (uint16_t)ml;
   cls.K_bytes4 = (size_t)((g.K + 31) / 32) * 4;
