@@ -71,14 +71,17 @@ def build_workload(args, rank):
     total = o
     llr_sets = [np.zeros(total, np.int8) for _ in range(args.input_sets)]
     msgs = None
+    tb_packed = None
     if args.population == "awgn":
         msgs = np.zeros((n_cbs, seg["K"]), np.uint8)
+        tb_packed = np.zeros((n_tbs, c["tbs"] // 8), np.uint8)
         for t in range(n_tbs):
             g = tb_shard(rank, n_tbs)[t]  # global transport-block index: every rank decodes different blocks
             rng = np.random.default_rng(100 + g)
             tb = rng.integers(0, 2, c["tbs"], dtype=np.uint8)
             _, bits, m = S.tb_encode(c["bg"], c["tbs"], tb, c["rv"], c["Qm"], 0, c["nof_layers"], c["G"])
             msgs[t * seg["C"]:(t + 1) * seg["C"]] = m
+            tb_packed[t] = np.packbits(tb)
             for s in range(args.input_sets):
                 llrs = S.awgn_llrs(bits, 8.0, args.sigma, 7919 * g + s + 1)
                 p = 0
@@ -90,7 +93,7 @@ def build_workload(args, rank):
         for s in range(args.input_sets):
             rng = np.random.default_rng(1000 * rank + 10 + s)
             llr_sets[s][:] = (rng.integers(0, 2, total, dtype=np.int8) * 20 - 10)
-    return dict(seg=seg, Es=Es, msgs=msgs, llr_sets=llr_sets, offs=offs, n_cbs=n_cbs, n_tbs=n_tbs,
+    return dict(seg=seg, Es=Es, msgs=msgs, tb_packed=tb_packed, llr_sets=llr_sets, offs=offs, n_cbs=n_cbs, n_tbs=n_tbs,
                 info_bits=n_tbs * c["tbs"], cfg=c)
 
 
@@ -457,6 +460,60 @@ def run_cuda_arm(args):
     h2d = int(sum(b1 - b0 for (_, _, b0, b1) in chunk_span)) + n * 60  # LLRs + device descriptors and launch order
     d2h = n * OUT_STRIDE + n * 8
 
+    # ---- transport-block leg: the same pipeline through pdc_submit_tbs / pdc_fetch_tbs, i.e. the code blocks
+    #      are also concatenated and CRC24A-checked on the device and one payload per transport block comes back -----------
+    from srsran_project_b200 import binding as B
+
+    tbs_bits = wl["cfg"]["tbs"]
+    TB_STRIDE = (tbs_bits // 8 + 3) // 4 * 4
+    h_tb = np.zeros(wl["n_tbs"] * TB_STRIDE, np.uint8)
+    chunk_tbd = []
+    for (lo, hi, _, _) in chunk_span:
+        tbd = np.zeros((hi - lo) // C, B.TB_DESC_DTYPE)
+        tbd["first_cb"], tbd["nof_cbs"], tbd["tbs_bits"] = np.arange(tbd.size) * C, C, tbs_bits
+        tbd["tb_offset"] = np.arange(tbd.size, dtype=np.uint64) * TB_STRIDE
+        chunk_tbd.append(tbd)
+
+    def tb_fetch_oldest(sink):
+        t, (plo, phi), _ = inflight.pop(0)
+        r, _cb = ctx.fetch_tbs(t, phi - plo, (phi - plo) // C, h_tb[(plo // C) * TB_STRIDE:(phi // C) * TB_STRIDE])
+        if sink is not None:
+            sink.append(r)
+
+    def tb_run(first_step, nsteps, sink_last):
+        for k in range(first_step, first_step + nsteps):
+            src = h_llrs[k % nsets]
+            last = sink_last is not None and k == first_step + nsteps - 1
+            for c in range(n_chunks):
+                lo, hi, b0, b1 = chunk_span[c]
+                if len(inflight) == nof_tickets:
+                    tb_fetch_oldest(sink_last if inflight[0][2] else None)
+                inflight.append((ctx.submit_tbs(chunk_descs[c], chunk_tbd[c], src[b0:b1]), (lo, hi), last))
+        while inflight:
+            tb_fetch_oldest(sink_last if inflight[0][2] else None)
+
+    tb_run(0, args.warmup, None)
+    barrier()
+    tb_res = []
+    t0 = time.perf_counter()
+    tb_run(0, args.steps, tb_res)
+    torch.cuda.synchronize()
+    tb_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    tb_res = np.concatenate(tb_res)
+    cb_ok_per_tb = ok.reshape(-1, C).all(axis=1)  # `ok`: CRC outcome of the last device-resident step = same LLR set
+    if not (tb_res["written"].astype(bool) == cb_ok_per_tb).all():
+        raise RuntimeError("transport-block path: TB assembly flags disagree with the code-block CRCs")
+    if wl["tb_packed"] is not None:
+        for k in np.nonzero(cb_ok_per_tb)[0]:
+            if not (tb_res[k]["tb_crc_ok"] and (h_tb[k * TB_STRIDE:k * TB_STRIDE + tbs_bits // 8] == wl["tb_packed"][k]).all()):
+                raise RuntimeError(f"transport-block path: TB {k} differs from the transmitted transport block")
+    tb_leg = {"value": total_info / tb_s / 1e9, "unit": "Gbit/s", "h2d_bytes_per_step": h2d + wl["n_tbs"] * 40,
+              "d2h_bytes_per_step": int(tb_res["written"].sum()) * (tbs_bits // 8) + n * 8 + wl["n_tbs"] * 4,
+              "ms_per_step": 1e3 * tb_s / args.steps,
+              "api": "pdc_submit_tbs / pdc_fetch_tbs: code blocks + TB concatenation + CRC24A on the device, payloads checked "
+                     "against the transmitted transport blocks"}
+
     # PCIe view of the end-to-end leg: LLR bytes per second against the host-to-device copy rate of this box, measured
     # here with plain pinned copies of one LLR set (rank 0 only, after the timed regions).
     pcie = None
@@ -553,7 +610,7 @@ def run_cuda_arm(args):
                     "ms_per_step": 1e3 * e2e_s / args.steps, "roofline": pcie,
                     "pipeline": f"{n_chunks} submissions of {args.chunk_tbs} TBs per step, {nof_tickets} in flight, "
                                 "not drained between steps"},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+            "e2e_tb": tb_leg, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
     ctx.close()
     ranks.close()

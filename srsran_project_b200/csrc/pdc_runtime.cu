@@ -8,24 +8,24 @@ static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
   CK(cudaStreamCreateWithFlags(&t.stream, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&t.done, cudaEventDisableTiming));
   size_t bits_bytes = (size_t)c.max_batch_cbs * (PDC_MAX_K / 8);
-  CK(cudaHostAlloc((void**)&t.h_cbs, sizeof(pdc_dev_cb) * c.max_batch_cbs, cudaHostAllocDefault));
+  // Transport-block descriptors / results travel in the same copies as the code-block ones: they are laid out right behind
+  // the n code-block entries of a submission, so each array has room for both.
+  const size_t desc_bytes = (sizeof(pdc_dev_cb) + sizeof(pdc_dev_tb)) * c.max_batch_cbs;
+  const size_t res_bytes  = (sizeof(pdc_cb_result) + sizeof(pdc_tb_result)) * c.max_batch_cbs;
+  CK(cudaHostAlloc((void**)&t.h_cbs, desc_bytes, cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&t.h_order, sizeof(uint32_t) * c.max_batch_cbs, cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&t.h_llrs, c.max_batch_llrs, cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&t.h_bits, bits_bytes, cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&t.h_res, sizeof(pdc_cb_result) * c.max_batch_cbs, cudaHostAllocDefault));
-  CK(cudaMalloc((void**)&t.d_cbs, sizeof(pdc_dev_cb) * c.max_batch_cbs));
+  CK(cudaHostAlloc((void**)&t.h_res, res_bytes, cudaHostAllocDefault));
+  CK(cudaMalloc((void**)&t.d_cbs, desc_bytes));
   CK(cudaMalloc((void**)&t.d_order, sizeof(uint32_t) * c.max_batch_cbs));
   CK(cudaMalloc((void**)&t.d_llrs, c.max_batch_llrs));
   CK(cudaMalloc((void**)&t.d_bits, bits_bytes));
-  CK(cudaMalloc((void**)&t.d_res, sizeof(pdc_cb_result) * c.max_batch_cbs));
+  CK(cudaMalloc((void**)&t.d_res, res_bytes));
   // Transport-block path: a TB is never larger than its code blocks together, and there are at most as many TBs as CBs.
-  CK(cudaHostAlloc((void**)&t.h_tbs, sizeof(pdc_dev_tb) * c.max_batch_cbs, cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&t.h_tbout, bits_bytes, cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&t.h_tbres, sizeof(pdc_tb_result) * c.max_batch_cbs, cudaHostAllocDefault));
-  CK(cudaMalloc((void**)&t.d_tbs, sizeof(pdc_dev_tb) * c.max_batch_cbs));
   CK(cudaMalloc((void**)&t.d_terms, sizeof(uint32_t) * c.max_batch_cbs));
   CK(cudaMalloc((void**)&t.d_tbout, bits_bytes));
-  CK(cudaMalloc((void**)&t.d_tbres, sizeof(pdc_tb_result) * c.max_batch_cbs));
   return PDC_OK;
 }
 
@@ -38,8 +38,8 @@ static void free_ticket(ticket_t& t)
   cudaFreeHost(t.h_res), cudaFreeHost(t.h_soft);
   cudaFree(t.d_cbs), cudaFree(t.d_order), cudaFree(t.d_llrs), cudaFree(t.d_bits), cudaFree(t.d_res);
   cudaFree(t.d_soft);
-  cudaFreeHost(t.h_tbs), cudaFreeHost(t.h_tbout), cudaFreeHost(t.h_tbres);
-  cudaFree(t.d_tbs), cudaFree(t.d_terms), cudaFree(t.d_tbout), cudaFree(t.d_tbres);
+  cudaFreeHost(t.h_tbout);
+  cudaFree(t.d_terms), cudaFree(t.d_tbout);
   if (t.done) {
     cudaEventDestroy(t.done);
   }
@@ -209,6 +209,8 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   }
   tb_plan tp;
   if (tbs) {
+    t->h_tbs   = reinterpret_cast<pdc_dev_tb*>(t->h_cbs + n), t->d_tbs = reinterpret_cast<pdc_dev_tb*>(t->d_cbs + n);
+    t->h_tbres = reinterpret_cast<pdc_tb_result*>(t->h_res + n), t->d_tbres = reinterpret_cast<pdc_tb_result*>(t->d_res + n);
     st = plan_tbs(tbs, ntb, descs, n, t->d_tbout, t->d_tbres, t->d_terms, t->h_tbs, tp);
     if (st == PDC_OK && tp.bytes_end > (size_t)ctx->cfg.max_batch_cbs * (PDC_MAX_K / 8)) {
       st = PDC_ERR_CAPACITY;
@@ -249,7 +251,8 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   if (llr_bytes != 0) {
     CKT(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
   }
-  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, t->stream));
+  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n + sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice,
+                      t->stream));
   if (!bp.identity) {
     CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
   }
@@ -266,16 +269,15 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
     return release_ticket(ctx, t, st);
   }
   if (tbs) {
-    // Assembly + TB CRC on the device; the payloads and the two result arrays come back, no per-CB bits.
-    CKT(cudaMemcpyAsync(t->d_tbs, t->h_tbs, sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, t->stream));
+    // Assembly + TB CRC on the device; the payloads and the two result arrays (one copy) come back, no per-CB bits.
     CKT(pdc_launch_tb(t->d_tbs, t->d_cbs, ctx->d_crc, (int)ntb, (int)tp.max_cbs, t->stream));
     ctx->launches += 2;
     CKT(cudaMemcpyAsync(t->h_tbout, t->d_tbout, tp.bytes_end, cudaMemcpyDeviceToHost, t->stream));
-    CKT(cudaMemcpyAsync(t->h_tbres, t->d_tbres, sizeof(pdc_tb_result) * ntb, cudaMemcpyDeviceToHost, t->stream));
   } else {
     CKT(cudaMemcpyAsync(t->h_bits, t->d_bits, bp.bits_end, cudaMemcpyDeviceToHost, t->stream));
   }
-  CKT(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n, cudaMemcpyDeviceToHost, t->stream));
+  CKT(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n + sizeof(pdc_tb_result) * ntb, cudaMemcpyDeviceToHost,
+                      t->stream));
   if (bp.any_host_soft) {
     CKT(cudaMemcpyAsync(t->h_soft, t->d_soft, bp.soft_end, cudaMemcpyDeviceToHost, t->stream));
   }
@@ -485,15 +487,13 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
   }
   tb_plan tp;
   if (st == PDC_OK && tbs) {
-    st = plan_tbs(tbs, ntb, descs, n, d_tb_bytes, d_tb_res, t->d_terms, t->h_tbs, tp);
+    t->h_tbs = reinterpret_cast<pdc_dev_tb*>(t->h_cbs + n), t->d_tbs = reinterpret_cast<pdc_dev_tb*>(t->d_cbs + n);
+    st       = plan_tbs(tbs, ntb, descs, n, d_tb_bytes, d_tb_res, t->d_terms, t->h_tbs, tp);
   }
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
   }
-  if (tbs) {
-    CKT(cudaMemcpyAsync(t->d_tbs, t->h_tbs, sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, stream));
-  }
-  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
+  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n + sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, stream));
   if (!bp.identity) {
     CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
   }
