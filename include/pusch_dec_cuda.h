@@ -14,6 +14,9 @@
  *                                                hw_accelerator_pusch_dec.h:83-115 (enqueue/dequeue/read_outputs/HARQ)
  *   srsran::pusch_decoder_impl::join_and_notify  lib/phy/upper/channel_processors/pusch/pusch_decoder_impl.cpp:396-505
  *     + concatenate_codeblocks                   (transport-block assembly and TB CRC24A: the pdc_*_tbs entry points)
+ *   srsran::demodulation_mapper::demodulate_soft include/srsran/phy/upper/channel_modulation/demodulation_mapper.h:66-69
+ *     + revert_scrambling                        lib/phy/upper/channel_processors/pusch/pusch_demodulator_impl.cpp:60-222,
+ *                                                :261-262,:397-405 (the LLR producers: the pdc_demodulate* entry points)
  *
  * Conventions: plain pointers and sizes only; every function returns a pdc_status (0 = ok) and never throws or
  * aborts; a context is thread-safe; there is NO CPU fallback — without a CUDA device pdc_create fails.
@@ -28,7 +31,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 2
+#define PDC_ABI_VERSION 3
 
 typedef enum {
   PDC_OK               = 0,
@@ -160,6 +163,40 @@ pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32
 pdc_status pdc_decode_device_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32_t n, const pdc_tb_desc* tbs_host,
                                  uint32_t ntb, const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits, pdc_cb_result* d_res,
                                  uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream);
+
+/* --- LLR producers on the device: soft demodulation + descrambling --------------------------------------
+ * One segment = ONE call of demodulation_mapper::demodulate_soft (in pusch_demodulator_impl.cpp:370-395 the resource elements
+ * of one OFDM symbol), optionally followed by revert_scrambling with the TS 38.211 5.2.1 sequence of c_init = rnti 2^15 + n_id
+ * (:261-262). The reference's result depends on a symbol's index within the call (AVX512 batches, then AVX2 batches, then
+ * single symbols, each with its own rounding); the kernel reproduces the AVX512-host build bit for bit, so segment boundaries
+ * must be the reference's call boundaries. The int8 LLRs land where pdc_decode_device reads them: no PCIe hop in between. */
+#define PDC_MOD_PI2_BPSK 0
+#define PDC_MOD_BPSK 1
+#define PDC_MOD_QPSK 2
+#define PDC_MOD_QAM16 4
+#define PDC_MOD_QAM64 6
+#define PDC_MOD_QAM256 8
+#define PDC_DEMOD_F_DESCRAMBLE 0x01u /* multiply LLR i of the segment by 1 - 2 c(scramble_offset + i) */
+
+typedef struct {
+  uint64_t sym_offset;      /* index of the segment's first symbol in symbols[] (complex) and noise_vars[] */
+  uint64_t llr_offset;      /* byte offset of its first LLR in llrs[]; nof_symbols * bits-per-symbol bytes are written */
+  uint32_t nof_symbols;
+  uint32_t c_init;          /* scrambling sequence initialiser (31 bits) */
+  uint32_t scramble_offset; /* sequence bits consumed before this segment (the LLRs of the codeword that precede it) */
+  uint8_t  mod;             /* PDC_MOD_* */
+  uint8_t  flags;           /* PDC_DEMOD_F_* */
+  uint16_t reserved;        /* 0 */
+} pdc_demod_seg;
+
+/* Device-resident: d_symbols = interleaved (re, im) floats (cf_t), d_noise_vars = one float per symbol (the equaliser's
+ * post-equalisation noise variances), d_llrs = int8 output; asynchronous on stream (a cudaStream_t, NULL = default). */
+pdc_status pdc_demodulate_device(pdc_ctx* ctx, const pdc_demod_seg* segs_host, uint32_t n, const float* d_symbols,
+                                 const float* d_noise_vars, int8_t* d_llrs, void* stream);
+/* Host buffers (what a demodulation_mapper adapter calls): copies in, runs, copies out, returns when the LLRs are in llrs.
+ * nof_symbols / llr_bytes: sizes of the host arrays (every segment must lie inside). */
+pdc_status pdc_demodulate(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, const float* symbols, const float* noise_vars,
+                          size_t nof_symbols, int8_t* llrs, size_t llr_bytes);
 
 /* --- HARQ arena (ext_harq_buffer_context_repository.h:36-107 / free_harq_context_entry) --------------------------- */
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot);                               /* zero-fills the slot */

@@ -22,6 +22,8 @@ INC="-I$REF/include -I$REF/external/fmt/include -I$REF/external -I$REF/lib -I$RE
 BASE="-std=c++17 -O3 -fPIC -march=x86-64-v3 -mtune=generic -fno-trapping-math -fno-math-errno -DFMT_HEADER_ONLY -DASSERTS_ENABLED -w"
 
 CC_DIR=lib/phy/upper/channel_coding
+CM_DIR=lib/phy/upper/channel_modulation
+AVX512_NATIVE="-mavx512f -mavx512bw -mavx512vl -mavx512dq -mavx512cd"
 declare -A EXTRA=(
   ["$CC_DIR/ldpc/ldpc_decoder_avx2.cpp"]="-mavx2"
   ["$CC_DIR/ldpc/ldpc_decoder_avx512.cpp"]="-mavx512f -mavx512bw"
@@ -29,6 +31,13 @@ declare -A EXTRA=(
   ["$CC_DIR/ldpc/ldpc_rate_dematcher_avx2_impl.cpp"]="-mavx2"
   ["$CC_DIR/ldpc/ldpc_rate_dematcher_avx512_impl.cpp"]="-mavx512f -mavx512bw -mavx512vbmi"
   ["$CC_DIR/crc_calculator_clmul_impl.cpp"]="-mpclmul -msse4.1"
+  # Soft demodulator: these files take the global -march in the reference's build (native); on the AVX512
+  # hosts the metric names that is the HAVE_AVX512 flavour of every modulation.
+  ["$CM_DIR/demodulation_mapper_impl.cpp"]="$AVX512_NATIVE"
+  ["$CM_DIR/demodulation_mapper_qpsk.cpp"]="$AVX512_NATIVE"
+  ["$CM_DIR/demodulation_mapper_qam16.cpp"]="$AVX512_NATIVE"
+  ["$CM_DIR/demodulation_mapper_qam64.cpp"]="$AVX512_NATIVE"
+  ["$CM_DIR/demodulation_mapper_qam256.cpp"]="$AVX512_NATIVE"
 )
 SRCS=(
   $CC_DIR/ldpc/ldpc_graph_impl.cpp
@@ -52,6 +61,12 @@ SRCS=(
   lib/srsvec/compare.cpp
   lib/srsvec/bit.cpp
   lib/phy/upper/channel_processors/pusch/pusch_codeblock_decoder.cpp
+  $CM_DIR/demodulation_mapper_impl.cpp
+  $CM_DIR/demodulation_mapper_qpsk.cpp
+  $CM_DIR/demodulation_mapper_qam16.cpp
+  $CM_DIR/demodulation_mapper_qam64.cpp
+  $CM_DIR/demodulation_mapper_qam256.cpp
+  lib/phy/upper/sequence_generators/pseudo_random_generator_impl.cpp
 )
 # Extra reference units may be appended by the caller (e.g. the whole pusch_decoder for the TB-level harness).
 SRCS+=(${REF_EXTRA_SRCS:-})
@@ -69,5 +84,6 @@ done
 for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
 
 $CXX $BASE $INC -c "$HERE/ref_shim.cpp" -o "$OBJ/ref_shim.o"
-$CXX -shared -o "$OUT/libsrsran_ref.so" "$OBJ/ref_shim.o" "${objs[@]}" -lpthread
+$CXX $BASE $INC -I$REF -c "$HERE/ref_shim_demod.cpp" -o "$OBJ/ref_shim_demod.o"
+$CXX -shared -o "$OUT/libsrsran_ref.so" "$OBJ/ref_shim.o" "$OBJ/ref_shim_demod.o" "${objs[@]}" -lpthread
 echo "built $OUT/libsrsran_ref.so"

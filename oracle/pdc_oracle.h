@@ -44,6 +44,13 @@ int orc_codeblock_decode(int flavour, int bg, int Z, int8_t* buf, const int8_t* 
 int orc_tb_assemble(int C, int K, int nof_filler, const uint8_t* cb_packed, int cb_stride, const uint8_t* cb_crc_ok,
                     int tbs_bits, uint8_t* tb_out, int* written);
 
+/* LLR producers, pdc_oracle_demod.c. mod: 0 pi/2-BPSK, 1 BPSK, 2 QPSK, 4 16QAM, 6 64QAM, 8 256QAM; symbols are
+ * (re, im) float pairs; one call = one call of demodulation_mapper::demodulate_soft (the vector-batch boundaries follow it). */
+void orc_demodulate_soft(int8_t* llrs, const float* symbols, const float* noise_vars, unsigned nof_symbols, int mod);
+void orc_prg_bits(uint8_t* out, unsigned n, uint32_t c_init, unsigned offset);
+void orc_descramble(int8_t* out, const int8_t* in, unsigned n, uint32_t c_init, unsigned offset);
+extern unsigned orc_demod_fused_mask;
+
 #ifdef __cplusplus
 }
 #endif

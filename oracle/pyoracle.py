@@ -31,7 +31,7 @@ def build_oracle():
     """Compiles the C restatement (seconds). Building the checker is not using it."""
     if not os.path.exists(ORACLE_SO) or any(
         os.path.getmtime(os.path.join(HERE, f)) > os.path.getmtime(ORACLE_SO)
-        for f in ("pdc_oracle.c", "pdc_oracle_decode.c", "pdc_oracle.h")
+        for f in ("pdc_oracle.c", "pdc_oracle_decode.c", "pdc_oracle_demod.c", "pdc_oracle.h")
     ):
         subprocess.check_call(["make", "-C", HERE, os.path.join(HERE, "libpdc_oracle.so")], stdout=subprocess.DEVNULL)
 
@@ -101,6 +101,68 @@ class Oracle:
         from tools import stimulus
 
         return stimulus.rate_match(bg, Z, cb_bits, rv, Qm, Nref, nof_filler, E)
+
+
+def _demod_call(lib, prefix, symbols, noise_vars, mod):
+    symbols = np.ascontiguousarray(symbols, np.float32).reshape(-1, 2)
+    noise_vars = np.ascontiguousarray(noise_vars, np.float32)
+    assert symbols.shape[0] == noise_vars.size
+    out = np.zeros(noise_vars.size * (1 if mod == 0 else mod), np.int8)
+    getattr(lib, prefix + "_demodulate_soft")(ctypes.c_void_p(out.ctypes.data), ctypes.c_void_p(symbols.ctypes.data),
+                                              ctypes.c_void_p(noise_vars.ctypes.data), ctypes.c_uint(noise_vars.size),
+                                              ctypes.c_int(mod))
+    return out
+
+
+def _descramble_call(lib, prefix, llrs, c_init, offset):
+    llrs = np.ascontiguousarray(llrs, np.int8)
+    out = np.zeros_like(llrs)
+    getattr(lib, prefix + "_descramble")(ctypes.c_void_p(out.ctypes.data), ctypes.c_void_p(llrs.ctypes.data),
+                                         ctypes.c_uint(llrs.size), ctypes.c_uint(c_init), ctypes.c_uint(offset))
+    return out
+
+
+def _prg_call(lib, prefix, n, c_init, offset):
+    out = np.zeros(n, np.uint8)
+    getattr(lib, prefix + "_prg_bits")(ctypes.c_void_p(out.ctypes.data), ctypes.c_uint(n), ctypes.c_uint(c_init),
+                                       ctypes.c_uint(offset))
+    return out
+
+
+class DemodOracle:
+    """LLR producers: the plain-C restatement in pdc_oracle_demod.c. mod: 0 pi/2-BPSK, 1 BPSK, 2, 4, 6, 8."""
+
+    def __init__(self):
+        build_oracle()
+        self.lib = ctypes.CDLL(ORACLE_SO)
+
+    def demodulate_soft(self, symbols, noise_vars, mod):
+        return _demod_call(self.lib, "orc", symbols, noise_vars, mod)
+
+    def descramble(self, llrs, c_init, offset=0):
+        return _descramble_call(self.lib, "orc", llrs, c_init, offset)
+
+    def prg_bits(self, n, c_init, offset=0):
+        return _prg_call(self.lib, "orc", n, c_init, offset)
+
+    def set_fused_mask(self, mask):
+        ctypes.c_uint.in_dll(self.lib, "orc_demod_fused_mask").value = mask
+
+
+class DemodReference:
+    """The UNMODIFIED demodulation_mapper_impl / pseudo_random_generator_impl behind oracle/ref_shim_demod.cpp."""
+
+    def __init__(self):
+        self.lib = ctypes.CDLL(REF_SO)
+
+    def demodulate_soft(self, symbols, noise_vars, mod):
+        return _demod_call(self.lib, "ref", symbols, noise_vars, mod)
+
+    def descramble(self, llrs, c_init, offset=0):
+        return _descramble_call(self.lib, "ref", llrs, c_init, offset)
+
+    def prg_bits(self, n, c_init, offset=0):
+        return _prg_call(self.lib, "ref", n, c_init, offset)
 
 
 def ref_available():

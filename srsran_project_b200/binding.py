@@ -49,6 +49,11 @@ DESC_DTYPE = np.dtype([("bg", np.uint8), ("Qm", np.uint8), ("rv", np.uint8), ("c
 TB_DESC_DTYPE = np.dtype([("first_cb", np.uint32), ("nof_cbs", np.uint32), ("tbs_bits", np.uint32), ("reserved", np.uint32),
                           ("tb_offset", np.uint64)])  # pdc_tb_desc
 TB_RESULT_DTYPE = np.dtype([("tb_crc_ok", np.uint8), ("written", np.uint8), ("nof_cbs_ok", np.uint16)])  # pdc_tb_result
+DEMOD_SEG_DTYPE = np.dtype([("sym_offset", np.uint64), ("llr_offset", np.uint64), ("nof_symbols", np.uint32),
+                            ("c_init", np.uint32), ("scramble_offset", np.uint32), ("mod", np.uint8), ("flags", np.uint8),
+                            ("reserved", np.uint16)])  # pdc_demod_seg
+PDC_MOD_PI2_BPSK, PDC_MOD_BPSK, PDC_MOD_QPSK, PDC_MOD_QAM16, PDC_MOD_QAM64, PDC_MOD_QAM256 = 0, 1, 2, 4, 6, 8
+PDC_DEMOD_F_DESCRAMBLE = 0x01
 assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
 assert TB_DESC_DTYPE.itemsize == 24 and TB_RESULT_DTYPE.itemsize == 4
 assert RESULT_DTYPE.itemsize == ctypes.sizeof(CbResult) == 8
@@ -93,6 +98,8 @@ def load_library():
                                    ctypes.POINTER(ctypes.c_int64)]
     lib.pdc_fetch_tbs.argtypes = [vp, ctypes.c_int64, vp, ctypes.c_size_t, vp, vp, vp, ctypes.c_size_t]
     lib.pdc_decode_device_tbs.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, vp, vp, vp, vp, vp, vp]
+    lib.pdc_demodulate_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp, vp]
+    lib.pdc_demodulate.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
     lib.pdc_harq_free.argtypes = [vp, ctypes.c_int32]
     lib.pdc_harq_read.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
@@ -108,7 +115,8 @@ def load_library():
 
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
-                    "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
+                    "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
+                    "pdc_demodulate_device", "pdc_demodulate", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
                     "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
 
 
@@ -206,6 +214,20 @@ class PuschDecCuda:
     def decode_device(self, descs, d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, stream_ptr=None):
         self._check(self.lib.pdc_decode_device(self.h, descs.ctypes.data, descs.size, d_llrs_ptr, d_soft_ptr,
                                                d_bits_ptr, d_res_ptr, stream_ptr))
+
+    # --- LLR producers (soft demodulation + descrambling) ------------------------------------------------------------------
+    def demodulate(self, segs, symbols, noise_vars, llr_bytes):
+        """Host-buffer entry: symbols = float32 (n, 2) (re, im), noise_vars = float32 (n,). Returns the int8 LLR array."""
+        symbols = np.ascontiguousarray(symbols, np.float32)
+        noise_vars = np.ascontiguousarray(noise_vars, np.float32)
+        llrs = np.zeros(llr_bytes, np.int8)
+        self._check(self.lib.pdc_demodulate(self.h, segs.ctypes.data, segs.size, symbols.ctypes.data, noise_vars.ctypes.data,
+                                            noise_vars.size, llrs.ctypes.data, llrs.size))
+        return llrs
+
+    def demodulate_device(self, segs, d_symbols_ptr, d_noise_ptr, d_llrs_ptr, stream_ptr=None):
+        self._check(self.lib.pdc_demodulate_device(self.h, segs.ctypes.data, segs.size, d_symbols_ptr, d_noise_ptr,
+                                                   d_llrs_ptr, stream_ptr))
 
     # --- HARQ arena ------------------------------------------------------------------------------------------------
     def harq_free(self, slot):

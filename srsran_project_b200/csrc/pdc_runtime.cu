@@ -103,6 +103,7 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   build_crc_tables(crc);
   build_crc_bit_tables(crc, crc_bit);
   if (!cuda_ok(ctx, pdc_kernels_init_device(&rows), "pdc_kernels_init_device") ||
+      !cuda_ok(ctx, pdc_demod_init_device(), "pdc_demod_init_device") ||
       !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_graphs, graphs.size() * 4), "cudaMalloc graphs") ||
       !cuda_ok(ctx, cudaMemcpy(ctx->d_graphs, graphs.data(), graphs.size() * 4, cudaMemcpyHostToDevice), "copy") ||
       !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_crc, crc.size() * 4), "cudaMalloc crc") ||
@@ -142,6 +143,16 @@ void pdc_destroy(pdc_ctx* ctx)
   }
   cudaFree(ctx->d_graphs), cudaFree(ctx->d_crc), cudaFree(ctx->d_crc_bit), cudaFree(ctx->d_harq);
   cudaFree(ctx->d_harq_bits);
+  for (pdc_ctx::demod_slot& d : ctx->demod_ring) {
+    cudaFree(d.d_desc);
+    if (d.done) {
+      cudaEventDestroy(d.done);
+    }
+  }
+  cudaFree(ctx->d_demod_in), cudaFree(ctx->d_demod_out);
+  if (ctx->demod_stream) {
+    cudaStreamDestroy(ctx->demod_stream);
+  }
   delete ctx;
 }
 
@@ -526,6 +537,147 @@ pdc_status pdc_decode_device_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_
     return PDC_ERR_INVALID_ARG;
   }
   return decode_device_common(ctx, descs, n, tbs, ntb, d_llrs, d_soft, d_bits, d_res, d_tb_bytes, d_tb_res, stream);
+}
+
+// ---- LLR producers ---------------------------------------------------------------------------------------------------------
+static int demod_bits_per_symbol(unsigned mod)
+{
+  switch (mod) {
+    case PDC_MOD_PI2_BPSK:
+    case PDC_MOD_BPSK:
+      return 1;
+    case PDC_MOD_QPSK:
+    case PDC_MOD_QAM16:
+    case PDC_MOD_QAM64:
+    case PDC_MOD_QAM256:
+      return (int)mod;
+    default:
+      return 0;
+  }
+}
+
+// Validates the segments against the array sizes (0 = unknown, device entry) and lists the chunks of 1024 symbols.
+static pdc_status demod_plan(const pdc_demod_seg* segs, uint32_t n, size_t nof_symbols, size_t llr_bytes,
+                             std::vector<uint32_t>& chunks, size_t& max_sym, size_t& max_llr)
+{
+  chunks.clear();
+  max_sym = max_llr = 0;
+  for (uint32_t i = 0; i != n; ++i) {
+    const pdc_demod_seg& s  = segs[i];
+    const int            qm = demod_bits_per_symbol(s.mod);
+    if (qm == 0 || (s.flags & ~PDC_DEMOD_F_DESCRAMBLE) != 0 || s.reserved != 0 ||
+        ((uint64_t)s.scramble_offset + (uint64_t)s.nof_symbols * qm + 1600u) >= (1ull << 28)) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    const size_t se = (size_t)s.sym_offset + s.nof_symbols, le = (size_t)s.llr_offset + (size_t)s.nof_symbols * qm;
+    if ((nof_symbols != 0 && se > nof_symbols) || (llr_bytes != 0 && le > llr_bytes)) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    max_sym = se > max_sym ? se : max_sym, max_llr = le > max_llr ? le : max_llr;
+    for (uint32_t first = 0; first < s.nof_symbols; first += 1024) {
+      chunks.push_back(i), chunks.push_back(first);
+    }
+  }
+  return PDC_OK;
+}
+
+pdc_status pdc_demodulate_device(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, const float* d_symbols,
+                                 const float* d_noise_vars, int8_t* d_llrs, void* stream_v)
+{
+  if (!ctx || !segs || n == 0 || !d_symbols || !d_noise_vars || !d_llrs) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::vector<uint32_t> chunks;
+  size_t                max_sym, max_llr;
+  pdc_status            st = demod_plan(segs, n, 0, 0, chunks, max_sym, max_llr);
+  if (st != PDC_OK) {
+    return st;
+  }
+  if (chunks.empty()) {
+    return PDC_OK; // only empty segments: the reference's loops do not run either
+  }
+  cudaStream_t stream = (cudaStream_t)stream_v;
+  CK(cudaSetDevice(ctx->cfg.device));
+  std::lock_guard<std::mutex> lock(ctx->demod_mtx);
+  pdc_ctx::demod_slot&        slot = ctx->demod_ring[ctx->demod_next++ % 8];
+  if (!slot.done) {
+    CK(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
+  }
+  if (slot.used) {
+    CK(cudaEventSynchronize(slot.done)); // the kernel that read this staging entry has finished
+  }
+  const size_t seg_bytes = ((size_t)n * sizeof(pdc_demod_seg) + 15) & ~(size_t)15, chunk_bytes = chunks.size() * 4;
+  if (slot.cap < seg_bytes + chunk_bytes) {
+    cudaFree(slot.d_desc);
+    slot.d_desc = nullptr, slot.cap = 0;
+    CK(cudaMalloc(&slot.d_desc, 2 * (seg_bytes + chunk_bytes)));
+    slot.cap = 2 * (seg_bytes + chunk_bytes);
+  }
+  // Pageable sources: the runtime stages them before the call returns, so the caller's array and `chunks` may go away.
+  CK(cudaMemcpyAsync(slot.d_desc, segs, (size_t)n * sizeof(pdc_demod_seg), cudaMemcpyHostToDevice, stream));
+  CK(cudaMemcpyAsync((char*)slot.d_desc + seg_bytes, chunks.data(), chunk_bytes, cudaMemcpyHostToDevice, stream));
+  CK(pdc_demod_launch((const pdc_demod_seg*)slot.d_desc, (char*)slot.d_desc + seg_bytes, (uint32_t)(chunks.size() / 2),
+                      d_symbols, d_noise_vars, d_llrs, stream));
+  ctx->launches += 1;
+  CK(cudaEventRecord(slot.done, stream));
+  slot.used = true;
+  return PDC_OK;
+}
+
+pdc_status pdc_demodulate(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, const float* symbols, const float* noise_vars,
+                          size_t nof_symbols, int8_t* llrs, size_t llr_bytes)
+{
+  if (!ctx || !segs || n == 0 || !symbols || !noise_vars || !llrs || nof_symbols == 0 || llr_bytes == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::vector<uint32_t> chunks;
+  size_t                max_sym, max_llr;
+  pdc_status            st = demod_plan(segs, n, nof_symbols, llr_bytes, chunks, max_sym, max_llr);
+  if (st != PDC_OK) {
+    return st;
+  }
+  if (chunks.empty()) {
+    return PDC_OK;
+  }
+  CK(cudaSetDevice(ctx->cfg.device));
+  // One call at a time on the context's demodulation stream and buffers (the adapter is synchronous like the reference's
+  // demodulate_soft).
+  std::lock_guard<std::mutex> call_lock(ctx->demod_call_mtx);
+  const size_t                sym4 = (max_sym + 3) & ~(size_t)3; // keeps the noise array 16-byte aligned behind the symbols
+  if (!ctx->demod_stream) {
+    CK(cudaStreamCreateWithFlags(&ctx->demod_stream, cudaStreamNonBlocking));
+  }
+  if (ctx->demod_in_cap < sym4 * 3) {
+    cudaFree(ctx->d_demod_in);
+    ctx->d_demod_in = nullptr, ctx->demod_in_cap = 0;
+    CK(cudaMalloc((void**)&ctx->d_demod_in, sym4 * 3 * sizeof(float) * 2));
+    ctx->demod_in_cap = sym4 * 3 * 2;
+  }
+  if (ctx->demod_out_cap < max_llr) {
+    cudaFree(ctx->d_demod_out);
+    ctx->d_demod_out = nullptr, ctx->demod_out_cap = 0;
+    CK(cudaMalloc((void**)&ctx->d_demod_out, max_llr * 2));
+    ctx->demod_out_cap = max_llr * 2;
+  }
+  cudaStream_t stream  = ctx->demod_stream;
+  float*       d_in    = ctx->d_demod_in;
+  float*       d_noise = d_in + 2 * sym4;
+  int8_t*      d_out   = ctx->d_demod_out;
+  CK(cudaMemcpyAsync(d_in, symbols, max_sym * 2 * sizeof(float), cudaMemcpyHostToDevice, stream));
+  CK(cudaMemcpyAsync(d_noise, noise_vars, max_sym * sizeof(float), cudaMemcpyHostToDevice, stream));
+  st = pdc_demodulate_device(ctx, segs, n, d_in, d_noise, d_out, stream);
+  if (st != PDC_OK) {
+    return st;
+  }
+  // Segments may leave gaps in llrs[]: only each segment's own bytes are copied back.
+  for (uint32_t i = 0; i != n; ++i) {
+    const size_t bytes = (size_t)segs[i].nof_symbols * demod_bits_per_symbol(segs[i].mod);
+    if (bytes != 0) {
+      CK(cudaMemcpyAsync(llrs + segs[i].llr_offset, d_out + segs[i].llr_offset, bytes, cudaMemcpyDeviceToHost, stream));
+    }
+  }
+  CK(cudaStreamSynchronize(stream));
+  return PDC_OK;
 }
 
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot)

@@ -24,6 +24,9 @@ extern "C" int         pdc_h2_supported(int bg, int Z);
 extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
 extern "C" size_t      pdc_h2g_smem_bytes(int bg, int Z, int max_layers);
 extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_demod_init_device();
+extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void* d_chunks, uint32_t nchunks,
+                                        const float* d_symbols, const float* d_noise, int8_t* d_llrs, cudaStream_t stream);
 extern "C" cudaError_t pdc_launch_tb(const pdc_dev_tb* d_tbs, const pdc_dev_cb* d_cbs, const uint32_t* crc_pow, int ntb,
                                      int max_cbs, cudaStream_t stream);
 
@@ -80,6 +83,21 @@ struct pdc_ctx {
   uint8_t*              d_harq_bits = nullptr; // decoded bits kept with every HARQ slot (transport-block path), PDC_MAX_K / 8 each
   std::atomic<uint64_t> launches{0};
   size_t                bits_stride_total = 0;
+  // LLR producers (pdc_demodulate*): a small ring of descriptor staging (segments + chunk table), stream-ordered through one
+  // event per entry, and grow-only device buffers for the host-buffer entry point.
+  struct demod_slot {
+    void*       d_desc = nullptr;
+    size_t      cap    = 0;
+    cudaEvent_t done   = nullptr;
+    bool        used   = false;
+  };
+  demod_slot   demod_ring[8];
+  unsigned     demod_next = 0;
+  std::mutex   demod_mtx, demod_call_mtx;
+  float*       d_demod_in = nullptr; // symbols, then noise variances
+  int8_t*      d_demod_out = nullptr;
+  size_t       demod_in_cap = 0, demod_out_cap = 0;
+  cudaStream_t demod_stream = nullptr;
 };
 
 namespace {

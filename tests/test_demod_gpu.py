@@ -1,0 +1,203 @@
+"""LLR producers on the device: pdc_demodulate / pdc_demodulate_device against the golden fixture recorded from
+the compiled reference, against the CPU oracle on fresh multi-segment batches (every modulation, ragged lengths, unaligned
+offsets, descrambling far into the sequence), at the full size of BASELINE config 2 (one OFDM symbol = 13104 256QAM symbols per
+call), and chained on the device into the code-block decode + transport-block assembly. Bit-exact: the LLRs are int8."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+from tests.demod_cases import golden_calls, golden_scrambling
+from tools import demod_stimulus as S
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def acc():
+    import srsran_project_b200 as pdc
+
+    a = pdc.PuschDecCuda(device=0, max_batch_cbs=512, max_batch_llrs=4 << 20, harq_slots=0, nof_tickets=2)
+    yield a
+    a.close()
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return pyoracle.DemodOracle()
+
+
+def pack_segments(B, calls, descramble=None, align=1):
+    """calls: list of (mod, symbols, noise_vars). Segments back to back (offsets rounded up to `align`)."""
+    segs = np.zeros(len(calls), B.DEMOD_SEG_DTYPE)
+    so = lo = 0
+    syms, nvs = [], []
+    for i, (mod, sym, nv) in enumerate(calls):
+        qm = S.bits_per_symbol(mod)
+        so, lo = -(-so // align) * align, -(-lo // align) * align
+        segs[i]["sym_offset"], segs[i]["llr_offset"], segs[i]["nof_symbols"], segs[i]["mod"] = so, lo, nv.size, mod
+        if descramble is not None:
+            segs[i]["flags"] = B.PDC_DEMOD_F_DESCRAMBLE
+            segs[i]["c_init"], segs[i]["scramble_offset"] = descramble[i]
+        syms.append((so, sym)), nvs.append((so, nv))
+        so += nv.size
+        lo += nv.size * qm
+    symbols, noise = np.zeros((max(so, 1), 2), np.float32), np.ones(max(so, 1), np.float32)
+    for o, x in syms:
+        symbols[o:o + x.shape[0]] = x
+    for o, x in nvs:
+        noise[o:o + x.size] = x
+    return segs, symbols, noise, max(lo, 1)
+
+
+def test_golden_calls_in_one_submission(acc):
+    from srsran_project_b200 import binding as B
+
+    calls = golden_calls()
+    for align in (1, 4, 16):
+        segs, symbols, noise, nllr = pack_segments(B, [(m, s, n) for _, m, s, n, _ in calls], align=align)
+        llrs = acc.demodulate(segs, symbols, noise, nllr)
+        for sg, (name, mod, _, _, want) in zip(segs, calls):
+            o = int(sg["llr_offset"])
+            got = llrs[o:o + want.size]
+            assert np.array_equal(got, want), (name, align, np.nonzero(got != want)[0][:4], got[:8], want[:8])
+
+
+def test_descrambling_golden(acc, orc):
+    """The sequence alone: constant LLRs through the BPSK demodulator would hide nothing, so use 256QAM symbols whose LLRs are
+    known from the oracle and compare the descrambled outputs with reference-descrambled oracle LLRs; plus the recorded cases
+    replayed through sign patterns."""
+    from srsran_project_b200 import binding as B
+
+    cases, _ = golden_scrambling()
+    for k, (c_init, off, x, want) in enumerate(cases):
+        n = x.size
+        # BPSK symbols with per-symbol noise variance chosen so that the LLR magnitude is |x| (or 0): sign pattern comes out.
+        sign = (want.astype(np.int16) * x.astype(np.int16)) < 0  # where the reference flipped
+        sym, nv, _ = S.equalised(n, 1, 40 + k, noise_var=0.3, special=False)
+        plain = orc.demodulate_soft(sym, nv, 1)
+        segs, symbols, noise, nllr = pack_segments(B, [(1, sym, nv)], descramble=[(c_init, off)])
+        got = acc.demodulate(segs, symbols, noise, nllr)
+        flipped = (got.astype(np.int16) * plain.astype(np.int16)) < 0
+        nz = (plain != 0) & (x != 0)
+        assert np.array_equal(flipped[nz], sign[nz]), (k, c_init, off)
+        assert np.array_equal(np.abs(got.astype(np.int16)), np.abs(plain.astype(np.int16)))
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_ragged_batches_with_descrambling_match_oracle(acc, orc, seed):
+    from srsran_project_b200 import binding as B
+
+    r = np.random.default_rng(seed)
+    calls, scr = [], []
+    for _ in range(40):
+        mod = int(r.choice(S.MODS))
+        n = int(r.choice([0, 1, 2, 5, 31, 32, 33, 100, 1023, 1024, 1025, 2500, 4099]))
+        sym, nv, _ = S.equalised(n, mod, int(r.integers(1 << 30)), noise_var=0.02 if mod >= 6 else 0.2)
+        if n == 0:
+            sym, nv = np.zeros((0, 2), np.float32), np.zeros(0, np.float32)
+        calls.append((mod, sym, nv))
+        scr.append((int(r.integers(0, 1 << 31)), int(r.choice([0, 1, 31, 32, 12345, 1_362_816, 9_000_000]))))
+    for align in (1, 16):
+        segs, symbols, noise, nllr = pack_segments(B, calls, descramble=scr, align=align)
+        llrs = acc.demodulate(segs, symbols, noise, nllr)
+        for sg, (mod, sym, nv), (c_init, off) in zip(segs, calls, scr):
+            want = orc.descramble(orc.demodulate_soft(sym, nv, mod), c_init, off)
+            o = int(sg["llr_offset"])
+            got = llrs[o:o + want.size]
+            assert np.array_equal(got, want), (mod, nv.size, c_init, off, align, np.nonzero(got != want)[0][:4])
+
+
+def test_contract_violations(acc):
+    from srsran_project_b200 import binding as B
+
+    segs = np.zeros(1, B.DEMOD_SEG_DTYPE)
+    segs[0]["nof_symbols"], segs[0]["mod"] = 8, 3
+    with pytest.raises(B.PdcError):
+        acc.demodulate(segs, np.zeros((8, 2), np.float32), np.ones(8, np.float32), 64)
+    segs[0]["mod"] = 8
+    with pytest.raises(B.PdcError):  # output array too small
+        acc.demodulate(segs, np.zeros((8, 2), np.float32), np.ones(8, np.float32), 63)
+    with pytest.raises(B.PdcError):  # input array too small
+        acc.demodulate(segs, np.zeros((7, 2), np.float32), np.ones(7, np.float32), 64)
+
+
+def config2_transmission(n_tbs, sigma2, seed):
+    """n_tbs config-2 transport blocks (273 PRB, 4 layers, 256QAM): scrambled, modulated, noisy equaliser outputs in the
+    order the demodulator sees them (13 data OFDM symbols of 13104 symbols each), plus the descriptors of every stage."""
+    from srsran_project_b200 import binding as B
+    from tools import stimulus as T
+
+    c = T.CONFIG2
+    seg = T.segmentation(c["bg"], c["tbs"])
+    Es = T.rm_lengths(seg["C"], c["G"], c["nof_layers"], c["Qm"])
+    orc = pyoracle.DemodOracle()
+    nsym_tb, per_call = c["G"] // 8, 273 * 12 * 4
+    assert nsym_tb % per_call == 0
+    symbols, noise = np.zeros((n_tbs * nsym_tb, 2), np.float32), np.zeros(n_tbs * nsym_tb, np.float32)
+    segs = np.zeros(n_tbs * (nsym_tb // per_call), B.DEMOD_SEG_DTYPE)
+    tbs_packed = []
+    r = np.random.default_rng(seed)
+    for t in range(n_tbs):
+        tb = r.integers(0, 2, c["tbs"], dtype=np.uint8)
+        tbs_packed.append(np.packbits(tb))
+        _, bits, _ = T.tb_encode(c["bg"], c["tbs"], tb, c["rv"], c["Qm"], 0, c["nof_layers"], c["G"])
+        c_init = ((0x4601 + t) << 15) + 41 + t
+        tx = bits ^ orc.prg_bits(c["G"], c_init, 0)
+        z = S.modulate(tx, 8)
+        z = z + (r.normal(0, np.sqrt(sigma2 / 2), z.size) + 1j * r.normal(0, np.sqrt(sigma2 / 2), z.size)).astype(np.complex64)
+        symbols[t * nsym_tb:(t + 1) * nsym_tb, 0], symbols[t * nsym_tb:(t + 1) * nsym_tb, 1] = z.real, z.imag
+        noise[t * nsym_tb:(t + 1) * nsym_tb] = np.float32(sigma2)
+        for k in range(nsym_tb // per_call):
+            s = segs[t * (nsym_tb // per_call) + k]
+            s["sym_offset"], s["llr_offset"] = t * nsym_tb + k * per_call, (t * nsym_tb + k * per_call) * 8
+            s["nof_symbols"], s["mod"], s["flags"] = per_call, 8, B.PDC_DEMOD_F_DESCRAMBLE
+            s["c_init"], s["scramble_offset"] = c_init, k * per_call * 8
+    descs = B.make_descs(n_tbs * seg["C"])
+    tbd = np.zeros(n_tbs, B.TB_DESC_DTYPE)
+    stride = (seg["K"] + 31) // 32 * 4
+    for t in range(n_tbs):
+        o = t * c["G"]
+        for q in range(seg["C"]):
+            d = descs[t * seg["C"] + q]
+            d["bg"], d["Z"], d["Qm"], d["rv"], d["crc_type"], d["max_iter"] = 1, seg["Z"], 8, 0, pyoracle.CRC24B, 6
+            d["flags"], d["E"], d["nof_filler"] = B.PDC_F_NEW_DATA | B.PDC_F_EARLY_STOP, Es[q], seg["F"]
+            d["llr_offset"], d["soft_offset"], d["out_offset"] = o, (t * seg["C"] + q) * 25344, (t * seg["C"] + q) * stride
+            o += Es[q]
+        tbd[t]["first_cb"], tbd[t]["nof_cbs"], tbd[t]["tbs_bits"], tbd[t]["tb_offset"] = t * seg["C"], seg["C"], c["tbs"], t * (c["tbs"] // 8)
+    return dict(symbols=symbols, noise=noise, segs=segs, descs=descs, tbd=tbd, tbs=tbs_packed, G=c["G"], C=seg["C"],
+                stride=stride, tbs_bytes=c["tbs"] // 8)
+
+
+def test_config2_symbols_to_transport_blocks_on_the_device(acc, orc):
+    """Equaliser outputs of two config-2 TBs in HBM -> demodulate + descramble -> decode + assemble, nothing but the TB
+    payloads leaves the device. LLRs bit-exact with the oracle; payloads equal to the transmitted transport blocks."""
+    import torch
+
+    w = config2_transmission(2, 0.0016, 21)
+    d_sym, d_nv = torch.from_numpy(w["symbols"]).cuda(), torch.from_numpy(w["noise"]).cuda()
+    n_cbs, n_tbs = w["descs"].size, w["tbd"].size
+    d_llrs = torch.zeros(n_tbs * w["G"], dtype=torch.int8, device="cuda")
+    d_soft = torch.zeros(n_cbs * 25344, dtype=torch.int8, device="cuda")
+    d_bits = torch.zeros(n_cbs * w["stride"], dtype=torch.uint8, device="cuda")
+    d_res = torch.zeros(n_cbs * 8, dtype=torch.uint8, device="cuda")
+    d_tb = torch.zeros(n_tbs * w["tbs_bytes"], dtype=torch.uint8, device="cuda")
+    d_tbres = torch.zeros(n_tbs * 4, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    acc.demodulate_device(w["segs"], d_sym.data_ptr(), d_nv.data_ptr(), d_llrs.data_ptr(), stream)
+    acc.decode_device_tbs(w["descs"], w["tbd"], d_llrs.data_ptr(), d_soft.data_ptr(), d_bits.data_ptr(), d_res.data_ptr(),
+                          d_tb.data_ptr(), d_tbres.data_ptr(), stream)
+    torch.cuda.synchronize()
+    llrs = d_llrs.cpu().numpy()
+    for sg in w["segs"]:
+        a, n = int(sg["sym_offset"]), int(sg["nof_symbols"])
+        want = orc.descramble(orc.demodulate_soft(w["symbols"][a:a + n], w["noise"][a:a + n], 8), int(sg["c_init"]),
+                              int(sg["scramble_offset"]))
+        o = int(sg["llr_offset"])
+        assert np.array_equal(llrs[o:o + want.size], want), (a, n)
+    from srsran_project_b200 import binding as B
+
+    tres = d_tbres.cpu().numpy().view(B.TB_RESULT_DTYPE)
+    assert (tres["tb_crc_ok"] == 1).all() and (tres["written"] == 1).all()
+    out = d_tb.cpu().numpy().reshape(n_tbs, -1)
+    for t in range(n_tbs):
+        assert np.array_equal(out[t], w["tbs"][t]), t
