@@ -155,6 +155,7 @@ def config2_transmission(n_tbs, sigma2, seed):
     descs = B.make_descs(n_tbs * seg["C"])
     tbd = np.zeros(n_tbs, B.TB_DESC_DTYPE)
     stride = (seg["K"] + 31) // 32 * 4
+    tb_stride = (c["tbs"] // 8 + 3) // 4 * 4  # pdc_tb_desc.tb_offset must be a multiple of 4
     for t in range(n_tbs):
         o = t * c["G"]
         for q in range(seg["C"]):
@@ -163,9 +164,9 @@ def config2_transmission(n_tbs, sigma2, seed):
             d["flags"], d["E"], d["nof_filler"] = B.PDC_F_NEW_DATA | B.PDC_F_EARLY_STOP, Es[q], seg["F"]
             d["llr_offset"], d["soft_offset"], d["out_offset"] = o, (t * seg["C"] + q) * 25344, (t * seg["C"] + q) * stride
             o += Es[q]
-        tbd[t]["first_cb"], tbd[t]["nof_cbs"], tbd[t]["tbs_bits"], tbd[t]["tb_offset"] = t * seg["C"], seg["C"], c["tbs"], t * (c["tbs"] // 8)
+        tbd[t]["first_cb"], tbd[t]["nof_cbs"], tbd[t]["tbs_bits"], tbd[t]["tb_offset"] = t * seg["C"], seg["C"], c["tbs"], t * tb_stride
     return dict(symbols=symbols, noise=noise, segs=segs, descs=descs, tbd=tbd, tbs=tbs_packed, G=c["G"], C=seg["C"],
-                stride=stride, tbs_bytes=c["tbs"] // 8)
+                stride=stride, tbs_bytes=c["tbs"] // 8, tb_stride=tb_stride)
 
 
 def test_config2_symbols_to_transport_blocks_on_the_device(acc, orc):
@@ -180,7 +181,7 @@ def test_config2_symbols_to_transport_blocks_on_the_device(acc, orc):
     d_soft = torch.zeros(n_cbs * 25344, dtype=torch.int8, device="cuda")
     d_bits = torch.zeros(n_cbs * w["stride"], dtype=torch.uint8, device="cuda")
     d_res = torch.zeros(n_cbs * 8, dtype=torch.uint8, device="cuda")
-    d_tb = torch.zeros(n_tbs * w["tbs_bytes"], dtype=torch.uint8, device="cuda")
+    d_tb = torch.zeros(n_tbs * w["tb_stride"], dtype=torch.uint8, device="cuda")
     d_tbres = torch.zeros(n_tbs * 4, dtype=torch.uint8, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
     acc.demodulate_device(w["segs"], d_sym.data_ptr(), d_nv.data_ptr(), d_llrs.data_ptr(), stream)
@@ -198,6 +199,6 @@ def test_config2_symbols_to_transport_blocks_on_the_device(acc, orc):
 
     tres = d_tbres.cpu().numpy().view(B.TB_RESULT_DTYPE)
     assert (tres["tb_crc_ok"] == 1).all() and (tres["written"] == 1).all()
-    out = d_tb.cpu().numpy().reshape(n_tbs, -1)
+    out = d_tb.cpu().numpy().reshape(n_tbs, -1)[:, :w["tbs_bytes"]]
     for t in range(n_tbs):
         assert np.array_equal(out[t], w["tbs"][t]), t
