@@ -16,22 +16,22 @@
 // single-precision one the host performs (subnormals included), and a fused multiply-add appears exactly where the
 // compiled reference has one (written as fmaf).
 //
-// Mapping: one CTA of 256 threads per chunk of 1024 symbols of one segment, 4 consecutive symbols per thread (4 Qm output
+// Mapping: persistent CTAs walk the list of 1024-symbol chunks (a chunk lies inside one segment): eight warps with 4 consecutive symbols per thread (4 Qm output
 // bytes, one aligned vector store). Bound: 20 B of HBM traffic per 256QAM symbol against ~150 issue slots — the kernel sits
 // between the HBM and the issue roofline.
 //
-// Scrambling sequence (TS 38.211 5.2.1) without a serial walk: warp 0 jumps both 31-bit LFSRs to the chunk's first bit with
+// Scrambling sequence (TS 38.211 5.2.1) without a serial walk: a ninth warp jumps both 31-bit LFSRs to the chunk's first bit with
 // precomputed powers of the transition matrix (binary expansion of the position: one 31-lane parity + ballot per set bit),
 // every lane then jumps a further 32 l bits to produce word l, and the remaining words follow from the word-level
 // recurrence W[j + 31] = W[j + 3] ^ W[j] (the characteristic polynomial over GF(2) commutes with squaring, so what holds
-// for bits at distance 1 holds for words at distance 32). The other seven warps do arithmetic meanwhile.
+// for bits at distance 1 holds for words at distance 32). The eight arithmetic warps meet it at one barrier before the stores.
 #include "../../include/pusch_dec_cuda.h"
 #include <cmath>
 #include <cstdint>
 #include <cuda_runtime.h>
 
 #define PDC_DEMOD_CHUNK 1024 /* symbols per CTA */
-#define PDC_DEMOD_THREADS 256
+#define PDC_DEMOD_THREADS 288 /* eight arithmetic warps (4 symbols per thread) + one warp that generates the scrambling words */
 #define PDC_DEMOD_JUMP_BITS 28
 
 struct pdc_demod_tables {
@@ -40,6 +40,7 @@ struct pdc_demod_tables {
   float    width[7];
   float    half_n[7];                            // nof_intervals / 2
   int      n_minus_1[7];
+  float    n_minus_1_f[7];
   float    qam16_gain, qam16_thr;                // 4 / sqrt(10), 2 / sqrt(10)
 };
 __constant__ pdc_demod_tables c_demod;
@@ -108,6 +109,49 @@ __device__ __forceinline__ float interval_scalar(float v, float rcp, int t, cons
 }
 
 enum { PATH_SCALAR = 0, PATH_AVX2 = 1, PATH_AVX512 = 2 };
+
+// ---- the common case of the AVX512 loop, without conversions or integer clamps -------------------------------------------------
+// When |re|, |im| < 1e8 and the noise reciprocal is finite, nothing in mm512::interval_function / quantize_ps can saturate a
+// conversion or produce a NaN, and both roundings can be done by the adder: floor(x) for 0 <= x < 2^22 is the low mantissa of
+// x + 2^23 rounded DOWN, round-half-even(y) for |y| <= 120 is the low byte of y + 1.5 * 2^23 rounded to nearest. The clamps
+// move in front of the roundings (they commute with them at integer bounds). Same results as interval_avx512 + q_avx512, with
+// the work on the FMA pipe instead of the quarter-rate conversion unit and the integer min / max.
+template <int T0, int NT>
+__device__ __forceinline__ void demod_interval_fast(uint32_t (&w)[2 * NT], const float (&re)[4], const float (&im)[4],
+                                                    const float (&rcp)[4], uint32_t tab_addr)
+{
+  uint32_t z[4][2 * NT]; // magic sums: the low byte is the LLR
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    const float v[2]  = {re[s], im[s]};
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const bool live = fabsf(v[c]) > NEAR_ZERO;
+#pragma unroll
+      for (int k = 0; k < NT; ++k) {
+        const int      t    = T0 + k;
+        const float    sidx = fminf(fmaxf(fmaf(v[c], c_demod.inv_width[t], c_demod.half_n[t]), 0.0f), c_demod.n_minus_1_f[t]);
+        const uint32_t bits = __float_as_uint(__fadd_rd(sidx, 8388608.0f));
+        float2         si;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(si.x), "=f"(si.y) : "r"(tab_addr + 128u * t + ((bits & 15u) << 3)));
+        float r = __fmul_rn(fmaf(si.x, v[c], si.y), rcp[s]);
+        r       = live ? r : 0.0f;
+        const float y = fminf(fmaxf(__fmul_rn(6.0f, r), -120.0f), 120.0f);
+        z[s][2 * k + c] = __float_as_uint(__fadd_rn(y, 12582912.0f));
+      }
+    }
+  }
+#pragma unroll
+  for (int word = 0; word < 2 * NT; ++word) {
+    uint32_t b[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int byte = 4 * word + q;
+      b[q]           = z[byte / (2 * NT)][byte % (2 * NT)];
+    }
+    w[word] = __byte_perm(__byte_perm(b[0], b[1], 0x0040), __byte_perm(b[2], b[3], 0x0040), 0x5410);
+  }
+}
 
 // One symbol of 64QAM (T0 = 0, NT = 3) or 256QAM (T0 = 3, NT = 4): q[2 k], q[2 k + 1] = bits 2k, 2k + 1.
 template <int T0, int NT>
@@ -201,37 +245,56 @@ __device__ __forceinline__ void demod_qam16(int (&q)[8], float re, float im, flo
 
 // ---- scrambling sequence ----------------------------------------------------------------------------------------------------
 // State s of an LFSR at position p: bit i = x(p + i), 31 bits. Returns M^pos s, computed by the 31 low lanes of a warp.
-__device__ __forceinline__ uint32_t prg_jump(uint32_t s, uint32_t pos, int lfsr, int lane)
+__device__ __forceinline__ uint32_t prg_jump(const uint32_t (*jump)[PDC_DEMOD_JUMP_BITS][32], uint32_t s, uint32_t pos,
+                                             int lfsr, int lane)
 {
   for (int j = 0; j < PDC_DEMOD_JUMP_BITS && (pos >> j) != 0; ++j) {
     if ((pos >> j) & 1u) {
-      const uint32_t row = d_prg_jump[lfsr][j][lane];
+      const uint32_t row = jump[lfsr][j][lane];
       s                  = __ballot_sync(0xffffffffu, (__popc(row & s) & 1) != 0) & 0x7fffffffu;
     }
   }
   return s;
 }
 // Word l of the sequence that starts at the position of state s: bits 32 l .. 32 l + 31.
-__device__ __forceinline__ uint32_t prg_word(uint32_t s, int lfsr, int lane)
+__device__ __forceinline__ uint32_t prg_word(const uint32_t (*word)[31][32], uint32_t s, int lfsr, int lane)
 {
   uint32_t t = 0;
 #pragma unroll
   for (int r = 0; r < 31; ++r) {
-    t |= (uint32_t)(__popc(d_prg_word[lfsr][r][lane] & s) & 1) << r;
+    t |= (uint32_t)(__popc(word[lfsr][r][lane] & s) & 1) << r;
   }
   const uint32_t taps = lfsr ? 0xfu : 0x9u;
   return t | ((uint32_t)(__popc(t & taps) & 1) << 31);
 }
-// Fills seq[0 .. nwords) with the scrambling sequence from bit `pos` on (LSB of a word first); one warp.
-__device__ __forceinline__ void prg_generate(uint32_t* seq, uint32_t* w1, uint32_t* w2, int nwords, uint32_t c_init,
-                                             uint32_t pos, int lane)
+// What the sequence warp remembers between chunks: w1 / w2 hold `n` words of the two LFSR sequences from bit `start` on.
+struct prg_history {
+  uint32_t c_init, start;
+  int      n;
+};
+// Fills seq[0 .. nwords) with the scrambling sequence from bit `pos` on (LSB of a word first); one warp. If the words kept
+// from the previous chunk reach 31 words past `pos` (the next chunk of the same codeword: consecutive chunks, and consecutive
+// OFDM symbols, continue the sequence), the recurrence simply carries on from them; otherwise both LFSRs jump.
+__device__ __forceinline__ void prg_generate(const uint32_t (*jump)[PDC_DEMOD_JUMP_BITS][32], const uint32_t (*word)[31][32],
+                                             uint32_t* seq, uint32_t* w1, uint32_t* w2, int nwords, uint32_t c_init,
+                                             uint32_t pos, int lane, prg_history& h)
 {
-  const uint32_t s1 = prg_jump(1u, 1600u + pos, 0, lane);
-  const uint32_t s2 = prg_jump(c_init & 0x7fffffffu, 1600u + pos, 1, lane);
-  w1[lane] = prg_word(s1, 0, lane);
-  w2[lane] = prg_word(s2, 1, lane);
+  const uint32_t d = pos - h.start;
+  if (h.n != 0 && h.c_init == c_init && pos >= h.start && (d & 31u) == 0 && (int)(d >> 5) + 32 <= h.n) {
+    const int      k = (int)(d >> 5);
+    const uint32_t a = w1[k + lane], b = w2[k + lane];
+    __syncwarp();
+    w1[lane] = a, w2[lane] = b;
+  } else {
+    const uint32_t s1 = prg_jump(jump, 1u, 1600u + pos, 0, lane);
+    const uint32_t s2 = prg_jump(jump, c_init & 0x7fffffffu, 1600u + pos, 1, lane);
+    w1[lane] = prg_word(word, s1, 0, lane);
+    w2[lane] = prg_word(word, s2, 1, lane);
+  }
   __syncwarp();
-  for (int base = 32; base < nwords; base += 28) {
+  // 32 words more than the chunk needs: the seed of the next one.
+  const int total = nwords + 32;
+  for (int base = 32; base < total; base += 28) {
     if (lane < 28) {
       const int j   = base + lane - 31;
       w1[base + lane] = w1[j + 3] ^ w1[j];
@@ -242,6 +305,8 @@ __device__ __forceinline__ void prg_generate(uint32_t* seq, uint32_t* w1, uint32
   for (int j = lane; j < nwords; j += 32) {
     seq[j] = w1[j] ^ w2[j];
   }
+  h.c_init = c_init, h.start = pos;
+  h.n      = 32 + ((total - 32 + 27) / 28) * 28;
 }
 
 // Negates the bytes of x whose bit in the low nibble of `bits` is set (byte k <-> bit k): -x = (x ^ 0xff) + 1 per byte.
@@ -252,15 +317,27 @@ __device__ __forceinline__ uint32_t negate_bytes(uint32_t x, uint32_t bits)
   return ((a & 0x7f7f7f7fu) + one) ^ (a & 0x80808080u);
 }
 
+// Named barriers of the producer / consumer pipeline: ids 1, 2 = "sequence buffer b is full", 3, 4 = "buffer b is free again".
+__device__ __forceinline__ void bar_sync(int id)
+{
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(PDC_DEMOD_THREADS) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id)
+{
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "n"(PDC_DEMOD_THREADS) : "memory");
+}
+
 struct pdc_demod_chunk {
   uint32_t seg;
   uint32_t first; // first symbol of the chunk within its segment
 };
 
+// Arithmetic first, one CTA barrier (the scrambling words of warp 0 are complete), then sign flips and stores: warp 0's
+// sequence generation overlaps the other warps' arithmetic instead of preceding it.
 template <int MOD>
 __device__ __forceinline__ void demod_chunk(const pdc_demod_seg& sg, uint32_t first, const float2* __restrict__ symbols,
                                             const float* __restrict__ noise, int8_t* __restrict__ llrs,
-                                            const float2 (*tab)[16], const uint32_t* seq, bool descramble, int tid)
+                                            const float2 (*tab)[16], const uint32_t* seq, bool descramble, int tid, int buf)
 {
   constexpr int QM   = (MOD == 0) ? 1 : MOD;
   constexpr int B512 = (MOD == 6) ? 32 : ((MOD == 8) ? 8 : 0);
@@ -269,10 +346,7 @@ __device__ __forceinline__ void demod_chunk(const pdc_demod_seg& sg, uint32_t fi
   const uint32_t end512 = B512 ? (nsym / B512) * B512 : 0u;
   const uint32_t end256 = B256 ? (nsym / B256) * B256 : 0u;
   const uint32_t i0   = first + 4u * (uint32_t)tid;
-  if (i0 >= nsym) {
-    return;
-  }
-  const uint32_t nvalid = min(4u, nsym - i0);
+  const uint32_t nvalid = (i0 < nsym) ? min(4u, nsym - i0) : 0u;
   const size_t   g      = (size_t)sg.sym_offset + i0;
 
   float re[4], im[4], nv[4];
@@ -297,8 +371,24 @@ __device__ __forceinline__ void demod_chunk(const pdc_demod_seg& sg, uint32_t fi
   for (int k = 0; k < QM; ++k) {
     w[k] = 0;
   }
+  bool done = false;
+  if constexpr (MOD == 6 || MOD == 8) {
+    if (nvalid == 4 && i0 + 3 < end512) {
+      float rcp[4];
+      bool  ok = true;
 #pragma unroll
-  for (int s = 0; s < 4; ++s) {
+      for (int s = 0; s < 4; ++s) {
+        rcp[s] = (nv[s] > 0.0f) ? __fdiv_rn(1.0f, nv[s]) : 0.0f;
+        ok     = ok && (fabsf(re[s]) < 1e8f) && (fabsf(im[s]) < 1e8f) && (rcp[s] < 3.0e38f);
+      }
+      if (ok) {
+        demod_interval_fast<(MOD == 6) ? 0 : 3, QM / 2>(w, re, im, rcp, (uint32_t)__cvta_generic_to_shared(tab));
+        done = true;
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < 4 && !done; ++s) {
     const uint32_t i    = i0 + s;
     const int      path = (B512 != 0 && i < end512) ? PATH_AVX512 : ((B256 != 0 && i < end256) ? PATH_AVX2 : PATH_SCALAR);
     int            q[8];
@@ -322,9 +412,14 @@ __device__ __forceinline__ void demod_chunk(const pdc_demod_seg& sg, uint32_t fi
     }
   }
 
+  bar_sync(1 + buf); // the producer warp has filled seq
+  const uint32_t b0 = 4u * QM * (uint32_t)tid;
+  const uint32_t lo = seq[b0 >> 5], hi = seq[(b0 >> 5) + 1];
+  bar_arrive(3 + buf); // ... and this thread has read its part of it
+  if (nvalid == 0) {
+    return;
+  }
   if (descramble) {
-    const uint32_t b0 = 4u * QM * (uint32_t)tid;
-    const uint32_t lo = seq[b0 >> 5], hi = seq[(b0 >> 5) + 1];
     const uint32_t c  = __funnelshift_r(lo, hi, b0 & 31u);
 #pragma unroll
     for (int k = 0; k < QM; ++k) {
@@ -370,44 +465,72 @@ __device__ __forceinline__ void demod_chunk(const pdc_demod_seg& sg, uint32_t fi
   }
 }
 
-__global__ void __launch_bounds__(PDC_DEMOD_THREADS)
-    pdc_demod_kernel(const pdc_demod_seg* __restrict__ segs, const pdc_demod_chunk* __restrict__ chunks,
+// Persistent CTAs (as many as fit the device at once), each walking a contiguous range of the chunk list. The ninth warp runs
+// one chunk AHEAD of the eight arithmetic warps through two sequence buffers, so the latency of its dependent chain (jump,
+// bootstrap, recurrence) overlaps the arithmetic of the previous chunk instead of adding to every chunk's lifetime.
+__global__ void __launch_bounds__(PDC_DEMOD_THREADS, 4)
+    pdc_demod_kernel(const pdc_demod_seg* __restrict__ segs, const pdc_demod_chunk* __restrict__ chunks, uint32_t nchunks,
                      const float2* __restrict__ symbols, const float* __restrict__ noise, int8_t* __restrict__ llrs)
 {
   __shared__ float2   s_tab[7][16];
-  __shared__ uint32_t s_seq[260], s_w1[292], s_w2[292];
+  __shared__ uint32_t s_seq[2][260], s_w1[320], s_w2[320];
+  // The jump matrices live in shared memory for the lifetime of the persistent CTA: the dependent chain of the sequence warp
+  // is one load per step, and from HBM-streaming L1 / L2 that load was the whole cost of a chunk (8.5 us per chunk measured).
+  __shared__ uint32_t s_jump[2][PDC_DEMOD_JUMP_BITS][32], s_word[2][31][32];
   const int           tid = threadIdx.x;
-  const pdc_demod_chunk ch = chunks[blockIdx.x];
-  const pdc_demod_seg   sg = segs[ch.seg];
   if (tid < 7 * 16) {
     s_tab[tid >> 4][tid & 15] = c_demod.interval[tid >> 4][tid & 15];
   }
-  const int  qm         = (sg.mod == 0) ? 1 : sg.mod;
-  const bool descramble = (sg.flags & PDC_DEMOD_F_DESCRAMBLE) != 0;
-  if (descramble && tid < 32) {
-    // 1024 Qm bits for the chunk, one word more for the unaligned window of the last thread.
-    prg_generate(s_seq, s_w1, s_w2, 32 * qm + 1, sg.c_init, sg.scramble_offset + ch.first * (uint32_t)qm, tid);
+  for (int q = tid; q < 2 * PDC_DEMOD_JUMP_BITS * 32; q += PDC_DEMOD_THREADS) {
+    (&s_jump[0][0][0])[q] = (&d_prg_jump[0][0][0])[q];
+  }
+  for (int q = tid; q < 2 * 31 * 32; q += PDC_DEMOD_THREADS) {
+    (&s_word[0][0][0])[q] = (&d_prg_word[0][0][0])[q];
   }
   __syncthreads();
-  switch (sg.mod) {
-    case 0:
-      demod_chunk<0>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq, descramble, tid);
-      break;
-    case 1:
-      demod_chunk<1>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq, descramble, tid);
-      break;
-    case 2:
-      demod_chunk<2>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq, descramble, tid);
-      break;
-    case 4:
-      demod_chunk<4>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq, descramble, tid);
-      break;
-    case 6:
-      demod_chunk<6>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq, descramble, tid);
-      break;
-    default:
-      demod_chunk<8>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq, descramble, tid);
-      break;
+  // A contiguous range of the chunk list per CTA: consecutive chunks of a codeword continue the scrambling sequence.
+  const uint32_t per = nchunks / gridDim.x, rem = nchunks % gridDim.x;
+  const uint32_t c0  = blockIdx.x * per + min(blockIdx.x, rem), c1 = c0 + per + (blockIdx.x < rem ? 1u : 0u);
+  prg_history    hist;
+  hist.c_init = 0, hist.start = 0, hist.n = 0;
+  int it = 0;
+  for (uint32_t c = c0; c < c1; ++c, ++it) {
+    const int             buf = it & 1;
+    const pdc_demod_chunk ch  = chunks[c];
+    const pdc_demod_seg   sg  = segs[ch.seg];
+    const int             qm  = (sg.mod == 0) ? 1 : sg.mod;
+    const bool            descramble = (sg.flags & PDC_DEMOD_F_DESCRAMBLE) != 0;
+    if (tid >= 256) {
+      if (it >= 2) {
+        bar_sync(3 + buf); // every arithmetic thread has read the words of two chunks ago
+      }
+      if (descramble) {
+        // 1024 Qm sequence bits, one word more for the unaligned window of the last thread.
+        prg_generate(s_jump, s_word, s_seq[buf], s_w1, s_w2, 32 * qm + 1, sg.c_init, sg.scramble_offset + ch.first * (uint32_t)qm, tid - 256, hist);
+      }
+      bar_arrive(1 + buf);
+      continue;
+    }
+    switch (sg.mod) {
+      case 0:
+        demod_chunk<0>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq[buf], descramble, tid, buf);
+        break;
+      case 1:
+        demod_chunk<1>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq[buf], descramble, tid, buf);
+        break;
+      case 2:
+        demod_chunk<2>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq[buf], descramble, tid, buf);
+        break;
+      case 4:
+        demod_chunk<4>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq[buf], descramble, tid, buf);
+        break;
+      case 6:
+        demod_chunk<6>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq[buf], descramble, tid, buf);
+        break;
+      default:
+        demod_chunk<8>(sg, ch.first, symbols, noise, llrs, s_tab, s_seq[buf], descramble, tid, buf);
+        break;
+    }
   }
 }
 
@@ -468,6 +591,7 @@ extern "C" cudaError_t pdc_demod_init_device()
     t.inv_width[k]   = 1.0f / t.width[k];
     t.half_n[k]      = (float)(nint[k] / 2);
     t.n_minus_1[k]   = nint[k] - 1;
+    t.n_minus_1_f[k] = (float)(nint[k] - 1);
     for (int i = 0; i != 16; ++i) {
       t.interval[k][i] = (i < nint[k]) ? make_float2((float)slope_k[k][i] * unit, (float)icpt_n[k][i] / den)
                                        : make_float2(0.f, 0.f);
@@ -514,7 +638,16 @@ extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void*
   if (nchunks == 0) {
     return cudaSuccess;
   }
-  pdc_demod_kernel<<<nchunks, PDC_DEMOD_THREADS, 0, stream>>>(d_segs, reinterpret_cast<const pdc_demod_chunk*>(d_chunks),
-                                                              reinterpret_cast<const float2*>(d_symbols), d_noise, d_llrs);
+  static int resident = 0; // persistent grid: CTAs that fit the device at once
+  if (resident == 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pdc_demod_kernel, PDC_DEMOD_THREADS, 0);
+    resident = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  const uint32_t grid = nchunks < (uint32_t)resident ? nchunks : (uint32_t)resident;
+  pdc_demod_kernel<<<grid, PDC_DEMOD_THREADS, 0, stream>>>(d_segs, reinterpret_cast<const pdc_demod_chunk*>(d_chunks), nchunks,
+                                                           reinterpret_cast<const float2*>(d_symbols), d_noise, d_llrs);
   return cudaGetLastError();
 }
