@@ -8,6 +8,7 @@
 //           block assembly + CRC24A on the device, in place of the reference's TB decoders.
 // Driven from Python (tests/test_adapters.py) through a small C ABI; the stimulus comes from tools/stimulus.
 #include "../../srsran_project_b200/adapters/channel_coding_factories_cuda.h"
+#include "../../srsran_project_b200/adapters/channel_modulation_factories_cuda.h"
 #include "../../srsran_project_b200/adapters/hw_accelerator_pusch_dec_cuda.h"
 #include "../../srsran_project_b200/adapters/pusch_decoder_cuda.h"
 #include "crc_calculator_clmul_impl.h"
@@ -237,6 +238,48 @@ int adt_decode_tb(void*         handle,
   stats[3]                      = any ? r.ldpc_decoder_stats.get_min() : 0;
   stats[4]                      = any ? r.ldpc_decoder_stats.get_max() : 0;
   stats[5]                      = any ? static_cast<int64_t>(r.ldpc_decoder_stats.get_mean() * 1000.0 + 0.5) : 0;
+  return 0;
+}
+
+// The CUDA demodulation_mapper adapter behind the reference's interface: one demodulate_soft call.
+// mod: 0 pi/2-BPSK, 1 BPSK, 2, 4, 6, 8. Returns 0, or -1 if the factory could not be created (no device).
+int adt_demodulate_soft(int8_t* llrs, const float* symbols_ri, const float* noise_vars, unsigned nof_symbols, int mod)
+{
+  static std::shared_ptr<demodulation_mapper_factory> factory;
+  static std::unique_ptr<demodulation_mapper>         mapper;
+  try {
+    if (!factory) {
+      factory = create_demodulation_mapper_factory_cuda();
+      mapper  = factory->create();
+    }
+  } catch (const std::exception&) {
+    return -1;
+  }
+  modulation_scheme scheme = modulation_scheme::QAM256;
+  switch (mod) {
+    case 0:
+      scheme = modulation_scheme::PI_2_BPSK;
+      break;
+    case 1:
+      scheme = modulation_scheme::BPSK;
+      break;
+    case 2:
+      scheme = modulation_scheme::QPSK;
+      break;
+    case 4:
+      scheme = modulation_scheme::QAM16;
+      break;
+    case 6:
+      scheme = modulation_scheme::QAM64;
+      break;
+    default:
+      break;
+  }
+  const unsigned qm = (mod == 0) ? 1 : static_cast<unsigned>(mod);
+  mapper->demodulate_soft(span<log_likelihood_ratio>(reinterpret_cast<log_likelihood_ratio*>(llrs), nof_symbols * qm),
+                          span<const cf_t>(reinterpret_cast<const cf_t*>(symbols_ri), nof_symbols),
+                          span<const float>(noise_vars, nof_symbols),
+                          scheme);
   return 0;
 }
 

@@ -121,7 +121,8 @@ def test_adapter_library_exports():
 
     syms = subprocess.run(["nm", "-D", "--defined-only", "-C", ADAPTERS], capture_output=True, text=True).stdout
     for s in ("srsran::create_ldpc_decoder_factory_cuda", "srsran::create_ldpc_rate_dematcher_factory_cuda",
-              "srsran::hal::create_cuda_pusch_dec_acc_factory", "srsran::create_pusch_decoder_factory_cuda"):
+              "srsran::hal::create_cuda_pusch_dec_acc_factory", "srsran::create_pusch_decoder_factory_cuda",
+              "srsran::create_demodulation_mapper_factory_cuda"):
         assert s in syms, s
 
 
@@ -146,3 +147,19 @@ def test_cuda_adapters_match_reference_decoder(mode, external, generic):
     finally:
         ref.close()
         dut.close()
+
+
+@pytest.mark.gpu
+def test_cuda_demodulation_mapper_adapter_reproduces_the_golden_calls():
+    """srsran::demodulation_mapper implemented over pdc_demodulate (adapters/channel_modulation_factories_cuda.cpp), driven
+    through the reference's interface, against the calls recorded from the compiled reference (tests/golden/demod_v1.npz)."""
+    from tests.demod_cases import golden_calls
+
+    lib = _lib()
+    for name, mod, sym, nv, want in golden_calls():
+        sym, nv = np.ascontiguousarray(sym, np.float32), np.ascontiguousarray(nv, np.float32)
+        got = np.zeros(want.size, np.int8)
+        rc = lib.adt_demodulate_soft(ctypes.c_void_p(got.ctypes.data), ctypes.c_void_p(sym.ctypes.data),
+                                     ctypes.c_void_p(nv.ctypes.data), ctypes.c_uint(nv.size), ctypes.c_int(mod))
+        assert rc == 0
+        assert np.array_equal(got, want), name
