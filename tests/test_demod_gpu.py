@@ -8,6 +8,7 @@ import pytest
 from oracle import pyoracle
 from tests.demod_cases import golden_calls, golden_scrambling
 from tools import demod_stimulus as S
+from tools.demod_stimulus import config2_transmission
 
 pytestmark = pytest.mark.gpu
 
@@ -119,54 +120,6 @@ def test_contract_violations(acc):
         acc.demodulate(segs, np.zeros((8, 2), np.float32), np.ones(8, np.float32), 63)
     with pytest.raises(B.PdcError):  # input array too small
         acc.demodulate(segs, np.zeros((7, 2), np.float32), np.ones(7, np.float32), 64)
-
-
-def config2_transmission(n_tbs, sigma2, seed):
-    """n_tbs config-2 transport blocks (273 PRB, 4 layers, 256QAM): scrambled, modulated, noisy equaliser outputs in the
-    order the demodulator sees them (13 data OFDM symbols of 13104 symbols each), plus the descriptors of every stage."""
-    from srsran_project_b200 import binding as B
-    from tools import stimulus as T
-
-    c = T.CONFIG2
-    seg = T.segmentation(c["bg"], c["tbs"])
-    Es = T.rm_lengths(seg["C"], c["G"], c["nof_layers"], c["Qm"])
-    orc = pyoracle.DemodOracle()
-    nsym_tb, per_call = c["G"] // 8, 273 * 12 * 4
-    assert nsym_tb % per_call == 0
-    symbols, noise = np.zeros((n_tbs * nsym_tb, 2), np.float32), np.zeros(n_tbs * nsym_tb, np.float32)
-    segs = np.zeros(n_tbs * (nsym_tb // per_call), B.DEMOD_SEG_DTYPE)
-    tbs_packed = []
-    r = np.random.default_rng(seed)
-    for t in range(n_tbs):
-        tb = r.integers(0, 2, c["tbs"], dtype=np.uint8)
-        tbs_packed.append(np.packbits(tb))
-        _, bits, _ = T.tb_encode(c["bg"], c["tbs"], tb, c["rv"], c["Qm"], 0, c["nof_layers"], c["G"])
-        c_init = ((0x4601 + t) << 15) + 41 + t
-        tx = bits ^ orc.prg_bits(c["G"], c_init, 0)
-        z = S.modulate(tx, 8)
-        z = z + (r.normal(0, np.sqrt(sigma2 / 2), z.size) + 1j * r.normal(0, np.sqrt(sigma2 / 2), z.size)).astype(np.complex64)
-        symbols[t * nsym_tb:(t + 1) * nsym_tb, 0], symbols[t * nsym_tb:(t + 1) * nsym_tb, 1] = z.real, z.imag
-        noise[t * nsym_tb:(t + 1) * nsym_tb] = np.float32(sigma2)
-        for k in range(nsym_tb // per_call):
-            s = segs[t * (nsym_tb // per_call) + k]
-            s["sym_offset"], s["llr_offset"] = t * nsym_tb + k * per_call, (t * nsym_tb + k * per_call) * 8
-            s["nof_symbols"], s["mod"], s["flags"] = per_call, 8, B.PDC_DEMOD_F_DESCRAMBLE
-            s["c_init"], s["scramble_offset"] = c_init, k * per_call * 8
-    descs = B.make_descs(n_tbs * seg["C"])
-    tbd = np.zeros(n_tbs, B.TB_DESC_DTYPE)
-    stride = (seg["K"] + 31) // 32 * 4
-    tb_stride = (c["tbs"] // 8 + 3) // 4 * 4  # pdc_tb_desc.tb_offset must be a multiple of 4
-    for t in range(n_tbs):
-        o = t * c["G"]
-        for q in range(seg["C"]):
-            d = descs[t * seg["C"] + q]
-            d["bg"], d["Z"], d["Qm"], d["rv"], d["crc_type"], d["max_iter"] = 1, seg["Z"], 8, 0, pyoracle.CRC24B, 6
-            d["flags"], d["E"], d["nof_filler"] = B.PDC_F_NEW_DATA | B.PDC_F_EARLY_STOP, Es[q], seg["F"]
-            d["llr_offset"], d["soft_offset"], d["out_offset"] = o, (t * seg["C"] + q) * 25344, (t * seg["C"] + q) * stride
-            o += Es[q]
-        tbd[t]["first_cb"], tbd[t]["nof_cbs"], tbd[t]["tbs_bits"], tbd[t]["tb_offset"] = t * seg["C"], seg["C"], c["tbs"], t * tb_stride
-    return dict(symbols=symbols, noise=noise, segs=segs, descs=descs, tbd=tbd, tbs=tbs_packed, G=c["G"], C=seg["C"],
-                stride=stride, tbs_bytes=c["tbs"] // 8, tb_stride=tb_stride)
 
 
 def test_config2_symbols_to_transport_blocks_on_the_device(acc, orc):

@@ -24,7 +24,7 @@ if ROOT not in sys.path:
 
 def build(n_tbs, sigma2=0.0016, seed=21, distinct=4):
     """`distinct` different transport blocks tiled to n_tbs (host preparation time; the device sees n_tbs full inputs)."""
-    from tests.test_demod_gpu import config2_transmission
+    from tools.demod_stimulus import config2_transmission
 
     base = config2_transmission(min(distinct, n_tbs), sigma2, seed)
     if n_tbs <= distinct:
