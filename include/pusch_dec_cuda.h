@@ -17,6 +17,8 @@
  *   srsran::demodulation_mapper::demodulate_soft include/srsran/phy/upper/channel_modulation/demodulation_mapper.h:66-69
  *     + revert_scrambling                        lib/phy/upper/channel_processors/pusch/pusch_demodulator_impl.cpp:60-222,
  *                                                :261-262,:397-405 (the LLR producers: the pdc_demodulate* entry points)
+ *   srsran::pdsch_encoder::encode                include/srsran/phy/upper/channel_processors/pdsch/pdsch_encoder.h:73
+ *                                                (the downlink mirror: the pdc_pdsch_encode* entry points)
  *
  * Conventions: plain pointers and sizes only; every function returns a pdc_status (0 = ok) and never throws or
  * aborts; a context is thread-safe; there is NO CPU fallback — without a CUDA device pdc_create fails.
@@ -31,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 3
+#define PDC_ABI_VERSION 4
 
 typedef enum {
   PDC_OK               = 0,
@@ -197,6 +199,29 @@ pdc_status pdc_demodulate_device(pdc_ctx* ctx, const pdc_demod_seg* segs_host, u
  * nof_symbols / llr_bytes: sizes of the host arrays (every segment must lie inside). */
 pdc_status pdc_demodulate(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, const float* symbols, const float* noise_vars,
                           size_t nof_symbols, int8_t* llrs, size_t llr_bytes);
+
+/* --- PDSCH transport-block encoder (the downlink mirror) ----------------------------------------------------
+ * pdsch_encoder::encode (pdsch_encoder.h:48-73, pdsch_encoder_impl.cpp:31-80): TB CRC attachment, segmentation, code-block
+ * CRC, LDPC encoding, rate matching + bit interleaving, code-block concatenation. One descriptor per transport block carries
+ * pdsch_encoder::configuration; the segmentation (C, Z, K', fillers, per-code-block rate-matched lengths: ldpc.h:128-214,
+ * ldpc_segmenter_helpers.h:82-100) is derived inside. The codeword comes back as the reference delivers it: one bit per
+ * byte, nof_ch_symbols * Qm bytes (nof_ch_symbols counts the resource elements of every layer, as in the reference). */
+typedef struct {
+  uint8_t  bg;             /* 1 | 2 */
+  uint8_t  Qm;             /* 1, 2, 4, 6, 8 (modulation_scheme as bits per symbol) */
+  uint8_t  rv;             /* 0..3 */
+  uint8_t  nof_layers;     /* 1..4 */
+  uint32_t tbs_bits;       /* transport block size in bits (multiple of 8) */
+  uint32_t nof_ch_symbols; /* channel symbols the transport block is mapped to, all layers together (multiple of nof_layers) */
+  uint32_t Nref;           /* limited-buffer rate matching length, 0 = none */
+  uint64_t tb_offset;      /* byte offset of the packed transport block (MSB first) in the input buffer */
+  uint64_t cw_offset;      /* byte offset of the codeword in the output buffer */
+} pdc_pdsch_tb_desc;
+
+pdc_status pdc_pdsch_encode(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t n, const uint8_t* tb_bytes, size_t tb_len,
+                            uint8_t* codewords, size_t cw_len); /* host buffers, returns when the codewords are there */
+pdc_status pdc_pdsch_encode_device(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs_host, uint32_t n, const uint8_t* d_tb_bytes,
+                                   uint8_t* d_codewords, void* stream); /* device pointers, asynchronous on stream */
 
 /* --- HARQ arena (ext_harq_buffer_context_repository.h:36-107 / free_harq_context_entry) --------------------------- */
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot);                               /* zero-fills the slot */

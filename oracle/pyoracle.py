@@ -165,6 +165,38 @@ class DemodReference:
         return _prg_call(self.lib, "ref", n, c_init, offset)
 
 
+class PdschEncReference:
+    """The UNMODIFIED pdsch_encoder_impl (+ ldpc_segmenter_tx_impl, ldpc_encoder_avx2 | generic, ldpc_rate_matcher_impl) behind
+    oracle/ref_shim_pdsch.cpp."""
+
+    def __init__(self, generic=False):
+        self.lib = ctypes.CDLL(REF_SO)
+        self.generic = 1 if generic else 0
+
+    def encode(self, tb_packed, tbs_bits, bg, rv, Qm, Nref, nof_layers, nof_ch_symbols):
+        tb_packed = np.ascontiguousarray(tb_packed, np.uint8)
+        cw = np.zeros(nof_ch_symbols * Qm, np.uint8)
+        rc = self.lib.ref_pdsch_encode(ctypes.c_void_p(cw.ctypes.data), ctypes.c_void_p(tb_packed.ctypes.data),
+                                       ctypes.c_uint(tbs_bits), ctypes.c_int(bg), ctypes.c_uint(rv), ctypes.c_uint(Qm),
+                                       ctypes.c_uint(Nref), ctypes.c_uint(nof_layers), ctypes.c_uint(nof_ch_symbols),
+                                       ctypes.c_int(self.generic))
+        assert rc == 0
+        return cw
+
+
+class PdschEncOracle:
+    """The TX-chain restatement (TB CRC, segmentation, CB CRC, LDPC encoding, rate matching, concatenation). It lives in
+    tools/stimulus/pdc_stimulus.c because it doubles as the stimulus generator of the decoder tests; as the oracle of the PDSCH
+    encoder it is pinned against the compiled pdsch_encoder_impl by tests/test_enc_oracle.py."""
+
+    def encode(self, tb_packed, tbs_bits, bg, rv, Qm, Nref, nof_layers, nof_ch_symbols):
+        from tools import stimulus as S
+
+        tb_bits = np.unpackbits(np.ascontiguousarray(tb_packed, np.uint8))[:tbs_bits]
+        _, bits, _ = S.tb_encode(bg, tbs_bits, tb_bits, rv, Qm, Nref, nof_layers, nof_ch_symbols * Qm)
+        return bits
+
+
 def ref_available():
     return os.path.exists(REF_SO)
 

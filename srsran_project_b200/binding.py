@@ -52,6 +52,9 @@ TB_RESULT_DTYPE = np.dtype([("tb_crc_ok", np.uint8), ("written", np.uint8), ("no
 DEMOD_SEG_DTYPE = np.dtype([("sym_offset", np.uint64), ("llr_offset", np.uint64), ("nof_symbols", np.uint32),
                             ("c_init", np.uint32), ("scramble_offset", np.uint32), ("mod", np.uint8), ("flags", np.uint8),
                             ("reserved", np.uint16)])  # pdc_demod_seg
+PDSCH_TB_DTYPE = np.dtype([("bg", np.uint8), ("Qm", np.uint8), ("rv", np.uint8), ("nof_layers", np.uint8),
+                           ("tbs_bits", np.uint32), ("nof_ch_symbols", np.uint32), ("Nref", np.uint32),
+                           ("tb_offset", np.uint64), ("cw_offset", np.uint64)])  # pdc_pdsch_tb_desc
 PDC_MOD_PI2_BPSK, PDC_MOD_BPSK, PDC_MOD_QPSK, PDC_MOD_QAM16, PDC_MOD_QAM64, PDC_MOD_QAM256 = 0, 1, 2, 4, 6, 8
 PDC_DEMOD_F_DESCRAMBLE = 0x01
 assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
@@ -100,6 +103,8 @@ def load_library():
     lib.pdc_decode_device_tbs.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, vp, vp, vp, vp, vp, vp]
     lib.pdc_demodulate_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp, vp]
     lib.pdc_demodulate.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
+    lib.pdc_pdsch_encode.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
+    lib.pdc_pdsch_encode_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp]
     lib.pdc_harq_free.argtypes = [vp, ctypes.c_int32]
     lib.pdc_harq_read.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
@@ -116,7 +121,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
-                    "pdc_demodulate_device", "pdc_demodulate", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
+                    "pdc_demodulate_device", "pdc_demodulate", "pdc_pdsch_encode", "pdc_pdsch_encode_device", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
                     "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
 
 
@@ -228,6 +233,18 @@ class PuschDecCuda:
     def demodulate_device(self, segs, d_symbols_ptr, d_noise_ptr, d_llrs_ptr, stream_ptr=None):
         self._check(self.lib.pdc_demodulate_device(self.h, segs.ctypes.data, segs.size, d_symbols_ptr, d_noise_ptr,
                                                    d_llrs_ptr, stream_ptr))
+
+    # --- PDSCH transport-block encoder (downlink mirror) -------------------------------------------------------------------
+    def pdsch_encode(self, tbs, tb_bytes, cw_len):
+        """Host-buffer entry: tb_bytes = packed transport blocks, returns the codewords (one bit per byte)."""
+        tb_bytes = np.ascontiguousarray(tb_bytes, np.uint8)
+        cw = np.zeros(cw_len, np.uint8)
+        self._check(self.lib.pdc_pdsch_encode(self.h, tbs.ctypes.data, tbs.size, tb_bytes.ctypes.data, tb_bytes.size,
+                                              cw.ctypes.data, cw.size))
+        return cw
+
+    def pdsch_encode_device(self, tbs, d_tb_ptr, d_cw_ptr, stream_ptr=None):
+        self._check(self.lib.pdc_pdsch_encode_device(self.h, tbs.ctypes.data, tbs.size, d_tb_ptr, d_cw_ptr, stream_ptr))
 
     # --- HARQ arena ------------------------------------------------------------------------------------------------
     def harq_free(self, slot):

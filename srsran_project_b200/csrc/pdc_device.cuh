@@ -27,6 +27,22 @@ struct pdc_launch_params {
   int               n;
 };
 
+// One code block of the PDSCH encoder (pdc_kernel_enc.cuh), planned on the host (pdc_runtime.cu: enc_plan).
+struct pdc_dev_enc_cb {
+  const uint8_t* tb;        // packed transport block (MSB first)
+  uint8_t*       out;       // this code block's E bytes of the codeword (one bit per byte)
+  uint32_t*      tb_crc;    // the transport block's CRC accumulator (xor of the code blocks' shares)
+  uint32_t       tbs_bits;  // transport block size
+  uint32_t       first_bit; // first TB bit (of payload ++ TB CRC ++ padding) this code block carries
+  uint32_t       nof_bits;  // how many it carries: K' - CB CRC length
+  uint32_t       E, Nref, nof_filler;
+  uint16_t       Z, graph_idx;
+  uint8_t        bg, Qm, rv, tb_crc_type; // tb_crc_type: PDC_CRC16 | PDC_CRC24A
+  uint8_t        cb_crc;                  // 1: append CRC24B
+  uint8_t        rows_needed;             // parity rows the rate matcher reads (>= 4)
+  uint16_t       reserved;
+};
+
 // Row structure of the two base graphs (degrees and prefix sums), uploaded once per process.
 struct pdc_bg_rows {
   uint16_t start[2][48];

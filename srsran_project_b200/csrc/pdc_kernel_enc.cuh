@@ -1,0 +1,313 @@
+// PDSCH transport-block encoder on the device (the downlink mirror of the decode chain): TB CRC attachment,
+// segmentation, code-block CRC, LDPC encoding, rate matching with bit interleaving and code-block concatenation.
+//
+// What it replaces in the reference:
+//   pdsch_encoder_impl::encode          lib/phy/upper/channel_processors/pdsch/pdsch_encoder_impl.cpp:31-80
+//   ldpc_segmenter_tx_impl              lib/phy/upper/channel_coding/ldpc/ldpc_segmenter_tx_impl.cpp (TB CRC, CB CRC, fillers,
+//                                       zero padding; segment sizes ldpc.h:128-214, rate-matched lengths
+//                                       ldpc_segmenter_helpers.h:82-100)
+//   ldpc_encoder_impl / _generic / _avx2 lib/phy/upper/channel_coding/ldpc/ldpc_encoder_impl.cpp, ldpc_encoder_generic.cpp
+//                                       (systematic bits, the four core parity blocks through the double-diagonal structure,
+//                                       extension parity blocks), TS 38.212 5.3.2
+//   ldpc_rate_matcher_impl              lib/phy/upper/channel_coding/ldpc/ldpc_rate_matcher_impl.cpp (select_bits from the
+//                                       circular buffer skipping the filler window, interleave_bits), TS 38.212 5.4.2
+//
+// Two launches per batch of transport blocks:
+//   pdc_enc_crc_kernel   one CTA per code block: the code block's share of the TB CRC. The CRC is linear: the remainder of the
+//                        whole block is the xor over code blocks of (remainder of the code block's payload) x^(bits that
+//                        follow it, CRC included) mod P; the first factor is a xor of per-bit powers, the second a
+//                        square-and-multiply chain of 24-bit carry-less products. 152 CTAs do in parallel what the
+//                        reference does in one serial pass over 160 KB.
+//   pdc_enc_cb_kernel    one CTA per code block: payload bits (+ TB CRC and zero padding in the last block) -> CB CRC24B ->
+//                        core and extension parity (only the rows the rate matcher will read) -> bit selection and interleaving
+//                        straight into the codeword, one byte per bit as pdsch_encoder::encode delivers it.
+// Bits live one per byte in shared memory: the circulant P^s of a Z-bit block is an index rotation, valid for every one of
+// the 51 lifting sizes. All arithmetic is GF(2): bit-exact by construction where the index algebra is right.
+#pragma once
+#include "pdc_device.cuh"
+
+// x^(2^k) mod P, k < 24, per CRC type (index crc_type - 1).
+__constant__ uint32_t c_enc_xpow2[3][24];
+
+__device__ __forceinline__ uint32_t pdc_crc_poly(int crc_type)
+{
+  return (crc_type == PDC_CRC16) ? 0x11021u : ((crc_type == PDC_CRC24A) ? 0x1864CFBu : 0x1800063u);
+}
+// a(x) b(x) mod P(x) over GF(2).
+__device__ __forceinline__ uint32_t pdc_crc_mulmod(uint32_t a, uint32_t b, int crc_type)
+{
+  const int      order = (crc_type == PDC_CRC16) ? 16 : 24;
+  const uint32_t poly = pdc_crc_poly(crc_type), top = 1u << order;
+  uint32_t       r = 0;
+  for (int i = order - 1; i >= 0; --i) {
+    r <<= 1;
+    if (r & top) {
+      r ^= poly;
+    }
+    if ((b >> i) & 1u) {
+      r ^= a;
+    }
+  }
+  return r;
+}
+// a(x) x^n mod P(x).
+__device__ __forceinline__ uint32_t pdc_crc_shift(uint32_t a, uint32_t n, int crc_type)
+{
+  for (int k = 0; k < 24 && (n >> k) != 0; ++k) {
+    if ((n >> k) & 1u) {
+      a = pdc_crc_mulmod(a, c_enc_xpow2[crc_type - 1][k], crc_type);
+    }
+  }
+  return a;
+}
+
+// Bit n of (payload ++ TB CRC ++ zero padding) of a transport block.
+__device__ __forceinline__ uint32_t pdc_enc_tb_bit(const pdc_dev_enc_cb& cb, uint32_t n, uint32_t tb_crc, int tb_crc_bits)
+{
+  if (n < cb.tbs_bits) {
+    return (cb.tb[n >> 3] >> (7 - (n & 7))) & 1u;
+  }
+  const uint32_t k = n - cb.tbs_bits;
+  return (k < (uint32_t)tb_crc_bits) ? ((tb_crc >> (tb_crc_bits - 1 - k)) & 1u) : 0u;
+}
+
+// XOR of `v` over the CTA; every thread gets the result. scratch: 32 words.
+__device__ __forceinline__ uint32_t pdc_enc_block_xor(uint32_t v, uint32_t* scratch, int tid, int nth)
+{
+  v = __reduce_xor_sync(0xffffffffu, v);
+  __syncthreads();
+  if ((tid & 31) == 0) {
+    scratch[tid >> 5] = v;
+  }
+  __syncthreads();
+  uint32_t r = 0;
+  for (int w = 0; w < (nth >> 5); ++w) {
+    r ^= scratch[w];
+  }
+  return r;
+}
+
+// The code block's share of the TB CRC (ldpc_segmenter_tx_impl: the CRC the segmenter computes before cutting the block).
+__global__ void __launch_bounds__(256) pdc_enc_crc_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ crc_pow)
+{
+  __shared__ uint32_t  scratch[32];
+  const pdc_dev_enc_cb cb  = cbs[blockIdx.x];
+  const int            tid = threadIdx.x, nth = blockDim.x;
+  if (cb.first_bit >= cb.tbs_bits) {
+    return; // nothing of the payload in this code block
+  }
+  const uint32_t  nbits = min(cb.nof_bits, cb.tbs_bits - cb.first_bit); // payload bits carried here
+  const uint32_t* pw    = crc_pow + (size_t)(cb.tb_crc_type - 1) * PDC_CRC_TABLE_LEN;
+  uint32_t        acc   = 0;
+  for (uint32_t n = tid; n < nbits; n += nth) {
+    const uint32_t g = cb.first_bit + n;
+    if ((cb.tb[g >> 3] >> (7 - (g & 7))) & 1u) {
+      acc ^= pw[nbits - 1 - n];
+    }
+  }
+  acc = pdc_enc_block_xor(acc, scratch, tid, nth);
+  if (tid == 0) {
+    const int      order = (cb.tb_crc_type == PDC_CRC16) ? 16 : 24;
+    const uint32_t after = cb.tbs_bits - (cb.first_bit + nbits) + (uint32_t)order;
+    atomicXor(cb.tb_crc, pdc_crc_shift(acc, after, cb.tb_crc_type));
+  }
+}
+
+// cw: (Kb + rows) Z bytes, one bit each: systematic blocks, then parity blocks.
+__global__ void __launch_bounds__(256) pdc_enc_cb_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ graphs,
+                                                         const uint32_t* __restrict__ crc_pow)
+{
+  extern __shared__ __align__(16) unsigned char cw[];
+  __shared__ uint32_t  scratch[32];
+  const pdc_dev_enc_cb cb  = cbs[blockIdx.x];
+  const int            tid = threadIdx.x, nth = blockDim.x;
+  const int            bgi = cb.bg - 1, Z = cb.Z;
+  const int            Kb = (cb.bg == 1) ? 22 : 10, Nfull = (cb.bg == 1) ? 68 : 52, M = Nfull - Kb;
+  const int            rows = min((int)cb.rows_needed, M);
+  const uint32_t*      gr   = graphs + (size_t)cb.graph_idx * PDC_GRAPH_STRIDE;
+  const int            K    = Kb * Z;
+
+  // ---- message: payload (++ TB CRC ++ padding) ++ CB CRC ++ fillers (zero while encoding) -------------------------------------
+  const int      tb_crc_bits = (cb.tb_crc_type == PDC_CRC16) ? 16 : 24;
+  const uint32_t tb_crc      = *cb.tb_crc;
+  for (int n = tid; n < (Kb + rows) * Z; n += nth) {
+    cw[n] = (n < (int)cb.nof_bits) ? (unsigned char)pdc_enc_tb_bit(cb, cb.first_bit + (uint32_t)n, tb_crc, tb_crc_bits) : 0;
+  }
+  __syncthreads();
+  if (cb.cb_crc) {
+    const uint32_t* pw  = crc_pow + (size_t)(PDC_CRC24B - 1) * PDC_CRC_TABLE_LEN;
+    const int       D   = (int)cb.nof_bits;
+    uint32_t        acc = 0;
+    for (int n = tid; n < D; n += nth) {
+      if (cw[n]) {
+        acc ^= pw[D - 1 - n + 24];
+      }
+    }
+    acc = pdc_enc_block_xor(acc, scratch, tid, nth);
+    if (tid < 24) {
+      cw[D + tid] = (unsigned char)((acc >> (23 - tid)) & 1u);
+    }
+    __syncthreads();
+  }
+
+  // ---- core parity (ldpc_encoder_impl.cpp high-rate region; TS 38.212 5.3.2): lambda_m = sum over the systematic columns
+  //      of P^shift s_col for the four core rows, kept in the parity blocks 1..3 and in a spare block ----------------------------
+  unsigned char* p1  = cw + K;                 // parity block of column Kb
+  unsigned char* lam = cw + (Kb + rows) * Z;   // 4 Z bytes of scratch behind the code word
+  for (int q = tid; q < 4 * Z; q += nth) {
+    const int m = q / Z, i = q - m * Z;
+    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
+    unsigned  b  = 0;
+    for (int e = e0; e < e1; ++e) {
+      const uint32_t ent = gr[e];
+      const int      col = (int)(ent & 0xffu);
+      if (col < Kb) {
+        int j = i + (int)(ent >> 8);
+        j -= (j >= Z) ? Z : 0;
+        b ^= cw[col * Z + j];
+      }
+    }
+    lam[q] = (unsigned char)b;
+  }
+  __syncthreads();
+  // Column Kb holds three circulants in the core rows, two of them equal: the sum of the four rows leaves P^b p1.
+  int c[4], bshift = 0;
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    c[m] = -1;
+    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
+    for (int e = e0; e < e1; ++e) {
+      if ((int)(gr[e] & 0xffu) == Kb) {
+        c[m] = (int)(gr[e] >> 8);
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    if (c[m] >= 0) {
+      int cnt = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        cnt += (c[k] == c[m]);
+      }
+      if (cnt & 1) {
+        bshift = c[m];
+      }
+    }
+  }
+  for (int i = tid; i < Z; i += nth) {
+    int j = i + bshift;
+    j -= (j >= Z) ? Z : 0;
+    p1[j] = lam[i] ^ lam[Z + i] ^ lam[2 * Z + i] ^ lam[3 * Z + i];
+  }
+  __syncthreads();
+  // Rows 0..2 give the next three parity blocks in turn: lambda_m + P^c_m p1 + p_m (m > 0) + p_(m+1) = 0.
+  for (int m = 0; m < 3; ++m) {
+    unsigned char* pn = cw + (Kb + 1 + m) * Z;
+    for (int i = tid; i < Z; i += nth) {
+      unsigned b = lam[m * Z + i];
+      if (c[m] >= 0) {
+        int j = i + c[m];
+        j -= (j >= Z) ? Z : 0;
+        b ^= p1[j];
+      }
+      if (m > 0) {
+        b ^= cw[(Kb + m) * Z + i];
+      }
+      pn[i] = (unsigned char)b;
+    }
+    __syncthreads();
+  }
+  // ---- extension rows: the parity block of row m >= 4 is the sum of everything else on the row (all of it known by now) --------
+  for (int q = tid; q < (rows - 4) * Z; q += nth) {
+    const int m = 4 + q / Z, i = q - (m - 4) * Z;
+    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
+    unsigned  b  = 0;
+    for (int e = e0; e < e1; ++e) {
+      const uint32_t ent = gr[e];
+      const int      col = (int)(ent & 0xffu);
+      if (col != Kb + m) {
+        int j = i + (int)(ent >> 8);
+        j -= (j >= Z) ? Z : 0;
+        b ^= cw[col * Z + j];
+      }
+    }
+    cw[(Kb + m) * Z + i] = (unsigned char)b;
+  }
+  __syncthreads();
+
+  // ---- rate matching (ldpc_rate_matcher_impl.cpp: select_bits + interleave_bits) ------------------------------------------------
+  // Circular buffer = code word without its first 2 Z bits, cut at Ncb; the filler window [n_info, n_sys) is never sent.
+  // t-th transmittable position: t < n_info ? t : t + fw. Output bit i Qm + q = selected bit q (E / Qm) + i.
+  const int    N = (Nfull - 2) * Z, Ncb = (cb.Nref > 0) ? min((int)cb.Nref, N) : N;
+  const int    n_sys = (Kb - 2) * Z, n_info = n_sys - (int)cb.nof_filler;
+  const int    fw = max(0, min(n_sys, Ncb) - min(n_info, Ncb)), Lc = Ncb - fw;
+  const int    f1[4] = {0, 17, 33, 56}, f2[4] = {0, 13, 25, 43};
+  const int    fr = (cb.bg == 1) ? f1[cb.rv & 3] : f2[cb.rv & 3];
+  const int    k0 = (int)(((long long)fr * Ncb) / N) * Z; // floor(f Ncb / N) Z: exact in integers
+  const int    t0 = (k0 < n_info) ? k0 : ((k0 >= n_sys) ? k0 - fw : n_info); // a start inside the window moves to its end
+  const int    E = (int)cb.E, Qm = cb.Qm, Kq = E / Qm;
+  const unsigned char* cbuf = cw + 2 * Z;
+  for (int o4 = tid * 4; o4 < E; o4 += nth * 4) {
+    uint32_t word = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int o = o4 + b;
+      if (o < E) {
+        const int i = o / Qm, q = o - i * Qm;
+        int       t = (t0 + q * Kq + i) % Lc;
+        const int idx = (t < n_info) ? t : t + fw;
+        word |= (uint32_t)cbuf[idx] << (8 * b);
+      }
+    }
+    if (o4 + 4 <= E && ((reinterpret_cast<uintptr_t>(cb.out) & 3) == 0)) {
+      *reinterpret_cast<uint32_t*>(cb.out + o4) = word;
+    } else {
+      for (int b = 0; b < 4 && o4 + b < E; ++b) {
+        cb.out[o4 + b] = (uint8_t)(word >> (8 * b));
+      }
+    }
+  }
+}
+
+extern "C" cudaError_t pdc_enc_init_device()
+{
+  static const uint32_t poly[3]  = {0x11021u, 0x1864CFBu, 0x1800063u};
+  static const int      order[3] = {16, 24, 24};
+  uint32_t              tab[3][24];
+  for (int c = 0; c != 3; ++c) {
+    const uint32_t top = 1u << order[c];
+    // x^(2^k): square repeatedly (a(x)^2 mod P by shift-and-add)
+    uint32_t v = 2u; // x
+    for (int k = 0; k != 24; ++k) {
+      tab[c][k]  = v;
+      uint32_t r = 0;
+      for (int i = order[c] - 1; i >= 0; --i) {
+        r <<= 1;
+        if (r & top) {
+          r ^= poly[c];
+        }
+        if ((v >> i) & 1u) {
+          r ^= v;
+        }
+      }
+      v = r;
+    }
+  }
+  cudaError_t e = cudaMemcpyToSymbol(c_enc_xpow2, tab, sizeof(tab));
+  if (e != cudaSuccess) {
+    return e;
+  }
+  return cudaFuncSetAttribute(pdc_enc_cb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+}
+
+extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_cb* d_cbs, uint32_t n, const uint32_t* graphs, const uint32_t* crc_pow,
+                                      size_t smem, cudaStream_t stream)
+{
+  if (n == 0) {
+    return cudaSuccess;
+  }
+  pdc_enc_crc_kernel<<<n, 256, 0, stream>>>(d_cbs, crc_pow);
+  pdc_enc_cb_kernel<<<n, 256, smem, stream>>>(d_cbs, graphs, crc_pow);
+  return cudaGetLastError();
+}

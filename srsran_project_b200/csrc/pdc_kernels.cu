@@ -6,6 +6,7 @@
 #include "pdc_kernel_h2.cuh"
 #include "pdc_kernel_h2g.cuh"
 #include "pdc_kernel_tb.cuh"
+#include "pdc_kernel_enc.cuh"
 #include "pdc_probe.cuh"
 
 extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, size_t smem, cudaStream_t stream)

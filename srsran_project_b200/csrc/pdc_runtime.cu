@@ -104,6 +104,7 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   build_crc_bit_tables(crc, crc_bit);
   if (!cuda_ok(ctx, pdc_kernels_init_device(&rows), "pdc_kernels_init_device") ||
       !cuda_ok(ctx, pdc_demod_init_device(), "pdc_demod_init_device") ||
+      !cuda_ok(ctx, pdc_enc_init_device(), "pdc_enc_init_device") ||
       !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_graphs, graphs.size() * 4), "cudaMalloc graphs") ||
       !cuda_ok(ctx, cudaMemcpy(ctx->d_graphs, graphs.data(), graphs.size() * 4, cudaMemcpyHostToDevice), "copy") ||
       !cuda_ok(ctx, cudaMalloc((void**)&ctx->d_crc, crc.size() * 4), "cudaMalloc crc") ||
@@ -149,6 +150,13 @@ void pdc_destroy(pdc_ctx* ctx)
       cudaEventDestroy(d.done);
     }
   }
+  for (pdc_ctx::demod_slot& d : ctx->enc_ring) {
+    cudaFree(d.d_desc);
+    if (d.done) {
+      cudaEventDestroy(d.done);
+    }
+  }
+  cudaFree(ctx->d_enc_in), cudaFree(ctx->d_enc_out);
   cudaFree(ctx->d_demod_in), cudaFree(ctx->d_demod_out);
   if (ctx->demod_stream) {
     cudaStreamDestroy(ctx->demod_stream);
@@ -675,6 +683,202 @@ pdc_status pdc_demodulate(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, c
     if (bytes != 0) {
       CK(cudaMemcpyAsync(llrs + segs[i].llr_offset, d_out + segs[i].llr_offset, bytes, cudaMemcpyDeviceToHost, stream));
     }
+  }
+  CK(cudaStreamSynchronize(stream));
+  return PDC_OK;
+}
+
+// ---- PDSCH transport-block encoder ----------------------------------------------------------------------------
+namespace {
+struct enc_seg {
+  int bg, Z, C, K, Kp, F, tb_crc_bits, cb_crc_bits;
+};
+// TS 38.212 5.2.2 as the reference derives it (ldpc.h:128-214, ldpc_segmenter_tx_impl.cpp): number of code blocks, lifting
+// size, segment length K' (every code block carries ceil(B' / C) bits, the transport block is zero-padded), fillers.
+bool enc_segmentation(int bg, uint32_t tbs, enc_seg& s)
+{
+  static const int sizes[PDC_NOF_LIFTING_SIZES] = {2,   3,   4,   5,   6,   7,   8,   9,   10,  11,  12,  13,  14,
+                                                   15,  16,  18,  20,  22,  24,  26,  28,  30,  32,  36,  40,  44,
+                                                   48,  52,  56,  60,  64,  72,  80,  88,  96,  104, 112, 120, 128,
+                                                   144, 160, 176, 192, 208, 224, 240, 256, 288, 320, 352, 384};
+  s.bg          = bg;
+  s.tb_crc_bits = (tbs > 3824) ? 24 : 16;
+  const int B   = (int)tbs + s.tb_crc_bits;
+  const int Kcb = (bg == 1) ? 8448 : 3840;
+  if (B <= Kcb) {
+    s.C = 1, s.cb_crc_bits = 0;
+  } else {
+    s.C           = (B + (Kcb - 24) - 1) / (Kcb - 24);
+    s.cb_crc_bits = 24;
+  }
+  const int Bp = B + s.C * s.cb_crc_bits;
+  s.Kp         = (Bp + s.C - 1) / s.C;
+  int Kb       = 22;
+  if (bg == 2) {
+    Kb = (B > 640) ? 10 : ((B > 560) ? 9 : ((B > 192) ? 8 : 6));
+  }
+  s.Z = -1;
+  for (int i = 0; i != PDC_NOF_LIFTING_SIZES; ++i) {
+    if (Kb * sizes[i] >= s.Kp) {
+      s.Z = sizes[i];
+      break;
+    }
+  }
+  if (s.Z < 0) {
+    return false;
+  }
+  s.K = ((bg == 1) ? 22 : 10) * s.Z;
+  s.F = s.K - s.Kp;
+  return true;
+}
+} // namespace
+
+static pdc_status enc_plan(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t n, size_t tb_len, size_t cw_len,
+                           const uint8_t* d_tb, uint8_t* d_cw, uint32_t* d_crc_acc, std::vector<pdc_dev_enc_cb>& cbs,
+                           size_t& smem, size_t& max_tb, size_t& max_cw)
+{
+  cbs.clear();
+  smem = max_tb = max_cw = 0;
+  for (uint32_t t = 0; t != n; ++t) {
+    const pdc_pdsch_tb_desc& d = tbs[t];
+    enc_seg                  s;
+    const bool qm_ok = d.Qm == 1 || d.Qm == 2 || d.Qm == 4 || d.Qm == 6 || d.Qm == 8;
+    if ((d.bg != 1 && d.bg != 2) || !qm_ok || d.rv > 3 || d.nof_layers == 0 || d.nof_layers > 4 || d.tbs_bits == 0 ||
+        (d.tbs_bits & 7) != 0 || d.tbs_bits + 24u > 1277992u || d.nof_ch_symbols == 0 || (d.nof_ch_symbols % d.nof_layers) != 0 ||
+        !enc_segmentation(d.bg, d.tbs_bits, s)) {
+      return PDC_ERR_INVALID_ARG; // ldpc_segmenter_tx_impl.cpp:40-55
+    }
+    const uint64_t G = (uint64_t)d.nof_ch_symbols * d.Qm; // nof_ch_symbols counts every layer (ldpc_segmenter_tx_impl.cpp:93-100)
+    const size_t   te = (size_t)d.tb_offset + d.tbs_bits / 8, ce = (size_t)d.cw_offset + (size_t)G;
+    if ((uint64_t)(d.nof_ch_symbols / d.nof_layers) < (uint64_t)s.C || (tb_len != 0 && te > tb_len) || (cw_len != 0 && ce > cw_len)) {
+      return PDC_ERR_INVALID_ARG; // ldpc_segmenter_tx: every code block needs at least one channel symbol
+    }
+    max_tb = te > max_tb ? te : max_tb, max_cw = ce > max_cw ? ce : max_cw;
+    const int Kb = (d.bg == 1) ? 22 : 10, Nfull = (d.bg == 1) ? 68 : 52, M = Nfull - Kb;
+    const int N = (Nfull - 2) * s.Z, Ncb = (d.Nref > 0) ? ((int)d.Nref < N ? (int)d.Nref : N) : N;
+    const int n_sys = (Kb - 2) * s.Z, n_info = n_sys - s.F;
+    const int fw = std::max(0, std::min(n_sys, Ncb) - std::min(n_info, Ncb)), Lc = Ncb - fw;
+    static const int f1[4] = {0, 17, 33, 56}, f2[4] = {0, 13, 25, 43};
+    const int fr = (d.bg == 1) ? f1[d.rv] : f2[d.rv];
+    const int k0 = (int)(((long long)fr * Ncb) / N) * s.Z;
+    const int t0 = (k0 < n_info) ? k0 : ((k0 >= n_sys) ? k0 - fw : n_info);
+    if (Lc <= 0) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    // Rate-matched lengths (ldpc_segmenter_helpers.h:82-100): the first C - rem code blocks get floor, the others ceil.
+    const uint32_t sym = d.nof_ch_symbols / d.nof_layers, base = sym / s.C, rem = sym % s.C;
+    uint64_t       off = 0;
+    const int      zi  = pdc_lifting_pos(s.Z);
+    for (int r = 0; r != s.C; ++r) {
+      pdc_dev_enc_cb c;
+      memset(&c, 0, sizeof(c));
+      const uint32_t E = (uint32_t)d.nof_layers * d.Qm * (((uint32_t)r < (uint32_t)s.C - rem) ? base : base + 1);
+      c.tb = d_tb + d.tb_offset, c.out = d_cw + d.cw_offset + off, c.tb_crc = d_crc_acc + t;
+      c.tbs_bits = d.tbs_bits, c.nof_bits = (uint32_t)(s.Kp - s.cb_crc_bits), c.first_bit = (uint32_t)r * c.nof_bits;
+      c.E = E, c.Nref = d.Nref, c.nof_filler = (uint32_t)s.F;
+      c.Z = (uint16_t)s.Z, c.graph_idx = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + zi);
+      c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.tb_crc_type = (s.tb_crc_bits == 24) ? PDC_CRC24A : PDC_CRC16;
+      c.cb_crc = s.cb_crc_bits ? 1 : 0;
+      int rows = M;
+      if ((long long)t0 + E <= Lc) {
+        const int tmax = t0 + (int)E - 1, idx = (tmax < n_info) ? tmax : tmax + fw;
+        rows = std::max(4, std::min(M, (idx / s.Z + 1) + 2 - Kb));
+      } else {
+        rows = std::max(4, std::min(M, (Ncb + s.Z - 1) / s.Z + 2 - Kb));
+      }
+      c.rows_needed = (uint8_t)rows;
+      smem          = std::max(smem, (size_t)(Kb + rows + 4) * s.Z);
+      cbs.push_back(c);
+      off += E;
+    }
+  }
+  (void)ctx;
+  return PDC_OK;
+}
+
+pdc_status pdc_pdsch_encode_device(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t n, const uint8_t* d_tb_bytes,
+                                   uint8_t* d_codewords, void* stream_v)
+{
+  if (!ctx || !tbs || n == 0 || !d_tb_bytes || !d_codewords) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_v;
+  CK(cudaSetDevice(ctx->cfg.device));
+  std::lock_guard<std::mutex> lock(ctx->demod_mtx);
+  pdc_ctx::demod_slot&        slot = ctx->enc_ring[ctx->enc_next++ % 8];
+  if (!slot.done) {
+    CK(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
+  }
+  if (slot.used) {
+    CK(cudaEventSynchronize(slot.done));
+  }
+  // Device staging: n CRC accumulators, then the code-block descriptors (their count is known after planning: plan against
+  // a null base first is not needed, the accumulators sit in front).
+  std::vector<pdc_dev_enc_cb> cbs;
+  size_t                      smem, max_tb, max_cw;
+  const size_t                acc_bytes = ((size_t)n * 4 + 15) & ~(size_t)15;
+  // Worst case 152 code blocks per transport block (ldpc.h MAX_NOF_SEGMENTS).
+  const size_t need = acc_bytes + (size_t)n * 152 * sizeof(pdc_dev_enc_cb);
+  if (slot.cap < need) {
+    cudaFree(slot.d_desc);
+    slot.d_desc = nullptr, slot.cap = 0;
+    CK(cudaMalloc(&slot.d_desc, need));
+    slot.cap = need;
+  }
+  uint32_t*  d_acc = (uint32_t*)slot.d_desc;
+  pdc_status st    = enc_plan(ctx, tbs, n, 0, 0, d_tb_bytes, d_codewords, d_acc, cbs, smem, max_tb, max_cw);
+  if (st != PDC_OK) {
+    return st;
+  }
+  pdc_dev_enc_cb* d_cbs = (pdc_dev_enc_cb*)((char*)slot.d_desc + acc_bytes);
+  CK(cudaMemsetAsync(d_acc, 0, acc_bytes, stream));
+  CK(cudaMemcpyAsync(d_cbs, cbs.data(), cbs.size() * sizeof(pdc_dev_enc_cb), cudaMemcpyHostToDevice, stream));
+  CK(pdc_enc_launch(d_cbs, (uint32_t)cbs.size(), ctx->d_graphs, ctx->d_crc, smem, stream));
+  ctx->launches += 2;
+  CK(cudaEventRecord(slot.done, stream));
+  slot.used = true;
+  return PDC_OK;
+}
+
+pdc_status pdc_pdsch_encode(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t n, const uint8_t* tb_bytes, size_t tb_len,
+                            uint8_t* codewords, size_t cw_len)
+{
+  if (!ctx || !tbs || n == 0 || !tb_bytes || !codewords || tb_len == 0 || cw_len == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  // Validate against the host array sizes first (no device pointers needed for that).
+  std::vector<pdc_dev_enc_cb> cbs;
+  size_t                      smem, max_tb, max_cw;
+  pdc_status                  st = enc_plan(ctx, tbs, n, tb_len, cw_len, nullptr, nullptr, nullptr, cbs, smem, max_tb, max_cw);
+  if (st != PDC_OK) {
+    return st;
+  }
+  CK(cudaSetDevice(ctx->cfg.device));
+  std::lock_guard<std::mutex> call_lock(ctx->demod_call_mtx);
+  if (!ctx->demod_stream) {
+    CK(cudaStreamCreateWithFlags(&ctx->demod_stream, cudaStreamNonBlocking));
+  }
+  if (ctx->enc_in_cap < max_tb) {
+    cudaFree(ctx->d_enc_in);
+    ctx->d_enc_in = nullptr, ctx->enc_in_cap = 0;
+    CK(cudaMalloc((void**)&ctx->d_enc_in, max_tb * 2));
+    ctx->enc_in_cap = max_tb * 2;
+  }
+  if (ctx->enc_out_cap < max_cw) {
+    cudaFree(ctx->d_enc_out);
+    ctx->d_enc_out = nullptr, ctx->enc_out_cap = 0;
+    CK(cudaMalloc((void**)&ctx->d_enc_out, max_cw * 2));
+    ctx->enc_out_cap = max_cw * 2;
+  }
+  cudaStream_t stream = ctx->demod_stream;
+  CK(cudaMemcpyAsync(ctx->d_enc_in, tb_bytes, max_tb, cudaMemcpyHostToDevice, stream));
+  st = pdc_pdsch_encode_device(ctx, tbs, n, ctx->d_enc_in, ctx->d_enc_out, stream);
+  if (st != PDC_OK) {
+    return st;
+  }
+  for (uint32_t t = 0; t != n; ++t) {
+    const size_t G = (size_t)tbs[t].nof_ch_symbols * tbs[t].Qm;
+    CK(cudaMemcpyAsync(codewords + tbs[t].cw_offset, ctx->d_enc_out + tbs[t].cw_offset, G, cudaMemcpyDeviceToHost, stream));
   }
   CK(cudaStreamSynchronize(stream));
   return PDC_OK;

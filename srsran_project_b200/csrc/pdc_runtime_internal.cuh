@@ -24,6 +24,9 @@ extern "C" int         pdc_h2_supported(int bg, int Z);
 extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
 extern "C" size_t      pdc_h2g_smem_bytes(int bg, int Z, int max_layers);
 extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_enc_init_device();
+extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_cb* d_cbs, uint32_t n, const uint32_t* graphs, const uint32_t* crc_pow,
+                                      size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_init_device();
 extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void* d_chunks, uint32_t nchunks,
                                         const float* d_symbols, const float* d_noise, int8_t* d_llrs, cudaStream_t stream);
@@ -98,6 +101,11 @@ struct pdc_ctx {
   int8_t*      d_demod_out = nullptr;
   size_t       demod_in_cap = 0, demod_out_cap = 0;
   cudaStream_t demod_stream = nullptr;
+  // PDSCH encoder (pdc_pdsch_encode*): same arrangement.
+  demod_slot   enc_ring[8];
+  unsigned     enc_next = 0;
+  uint8_t*     d_enc_in = nullptr, *d_enc_out = nullptr;
+  size_t       enc_in_cap = 0, enc_out_cap = 0;
 };
 
 namespace {
