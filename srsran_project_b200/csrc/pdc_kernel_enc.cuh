@@ -26,8 +26,10 @@
 #pragma once
 #include "pdc_device.cuh"
 
-// x^(2^k) mod P, k < 24, per CRC type (index crc_type - 1).
+// x^(2^k) mod P, k < 24, per CRC type (index crc_type - 1), and x^(2^k + j) mod P for j < 24: multiplication of a 24-bit
+// remainder by x^(2^k) is then the xor of the rows its set bits select (one warp: a lane per bit).
 __constant__ uint32_t c_enc_xpow2[3][24];
+__device__ uint32_t   d_enc_xpow2_rows[3][24][32];
 
 __device__ __forceinline__ uint32_t pdc_crc_poly(int crc_type)
 {
@@ -61,6 +63,18 @@ __device__ __forceinline__ uint32_t pdc_crc_shift(uint32_t a, uint32_t n, int cr
   return a;
 }
 
+// a(x) x^n mod P(x), computed by one full warp (every lane passes the same a and n and gets the result).
+__device__ __forceinline__ uint32_t pdc_crc_shift_warp(uint32_t a, uint32_t n, int crc_type, int lane)
+{
+  for (int k = 0; k < 24 && (n >> k) != 0; ++k) {
+    if ((n >> k) & 1u) {
+      const uint32_t term = ((a >> lane) & 1u) ? d_enc_xpow2_rows[crc_type - 1][k][lane] : 0u;
+      a                   = __reduce_xor_sync(0xffffffffu, term);
+    }
+  }
+  return a;
+}
+
 // Bit n of (payload ++ TB CRC ++ zero padding) of a transport block.
 __device__ __forceinline__ uint32_t pdc_enc_tb_bit(const pdc_dev_enc_cb& cb, uint32_t n, uint32_t tb_crc, int tb_crc_bits)
 {
@@ -87,8 +101,21 @@ __device__ __forceinline__ uint32_t pdc_enc_block_xor(uint32_t v, uint32_t* scra
   return r;
 }
 
+// 32 bits of the packed transport block starting at bit g (MSB first in the bytes), as a word whose bit j is stream bit g + j.
+// The caller guarantees g + 32 <= number of bits in the block.
+__device__ __forceinline__ uint32_t pdc_enc_tb_word(const uint8_t* __restrict__ tb, uint32_t g)
+{
+  const uint32_t B = g >> 3, sh = g & 7u;
+  const uint32_t hi = ((uint32_t)tb[B] << 24) | ((uint32_t)tb[B + 1] << 16) | ((uint32_t)tb[B + 2] << 8) | (uint32_t)tb[B + 3];
+  uint32_t       be = hi << sh; // big-endian window: stream bit g at bit 31
+  if (sh != 0) {
+    be |= (uint32_t)tb[B + 4] >> (8 - sh);
+  }
+  return __brev(be);
+}
+
 // The code block's share of the TB CRC (ldpc_segmenter_tx_impl: the CRC the segmenter computes before cutting the block).
-__global__ void __launch_bounds__(256) pdc_enc_crc_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ crc_pow)
+__global__ void __launch_bounds__(128) pdc_enc_crc_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ crc_pow)
 {
   __shared__ uint32_t  scratch[32];
   const pdc_dev_enc_cb cb  = cbs[blockIdx.x];
@@ -99,21 +126,234 @@ __global__ void __launch_bounds__(256) pdc_enc_crc_kernel(const pdc_dev_enc_cb* 
   const uint32_t  nbits = min(cb.nof_bits, cb.tbs_bits - cb.first_bit); // payload bits carried here
   const uint32_t* pw    = crc_pow + (size_t)(cb.tb_crc_type - 1) * PDC_CRC_TABLE_LEN;
   uint32_t        acc   = 0;
-  for (uint32_t n = tid; n < nbits; n += nth) {
-    const uint32_t g = cb.first_bit + n;
-    if ((cb.tb[g >> 3] >> (7 - (g & 7))) & 1u) {
-      acc ^= pw[nbits - 1 - n];
+  for (uint32_t w = tid; 32u * w < nbits; w += nth) {
+    const uint32_t n0 = 32u * w;
+    uint32_t       v;
+    if (n0 + 32u <= nbits) {
+      v = pdc_enc_tb_word(cb.tb, cb.first_bit + n0);
+    } else {
+      v = 0;
+      for (uint32_t j = 0; n0 + j < nbits; ++j) {
+        const uint32_t g = cb.first_bit + n0 + j;
+        v |= (uint32_t)((cb.tb[g >> 3] >> (7 - (g & 7))) & 1u) << j;
+      }
+    }
+    while (v != 0) { // the remainder is the xor of one table entry per set bit
+      const uint32_t j = (uint32_t)__ffs((int)v) - 1u;
+      acc ^= pw[nbits - 1u - (n0 + j)];
+      v &= v - 1u;
     }
   }
   acc = pdc_enc_block_xor(acc, scratch, tid, nth);
-  if (tid == 0) {
+  if (tid < 32) {
     const int      order = (cb.tb_crc_type == PDC_CRC16) ? 16 : 24;
     const uint32_t after = cb.tbs_bits - (cb.first_bit + nbits) + (uint32_t)order;
-    atomicXor(cb.tb_crc, pdc_crc_shift(acc, after, cb.tb_crc_type));
+    const uint32_t share = pdc_crc_shift_warp(acc, after, cb.tb_crc_type, tid);
+    if (tid == 0) {
+      atomicXor(cb.tb_crc, share);
+    }
   }
 }
 
-// cw: (Kb + rows) Z bytes, one bit each: systematic blocks, then parity blocks.
+
+// ---- word path: lifting sizes that are multiples of 32 (12 of the 51, among them every Z >= 256) -------------------------------
+// A Z-bit block is nw = Z / 32 words, bit i of the block = bit (i & 31) of word i >> 5. The circulant P^s is a funnel shift
+// across neighbouring words of the block.
+__device__ __forceinline__ uint32_t pdc_enc_rot_word(const uint32_t* blk, int w, int s, int nw)
+{
+  int a = w + (s >> 5);
+  a -= (a >= nw) ? nw : 0;
+  int b = a + 1;
+  b -= (b >= nw) ? nw : 0;
+  return __funnelshift_r(blk[a], blk[b], (unsigned)(s & 31));
+}
+
+template <int QM>
+__device__ __forceinline__ void pdc_enc_rate_match_words(const pdc_dev_enc_cb& cb, const uint32_t* cbuf, const int* base,
+                                                         int Lc, int n_info, int fw, int tid, int nth)
+{
+  const int E = (int)cb.E;
+  const bool aligned = (reinterpret_cast<uintptr_t>(cb.out) & 3) == 0;
+  for (int o4 = tid * 4; o4 < E; o4 += nth * 4) {
+    uint32_t word = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int o = o4 + b;
+      if (o < E) {
+        const int i = o / QM, q = o - i * QM;
+        int       t = base[q] + i;
+        while (t >= Lc) {
+          t -= Lc;
+        }
+        const int idx = (t < n_info) ? t : t + fw;
+        word |= ((cbuf[idx >> 5] >> (idx & 31)) & 1u) << (8 * b);
+      }
+    }
+    if (o4 + 4 <= E && aligned) {
+      *reinterpret_cast<uint32_t*>(cb.out + o4) = word;
+    } else {
+      for (int b = 0; b < 4 && o4 + b < E; ++b) {
+        cb.out[o4 + b] = (uint8_t)(word >> (8 * b));
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void pdc_enc_cb_words(const pdc_dev_enc_cb& cb, const uint32_t* __restrict__ gr,
+                                                 const uint32_t* __restrict__ crc_pow, uint32_t* cww, uint32_t* scratch,
+                                                 int* s_base, int tid, int nth)
+{
+  const int bgi = cb.bg - 1, Z = cb.Z, nw = Z >> 5;
+  const int Kb = (cb.bg == 1) ? 22 : 10, Nfull = (cb.bg == 1) ? 68 : 52, M = Nfull - Kb;
+  const int rows = min((int)cb.rows_needed, M);
+  uint32_t* lam  = cww + (Kb + rows) * nw;
+  // ---- message words -----------------------------------------------------------------------------------------------------------
+  const int      tb_crc_bits = (cb.tb_crc_type == PDC_CRC16) ? 16 : 24;
+  const uint32_t tb_crc      = *cb.tb_crc;
+  const uint32_t D           = cb.nof_bits;
+  for (int w = tid; w < (Kb + rows) * nw; w += nth) {
+    const uint32_t n0 = 32u * (uint32_t)w;
+    uint32_t       v  = 0;
+    if (n0 + 32u <= D && cb.first_bit + n0 + 32u <= cb.tbs_bits) {
+      v = pdc_enc_tb_word(cb.tb, cb.first_bit + n0);
+    } else if (n0 < D) {
+      for (uint32_t j = 0; j < 32u && n0 + j < D; ++j) {
+        v |= pdc_enc_tb_bit(cb, cb.first_bit + n0 + j, tb_crc, tb_crc_bits) << j;
+      }
+    }
+    cww[w] = v;
+  }
+  __syncthreads();
+  if (cb.cb_crc) {
+    const uint32_t* pw  = crc_pow + (size_t)(PDC_CRC24B - 1) * PDC_CRC_TABLE_LEN;
+    uint32_t        acc = 0;
+    for (uint32_t w = tid; 32u * w < D; w += nth) {
+      uint32_t v = cww[w];
+      while (v != 0) {
+        const uint32_t j = (uint32_t)__ffs((int)v) - 1u;
+        acc ^= pw[D - 1u - (32u * w + j) + 24u];
+        v &= v - 1u;
+      }
+    }
+    acc = pdc_enc_block_xor(acc, scratch, tid, nth);
+    if (tid < 24) {
+      const uint32_t n = D + (uint32_t)tid;
+      atomicOr(&cww[n >> 5], ((acc >> (23 - tid)) & 1u) << (n & 31u));
+    }
+    __syncthreads();
+  }
+  // ---- core parity --------------------------------------------------------------------------------------------------------------
+  for (int q = tid; q < 4 * nw; q += nth) {
+    const int m = q / nw, w = q - m * nw;
+    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
+    uint32_t  b  = 0;
+    for (int e = e0; e < e1; ++e) {
+      const uint32_t ent = gr[e];
+      const int      col = (int)(ent & 0xffu);
+      if (col < Kb) {
+        b ^= pdc_enc_rot_word(cww + col * nw, w, (int)(ent >> 8), nw);
+      }
+    }
+    lam[q] = b;
+  }
+  int c[4], bshift = 0;
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    c[m] = -1;
+    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
+    for (int e = e0; e < e1; ++e) {
+      if ((int)(gr[e] & 0xffu) == Kb) {
+        c[m] = (int)(gr[e] >> 8);
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < 4; ++m) {
+    if (c[m] >= 0) {
+      int cnt = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        cnt += (c[k] == c[m]);
+      }
+      if (cnt & 1) {
+        bshift = c[m];
+      }
+    }
+  }
+  __syncthreads();
+  uint32_t* p1  = cww + Kb * nw;
+  uint32_t* sum = lam + 4 * nw; // nw words more of scratch
+  for (int w = tid; w < nw; w += nth) {
+    sum[w] = lam[w] ^ lam[nw + w] ^ lam[2 * nw + w] ^ lam[3 * nw + w];
+  }
+  __syncthreads();
+  for (int w = tid; w < nw; w += nth) {
+    p1[w] = pdc_enc_rot_word(sum, w, (Z - bshift) % Z, nw); // sum = P^b p1
+  }
+  __syncthreads();
+  for (int m = 0; m < 3; ++m) {
+    uint32_t* pn = cww + (Kb + 1 + m) * nw;
+    for (int w = tid; w < nw; w += nth) {
+      uint32_t b = lam[m * nw + w];
+      if (c[m] >= 0) {
+        b ^= pdc_enc_rot_word(p1, w, c[m], nw);
+      }
+      if (m > 0) {
+        b ^= cww[(Kb + m) * nw + w];
+      }
+      pn[w] = b;
+    }
+    __syncthreads();
+  }
+  // ---- extension rows -------------------------------------------------------------------------------------------------------------
+  for (int q = tid; q < (rows - 4) * nw; q += nth) {
+    const int m = 4 + q / nw, w = q - (m - 4) * nw;
+    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
+    uint32_t  b  = 0;
+    for (int e = e0; e < e1; ++e) {
+      const uint32_t ent = gr[e];
+      const int      col = (int)(ent & 0xffu);
+      if (col != Kb + m) {
+        b ^= pdc_enc_rot_word(cww + col * nw, w, (int)(ent >> 8), nw);
+      }
+    }
+    cww[(Kb + m) * nw + w] = b;
+  }
+  // ---- rate matching ----------------------------------------------------------------------------------------------------------------
+  const int N = (Nfull - 2) * Z, Ncb = (cb.Nref > 0) ? min((int)cb.Nref, N) : N;
+  const int n_sys = (Kb - 2) * Z, n_info = n_sys - (int)cb.nof_filler;
+  const int fw = max(0, min(n_sys, Ncb) - min(n_info, Ncb)), Lc = Ncb - fw;
+  const int f1[4] = {0, 17, 33, 56}, f2[4] = {0, 13, 25, 43};
+  const int fr = (cb.bg == 1) ? f1[cb.rv & 3] : f2[cb.rv & 3];
+  const int k0 = (int)(((long long)fr * Ncb) / N) * Z;
+  const int t0 = (k0 < n_info) ? k0 : ((k0 >= n_sys) ? k0 - fw : n_info);
+  const int Kq = (int)cb.E / cb.Qm;
+  if (tid < cb.Qm) {
+    s_base[tid] = (int)(((long long)t0 + (long long)tid * Kq) % Lc); // start of interleaver row q in the compacted buffer
+  }
+  __syncthreads();
+  const uint32_t* cbuf = cww + 2 * nw;
+  switch (cb.Qm) {
+    case 1:
+      pdc_enc_rate_match_words<1>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      break;
+    case 2:
+      pdc_enc_rate_match_words<2>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      break;
+    case 4:
+      pdc_enc_rate_match_words<4>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      break;
+    case 6:
+      pdc_enc_rate_match_words<6>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      break;
+    default:
+      pdc_enc_rate_match_words<8>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      break;
+  }
+}
+
+// cw: (Kb + rows) Z bytes, one bit each: systematic blocks, then parity blocks (lifting sizes that are not multiples of 32;
+// the others take pdc_enc_cb_words above).
 __global__ void __launch_bounds__(256) pdc_enc_cb_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ graphs,
                                                          const uint32_t* __restrict__ crc_pow)
 {
@@ -126,6 +366,11 @@ __global__ void __launch_bounds__(256) pdc_enc_cb_kernel(const pdc_dev_enc_cb* _
   const int            rows = min((int)cb.rows_needed, M);
   const uint32_t*      gr   = graphs + (size_t)cb.graph_idx * PDC_GRAPH_STRIDE;
   const int            K    = Kb * Z;
+  if ((Z & 31) == 0) {
+    __shared__ int s_base[8];
+    pdc_enc_cb_words(cb, gr, crc_pow, reinterpret_cast<uint32_t*>(cw), scratch, s_base, tid, nth);
+    return;
+  }
 
   // ---- message: payload (++ TB CRC ++ padding) ++ CB CRC ++ fillers (zero while encoding) -------------------------------------
   const int      tb_crc_bits = (cb.tb_crc_type == PDC_CRC16) ? 16 : 24;
@@ -298,6 +543,24 @@ extern "C" cudaError_t pdc_enc_init_device()
   if (e != cudaSuccess) {
     return e;
   }
+  static uint32_t rows[3][24][32];
+  for (int c = 0; c != 3; ++c) {
+    const uint32_t top = 1u << order[c];
+    for (int k = 0; k != 24; ++k) {
+      uint32_t v = tab[c][k]; // x^(2^k + j) = x^(2^k) x^j
+      for (int j = 0; j != 32; ++j) {
+        rows[c][k][j] = (j < order[c]) ? v : 0u;
+        v <<= 1;
+        if (v & top) {
+          v ^= poly[c];
+        }
+      }
+    }
+  }
+  e = cudaMemcpyToSymbol(d_enc_xpow2_rows, rows, sizeof(rows));
+  if (e != cudaSuccess) {
+    return e;
+  }
   return cudaFuncSetAttribute(pdc_enc_cb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
 }
 
@@ -307,7 +570,7 @@ extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_cb* d_cbs, uint32_t n, c
   if (n == 0) {
     return cudaSuccess;
   }
-  pdc_enc_crc_kernel<<<n, 256, 0, stream>>>(d_cbs, crc_pow);
+  pdc_enc_crc_kernel<<<n, 128, 0, stream>>>(d_cbs, crc_pow);
   pdc_enc_cb_kernel<<<n, 256, smem, stream>>>(d_cbs, graphs, crc_pow);
   return cudaGetLastError();
 }
