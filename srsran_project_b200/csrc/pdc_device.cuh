@@ -40,8 +40,38 @@ struct pdc_dev_enc_cb {
   uint8_t        bg, Qm, rv, tb_crc_type; // tb_crc_type: PDC_CRC16 | PDC_CRC24A
   uint8_t        cb_crc;                  // 1: append CRC24B
   uint8_t        rows_needed;             // parity rows the rate matcher reads (>= 4)
-  uint16_t       reserved;
+  uint16_t       bshift;                  // shift b of the core parity solve: the four core rows sum to P^b p1
+  int16_t        core_shift[4];           // shift of column Kb in core row m, -1 if the row does not hold it
 };
+
+// One transport block of the PDSCH encoder as the host plans it; the kernels derive their code block (blockIdx.x) from it, so
+// a submission uploads one small structure per transport block, not one per code block.
+struct pdc_dev_enc_tb {
+  const uint8_t* tb;
+  uint8_t*       out;      // the transport block's codeword (one bit per byte)
+  uint32_t*      tb_crc;
+  uint32_t       tbs_bits, nof_bits; // nof_bits: TB bits per code block (K' - CB CRC length)
+  uint32_t       nof_cbs, nof_short; // code blocks; how many of them (the first ones) have the short rate-matched length
+  uint32_t       E_short, E_long, Nref, nof_filler;
+  uint16_t       Z, graph_idx;
+  uint8_t        bg, Qm, rv, tb_crc_type, cb_crc, rows_short, rows_long, pad;
+  uint16_t       bshift;
+  int16_t        core_shift[4];
+};
+__device__ __forceinline__ pdc_dev_enc_cb pdc_enc_cb_of(const pdc_dev_enc_tb& t, uint32_t r)
+{
+  pdc_dev_enc_cb c;
+  const bool     is_short = r < t.nof_short;
+  c.tb = t.tb, c.tb_crc = t.tb_crc;
+  c.out = t.out + (is_short ? (size_t)r * t.E_short : (size_t)t.nof_short * t.E_short + (size_t)(r - t.nof_short) * t.E_long);
+  c.tbs_bits = t.tbs_bits, c.nof_bits = t.nof_bits, c.first_bit = r * t.nof_bits;
+  c.E = is_short ? t.E_short : t.E_long, c.Nref = t.Nref, c.nof_filler = t.nof_filler;
+  c.Z = t.Z, c.graph_idx = t.graph_idx, c.bg = t.bg, c.Qm = t.Qm, c.rv = t.rv, c.tb_crc_type = t.tb_crc_type;
+  c.cb_crc = t.cb_crc, c.rows_needed = is_short ? t.rows_short : t.rows_long, c.bshift = t.bshift;
+  c.core_shift[0] = t.core_shift[0], c.core_shift[1] = t.core_shift[1], c.core_shift[2] = t.core_shift[2];
+  c.core_shift[3] = t.core_shift[3];
+  return c;
+}
 
 // Row structure of the two base graphs (degrees and prefix sums), uploaded once per process.
 struct pdc_bg_rows {

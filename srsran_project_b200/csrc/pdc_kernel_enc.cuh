@@ -115,10 +115,13 @@ __device__ __forceinline__ uint32_t pdc_enc_tb_word(const uint8_t* __restrict__ 
 }
 
 // The code block's share of the TB CRC (ldpc_segmenter_tx_impl: the CRC the segmenter computes before cutting the block).
-__global__ void __launch_bounds__(128) pdc_enc_crc_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ crc_pow)
+__global__ void __launch_bounds__(128) pdc_enc_crc_kernel(const pdc_dev_enc_tb* __restrict__ tbs, const uint32_t* __restrict__ crc_pow)
 {
   __shared__ uint32_t  scratch[32];
-  const pdc_dev_enc_cb cb  = cbs[blockIdx.x];
+  if (blockIdx.x >= tbs[blockIdx.y].nof_cbs) {
+    return;
+  }
+  const pdc_dev_enc_cb cb  = pdc_enc_cb_of(tbs[blockIdx.y], blockIdx.x);
   const int            tid = threadIdx.x, nth = blockDim.x;
   if (cb.first_bit >= cb.tbs_bits) {
     return; // nothing of the payload in this code block
@@ -166,6 +169,70 @@ __device__ __forceinline__ uint32_t pdc_enc_rot_word(const uint32_t* blk, int w,
   int b = a + 1;
   b -= (b >= nw) ? nw : 0;
   return __funnelshift_r(blk[a], blk[b], (unsigned)(s & 31));
+}
+
+// Four consecutive bits t .. t + 3 of the compacted circular buffer (t + 3 < Lc, not straddling the filler window), bit k of the
+// result = position t + k.
+__device__ __forceinline__ uint32_t pdc_enc_nibble(const uint32_t* cbuf, int t, int n_info, int fw)
+{
+  const int idx = (t < n_info) ? t : t + fw;
+  const int w   = idx >> 5;
+  return __funnelshift_r(cbuf[w], cbuf[w + 1], (unsigned)(idx & 31)) & 0xfu; // one word of slack behind the buffer
+}
+
+// Interleaver for Qm = 8 and 4: a thread takes four consecutive columns i of the Qm x (E / Qm) interleaver, i.e. 4 Qm
+// consecutive output bytes. Row q contributes four consecutive buffer bits (one funnel shift); with the nibbles of four rows
+// side by side in one register, (X >> k) & 0x01010101 is a finished output word. Returns false if the geometry does not fit
+// (the caller then runs the general loop).
+template <int QM>
+__device__ __forceinline__ bool pdc_enc_rate_match_fast(const pdc_dev_enc_cb& cb, const uint32_t* cbuf, const int* base,
+                                                        int Lc, int n_info, int fw, int tid, int nth)
+{
+  const int Kq = (int)cb.E / QM;
+  if ((Kq & 3) != 0 || (reinterpret_cast<uintptr_t>(cb.out) & 15) != 0) {
+    return false;
+  }
+  int bq[QM];
+#pragma unroll
+  for (int q = 0; q < QM; ++q) {
+    bq[q] = base[q];
+  }
+  for (int i0 = 4 * tid; i0 < Kq; i0 += 4 * nth) {
+    uint32_t nib[QM];
+#pragma unroll
+    for (int q = 0; q < QM; ++q) {
+      int t = bq[q] + i0;
+      while (t >= Lc) {
+        t -= Lc;
+      }
+      if (t + 3 < Lc && (t + 3 < n_info || t >= n_info)) {
+        nib[q] = pdc_enc_nibble(cbuf, t, n_info, fw);
+      } else { // wraps around the buffer or jumps over the filler window inside these four bits
+        nib[q] = 0;
+        for (int k = 0; k < 4; ++k) {
+          int tk = t + k;
+          tk -= (tk >= Lc) ? Lc : 0;
+          const int idx = (tk < n_info) ? tk : tk + fw;
+          nib[q] |= ((cbuf[idx >> 5] >> (idx & 31)) & 1u) << k;
+        }
+      }
+    }
+    uint32_t out[QM];
+#pragma unroll
+    for (int h = 0; h < QM / 4; ++h) {
+      const uint32_t X = nib[4 * h] | (nib[4 * h + 1] << 8) | (nib[4 * h + 2] << 16) | (nib[4 * h + 3] << 24);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        out[k * (QM / 4) + h] = (X >> k) & 0x01010101u; // bytes (i0 + k) QM + 4 h .. + 3
+      }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(cb.out + (size_t)i0 * QM);
+#pragma unroll
+    for (int v = 0; v < QM / 4; ++v) {
+      dst[v] = make_uint4(out[4 * v], out[4 * v + 1], out[4 * v + 2], out[4 * v + 3]);
+    }
+  }
+  return true;
 }
 
 template <int QM>
@@ -242,44 +309,25 @@ __device__ __forceinline__ void pdc_enc_cb_words(const pdc_dev_enc_cb& cb, const
     }
     __syncthreads();
   }
-  // ---- core parity --------------------------------------------------------------------------------------------------------------
-  for (int q = tid; q < 4 * nw; q += nth) {
-    const int m = q / nw, w = q - m * nw;
+  // ---- core parity: lambda_m word by word, the edges of a row split over four threads (4 rows x nw words x 4 slices) ---------------
+  for (int q = tid; q < 5 * nw; q += nth) {
+    lam[q] = 0; // lambda and the sum block behind it
+  }
+  __syncthreads();
+  for (int q = tid; q < 16 * nw; q += nth) {
+    const int slice = q & 3, mw = q >> 2, m = mw / nw, w = mw - m * nw;
     const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
     uint32_t  b  = 0;
-    for (int e = e0; e < e1; ++e) {
+    for (int e = e0 + slice; e < e1; e += 4) {
       const uint32_t ent = gr[e];
       const int      col = (int)(ent & 0xffu);
       if (col < Kb) {
         b ^= pdc_enc_rot_word(cww + col * nw, w, (int)(ent >> 8), nw);
       }
     }
-    lam[q] = b;
+    atomicXor(&lam[mw], b);
   }
-  int c[4], bshift = 0;
-#pragma unroll
-  for (int m = 0; m < 4; ++m) {
-    c[m] = -1;
-    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
-    for (int e = e0; e < e1; ++e) {
-      if ((int)(gr[e] & 0xffu) == Kb) {
-        c[m] = (int)(gr[e] >> 8);
-      }
-    }
-  }
-#pragma unroll
-  for (int m = 0; m < 4; ++m) {
-    if (c[m] >= 0) {
-      int cnt = 0;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        cnt += (c[k] == c[m]);
-      }
-      if (cnt & 1) {
-        bshift = c[m];
-      }
-    }
-  }
+  const int c[4] = {cb.core_shift[0], cb.core_shift[1], cb.core_shift[2], cb.core_shift[3]}, bshift = cb.bshift;
   __syncthreads();
   uint32_t* p1  = cww + Kb * nw;
   uint32_t* sum = lam + 4 * nw; // nw words more of scratch
@@ -341,25 +389,32 @@ __device__ __forceinline__ void pdc_enc_cb_words(const pdc_dev_enc_cb& cb, const
       pdc_enc_rate_match_words<2>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
       break;
     case 4:
-      pdc_enc_rate_match_words<4>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      if (!pdc_enc_rate_match_fast<4>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth)) {
+        pdc_enc_rate_match_words<4>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      }
       break;
     case 6:
       pdc_enc_rate_match_words<6>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
       break;
     default:
-      pdc_enc_rate_match_words<8>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      if (!pdc_enc_rate_match_fast<8>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth)) {
+        pdc_enc_rate_match_words<8>(cb, cbuf, s_base, Lc, n_info, fw, tid, nth);
+      }
       break;
   }
 }
 
 // cw: (Kb + rows) Z bytes, one bit each: systematic blocks, then parity blocks (lifting sizes that are not multiples of 32;
 // the others take pdc_enc_cb_words above).
-__global__ void __launch_bounds__(256) pdc_enc_cb_kernel(const pdc_dev_enc_cb* __restrict__ cbs, const uint32_t* __restrict__ graphs,
+__global__ void __launch_bounds__(256) pdc_enc_cb_kernel(const pdc_dev_enc_tb* __restrict__ tbs, const uint32_t* __restrict__ graphs,
                                                          const uint32_t* __restrict__ crc_pow)
 {
   extern __shared__ __align__(16) unsigned char cw[];
   __shared__ uint32_t  scratch[32];
-  const pdc_dev_enc_cb cb  = cbs[blockIdx.x];
+  if (blockIdx.x >= tbs[blockIdx.y].nof_cbs) {
+    return;
+  }
+  const pdc_dev_enc_cb cb  = pdc_enc_cb_of(tbs[blockIdx.y], blockIdx.x);
   const int            tid = threadIdx.x, nth = blockDim.x;
   const int            bgi = cb.bg - 1, Z = cb.Z;
   const int            Kb = (cb.bg == 1) ? 22 : 10, Nfull = (cb.bg == 1) ? 68 : 52, M = Nfull - Kb;
@@ -416,30 +471,7 @@ __global__ void __launch_bounds__(256) pdc_enc_cb_kernel(const pdc_dev_enc_cb* _
   }
   __syncthreads();
   // Column Kb holds three circulants in the core rows, two of them equal: the sum of the four rows leaves P^b p1.
-  int c[4], bshift = 0;
-#pragma unroll
-  for (int m = 0; m < 4; ++m) {
-    c[m] = -1;
-    const int e0 = c_bg_rows.start[bgi][m], e1 = e0 + c_bg_rows.deg[bgi][m];
-    for (int e = e0; e < e1; ++e) {
-      if ((int)(gr[e] & 0xffu) == Kb) {
-        c[m] = (int)(gr[e] >> 8);
-      }
-    }
-  }
-#pragma unroll
-  for (int m = 0; m < 4; ++m) {
-    if (c[m] >= 0) {
-      int cnt = 0;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        cnt += (c[k] == c[m]);
-      }
-      if (cnt & 1) {
-        bshift = c[m];
-      }
-    }
-  }
+  const int c[4] = {cb.core_shift[0], cb.core_shift[1], cb.core_shift[2], cb.core_shift[3]}, bshift = cb.bshift;
   for (int i = tid; i < Z; i += nth) {
     int j = i + bshift;
     j -= (j >= Z) ? Z : 0;
@@ -564,13 +596,14 @@ extern "C" cudaError_t pdc_enc_init_device()
   return cudaFuncSetAttribute(pdc_enc_cb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
 }
 
-extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_cb* d_cbs, uint32_t n, const uint32_t* graphs, const uint32_t* crc_pow,
-                                      size_t smem, cudaStream_t stream)
+extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb, uint32_t max_cbs, const uint32_t* graphs,
+                                      const uint32_t* crc_pow, size_t smem, cudaStream_t stream)
 {
-  if (n == 0) {
-    return cudaSuccess;
+  // grid.y is limited to 65535 transport blocks per launch
+  for (uint32_t t0 = 0; t0 < ntb; t0 += 65535u) {
+    const uint32_t nt = (ntb - t0 < 65535u) ? ntb - t0 : 65535u;
+    pdc_enc_crc_kernel<<<dim3(max_cbs, nt), 128, 0, stream>>>(d_tbs + t0, crc_pow);
+    pdc_enc_cb_kernel<<<dim3(max_cbs, nt), 256, smem, stream>>>(d_tbs + t0, graphs, crc_pow);
   }
-  pdc_enc_crc_kernel<<<n, 128, 0, stream>>>(d_cbs, crc_pow);
-  pdc_enc_cb_kernel<<<n, 256, smem, stream>>>(d_cbs, graphs, crc_pow);
   return cudaGetLastError();
 }

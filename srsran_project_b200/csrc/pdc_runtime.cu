@@ -734,11 +734,12 @@ bool enc_segmentation(int bg, uint32_t tbs, enc_seg& s)
 } // namespace
 
 static pdc_status enc_plan(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t n, size_t tb_len, size_t cw_len,
-                           const uint8_t* d_tb, uint8_t* d_cw, uint32_t* d_crc_acc, std::vector<pdc_dev_enc_cb>& cbs,
-                           size_t& smem, size_t& max_tb, size_t& max_cw)
+                           const uint8_t* d_tb, uint8_t* d_cw, uint32_t* d_crc_acc, std::vector<pdc_dev_enc_tb>& out,
+                           size_t& smem, size_t& max_tb, size_t& max_cw, uint32_t& max_cbs)
 {
-  cbs.clear();
+  out.clear();
   smem = max_tb = max_cw = 0;
+  max_cbs = 0;
   for (uint32_t t = 0; t != n; ++t) {
     const pdc_pdsch_tb_desc& d = tbs[t];
     enc_seg                  s;
@@ -765,32 +766,58 @@ static pdc_status enc_plan(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t 
     if (Lc <= 0) {
       return PDC_ERR_INVALID_ARG;
     }
+    // Column Kb in the four core rows: three circulants, two of them equal (TS 38.212 tables 5.3.2-2/3); the odd one out is the
+    // shift b with which the sum of the four rows leaves P^b p1 (ldpc_encoder_impl.cpp, high-rate region).
+    int core_shift[4] = {-1, -1, -1, -1}, bshift = 0;
+    {
+      const uint8_t*  deg = (d.bg == 1) ? pdc_bg1_row_deg : pdc_bg2_row_deg;
+      const uint8_t*  col = (d.bg == 1) ? pdc_bg1_edge_col : pdc_bg2_edge_col;
+      const uint16_t* sh  = (d.bg == 1) ? pdc_bg1_edge_shift[lifting_set_index(s.Z)] : pdc_bg2_edge_shift[lifting_set_index(s.Z)];
+      int             e   = 0;
+      for (int m = 0; m != 4; ++m) {
+        for (int k = 0; k != deg[m]; ++k, ++e) {
+          if (col[e] == Kb) {
+            core_shift[m] = sh[e] % s.Z;
+          }
+        }
+      }
+      for (int m = 0; m != 4; ++m) {
+        int cnt = 0;
+        for (int k = 0; k != 4; ++k) {
+          cnt += (core_shift[m] >= 0 && core_shift[k] == core_shift[m]);
+        }
+        if (cnt & 1) {
+          bshift = core_shift[m];
+        }
+      }
+    }
     // Rate-matched lengths (ldpc_segmenter_helpers.h:82-100): the first C - rem code blocks get floor, the others ceil.
     const uint32_t sym = d.nof_ch_symbols / d.nof_layers, base = sym / s.C, rem = sym % s.C;
-    uint64_t       off = 0;
-    const int      zi  = pdc_lifting_pos(s.Z);
-    for (int r = 0; r != s.C; ++r) {
-      pdc_dev_enc_cb c;
-      memset(&c, 0, sizeof(c));
-      const uint32_t E = (uint32_t)d.nof_layers * d.Qm * (((uint32_t)r < (uint32_t)s.C - rem) ? base : base + 1);
-      c.tb = d_tb + d.tb_offset, c.out = d_cw + d.cw_offset + off, c.tb_crc = d_crc_acc + t;
-      c.tbs_bits = d.tbs_bits, c.nof_bits = (uint32_t)(s.Kp - s.cb_crc_bits), c.first_bit = (uint32_t)r * c.nof_bits;
-      c.E = E, c.Nref = d.Nref, c.nof_filler = (uint32_t)s.F;
-      c.Z = (uint16_t)s.Z, c.graph_idx = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + zi);
-      c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.tb_crc_type = (s.tb_crc_bits == 24) ? PDC_CRC24A : PDC_CRC16;
-      c.cb_crc = s.cb_crc_bits ? 1 : 0;
-      int rows = M;
+    auto rows_for = [&](uint32_t E) {
       if ((long long)t0 + E <= Lc) {
         const int tmax = t0 + (int)E - 1, idx = (tmax < n_info) ? tmax : tmax + fw;
-        rows = std::max(4, std::min(M, (idx / s.Z + 1) + 2 - Kb));
-      } else {
-        rows = std::max(4, std::min(M, (Ncb + s.Z - 1) / s.Z + 2 - Kb));
+        return std::max(4, std::min(M, (idx / s.Z + 1) + 2 - Kb));
       }
-      c.rows_needed = (uint8_t)rows;
-      smem          = std::max(smem, (size_t)(Kb + rows + 4) * s.Z);
-      cbs.push_back(c);
-      off += E;
+      return std::max(4, std::min(M, (Ncb + s.Z - 1) / s.Z + 2 - Kb));
+    };
+    pdc_dev_enc_tb c;
+    memset(&c, 0, sizeof(c));
+    c.tb = d_tb + d.tb_offset, c.out = d_cw + d.cw_offset, c.tb_crc = d_crc_acc + t;
+    c.tbs_bits = d.tbs_bits, c.nof_bits = (uint32_t)(s.Kp - s.cb_crc_bits);
+    c.nof_cbs = (uint32_t)s.C, c.nof_short = (uint32_t)s.C - rem;
+    c.E_short = (uint32_t)d.nof_layers * d.Qm * base, c.E_long = (uint32_t)d.nof_layers * d.Qm * (base + 1);
+    c.Nref = d.Nref, c.nof_filler = (uint32_t)s.F;
+    c.Z = (uint16_t)s.Z, c.graph_idx = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(s.Z));
+    c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.tb_crc_type = (s.tb_crc_bits == 24) ? PDC_CRC24A : PDC_CRC16;
+    c.cb_crc = s.cb_crc_bits ? 1 : 0;
+    c.rows_short = (uint8_t)rows_for(c.E_short), c.rows_long = (uint8_t)rows_for(c.E_long);
+    c.bshift = (uint16_t)bshift;
+    for (int m = 0; m != 4; ++m) {
+      c.core_shift[m] = (int16_t)core_shift[m];
     }
+    smem    = std::max(smem, (size_t)(Kb + std::max(c.rows_short, c.rows_long) + 5) * s.Z);
+    max_cbs = std::max(max_cbs, (uint32_t)s.C);
+    out.push_back(c);
   }
   (void)ctx;
   return PDC_OK;
@@ -812,13 +839,12 @@ pdc_status pdc_pdsch_encode_device(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, u
   if (slot.used) {
     CK(cudaEventSynchronize(slot.done));
   }
-  // Device staging: n CRC accumulators, then the code-block descriptors (their count is known after planning: plan against
-  // a null base first is not needed, the accumulators sit in front).
-  std::vector<pdc_dev_enc_cb> cbs;
+  // Device staging: n CRC accumulators, then one descriptor per transport block (the kernels derive their code block).
+  std::vector<pdc_dev_enc_tb> cbs;
   size_t                      smem, max_tb, max_cw;
+  uint32_t                    max_cbs;
   const size_t                acc_bytes = ((size_t)n * 4 + 15) & ~(size_t)15;
-  // Worst case 152 code blocks per transport block (ldpc.h MAX_NOF_SEGMENTS).
-  const size_t need = acc_bytes + (size_t)n * 152 * sizeof(pdc_dev_enc_cb);
+  const size_t                need      = acc_bytes + (size_t)n * sizeof(pdc_dev_enc_tb);
   if (slot.cap < need) {
     cudaFree(slot.d_desc);
     slot.d_desc = nullptr, slot.cap = 0;
@@ -826,14 +852,14 @@ pdc_status pdc_pdsch_encode_device(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, u
     slot.cap = need;
   }
   uint32_t*  d_acc = (uint32_t*)slot.d_desc;
-  pdc_status st    = enc_plan(ctx, tbs, n, 0, 0, d_tb_bytes, d_codewords, d_acc, cbs, smem, max_tb, max_cw);
+  pdc_status st    = enc_plan(ctx, tbs, n, 0, 0, d_tb_bytes, d_codewords, d_acc, cbs, smem, max_tb, max_cw, max_cbs);
   if (st != PDC_OK) {
     return st;
   }
-  pdc_dev_enc_cb* d_cbs = (pdc_dev_enc_cb*)((char*)slot.d_desc + acc_bytes);
+  pdc_dev_enc_tb* d_tbs = (pdc_dev_enc_tb*)((char*)slot.d_desc + acc_bytes);
   CK(cudaMemsetAsync(d_acc, 0, acc_bytes, stream));
-  CK(cudaMemcpyAsync(d_cbs, cbs.data(), cbs.size() * sizeof(pdc_dev_enc_cb), cudaMemcpyHostToDevice, stream));
-  CK(pdc_enc_launch(d_cbs, (uint32_t)cbs.size(), ctx->d_graphs, ctx->d_crc, smem, stream));
+  CK(cudaMemcpyAsync(d_tbs, cbs.data(), cbs.size() * sizeof(pdc_dev_enc_tb), cudaMemcpyHostToDevice, stream));
+  CK(pdc_enc_launch(d_tbs, n, max_cbs, ctx->d_graphs, ctx->d_crc, smem, stream));
   ctx->launches += 2;
   CK(cudaEventRecord(slot.done, stream));
   slot.used = true;
@@ -847,9 +873,10 @@ pdc_status pdc_pdsch_encode(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t
     return PDC_ERR_INVALID_ARG;
   }
   // Validate against the host array sizes first (no device pointers needed for that).
-  std::vector<pdc_dev_enc_cb> cbs;
+  std::vector<pdc_dev_enc_tb> cbs;
   size_t                      smem, max_tb, max_cw;
-  pdc_status                  st = enc_plan(ctx, tbs, n, tb_len, cw_len, nullptr, nullptr, nullptr, cbs, smem, max_tb, max_cw);
+  uint32_t                    max_cbs;
+  pdc_status st = enc_plan(ctx, tbs, n, tb_len, cw_len, nullptr, nullptr, nullptr, cbs, smem, max_tb, max_cw, max_cbs);
   if (st != PDC_OK) {
     return st;
   }

@@ -25,8 +25,8 @@ extern "C" size_t      pdc_h2_smem_bytes(int bg, int Z, int max_layers);
 extern "C" size_t      pdc_h2g_smem_bytes(int bg, int Z, int max_layers);
 extern "C" cudaError_t pdc_launch_h2g(const pdc_launch_params& prm, int bg, int block, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_enc_init_device();
-extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_cb* d_cbs, uint32_t n, const uint32_t* graphs, const uint32_t* crc_pow,
-                                      size_t smem, cudaStream_t stream);
+extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb, uint32_t max_cbs, const uint32_t* graphs,
+                                      const uint32_t* crc_pow, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_init_device();
 extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void* d_chunks, uint32_t nchunks,
                                         const float* d_symbols, const float* d_noise, int8_t* d_llrs, cudaStream_t stream);
