@@ -10,6 +10,7 @@
 #include "../../srsran_project_b200/adapters/channel_coding_factories_cuda.h"
 #include "../../srsran_project_b200/adapters/channel_modulation_factories_cuda.h"
 #include "../../srsran_project_b200/adapters/hw_accelerator_pusch_dec_cuda.h"
+#include "../../srsran_project_b200/adapters/pdsch_encoder_cuda.h"
 #include "../../srsran_project_b200/adapters/pusch_decoder_cuda.h"
 #include "crc_calculator_clmul_impl.h"
 #include "crc_calculator_lut_impl.h"
@@ -280,6 +281,42 @@ int adt_demodulate_soft(int8_t* llrs, const float* symbols_ri, const float* nois
                           span<const cf_t>(reinterpret_cast<const cf_t*>(symbols_ri), nof_symbols),
                           span<const float>(noise_vars, nof_symbols),
                           scheme);
+  return 0;
+}
+
+// The CUDA pdsch_encoder adapter behind the reference's interface: one encode() call. Returns 0, -1 = no device.
+int adt_pdsch_encode(uint8_t*       codeword,
+                     const uint8_t* tb_bytes,
+                     unsigned       tbs_bits,
+                     int            bg,
+                     unsigned       rv,
+                     unsigned       qm,
+                     unsigned       Nref,
+                     unsigned       nof_layers,
+                     unsigned       nof_ch_symbols)
+{
+  static std::shared_ptr<pdsch_encoder_factory> factory;
+  static std::unique_ptr<pdsch_encoder>              encoder;
+  try {
+    if (!factory) {
+      factory = create_pdsch_encoder_factory_cuda();
+      encoder = factory->create();
+    }
+  } catch (const std::exception&) {
+    return -1;
+  }
+  pdsch_encoder::configuration cfg;
+  cfg.base_graph     = (bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+  cfg.rv             = rv;
+  cfg.Nref           = Nref;
+  cfg.nof_layers     = nof_layers;
+  cfg.nof_ch_symbols = nof_ch_symbols;
+  cfg.mod            = (qm == 1)   ? modulation_scheme::BPSK
+                       : (qm == 2) ? modulation_scheme::QPSK
+                       : (qm == 4) ? modulation_scheme::QAM16
+                       : (qm == 6) ? modulation_scheme::QAM64
+                                   : modulation_scheme::QAM256;
+  encoder->encode(span<uint8_t>(codeword, nof_ch_symbols * qm), span<const uint8_t>(tb_bytes, tbs_bits / 8), cfg);
   return 0;
 }
 
