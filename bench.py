@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--chunk-tbs", type=int, default=8, help="transport blocks per submit on the end-to-end path")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target wall time of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-llr-producers", action="store_true", help="skip the soft demodulator + descrambler leg (SURVEY 8f N2)")
+    ap.add_argument("--no-llr-producers", action="store_true", help="skip the legs of the rows either side of the chain: soft demodulator + descrambler (SURVEY 8f N2), PDSCH encoder (N4)")
     ap.add_argument("--preheat-ms", type=float, default=200.0, help="untimed load before the warm-up steps (clock ramp)")
     return ap.parse_args()
 
@@ -609,6 +609,14 @@ def run_cuda_arm(args):
         llr_producers = bench_demod.run(ctx, n_tbs=wl["n_tbs"], steps=min(args.steps, 20), warmup=args.warmup,
                                         cpu=not args.no_cpu_baseline, hbm_peak_gbs=hbm_peak)
 
+    # ---- PDSCH encoder: the downlink mirror on the same slot shape; tools/bench_enc.py holds the leg ---------------
+    pdsch_encoder = None
+    if world == 1 and not args.no_llr_producers:
+        from tools import bench_enc
+
+        pdsch_encoder = bench_enc.run(ctx, n_tbs=wl["n_tbs"], steps=min(args.steps, 20), warmup=args.warmup,
+                                      cpu=not args.no_cpu_baseline, hbm_peak_gbs=hbm_peak)
+
     cfg = workload_config(args, wl)
     cfg["avg_iterations"] = float(np.where(res["iterations"] > 0, res["iterations"], MAX_ITER).mean())
     cfg["cb_crc_pass_fraction"] = float(ok.mean())
@@ -621,7 +629,7 @@ def run_cuda_arm(args):
                     "pipeline": f"{n_chunks} submissions of {args.chunk_tbs} TBs per step, {nof_tickets} in flight, "
                                 "not drained between steps"},
             "e2e_tb": tb_leg, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "llr_producers": llr_producers}
+            "llr_producers": llr_producers, "pdsch_encoder": pdsch_encoder}
     print(json.dumps(line), flush=True)
     ctx.close()
     ranks.close()
