@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 4
+#define PDC_ABI_VERSION 5
 
 typedef enum {
   PDC_OK               = 0,
@@ -210,18 +210,32 @@ typedef struct {
   uint8_t  bg;             /* 1 | 2 */
   uint8_t  Qm;             /* 1, 2, 4, 6, 8 (modulation_scheme as bits per symbol) */
   uint8_t  rv;             /* 0..3 */
-  uint8_t  nof_layers;     /* 1..4 */
+  uint8_t  nof_layers;     /* 1..4 (ignored when nof_ch_symbols == 0) */
   uint32_t tbs_bits;       /* transport block size in bits (multiple of 8) */
-  uint32_t nof_ch_symbols; /* channel symbols the transport block is mapped to, all layers together (multiple of nof_layers) */
+  uint32_t nof_ch_symbols; /* channel symbols the transport block is mapped to, all layers together (multiple of nof_layers);
+                              0 = the rate-matched lengths below are given explicitly */
   uint32_t Nref;           /* limited-buffer rate matching length, 0 = none */
   uint64_t tb_offset;      /* byte offset of the packed transport block (MSB first) in the input buffer */
   uint64_t cw_offset;      /* byte offset of the codeword in the output buffer */
+  /* Explicit rate-matched lengths, as hal::hw_pdsch_encoder_configuration carries them (hw_accelerator_pdsch_enc.h:44-51:
+   * that structure has no layer count, so E_r cannot be re-derived). Used only when nof_ch_symbols == 0, all 0 otherwise:
+   * the first nof_short_segments code blocks get cw_length_a bits, the others cw_length_b (multiples of Qm). */
+  uint32_t cw_length_a;
+  uint32_t cw_length_b;
+  uint32_t nof_short_segments;
+  uint32_t reserved;       /* 0 */
 } pdc_pdsch_tb_desc;
 
 pdc_status pdc_pdsch_encode(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t n, const uint8_t* tb_bytes, size_t tb_len,
                             uint8_t* codewords, size_t cw_len); /* host buffers, returns when the codewords are there */
 pdc_status pdc_pdsch_encode_device(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs_host, uint32_t n, const uint8_t* d_tb_bytes,
                                    uint8_t* d_codewords, void* stream); /* device pointers, asynchronous on stream */
+
+/* The segmentation pdc_pdsch_encode will use for a transport block (TS 38.212 5.2.2 as ldpc.h:128-214 and
+ * ldpc_segmenter_tx_impl.cpp derive it): number of code blocks C, lifting size Z, bits per code block before fillers K'
+ * (information + CRCs), filler bits K - K'. Any output pointer may be NULL. Host-only, no device work. */
+pdc_status pdc_pdsch_segmentation(int bg, uint32_t tbs_bits, uint32_t* nof_cbs, uint32_t* lifting_size, uint32_t* cb_info_bits,
+                                  uint32_t* nof_filler_bits);
 
 /* --- HARQ arena (ext_harq_buffer_context_repository.h:36-107 / free_harq_context_entry) --------------------------- */
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot);                               /* zero-fills the slot */

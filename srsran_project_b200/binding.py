@@ -54,7 +54,9 @@ DEMOD_SEG_DTYPE = np.dtype([("sym_offset", np.uint64), ("llr_offset", np.uint64)
                             ("reserved", np.uint16)])  # pdc_demod_seg
 PDSCH_TB_DTYPE = np.dtype([("bg", np.uint8), ("Qm", np.uint8), ("rv", np.uint8), ("nof_layers", np.uint8),
                            ("tbs_bits", np.uint32), ("nof_ch_symbols", np.uint32), ("Nref", np.uint32),
-                           ("tb_offset", np.uint64), ("cw_offset", np.uint64)])  # pdc_pdsch_tb_desc
+                           ("tb_offset", np.uint64), ("cw_offset", np.uint64), ("cw_length_a", np.uint32),
+                           ("cw_length_b", np.uint32), ("nof_short_segments", np.uint32),
+                           ("reserved", np.uint32)])  # pdc_pdsch_tb_desc
 PDC_MOD_PI2_BPSK, PDC_MOD_BPSK, PDC_MOD_QPSK, PDC_MOD_QAM16, PDC_MOD_QAM64, PDC_MOD_QAM256 = 0, 1, 2, 4, 6, 8
 PDC_DEMOD_F_DESCRAMBLE = 0x01
 assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
@@ -105,6 +107,8 @@ def load_library():
     lib.pdc_demodulate.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
     lib.pdc_pdsch_encode.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
     lib.pdc_pdsch_encode_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp]
+    u32p = ctypes.POINTER(ctypes.c_uint32)
+    lib.pdc_pdsch_segmentation.argtypes = [ctypes.c_int, ctypes.c_uint32, u32p, u32p, u32p, u32p]
     lib.pdc_harq_free.argtypes = [vp, ctypes.c_int32]
     lib.pdc_harq_read.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
@@ -121,8 +125,18 @@ def load_library():
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
-                    "pdc_demodulate_device", "pdc_demodulate", "pdc_pdsch_encode", "pdc_pdsch_encode_device", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
+                    "pdc_demodulate_device", "pdc_demodulate", "pdc_pdsch_encode", "pdc_pdsch_encode_device",
+                    "pdc_pdsch_segmentation", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
                     "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
+
+
+def pdsch_segmentation(bg, tbs_bits):
+    """(C, Z, K', fillers) the device encoder will use for a transport block (pdc_pdsch_segmentation); host-only."""
+    v = [ctypes.c_uint32() for _ in range(4)]
+    st = load_library().pdc_pdsch_segmentation(bg, tbs_bits, *[ctypes.byref(x) for x in v])
+    if st != 0:
+        raise PdcError(st)
+    return tuple(x.value for x in v)
 
 
 def make_descs(n):

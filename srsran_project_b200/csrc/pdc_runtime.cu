@@ -744,15 +744,34 @@ static pdc_status enc_plan(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t 
     const pdc_pdsch_tb_desc& d = tbs[t];
     enc_seg                  s;
     const bool qm_ok = d.Qm == 1 || d.Qm == 2 || d.Qm == 4 || d.Qm == 6 || d.Qm == 8;
-    if ((d.bg != 1 && d.bg != 2) || !qm_ok || d.rv > 3 || d.nof_layers == 0 || d.nof_layers > 4 || d.tbs_bits == 0 ||
-        (d.tbs_bits & 7) != 0 || d.tbs_bits + 24u > 1277992u || d.nof_ch_symbols == 0 || (d.nof_ch_symbols % d.nof_layers) != 0 ||
-        !enc_segmentation(d.bg, d.tbs_bits, s)) {
+    if ((d.bg != 1 && d.bg != 2) || !qm_ok || d.rv > 3 || d.tbs_bits == 0 || (d.tbs_bits & 7) != 0 || d.tbs_bits + 24u > 1277992u ||
+        d.reserved != 0 || !enc_segmentation(d.bg, d.tbs_bits, s)) {
       return PDC_ERR_INVALID_ARG; // ldpc_segmenter_tx_impl.cpp:40-55
     }
-    const uint64_t G = (uint64_t)d.nof_ch_symbols * d.Qm; // nof_ch_symbols counts every layer (ldpc_segmenter_tx_impl.cpp:93-100)
+    // Rate-matched lengths: derived from the channel symbols (ldpc_segmenter_helpers.h:82-100: the first C - rem code blocks
+    // get floor, the others ceil), or taken as given (nof_ch_symbols == 0: hal::hw_pdsch_encoder_configuration carries
+    // cw_length_a / cw_length_b / nof_short_segments and no layer count, hw_accelerator_pdsch_enc.h:44-51).
+    uint32_t nof_short = 0, E_short = 0, E_long = 0;
+    if (d.nof_ch_symbols != 0) {
+      if (d.nof_layers == 0 || d.nof_layers > 4 || (d.nof_ch_symbols % d.nof_layers) != 0 || d.cw_length_a != 0 || d.cw_length_b != 0 ||
+          d.nof_short_segments != 0 || (uint64_t)(d.nof_ch_symbols / d.nof_layers) < (uint64_t)s.C) {
+        return PDC_ERR_INVALID_ARG; // every code block needs at least one channel symbol
+      }
+      const uint32_t sym = d.nof_ch_symbols / d.nof_layers, base = sym / s.C, rem = sym % s.C;
+      nof_short = (uint32_t)s.C - rem;
+      E_short = (uint32_t)d.nof_layers * d.Qm * base, E_long = (uint32_t)d.nof_layers * d.Qm * (base + 1);
+    } else {
+      nof_short = d.nof_short_segments, E_short = d.cw_length_a, E_long = d.cw_length_b;
+      if (nof_short == 0 || nof_short > (uint32_t)s.C || E_short == 0 || (E_short % d.Qm) != 0 || (E_long % d.Qm) != 0 ||
+          (nof_short < (uint32_t)s.C && E_long == 0)) {
+        return PDC_ERR_INVALID_ARG;
+      }
+      E_long = (nof_short == (uint32_t)s.C) ? E_short : E_long;
+    }
+    const uint64_t G = (uint64_t)nof_short * E_short + (uint64_t)((uint32_t)s.C - nof_short) * E_long; // == nof_ch_symbols * Qm
     const size_t   te = (size_t)d.tb_offset + d.tbs_bits / 8, ce = (size_t)d.cw_offset + (size_t)G;
-    if ((uint64_t)(d.nof_ch_symbols / d.nof_layers) < (uint64_t)s.C || (tb_len != 0 && te > tb_len) || (cw_len != 0 && ce > cw_len)) {
-      return PDC_ERR_INVALID_ARG; // ldpc_segmenter_tx: every code block needs at least one channel symbol
+    if ((tb_len != 0 && te > tb_len) || (cw_len != 0 && ce > cw_len)) {
+      return PDC_ERR_INVALID_ARG;
     }
     max_tb = te > max_tb ? te : max_tb, max_cw = ce > max_cw ? ce : max_cw;
     const int Kb = (d.bg == 1) ? 22 : 10, Nfull = (d.bg == 1) ? 68 : 52, M = Nfull - Kb;
@@ -791,8 +810,6 @@ static pdc_status enc_plan(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t 
         }
       }
     }
-    // Rate-matched lengths (ldpc_segmenter_helpers.h:82-100): the first C - rem code blocks get floor, the others ceil.
-    const uint32_t sym = d.nof_ch_symbols / d.nof_layers, base = sym / s.C, rem = sym % s.C;
     auto rows_for = [&](uint32_t E) {
       if ((long long)t0 + E <= Lc) {
         const int tmax = t0 + (int)E - 1, idx = (tmax < n_info) ? tmax : tmax + fw;
@@ -804,8 +821,8 @@ static pdc_status enc_plan(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t 
     memset(&c, 0, sizeof(c));
     c.tb = d_tb + d.tb_offset, c.out = d_cw + d.cw_offset, c.tb_crc = d_crc_acc + t;
     c.tbs_bits = d.tbs_bits, c.nof_bits = (uint32_t)(s.Kp - s.cb_crc_bits);
-    c.nof_cbs = (uint32_t)s.C, c.nof_short = (uint32_t)s.C - rem;
-    c.E_short = (uint32_t)d.nof_layers * d.Qm * base, c.E_long = (uint32_t)d.nof_layers * d.Qm * (base + 1);
+    c.nof_cbs = (uint32_t)s.C, c.nof_short = nof_short;
+    c.E_short = E_short, c.E_long = E_long;
     c.Nref = d.Nref, c.nof_filler = (uint32_t)s.F;
     c.Z = (uint16_t)s.Z, c.graph_idx = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(s.Z));
     c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.tb_crc_type = (s.tb_crc_bits == 24) ? PDC_CRC24A : PDC_CRC16;
@@ -904,7 +921,7 @@ pdc_status pdc_pdsch_encode(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, uint32_t
     return st;
   }
   for (uint32_t t = 0; t != n; ++t) {
-    const size_t G = (size_t)tbs[t].nof_ch_symbols * tbs[t].Qm;
+    const size_t G = (size_t)cbs[t].nof_short * cbs[t].E_short + (size_t)(cbs[t].nof_cbs - cbs[t].nof_short) * cbs[t].E_long;
     CK(cudaMemcpyAsync(codewords + tbs[t].cw_offset, ctx->d_enc_out + tbs[t].cw_offset, G, cudaMemcpyDeviceToHost, stream));
   }
   CK(cudaStreamSynchronize(stream));
@@ -985,6 +1002,28 @@ uint32_t pdc_cb_max_layers(const pdc_cb_desc* d)
     return 0;
   }
   return (uint32_t)ml;
+}
+
+pdc_status pdc_pdsch_segmentation(int bg, uint32_t tbs_bits, uint32_t* nof_cbs, uint32_t* lifting_size, uint32_t* cb_info_bits,
+                                  uint32_t* nof_filler_bits)
+{
+  enc_seg s;
+  if ((bg != 1 && bg != 2) || tbs_bits == 0 || (tbs_bits & 7) != 0 || tbs_bits + 24u > 1277992u || !enc_segmentation(bg, tbs_bits, s)) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  if (nof_cbs) {
+    *nof_cbs = (uint32_t)s.C;
+  }
+  if (lifting_size) {
+    *lifting_size = (uint32_t)s.Z;
+  }
+  if (cb_info_bits) {
+    *cb_info_bits = (uint32_t)s.Kp;
+  }
+  if (nof_filler_bits) {
+    *nof_filler_bits = (uint32_t)s.F;
+  }
+  return PDC_OK;
 }
 
 } // extern "C"

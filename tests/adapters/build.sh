@@ -1,6 +1,7 @@
 #!/usr/bin/env bash
 # TEST INFRASTRUCTURE ONLY. Builds tests/adapters/_build/libadapter_harness.so: the UNMODIFIED reference transport-block
-# decoders (pusch_decoder_impl, pusch_decoder_hw_impl, rx_buffer_pool) compiled from the sources where they lie under
+# decoders (pusch_decoder_impl, pusch_decoder_hw_impl, rx_buffer_pool) and the reference's
+# pdsch_encoder_hw_impl, compiled from the sources where they lie under
 # /root/reference, linked with the CUDA adapters, behind the small C ABI of harness.cpp. Reuses the reference objects that
 # oracle/build_ref.sh already compiled (oracle/_ref/obj). Nothing is copied into the repo; outputs are git-ignored.
 set -euo pipefail
@@ -23,6 +24,7 @@ BASE="-std=c++17 -O2 -fPIC -march=x86-64-v3 -mtune=generic -DFMT_HEADER_ONLY -DA
 SRCS=(
   lib/phy/upper/channel_processors/pusch/pusch_decoder_impl.cpp
   lib/phy/upper/channel_processors/pusch/pusch_decoder_hw_impl.cpp
+  lib/phy/upper/channel_processors/pdsch/pdsch_encoder_hw_impl.cpp
   lib/phy/upper/rx_buffer_pool_impl.cpp
   lib/support/cpu_architecture_info.cpp
   lib/srsvec/copy.cpp

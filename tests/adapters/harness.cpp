@@ -6,9 +6,12 @@
 //   mode 2: the CUDA hal::hw_accelerator_pusch_dec inside the reference's pusch_decoder_hw_impl (drop-in boundary 2),
 //   mode 3: the CUDA srsran::pusch_decoder (srsran_project_b200/adapters/pusch_decoder_cuda.h): code blocks AND transport
 //           block assembly + CRC24A on the device, in place of the reference's TB decoders.
+// Downlink mirror: the CUDA srsran::pdsch_encoder, and the CUDA hal::hw_accelerator_pdsch_enc inside the
+// reference's UNMODIFIED pdsch_encoder_hw_impl (its segmenter and TB CRC on the host, everything else on the device).
 // Driven from Python (tests/test_adapters.py) through a small C ABI; the stimulus comes from tools/stimulus.
 #include "../../srsran_project_b200/adapters/channel_coding_factories_cuda.h"
 #include "../../srsran_project_b200/adapters/channel_modulation_factories_cuda.h"
+#include "../../srsran_project_b200/adapters/hw_accelerator_pdsch_enc_cuda.h"
 #include "../../srsran_project_b200/adapters/hw_accelerator_pusch_dec_cuda.h"
 #include "../../srsran_project_b200/adapters/pdsch_encoder_cuda.h"
 #include "../../srsran_project_b200/adapters/pusch_decoder_cuda.h"
@@ -21,6 +24,8 @@
 #include "ldpc/ldpc_rate_dematcher_avx512_impl.h"
 #include "ldpc/ldpc_rate_dematcher_impl.h"
 #include "ldpc/ldpc_segmenter_rx_impl.h"
+#include "ldpc/ldpc_segmenter_tx_impl.h"
+#include "phy/upper/channel_processors/pdsch/pdsch_encoder_hw_impl.h"
 #include "pusch_codeblock_decoder.h"
 #include "pusch_decoder_hw_impl.h"
 #include "pusch_decoder_impl.h"
@@ -301,6 +306,47 @@ int adt_pdsch_encode(uint8_t*       codeword,
     if (!factory) {
       factory = create_pdsch_encoder_factory_cuda();
       encoder = factory->create();
+    }
+  } catch (const std::exception&) {
+    return -1;
+  }
+  pdsch_encoder::configuration cfg;
+  cfg.base_graph     = (bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+  cfg.rv             = rv;
+  cfg.Nref           = Nref;
+  cfg.nof_layers     = nof_layers;
+  cfg.nof_ch_symbols = nof_ch_symbols;
+  cfg.mod            = (qm == 1)   ? modulation_scheme::BPSK
+                       : (qm == 2) ? modulation_scheme::QPSK
+                       : (qm == 4) ? modulation_scheme::QAM16
+                       : (qm == 6) ? modulation_scheme::QAM64
+                                   : modulation_scheme::QAM256;
+  encoder->encode(span<uint8_t>(codeword, nof_ch_symbols * qm), span<const uint8_t>(tb_bytes, tbs_bits / 8), cfg);
+  return 0;
+}
+
+// The CUDA hal::hw_accelerator_pdsch_enc inside the reference's pdsch_encoder_hw_impl (pdsch_encoder_hw_impl.cpp:31-186):
+// the reference computes the segmentation and hands the accelerator hal::hw_pdsch_encoder_configuration. Returns 0, -1 = no device.
+int adt_pdsch_encode_hw(uint8_t*       codeword,
+                        const uint8_t* tb_bytes,
+                        unsigned       tbs_bits,
+                        int            bg,
+                        unsigned       rv,
+                        unsigned       qm,
+                        unsigned       Nref,
+                        unsigned       nof_layers,
+                        unsigned       nof_ch_symbols)
+{
+  static std::unique_ptr<pdsch_encoder> encoder;
+  try {
+    if (!encoder) {
+      std::shared_ptr<hal::hw_accelerator_pdsch_enc_factory> hw_factory = hal::create_cuda_pdsch_enc_acc_factory({});
+      pdsch_encoder_hw_impl::sch_crc                         crcs       = {
+          make_crc(crc_generator_poly::CRC16), make_crc(crc_generator_poly::CRC24A), make_crc(crc_generator_poly::CRC24B)};
+      ldpc_segmenter_tx_impl::sch_crc seg_crcs = {
+          make_crc(crc_generator_poly::CRC16), make_crc(crc_generator_poly::CRC24A), make_crc(crc_generator_poly::CRC24B)};
+      encoder = std::make_unique<pdsch_encoder_hw_impl>(
+          crcs, std::make_unique<ldpc_segmenter_tx_impl>(seg_crcs), hw_factory->create());
     }
   } catch (const std::exception&) {
     return -1;

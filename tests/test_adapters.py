@@ -122,7 +122,8 @@ def test_adapter_library_exports():
     syms = subprocess.run(["nm", "-D", "--defined-only", "-C", ADAPTERS], capture_output=True, text=True).stdout
     for s in ("srsran::create_ldpc_decoder_factory_cuda", "srsran::create_ldpc_rate_dematcher_factory_cuda",
               "srsran::hal::create_cuda_pusch_dec_acc_factory", "srsran::create_pusch_decoder_factory_cuda",
-              "srsran::create_demodulation_mapper_factory_cuda", "srsran::create_pdsch_encoder_factory_cuda"):
+              "srsran::create_demodulation_mapper_factory_cuda", "srsran::create_pdsch_encoder_factory_cuda",
+              "srsran::hal::create_cuda_pdsch_enc_acc_factory"):
         assert s in syms, s
 
 
@@ -181,6 +182,28 @@ def test_cuda_pdsch_encoder_adapter_reproduces_the_golden_codewords():
         rc = lib.adt_pdsch_encode(ctypes.c_void_p(cw.ctypes.data), ctypes.c_void_p(tb.ctypes.data), ctypes.c_uint(tbs),
                                   ctypes.c_int(bg), ctypes.c_uint(rv), ctypes.c_uint(Qm), ctypes.c_uint(Nref),
                                   ctypes.c_uint(L), ctypes.c_uint(nsym))
+        assert rc == 0
+        got = np.frombuffer(hashlib.sha256(np.packbits(cw).tobytes()).digest(), np.uint8)
+        assert np.array_equal(got, g["digests"][k]), CASES[k]
+
+
+@pytest.mark.gpu
+def test_cuda_pdsch_enc_accelerator_inside_the_reference_hw_encoder():
+    """hal::hw_accelerator_pdsch_enc over pdc_pdsch_encode (adapters/hw_accelerator_pdsch_enc_cuda.cpp) inside the reference's
+    UNMODIFIED pdsch_encoder_hw_impl (TB mode: the reference segments and computes the TB CRC on the host, hands over
+    hal::hw_pdsch_encoder_configuration), against the digests recorded from the compiled pdsch_encoder_impl."""
+    import hashlib
+
+    from tools.enc_cases import CASES
+
+    lib = _lib()
+    g = np.load(os.path.join(HERE, "golden", "pdsch_enc_v1.npz"))
+    for k, (bg, tbs, Qm, L, nsym, rv, Nref) in enumerate(CASES):
+        tb = np.random.default_rng(500 + k).integers(0, 256, tbs // 8, dtype=np.uint8)
+        cw = np.zeros(nsym * Qm, np.uint8)
+        rc = lib.adt_pdsch_encode_hw(ctypes.c_void_p(cw.ctypes.data), ctypes.c_void_p(tb.ctypes.data), ctypes.c_uint(tbs),
+                                     ctypes.c_int(bg), ctypes.c_uint(rv), ctypes.c_uint(Qm), ctypes.c_uint(Nref),
+                                     ctypes.c_uint(L), ctypes.c_uint(nsym))
         assert rc == 0
         got = np.frombuffer(hashlib.sha256(np.packbits(cw).tobytes()).digest(), np.uint8)
         assert np.array_equal(got, g["digests"][k]), CASES[k]

@@ -93,6 +93,26 @@ def test_host_only_helpers():
     assert lib.pdc_cb_max_layers(d[0:1].ctypes.data) == 0
 
 
+def test_pdsch_segmentation_helper():
+    """pdc_pdsch_segmentation (host-only) against the TX-chain restatement of TS 38.212 5.2.2 (tools/stimulus, pinned to the
+    compiled reference by tests/test_enc_oracle.py) over a sweep of transport block sizes, and its contract."""
+    from srsran_project_b200 import binding as B
+    from tools import stimulus as S
+
+    rng = np.random.default_rng(12)
+    sizes = [8, 24, 96, 288, 296, 3816, 3824, 3832, 8424, 8448, 8456, 16896, 25344, 1277968]
+    sizes += [int(v) * 8 for v in rng.integers(1, 159746, 200)]
+    for bg in (1, 2):
+        for tbs in sizes:
+            seg = S.segmentation(bg, tbs)
+            C, Z, Kp, F = B.pdsch_segmentation(bg, tbs)
+            assert (C, Z, F) == (seg["C"], seg["Z"], seg["F"]), (bg, tbs)
+            assert Kp + F == seg["K"], (bg, tbs)
+    for bg, tbs in ((0, 96), (3, 96), (1, 0), (1, 100), (1, 1277976)):
+        with pytest.raises(B.PdcError):
+            B.pdsch_segmentation(bg, tbs)
+
+
 def test_no_device_means_no_context():
     """No CPU fallback: without a CUDA device the library refuses to create a context and says why."""
     from srsran_project_b200 import binding as B

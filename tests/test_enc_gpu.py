@@ -92,6 +92,39 @@ def test_contract_violations(acc):
         acc.pdsch_encode(tbs, data, cw_len - 1)
 
 
+def test_explicit_rate_matched_lengths_give_the_same_codewords(acc):
+    """nof_ch_symbols == 0: the code-block lengths come as hal::hw_pdsch_encoder_configuration carries them (cw_length_a,
+    cw_length_b, nof_short_segments); same codewords as the derived lengths, and the contract of that mode."""
+    from srsran_project_b200 import binding as B
+    from tools import stimulus as S
+
+    cases = list(CASES)
+    tbs, data, cw_len = make_batch(B, cases)
+    want = acc.pdsch_encode(tbs, data, cw_len)
+    explicit = tbs.copy()
+    for d, (bg, nbits, Qm, L, nsym, rv, Nref) in zip(explicit, cases):
+        C = B.pdsch_segmentation(bg, nbits)[0]
+        Es = S.rm_lengths(C, nsym * Qm, L, Qm)
+        nshort = sum(1 for e in Es if e == Es[0])
+        d["nof_layers"], d["nof_ch_symbols"] = 0, 0
+        d["cw_length_a"], d["cw_length_b"], d["nof_short_segments"] = Es[0], (Es[-1] if nshort < C else 0), nshort
+    got = acc.pdsch_encode(explicit, data, cw_len)
+    assert np.array_equal(got, want)
+    one = explicit[-2:-1].copy()  # a segmented transport block
+    assert B.pdsch_segmentation(int(one[0]["bg"]), int(one[0]["tbs_bits"]))[0] > 1
+    one[0]["tb_offset"], one[0]["cw_offset"] = 0, 0
+    for field, value in (("cw_length_a", 0), ("cw_length_a", int(one[0]["cw_length_a"]) + 1), ("nof_short_segments", 0),
+                         ("nof_short_segments", 153), ("reserved", 1)):
+        bad = one.copy()
+        bad[0][field] = value
+        with pytest.raises(B.PdcError):
+            acc.pdsch_encode(bad, np.zeros(200000, np.uint8), 4 << 20)
+    mixed = tbs[:1].copy()  # both forms at once
+    mixed[0]["cw_length_a"] = 8
+    with pytest.raises(B.PdcError):
+        acc.pdsch_encode(mixed, data, cw_len)
+
+
 def test_encode_then_decode_on_the_device(acc):
     """Downlink mirror meets uplink chain: the device encodes a 152-code-block transport block, the codeword bits become LLRs
     (+-20, three in a thousand flipped to weak wrong values) on the device, and pdc_decode_device_tbs returns the transport block."""
