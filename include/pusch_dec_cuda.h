@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 5
+#define PDC_ABI_VERSION 6
 
 typedef enum {
   PDC_OK               = 0,
@@ -199,6 +199,51 @@ pdc_status pdc_demodulate_device(pdc_ctx* ctx, const pdc_demod_seg* segs_host, u
  * nof_symbols / llr_bytes: sizes of the host arrays (every segment must lie inside). */
 pdc_status pdc_demodulate(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, const float* symbols, const float* noise_vars,
                           size_t nof_symbols, int8_t* llrs, size_t llr_bytes);
+
+/* --- UL-SCH demultiplexer: ulsch_demultiplex (ulsch_demultiplex.h:36-103, ulsch_demultiplex_impl.cpp) ---------
+ * Splits the descrambled soft bits of one PUSCH codeword into the UL-SCH data stream (what the code-block chain consumes) and the
+ * HARQ-ACK / CSI Part 1 / CSI Part 2 streams (TS 38.212 6.2.7), with the reference's handling of the reserved REs (1- or 2-bit
+ * HARQ-ACK punctures them: those soft bits reach the other streams as zeros) and of the x / y placeholder bits (their
+ * scrambling is undone: needs c_init). One descriptor per codeword carries ulsch_demultiplex::configuration; the input is the
+ * whole allocation in demodulation order (OFDM symbol by symbol, the output of pdc_demodulate* with PDC_DEMOD_F_DESCRAMBLE,
+ * scramble_offset == position in the codeword). A PUSCH without UCI needs no call: its soft bits are the UL-SCH stream. */
+#define PDC_DEMUX_F_CSI2_AFTER_CSI1 0x01 /* CSI Part 2 REs are allocated from the OFDM symbol in which CSI Part 1 ends, as when
+                                            set_csi_part2() is called from the CSI Part 1 feedback (pusch_processor_impl.cpp:73-98);
+                                            without the flag: from the first symbol (set right after demultiplex(), TS 38.212) */
+typedef struct {
+  uint8_t  Qm;                          /* 1, 2, 4, 6, 8 */
+  uint8_t  nof_layers;                  /* 1..4 */
+  uint8_t  start_symbol_index;          /* first OFDM symbol of the allocation */
+  uint8_t  nof_symbols;                 /* start_symbol_index + nof_symbols <= 14 */
+  uint8_t  dmrs_type;                   /* 1 | 2 */
+  uint8_t  nof_cdm_groups_without_data; /* 1..2 (type 1), 1..3 (type 2) */
+  uint16_t dmrs_symbol_mask;            /* bit l: OFDM symbol l of the slot carries DM-RS */
+  uint16_t nof_prb;                     /* 1..275 */
+  uint8_t  flags;                       /* PDC_DEMUX_F_* */
+  uint8_t  reserved;                    /* 0 */
+  uint32_t nof_harq_ack_rvd;            /* soft bits reserved for HARQ-ACK (0 unless nof_harq_ack_bits <= 2) */
+  uint32_t nof_harq_ack_bits, nof_enc_harq_ack_bits;
+  uint32_t nof_csi_part1_bits, nof_enc_csi_part1_bits;
+  uint32_t nof_csi_part2_bits, nof_enc_csi_part2_bits;
+  uint32_t c_init;                      /* scrambling initial state of the codeword */
+  uint32_t reserved2;                   /* 0 */
+  uint64_t in_offset;                   /* byte offset of the codeword's first soft bit in the input buffer */
+  uint64_t sch_offset;                  /* byte offsets of the four streams in the output buffer */
+  uint64_t harq_ack_offset;
+  uint64_t csi_part1_offset;
+  uint64_t csi_part2_offset;
+} pdc_ulsch_demux_desc;
+
+/* Soft bits of the codeword and of each stream: lens[0] input, [1] UL-SCH, [2] HARQ-ACK, [3] CSI Part 1, [4] CSI Part 2.
+ * PDC_ERR_INVALID_ARG if the configuration is inconsistent (the reference asserts: UCI that does not fit the allocation,
+ * encoded lengths that are not whole REs, ...). Host-only. */
+pdc_status pdc_ulsch_demux_lengths(const pdc_ulsch_demux_desc* d, uint32_t lens[5]);
+/* Device pointers, asynchronous on stream. Streams of different codewords / kinds must not overlap in d_out. */
+pdc_status pdc_ulsch_demultiplex_device(pdc_ctx* ctx, const pdc_ulsch_demux_desc* descs_host, uint32_t n, const int8_t* d_in,
+                                        int8_t* d_out, void* stream);
+/* Host buffers: copies in, runs, copies the streams out, returns when they are in `out`. */
+pdc_status pdc_ulsch_demultiplex(pdc_ctx* ctx, const pdc_ulsch_demux_desc* descs, uint32_t n, const int8_t* in, size_t in_len,
+                                 int8_t* out, size_t out_len);
 
 /* --- PDSCH transport-block encoder (the downlink mirror) ----------------------------------------------------
  * pdsch_encoder::encode (pdsch_encoder.h:48-73, pdsch_encoder_impl.cpp:31-80): TB CRC attachment, segmentation, code-block

@@ -69,6 +69,7 @@ SRCS=(
   lib/phy/upper/sequence_generators/pseudo_random_generator_impl.cpp
   $CC_DIR/ldpc/ldpc_segmenter_tx_impl.cpp
   lib/phy/upper/channel_processors/pdsch/pdsch_encoder_impl.cpp
+  lib/phy/upper/channel_processors/pusch/ulsch_demultiplex_impl.cpp
 )
 # Extra reference units may be appended by the caller (e.g. the whole pusch_decoder for the TB-level harness).
 SRCS+=(${REF_EXTRA_SRCS:-})
@@ -88,5 +89,6 @@ for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
 $CXX $BASE $INC -c "$HERE/ref_shim.cpp" -o "$OBJ/ref_shim.o"
 $CXX $BASE $INC -I$REF -c "$HERE/ref_shim_demod.cpp" -o "$OBJ/ref_shim_demod.o"
 $CXX $BASE $INC -I$REF -c "$HERE/ref_shim_pdsch.cpp" -o "$OBJ/ref_shim_pdsch.o"
-$CXX -shared -o "$OUT/libsrsran_ref.so" "$OBJ/ref_shim.o" "$OBJ/ref_shim_demod.o" "$OBJ/ref_shim_pdsch.o" "${objs[@]}" -lpthread
+$CXX $BASE $INC -I$REF -c "$HERE/ref_shim_demux.cpp" -o "$OBJ/ref_shim_demux.o"
+$CXX -shared -o "$OUT/libsrsran_ref.so" "$OBJ/ref_shim.o" "$OBJ/ref_shim_demod.o" "$OBJ/ref_shim_pdsch.o" "$OBJ/ref_shim_demux.o" "${objs[@]}" -lpthread
 echo "built $OUT/libsrsran_ref.so"

@@ -57,6 +57,16 @@ PDSCH_TB_DTYPE = np.dtype([("bg", np.uint8), ("Qm", np.uint8), ("rv", np.uint8),
                            ("tb_offset", np.uint64), ("cw_offset", np.uint64), ("cw_length_a", np.uint32),
                            ("cw_length_b", np.uint32), ("nof_short_segments", np.uint32),
                            ("reserved", np.uint32)])  # pdc_pdsch_tb_desc
+ULSCH_DEMUX_DTYPE = np.dtype([("Qm", np.uint8), ("nof_layers", np.uint8), ("start_symbol_index", np.uint8),
+                              ("nof_symbols", np.uint8), ("dmrs_type", np.uint8), ("nof_cdm_groups_without_data", np.uint8),
+                              ("dmrs_symbol_mask", np.uint16), ("nof_prb", np.uint16), ("flags", np.uint8), ("reserved", np.uint8),
+                              ("nof_harq_ack_rvd", np.uint32), ("nof_harq_ack_bits", np.uint32),
+                              ("nof_enc_harq_ack_bits", np.uint32), ("nof_csi_part1_bits", np.uint32),
+                              ("nof_enc_csi_part1_bits", np.uint32), ("nof_csi_part2_bits", np.uint32),
+                              ("nof_enc_csi_part2_bits", np.uint32), ("c_init", np.uint32), ("reserved2", np.uint32),
+                              ("in_offset", np.uint64), ("sch_offset", np.uint64), ("harq_ack_offset", np.uint64),
+                              ("csi_part1_offset", np.uint64), ("csi_part2_offset", np.uint64)])  # pdc_ulsch_demux_desc
+PDC_DEMUX_F_CSI2_AFTER_CSI1 = 0x01
 PDC_MOD_PI2_BPSK, PDC_MOD_BPSK, PDC_MOD_QPSK, PDC_MOD_QAM16, PDC_MOD_QAM64, PDC_MOD_QAM256 = 0, 1, 2, 4, 6, 8
 PDC_DEMOD_F_DESCRAMBLE = 0x01
 assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
@@ -105,6 +115,9 @@ def load_library():
     lib.pdc_decode_device_tbs.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, vp, vp, vp, vp, vp, vp]
     lib.pdc_demodulate_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp, vp]
     lib.pdc_demodulate.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
+    lib.pdc_ulsch_demux_lengths.argtypes = [vp, vp]
+    lib.pdc_ulsch_demultiplex_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp]
+    lib.pdc_ulsch_demultiplex.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
     lib.pdc_pdsch_encode.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
     lib.pdc_pdsch_encode_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp]
     u32p = ctypes.POINTER(ctypes.c_uint32)
@@ -125,7 +138,8 @@ def load_library():
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
-                    "pdc_demodulate_device", "pdc_demodulate", "pdc_pdsch_encode", "pdc_pdsch_encode_device",
+                    "pdc_demodulate_device", "pdc_demodulate", "pdc_ulsch_demux_lengths",
+                    "pdc_ulsch_demultiplex_device", "pdc_ulsch_demultiplex", "pdc_pdsch_encode", "pdc_pdsch_encode_device",
                     "pdc_pdsch_segmentation", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
                     "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
 
@@ -137,6 +151,15 @@ def pdsch_segmentation(bg, tbs_bits):
     if st != 0:
         raise PdcError(st)
     return tuple(x.value for x in v)
+
+
+def ulsch_demux_lengths(desc):
+    """(input, UL-SCH, HARQ-ACK, CSI Part 1, CSI Part 2) soft bits for one pdc_ulsch_demux_desc record; host-only."""
+    lens = np.zeros(5, np.uint32)
+    st = load_library().pdc_ulsch_demux_lengths(desc.ctypes.data, lens.ctypes.data)
+    if st != 0:
+        raise PdcError(st)
+    return tuple(int(v) for v in lens)
 
 
 def make_descs(n):
@@ -247,6 +270,19 @@ class PuschDecCuda:
     def demodulate_device(self, segs, d_symbols_ptr, d_noise_ptr, d_llrs_ptr, stream_ptr=None):
         self._check(self.lib.pdc_demodulate_device(self.h, segs.ctypes.data, segs.size, d_symbols_ptr, d_noise_ptr,
                                                    d_llrs_ptr, stream_ptr))
+
+    # --- UL-SCH demultiplexer -----------------------------------------------------------------------------------------------
+    def ulsch_demultiplex(self, descs, llrs, out_len):
+        """Host-buffer entry: llrs = descrambled codewords, returns the output buffer holding the four streams of each."""
+        llrs = np.ascontiguousarray(llrs, np.int8)
+        out = np.zeros(out_len, np.int8)
+        self._check(self.lib.pdc_ulsch_demultiplex(self.h, descs.ctypes.data, descs.size, llrs.ctypes.data, llrs.size,
+                                                   out.ctypes.data, out.size))
+        return out
+
+    def ulsch_demultiplex_device(self, descs, d_in_ptr, d_out_ptr, stream_ptr=None):
+        self._check(self.lib.pdc_ulsch_demultiplex_device(self.h, descs.ctypes.data, descs.size, d_in_ptr, d_out_ptr,
+                                                          stream_ptr))
 
     # --- PDSCH transport-block encoder (downlink mirror) -------------------------------------------------------------------
     def pdsch_encode(self, tbs, tb_bytes, cw_len):

@@ -26,6 +26,7 @@
 // recurrence W[j + 31] = W[j + 3] ^ W[j] (the characteristic polynomial over GF(2) commutes with squaring, so what holds
 // for bits at distance 1 holds for words at distance 32). The eight arithmetic warps meet it at one barrier before the stores.
 #include "../../include/pusch_dec_cuda.h"
+#include "pdc_device.cuh"
 #include <cmath>
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -533,6 +534,8 @@ __global__ void __launch_bounds__(PDC_DEMOD_THREADS, 4)
     }
   }
 }
+
+#include "pdc_kernel_demux.cuh"
 
 // ---- host side ---------------------------------------------------------------------------------------------------------------
 namespace {

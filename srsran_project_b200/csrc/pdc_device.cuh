@@ -73,6 +73,22 @@ __device__ __forceinline__ pdc_dev_enc_cb pdc_enc_cb_of(const pdc_dev_enc_tb& t,
   return c;
 }
 
+// One OFDM symbol of one codeword for the UL-SCH demultiplexer, as the host plans it (ulsch_demultiplex_impl.cpp:330-463 in
+// closed form: every RE set of the reference is "every d-th candidate, the first m of them"); the kernel rebuilds the sets.
+struct pdc_dev_demux_sym {
+  const int8_t* in;                           // first soft bit of the symbol (descrambled)
+  int8_t *      sch, *harq, *csi1, *csi2;     // where this symbol's share of each stream starts
+  uint32_t      nof_re, nbpr;                 // REs of the symbol, soft bits per RE (Qm * layers)
+  uint32_t      scramble_pos, c_init;         // position of the symbol's first soft bit in the scrambling sequence
+  uint32_t      rvd_d, rvd_m;                 // reserved REs: of all REs
+  uint32_t      harq_d, harq_m;               // HARQ-ACK: of all REs (more than 2 bits) or of the reserved ones (harq_of_rvd)
+  uint32_t      csi1_d, csi1_m;               // CSI Part 1: of the REs that are neither HARQ-ACK nor reserved
+  uint32_t      csi2_d, csi2_m;               // CSI Part 2: of the REs that are neither HARQ-ACK (> 2 bits) nor CSI Part 1
+  uint8_t       Qm, harq_of_rvd;
+  uint8_t       harq_ph, csi1_ph, csi2_ph;    // 1 | 2: placeholder handling for that many bits, 0: plain copy
+  uint8_t       pad[3];
+};
+
 // Row structure of the two base graphs (degrees and prefix sums), uploaded once per process.
 struct pdc_bg_rows {
   uint16_t start[2][48];

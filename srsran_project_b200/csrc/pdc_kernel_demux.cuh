@@ -1,0 +1,222 @@
+// UL-SCH demultiplexer on the device: ulsch_demultiplex_impl.cpp. Included by pdc_demod.cu (it shares the
+// scrambling-sequence generator, needed to undo the scrambling of the placeholder bits).
+//
+// One CTA per (codeword, OFDM symbol). The host has reduced the reference's per-symbol set construction (:330-463) to a few
+// integers: every set is "every d-th candidate, the first m of them" (re_set_select, :77-100). The CTA rebuilds the sets:
+//   reserved  = select(all REs)                                      rank closed-form (i / d)
+//   HARQ-ACK  = select(all REs)           (more than 2 bits)         rank closed-form
+//             = select(reserved)          (1 or 2 bits)              rank closed-form ((i / rvd_d) / d)
+//   CSI 1     = select(not HARQ-ACK, not reserved)                   candidate rank by a block scan
+//   CSI 2     = select(not HARQ-ACK (> 2 bits), not CSI 1)           candidate rank by a block scan
+//   UL-SCH    = not HARQ-ACK (> 2 bits), not CSI 1, not CSI 2        rank by a block scan
+// then moves the soft bits: every RE goes to its stream at rank * nbpr; REs punctured by a 1- or 2-bit HARQ-ACK go to the
+// HARQ-ACK stream as well and reach their own stream as zeros (:487-500); placeholder REs get the scrambling of their x / y
+// bits undone (:106-196).
+#pragma once
+
+#define PDC_DEMUX_THREADS 256
+#define PDC_DEMUX_MAX_RE 3300 /* MAX_RB * NRE */
+
+// Exclusive prefix of `count` over the CTA (contiguous REs per thread, so thread order is RE order).
+__device__ __forceinline__ uint32_t demux_block_scan(uint32_t count, uint32_t* s_warp)
+{
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t  incl = count;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) {
+      incl += v;
+    }
+  }
+  __syncthreads(); // s_warp may still be read from the previous scan
+  if (lane == 31) {
+    s_warp[warp] = incl;
+  }
+  __syncthreads();
+  uint32_t base = 0;
+#pragma unroll
+  for (int w = 0; w < PDC_DEMUX_THREADS / 32; ++w) {
+    base += (w < warp) ? s_warp[w] : 0u;
+  }
+  return base + incl - count;
+}
+
+__device__ __forceinline__ bool demux_selected(uint32_t rank, uint32_t d, uint32_t m)
+{
+  return m != 0 && (rank % d) == 0 && (rank / d) < m;
+}
+
+// Placeholder handling of one soft bit: b = index within its modulation symbol, mask / mask_prev = scrambling bits of this soft
+// bit and of the one before it. 1 bit (:106-150): bit 0 kept, bit 1 re-scrambled with the mask of bit 0, others unscrambled.
+// 2 bits (:152-196): bits 0 and 1 kept, others unscrambled.
+__device__ __forceinline__ int demux_placeholder(int v, uint32_t b, uint32_t mask, uint32_t mask_prev, int ph)
+{
+  if (b == 0 || (b == 1 && ph == 2)) {
+    return v;
+  }
+  const uint32_t flip = (b == 1) ? (mask ^ mask_prev) : mask;
+  return flip ? -v : v;
+}
+
+// Per-RE word in s_cls: [2:0] stream (0 UL-SCH, 1 HARQ-ACK, 2 CSI Part 1, 3 CSI Part 2), [3] punctured by a 1- / 2-bit
+// HARQ-ACK, [15:4] rank in its stream, [27:16] rank in the HARQ-ACK stream when punctured.
+template <bool WORDS>
+__device__ __forceinline__ void demux_move(const pdc_dev_demux_sym& sy, const uint32_t* s_cls, const uint32_t* s_seq, bool any_ph)
+{
+  constexpr uint32_t W     = WORDS ? 4u : 1u;
+  const uint32_t     total = sy.nof_re * sy.nbpr;
+  const uint32_t     qm    = sy.Qm;
+  for (uint32_t j = threadIdx.x * W; j < total; j += PDC_DEMUX_THREADS * W) {
+    const uint32_t re = j / sy.nbpr, k = j - re * sy.nbpr;
+    const uint32_t c  = s_cls[re];
+    const uint32_t stream = c & 7u, rank = (c >> 4) & 0xfffu;
+    const bool     punct  = (c & 8u) != 0;
+    uint32_t       raw;
+    if (WORDS) {
+      raw = *reinterpret_cast<const uint32_t*>(sy.in + j);
+    } else {
+      raw = (uint8_t)sy.in[j];
+    }
+    int8_t*   dst = (stream == 0) ? sy.sch : (stream == 1) ? sy.harq : (stream == 2) ? sy.csi1 : sy.csi2;
+    const int ph  = (stream == 1) ? sy.harq_ph : (stream == 2) ? sy.csi1_ph : (stream == 3) ? sy.csi2_ph : 0;
+    uint32_t  own = 0, hq = 0;
+#pragma unroll
+    for (uint32_t q = 0; q < W; ++q) {
+      int v = (int8_t)(raw >> (8 * q));
+      if (any_ph && qm > 1 && (punct || ph != 0)) {
+        const uint32_t p = j + q, b = (k + q) % qm;
+        const uint32_t mk = (s_seq[p >> 5] >> (p & 31u)) & 1u;
+        const uint32_t mp = (p == 0) ? 0u : (s_seq[(p - 1) >> 5] >> ((p - 1) & 31u)) & 1u;
+        if (punct) {
+          hq |= (uint32_t)(uint8_t)demux_placeholder(v, b, mk, mp, sy.harq_ph) << (8 * q);
+        }
+        if (ph != 0) {
+          v = demux_placeholder(v, b, mk, mp, ph);
+        }
+      } else if (punct) {
+        hq |= (uint32_t)(uint8_t)v << (8 * q);
+      }
+      own |= (uint32_t)(uint8_t)v << (8 * q);
+    }
+    if (punct) {
+      const uint32_t rh = (c >> 16) & 0xfffu;
+      if (WORDS) {
+        *reinterpret_cast<uint32_t*>(sy.harq + rh * sy.nbpr + k) = hq;
+      } else {
+        sy.harq[rh * sy.nbpr + k] = (int8_t)hq;
+      }
+      own = 0; // srsvec::zero(re_data) after the HARQ-ACK extraction
+    }
+    if (WORDS) {
+      *reinterpret_cast<uint32_t*>(dst + rank * sy.nbpr + k) = own;
+    } else {
+      dst[rank * sy.nbpr + k] = (int8_t)own;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(const pdc_dev_demux_sym* __restrict__ syms)
+{
+  extern __shared__ uint32_t s_dyn[];
+  __shared__ uint32_t        s_warp[PDC_DEMUX_THREADS / 32];
+  const pdc_dev_demux_sym    sy    = syms[blockIdx.x];
+  uint32_t*                  s_cls = s_dyn;                    // nof_re words
+  uint32_t*                  s_w1  = s_dyn + PDC_DEMUX_MAX_RE; // sequence words (and the x1 history), then the x2 history
+  const uint32_t             M     = sy.nof_re;
+  const int                  tid   = threadIdx.x;
+  const bool any_ph = sy.Qm > 1 && ((sy.harq_m != 0 && sy.harq_ph != 0) || (sy.csi1_m != 0 && sy.csi1_ph != 0) ||
+                                    (sy.csi2_m != 0 && sy.csi2_ph != 0));
+
+  // ---- scrambling bits of the symbol (only when a placeholder RE lies in it): the last warp ------------------------------------
+  const uint32_t nwords = (M * sy.nbpr + 31) / 32 + 1;
+  if (any_ph && tid >= PDC_DEMUX_THREADS - 32) {
+    uint32_t*   s_w2 = s_w1 + nwords + 64;
+    prg_history h;
+    h.c_init = 0, h.start = 0, h.n = 0;
+    prg_generate(d_prg_jump, d_prg_word, s_w1, s_w1, s_w2, (int)nwords, sy.c_init, sy.scramble_pos, tid & 31, h);
+  }
+
+  // ---- sets: contiguous REs per thread, up to three scans ---------------------------------------------------------------------
+  const uint32_t per = (M + PDC_DEMUX_THREADS - 1) / PDC_DEMUX_THREADS;
+  const uint32_t i0 = min(M, (uint32_t)tid * per), i1 = min(M, i0 + per);
+  auto is_rvd  = [&](uint32_t i) { return demux_selected(i, sy.rvd_d, sy.rvd_m); };
+  auto is_hq_a = [&](uint32_t i) { return !sy.harq_of_rvd && demux_selected(i, sy.harq_d, sy.harq_m); };
+  // CSI Part 1 among the REs that are neither HARQ-ACK nor reserved.
+  {
+    uint32_t n = 0;
+    for (uint32_t i = i0; i < i1; ++i) {
+      n += (!is_hq_a(i) && !is_rvd(i)) ? 1u : 0u;
+    }
+    uint32_t r = (sy.csi1_m != 0) ? demux_block_scan(n, s_warp) : 0u;
+    for (uint32_t i = i0; i < i1; ++i) {
+      uint32_t c = 0;
+      if (is_hq_a(i)) {
+        c = 1u | ((i / sy.harq_d) << 4);
+      } else if (!is_rvd(i)) {
+        if (demux_selected(r, sy.csi1_d, sy.csi1_m)) {
+          c = 2u | ((r / sy.csi1_d) << 4);
+        }
+        ++r;
+      }
+      s_cls[i] = c;
+    }
+  }
+  // CSI Part 2 among what is left of the UCI candidates (reserved REs included).
+  if (sy.csi2_m != 0) {
+    uint32_t n = 0;
+    for (uint32_t i = i0; i < i1; ++i) {
+      n += (s_cls[i] == 0) ? 1u : 0u;
+    }
+    uint32_t r = demux_block_scan(n, s_warp);
+    for (uint32_t i = i0; i < i1; ++i) {
+      if (s_cls[i] == 0) {
+        if (demux_selected(r, sy.csi2_d, sy.csi2_m)) {
+          s_cls[i] = 3u | ((r / sy.csi2_d) << 4);
+        }
+        ++r;
+      }
+    }
+  }
+  // UL-SCH: everything else; HARQ-ACK of 1 or 2 bits punctures its reserved REs whatever they carry.
+  {
+    uint32_t n = 0;
+    for (uint32_t i = i0; i < i1; ++i) {
+      n += (s_cls[i] == 0) ? 1u : 0u;
+    }
+    uint32_t r = demux_block_scan(n, s_warp);
+    for (uint32_t i = i0; i < i1; ++i) {
+      uint32_t c = s_cls[i];
+      if (c == 0) {
+        c = r << 4;
+        ++r;
+      }
+      if (sy.harq_of_rvd && is_rvd(i) && demux_selected(i / sy.rvd_d, sy.harq_d, sy.harq_m)) {
+        c |= 8u | (((i / sy.rvd_d) / sy.harq_d) << 16);
+      }
+      s_cls[i] = c;
+    }
+  }
+  __syncthreads();
+
+  // ---- soft bits ----------------------------------------------------------------------------------------------------------------
+  const uintptr_t align = reinterpret_cast<uintptr_t>(sy.in) | reinterpret_cast<uintptr_t>(sy.sch) |
+                          reinterpret_cast<uintptr_t>(sy.harq) | reinterpret_cast<uintptr_t>(sy.csi1) |
+                          reinterpret_cast<uintptr_t>(sy.csi2) | sy.nbpr;
+  if ((align & 3u) == 0) {
+    demux_move<true>(sy, s_cls, s_w1, any_ph);
+  } else {
+    demux_move<false>(sy, s_cls, s_w1, any_ph);
+  }
+}
+
+extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_t nsyms, bool placeholders, cudaStream_t stream)
+{
+  if (nsyms == 0) {
+    return cudaSuccess;
+  }
+  // Set words; with placeholders also the sequence words of the largest symbol (3300 REs x 32 soft bits) and the two histories.
+  const size_t smem = sizeof(uint32_t) * (PDC_DEMUX_MAX_RE + (placeholders ? 2 * (PDC_DEMUX_MAX_RE + 2 + 64) : 0));
+  pdc_ulsch_demux_kernel<<<nsyms, PDC_DEMUX_THREADS, smem, stream>>>(d_syms);
+  return cudaGetLastError();
+}

@@ -150,6 +150,13 @@ void pdc_destroy(pdc_ctx* ctx)
       cudaEventDestroy(d.done);
     }
   }
+  for (pdc_ctx::demod_slot& d : ctx->demux_ring) {
+    cudaFree(d.d_desc);
+    if (d.done) {
+      cudaEventDestroy(d.done);
+    }
+  }
+  cudaFree(ctx->d_demux_in), cudaFree(ctx->d_demux_out);
   for (pdc_ctx::demod_slot& d : ctx->enc_ring) {
     cudaFree(d.d_desc);
     if (d.done) {
@@ -687,6 +694,265 @@ pdc_status pdc_demodulate(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32_t n, c
   CK(cudaStreamSynchronize(stream));
   return PDC_OK;
 }
+
+// ---- UL-SCH demultiplexer --------------------------------------------------------------------------------------
+namespace {
+// d and the number of REs taken when `remainder` REs are still to place among `avail` candidates
+// (ulsch_demultiplex_impl.cpp:361-366 and the four copies of it).
+inline void demux_step(uint32_t remainder, uint32_t avail, uint32_t& d, uint32_t& m)
+{
+  d = 1, m = avail;
+  if (remainder < avail) {
+    d = avail / remainder, m = remainder;
+  }
+}
+
+// configure_current_ofdm_symbol (ulsch_demultiplex_impl.cpp:330-463) for every OFDM symbol of the allocation, in closed form:
+// the sets are never built on the host, only their sizes. Offsets in `syms` are relative to the codeword / stream starts
+// (kept in the pointer fields as integers until the caller rebases them). lens: input, UL-SCH, HARQ-ACK, CSI 1, CSI 2.
+pdc_status demux_plan(const pdc_ulsch_demux_desc& c, std::vector<pdc_dev_demux_sym>* syms, uint32_t lens[5], bool& placeholders)
+{
+  const bool qm_ok = c.Qm == 1 || c.Qm == 2 || c.Qm == 4 || c.Qm == 6 || c.Qm == 8;
+  if (!qm_ok || c.nof_layers == 0 || c.nof_layers > 4 || c.nof_prb == 0 || c.nof_prb > 275 || c.nof_symbols == 0 ||
+      c.start_symbol_index + c.nof_symbols > 14 || (c.dmrs_type != 1 && c.dmrs_type != 2) || c.nof_cdm_groups_without_data == 0 ||
+      c.nof_cdm_groups_without_data > (c.dmrs_type == 1 ? 2 : 3) || (c.dmrs_symbol_mask >> 14) != 0 ||
+      (c.flags & ~PDC_DEMUX_F_CSI2_AFTER_CSI1) != 0 || c.reserved != 0 || c.reserved2 != 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  // A stream without message bits has no encoded bits; reserved REs only exist for HARQ-ACK of at most two bits (TS 38.212 6.2.7).
+  if ((c.nof_harq_ack_bits == 0 && c.nof_enc_harq_ack_bits != 0) || (c.nof_csi_part1_bits == 0 && c.nof_enc_csi_part1_bits != 0) ||
+      (c.nof_csi_part2_bits == 0 && c.nof_enc_csi_part2_bits != 0) || (c.nof_harq_ack_bits > 2 && c.nof_harq_ack_rvd != 0)) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  // get_ulsch_demultiplex_l1 / _l1_csi (:32-55): first symbol without DM-RS after the first DM-RS symbol / at all.
+  int first_dmrs = -1, l1 = -1, l1_csi = -1;
+  for (int l = 0; l != 14; ++l) {
+    const bool dm = ((c.dmrs_symbol_mask >> l) & 1) != 0;
+    if (dm && first_dmrs < 0) {
+      first_dmrs = l;
+    }
+    if (!dm && l1_csi < 0) {
+      l1_csi = l;
+    }
+    if (!dm && first_dmrs >= 0 && l1 < 0) {
+      l1 = l;
+    }
+  }
+  if (first_dmrs < 0 || l1 < 0 || l1_csi < 0) {
+    return PDC_ERR_INVALID_ARG; // "No DM-RS symbol found."
+  }
+  const uint32_t nbpr        = (uint32_t)c.Qm * c.nof_layers;
+  const uint32_t re_dmrs_prb = 12u - c.nof_cdm_groups_without_data * (c.dmrs_type == 1 ? 6u : 4u);
+  uint32_t       m_rvd = 0, m_harq = 0, m_csi1 = 0, m_csi2 = 0;
+  uint32_t       off_in = 0, off_sch = 0;
+  bool           csi2_active = c.nof_enc_csi_part2_bits != 0 && (c.flags & PDC_DEMUX_F_CSI2_AFTER_CSI1) == 0;
+  placeholders               = false;
+  for (uint32_t l = c.start_symbol_index; l != (uint32_t)c.start_symbol_index + c.nof_symbols; ++l) {
+    const bool        dm = ((c.dmrs_symbol_mask >> l) & 1) != 0;
+    pdc_dev_demux_sym s;
+    memset(&s, 0, sizeof(s));
+    s.nof_re = (dm ? re_dmrs_prb : 12u) * c.nof_prb, s.nbpr = nbpr, s.Qm = c.Qm;
+    s.scramble_pos = off_in, s.c_init = c.c_init;
+    s.in = (const int8_t*)(uintptr_t)off_in, s.sch = (int8_t*)(uintptr_t)off_sch;
+    s.harq = (int8_t*)(uintptr_t)m_harq, s.csi1 = (int8_t*)(uintptr_t)m_csi1, s.csi2 = (int8_t*)(uintptr_t)m_csi2;
+    uint32_t       M_uci   = dm ? 0u : s.nof_re;
+    const uint32_t rem_rvd = (c.nof_harq_ack_rvd - m_rvd) / nbpr;
+    if ((int)l >= l1 && M_uci > 0 && rem_rvd > 0) { // step 1
+      demux_step(rem_rvd, M_uci, s.rvd_d, s.rvd_m);
+      m_rvd += s.rvd_m * nbpr;
+    }
+    const uint32_t rem_harq = (c.nof_enc_harq_ack_bits - m_harq) / nbpr;
+    if ((int)l >= l1 && M_uci > 0 && c.nof_harq_ack_bits > 2 && rem_harq > 0) { // step 2
+      demux_step(rem_harq, M_uci, s.harq_d, s.harq_m);
+      M_uci -= s.harq_m;
+      m_harq += s.harq_m * nbpr;
+    }
+    const uint32_t rem_csi1 = (c.nof_enc_csi_part1_bits - m_csi1) / nbpr;
+    const uint32_t M_rvd    = s.rvd_m;
+    if ((int)l >= l1_csi && M_uci > M_rvd && rem_csi1 > 0) { // step 3: candidates exclude the reserved REs
+      demux_step(rem_csi1, M_uci - M_rvd, s.csi1_d, s.csi1_m);
+      M_uci -= s.csi1_m;
+      m_csi1 += s.csi1_m * nbpr;
+      if (m_csi1 == c.nof_enc_csi_part1_bits && c.nof_enc_csi_part2_bits != 0) {
+        csi2_active = true; // the CSI Part 1 feedback configures CSI Part 2 within this symbol (:241-251, :528-533)
+      }
+    }
+    const uint32_t rem_csi2 = (c.nof_enc_csi_part2_bits - m_csi2) / nbpr;
+    if (csi2_active && (int)l >= l1_csi && M_uci > 0 && rem_csi2 > 0) { // step 3bis: reserved REs are candidates
+      demux_step(rem_csi2, M_uci, s.csi2_d, s.csi2_m);
+      m_csi2 += s.csi2_m * nbpr;
+    }
+    if (M_rvd > 0 && c.nof_harq_ack_bits <= 2 && rem_harq > 0) { // step 5: HARQ-ACK of 1 or 2 bits punctures reserved REs
+      demux_step(rem_harq, M_rvd, s.harq_d, s.harq_m);
+      s.harq_of_rvd = 1;
+      m_harq += s.harq_m * nbpr;
+    }
+    s.harq_ph = (c.nof_harq_ack_bits == 1 || c.nof_harq_ack_bits == 2) ? (uint8_t)c.nof_harq_ack_bits : 0;
+    s.csi1_ph = (c.nof_csi_part1_bits == 1 || c.nof_csi_part1_bits == 2) ? (uint8_t)c.nof_csi_part1_bits : 0;
+    s.csi2_ph = (c.nof_csi_part2_bits == 1 || c.nof_csi_part2_bits == 2) ? (uint8_t)c.nof_csi_part2_bits : 0;
+    if (c.Qm > 1 && ((s.harq_m && s.harq_ph) || (s.csi1_m && s.csi1_ph) || (s.csi2_m && s.csi2_ph))) {
+      placeholders = true;
+    }
+    const uint32_t sch_re = s.nof_re - (s.harq_of_rvd ? 0u : s.harq_m) - s.csi1_m - s.csi2_m;
+    off_in += s.nof_re * nbpr;
+    off_sch += sch_re * nbpr;
+    if (syms) {
+      syms->push_back(s);
+    }
+  }
+  // on_end_codeword (:321-328) asserts that every UCI stream has been delivered in full.
+  if (m_harq != c.nof_enc_harq_ack_bits || m_csi1 != c.nof_enc_csi_part1_bits || m_csi2 != c.nof_enc_csi_part2_bits) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  lens[0] = off_in, lens[1] = off_sch, lens[2] = m_harq, lens[3] = m_csi1, lens[4] = m_csi2;
+  return PDC_OK;
+}
+
+// Plans every codeword and rebases the symbol records on the buffers. in_len / out_len: host array sizes (0 = unknown).
+pdc_status demux_plan_all(const pdc_ulsch_demux_desc* descs, uint32_t n, const int8_t* d_in, int8_t* d_out, size_t in_len,
+                          size_t out_len, std::vector<pdc_dev_demux_sym>& syms, bool& placeholders, size_t& max_in, size_t& max_out)
+{
+  syms.clear();
+  placeholders = false;
+  max_in = max_out = 0;
+  for (uint32_t t = 0; t != n; ++t) {
+    const pdc_ulsch_demux_desc& c = descs[t];
+    uint32_t                    lens[5];
+    bool                        ph    = false;
+    const size_t                first = syms.size();
+    const pdc_status            st    = demux_plan(c, &syms, lens, ph);
+    if (st != PDC_OK) {
+      return st;
+    }
+    placeholders = placeholders || ph;
+    const size_t ends[5] = {(size_t)c.in_offset + lens[0], (size_t)c.sch_offset + lens[1], (size_t)c.harq_ack_offset + lens[2],
+                            (size_t)c.csi_part1_offset + lens[3], (size_t)c.csi_part2_offset + lens[4]};
+    max_in               = std::max(max_in, ends[0]);
+    for (int k = 1; k != 5; ++k) {
+      if (lens[k] != 0) {
+        max_out = std::max(max_out, ends[k]);
+      }
+    }
+    if ((in_len != 0 && max_in > in_len) || (out_len != 0 && max_out > out_len)) {
+      return PDC_ERR_INVALID_ARG;
+    }
+    for (size_t q = first; q != syms.size(); ++q) {
+      pdc_dev_demux_sym& s = syms[q];
+      s.in   = d_in + c.in_offset + (uintptr_t)s.in;
+      s.sch  = d_out + c.sch_offset + (uintptr_t)s.sch;
+      s.harq = d_out + c.harq_ack_offset + (uintptr_t)s.harq;
+      s.csi1 = d_out + c.csi_part1_offset + (uintptr_t)s.csi1;
+      s.csi2 = d_out + c.csi_part2_offset + (uintptr_t)s.csi2;
+    }
+  }
+  return PDC_OK;
+}
+} // namespace
+
+extern "C" {
+
+pdc_status pdc_ulsch_demux_lengths(const pdc_ulsch_demux_desc* d, uint32_t lens[5])
+{
+  if (!d || !lens) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  bool ph = false;
+  return demux_plan(*d, nullptr, lens, ph);
+}
+
+pdc_status pdc_ulsch_demultiplex_device(pdc_ctx* ctx, const pdc_ulsch_demux_desc* descs, uint32_t n, const int8_t* d_in,
+                                        int8_t* d_out, void* stream_v)
+{
+  if (!ctx || !descs || n == 0 || !d_in || !d_out) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::vector<pdc_dev_demux_sym> syms;
+  bool                           placeholders;
+  size_t                         max_in, max_out;
+  const pdc_status               st = demux_plan_all(descs, n, d_in, d_out, 0, 0, syms, placeholders, max_in, max_out);
+  if (st != PDC_OK) {
+    return st;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_v;
+  CK(cudaSetDevice(ctx->cfg.device));
+  std::lock_guard<std::mutex> lock(ctx->demod_mtx);
+  pdc_ctx::demod_slot&        slot = ctx->demux_ring[ctx->demux_next++ % 8];
+  if (!slot.done) {
+    CK(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
+  }
+  if (slot.used) {
+    CK(cudaEventSynchronize(slot.done)); // the kernel that read this staging entry has finished
+  }
+  const size_t bytes = syms.size() * sizeof(pdc_dev_demux_sym);
+  if (slot.cap < bytes) {
+    cudaFree(slot.d_desc);
+    slot.d_desc = nullptr, slot.cap = 0;
+    CK(cudaMalloc(&slot.d_desc, 2 * bytes));
+    slot.cap = 2 * bytes;
+  }
+  CK(cudaMemcpyAsync(slot.d_desc, syms.data(), bytes, cudaMemcpyHostToDevice, stream)); // pageable: staged before returning
+  CK(pdc_demux_launch((const pdc_dev_demux_sym*)slot.d_desc, (uint32_t)syms.size(), placeholders, stream));
+  ctx->launches += 1;
+  CK(cudaEventRecord(slot.done, stream));
+  slot.used = true;
+  return PDC_OK;
+}
+
+pdc_status pdc_ulsch_demultiplex(pdc_ctx* ctx, const pdc_ulsch_demux_desc* descs, uint32_t n, const int8_t* in, size_t in_len,
+                                 int8_t* out, size_t out_len)
+{
+  if (!ctx || !descs || n == 0 || !in || !out || in_len == 0 || out_len == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::vector<pdc_dev_demux_sym> syms;
+  bool                           placeholders;
+  size_t                         max_in, max_out;
+  pdc_status                     st = demux_plan_all(descs, n, nullptr, nullptr, in_len, out_len, syms, placeholders, max_in, max_out);
+  if (st != PDC_OK) {
+    return st;
+  }
+  CK(cudaSetDevice(ctx->cfg.device));
+  std::lock_guard<std::mutex> call_lock(ctx->demod_call_mtx); // one host-buffer call at a time on the context's stream
+  if (!ctx->demod_stream) {
+    CK(cudaStreamCreateWithFlags(&ctx->demod_stream, cudaStreamNonBlocking));
+  }
+  if (ctx->demux_in_cap < max_in) {
+    cudaFree(ctx->d_demux_in);
+    ctx->d_demux_in = nullptr, ctx->demux_in_cap = 0;
+    CK(cudaMalloc((void**)&ctx->d_demux_in, max_in * 2));
+    ctx->demux_in_cap = max_in * 2;
+  }
+  if (ctx->demux_out_cap < max_out + 4) {
+    cudaFree(ctx->d_demux_out);
+    ctx->d_demux_out = nullptr, ctx->demux_out_cap = 0;
+    CK(cudaMalloc((void**)&ctx->d_demux_out, (max_out + 4) * 2));
+    ctx->demux_out_cap = (max_out + 4) * 2;
+  }
+  cudaStream_t stream = ctx->demod_stream;
+  CK(cudaMemcpyAsync(ctx->d_demux_in, in, max_in, cudaMemcpyHostToDevice, stream));
+  st = pdc_ulsch_demultiplex_device(ctx, descs, n, ctx->d_demux_in, ctx->d_demux_out, stream);
+  if (st != PDC_OK) {
+    return st;
+  }
+  if (max_out != 0) {
+    // The streams tile disjoint ranges of `out`; bytes between them are not the library's to touch: copy stream by stream.
+    for (uint32_t t = 0; t != n; ++t) {
+      uint32_t lens[5];
+      bool     ph = false;
+      demux_plan(descs[t], nullptr, lens, ph);
+      const uint64_t offs[4] = {descs[t].sch_offset, descs[t].harq_ack_offset, descs[t].csi_part1_offset, descs[t].csi_part2_offset};
+      for (int k = 0; k != 4; ++k) {
+        if (lens[k + 1] != 0) {
+          CK(cudaMemcpyAsync(out + offs[k], ctx->d_demux_out + offs[k], lens[k + 1], cudaMemcpyDeviceToHost, stream));
+        }
+      }
+    }
+  }
+  CK(cudaStreamSynchronize(stream));
+  return PDC_OK;
+}
+
+} // extern "C"
 
 // ---- PDSCH transport-block encoder ----------------------------------------------------------------------------
 namespace {

@@ -28,6 +28,7 @@ extern "C" cudaError_t pdc_enc_init_device();
 extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb, uint32_t max_cbs, const uint32_t* graphs,
                                       const uint32_t* crc_pow, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_init_device();
+extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_t nsyms, bool placeholders, cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void* d_chunks, uint32_t nchunks,
                                         const float* d_symbols, const float* d_noise, int8_t* d_llrs, cudaStream_t stream);
 extern "C" cudaError_t pdc_launch_tb(const pdc_dev_tb* d_tbs, const pdc_dev_cb* d_cbs, const uint32_t* crc_pow, int ntb,
@@ -101,6 +102,11 @@ struct pdc_ctx {
   int8_t*      d_demod_out = nullptr;
   size_t       demod_in_cap = 0, demod_out_cap = 0;
   cudaStream_t demod_stream = nullptr;
+  // UL-SCH demultiplexer (pdc_ulsch_demultiplex*): same arrangement.
+  demod_slot   demux_ring[8];
+  unsigned     demux_next = 0;
+  int8_t*      d_demux_in = nullptr, *d_demux_out = nullptr;
+  size_t       demux_in_cap = 0, demux_out_cap = 0;
   // PDSCH encoder (pdc_pdsch_encode*): same arrangement.
   demod_slot   enc_ring[8];
   unsigned     enc_next = 0;
