@@ -52,7 +52,8 @@ def test_structure_layouts_match_the_compiler(tmp_path):
     from srsran_project_b200 import binding as B
 
     structs = {"pdc_cb_desc": B.DESC_DTYPE, "pdc_cb_result": B.RESULT_DTYPE, "pdc_tb_desc": B.TB_DESC_DTYPE,
-               "pdc_tb_result": B.TB_RESULT_DTYPE, "pdc_demod_seg": B.DEMOD_SEG_DTYPE, "pdc_pdsch_tb_desc": B.PDSCH_TB_DTYPE}
+               "pdc_tb_result": B.TB_RESULT_DTYPE, "pdc_demod_seg": B.DEMOD_SEG_DTYPE, "pdc_pdsch_tb_desc": B.PDSCH_TB_DTYPE,
+               "pdc_ulsch_demux_desc": B.ULSCH_DEMUX_DTYPE}
     lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', "int main(void) {"]
     for s, dt in structs.items():
         lines.append(f'printf("{s} %zu\\n", sizeof({s}));')
