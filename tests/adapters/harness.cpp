@@ -15,6 +15,10 @@
 #include "../../srsran_project_b200/adapters/hw_accelerator_pusch_dec_cuda.h"
 #include "../../srsran_project_b200/adapters/pdsch_encoder_cuda.h"
 #include "../../srsran_project_b200/adapters/pusch_decoder_cuda.h"
+#include "../../srsran_project_b200/adapters/ulsch_demultiplex_cuda.h"
+#include "phy/upper/sequence_generators/pseudo_random_generator_impl.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_codeword_buffer.h"
+#include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_buffer.h"
 #include "crc_calculator_clmul_impl.h"
 #include "crc_calculator_lut_impl.h"
 #include "ldpc/ldpc_decoder_avx2.h"
@@ -363,6 +367,116 @@ int adt_pdsch_encode_hw(uint8_t*       codeword,
                        : (qm == 6) ? modulation_scheme::QAM64
                                    : modulation_scheme::QAM256;
   encoder->encode(span<uint8_t>(codeword, nof_ch_symbols * qm), span<const uint8_t>(tb_bytes, tbs_bits / 8), cfg);
+  return 0;
+}
+
+// The CUDA srsran::ulsch_demultiplex behind the reference's interface, driven the way pusch_demodulator_impl
+// drives it: blocks of descrambled soft bits with their scrambling bits, through get_next_block_view when `use_view`.
+// cfg as in oracle/ref_shim_demux.cpp (cfg[15]: 0 = set_csi_part2 before the data, 1 = from the CSI Part 1 end-of-stream
+// callback; cfg[17]: block size, 0 = one block), cfg[18]: use_view. Returns 0, -1 = no device.
+int adt_ulsch_demultiplex(const uint32_t* cfg,
+                          const int8_t*   in,
+                          unsigned        n_in,
+                          int8_t*         out_sch,
+                          int8_t*         out_harq,
+                          int8_t*         out_csi1,
+                          int8_t*         out_csi2,
+                          unsigned        cap,
+                          unsigned*       lens)
+{
+  struct collector : public pusch_decoder_buffer {
+    std::vector<log_likelihood_ratio> data;
+    unsigned                          ended = 0;
+    ulsch_demultiplex*                demux = nullptr;
+    pusch_decoder_buffer*             csi2  = nullptr;
+    unsigned                          csi2_bits = 0, csi2_enc_bits = 0;
+    span<log_likelihood_ratio>        get_next_block_view(unsigned) override { return {}; }
+    void on_new_softbits(span<const log_likelihood_ratio> softbits) override { data.insert(data.end(), softbits.begin(), softbits.end()); }
+    void on_end_softbits() override
+    {
+      ++ended;
+      if (demux != nullptr) {
+        demux->set_csi_part2(*csi2, csi2_bits, csi2_enc_bits);
+      }
+    }
+  };
+  static std::shared_ptr<ulsch_demultiplex_factory> factory;
+  static std::unique_ptr<ulsch_demultiplex>         demux;
+  try {
+    if (!factory) {
+      factory = create_ulsch_demultiplex_factory_cuda();
+      demux   = factory->create();
+    }
+  } catch (const std::exception&) {
+    return -1;
+  }
+  ulsch_demultiplex::configuration c;
+  c.modulation         = (cfg[0] == 1)   ? modulation_scheme::PI_2_BPSK
+                         : (cfg[0] == 2) ? modulation_scheme::QPSK
+                         : (cfg[0] == 4) ? modulation_scheme::QAM16
+                         : (cfg[0] == 6) ? modulation_scheme::QAM64
+                                         : modulation_scheme::QAM256;
+  c.nof_layers         = cfg[1];
+  c.nof_prb            = cfg[2];
+  c.start_symbol_index = cfg[3];
+  c.nof_symbols        = cfg[4];
+  c.nof_harq_ack_rvd   = cfg[5];
+  c.dmrs               = (cfg[6] == 1) ? dmrs_type::TYPE1 : dmrs_type::TYPE2;
+  c.dmrs_symbol_mask   = symbol_slot_mask(14);
+  for (unsigned l = 0; l != 14; ++l) {
+    c.dmrs_symbol_mask.set(l, ((cfg[7] >> l) & 1u) != 0);
+  }
+  c.nof_cdm_groups_without_data = cfg[8];
+  c.nof_harq_ack_bits           = cfg[9];
+  c.nof_enc_harq_ack_bits       = cfg[10];
+  c.nof_csi_part1_bits          = cfg[11];
+  c.nof_enc_csi_part1_bits      = cfg[12];
+  collector              sch, harq, csi1, csi2;
+  pusch_codeword_buffer& cw = demux->demultiplex(sch, harq, csi1, c);
+  if (cfg[14] != 0) {
+    if (cfg[15] == 0) {
+      demux->set_csi_part2(csi2, cfg[13], cfg[14]);
+    } else {
+      csi1.demux = demux.get(), csi1.csi2 = &csi2, csi1.csi2_bits = cfg[13], csi1.csi2_enc_bits = cfg[14];
+    }
+  }
+  pseudo_random_generator_impl prg;
+  prg.init(cfg[16]);
+  dynamic_bit_buffer seq(n_in);
+  prg.generate(seq);
+  const unsigned block = (cfg[17] == 0) ? n_in : cfg[17];
+  for (unsigned o = 0; o < n_in;) {
+    unsigned                   n    = (n_in - o < block) ? n_in - o : block;
+    span<log_likelihood_ratio> view = (cfg[18] != 0) ? cw.get_next_block_view(n) : span<log_likelihood_ratio>();
+    std::vector<log_likelihood_ratio> local;
+    if (!view.empty()) {
+      n = static_cast<unsigned>(view.size()); // the buffer may hand out less than asked for
+      std::memcpy(view.data(), in + o, n);
+    } else {
+      local.assign(in + o, in + o + n);
+      view = local;
+    }
+    dynamic_bit_buffer part(n);
+    for (unsigned k = 0; k != n; ++k) {
+      part.insert(seq.extract(o + k, 1), k, 1);
+    }
+    cw.on_new_block(view, part);
+    o += n;
+  }
+  cw.on_end_codeword();
+  const collector* all[4]  = {&sch, &harq, &csi1, &csi2};
+  int8_t*          outs[4] = {out_sch, out_harq, out_csi1, out_csi2};
+  for (int q = 0; q != 4; ++q) {
+    lens[q] = static_cast<unsigned>(all[q]->data.size());
+    if (lens[q] <= cap && lens[q] != 0) {
+      std::memcpy(outs[q], all[q]->data.data(), lens[q]);
+    }
+    // Every configured stream ends exactly once.
+    const bool configured = (q == 0) || (q == 1 && cfg[9] != 0) || (q == 2 && cfg[11] != 0) || (q == 3 && cfg[14] != 0);
+    if (all[q]->ended != (configured ? 1u : 0u)) {
+      return -2 - q;
+    }
+  }
   return 0;
 }
 

@@ -123,7 +123,7 @@ def test_adapter_library_exports():
     for s in ("srsran::create_ldpc_decoder_factory_cuda", "srsran::create_ldpc_rate_dematcher_factory_cuda",
               "srsran::hal::create_cuda_pusch_dec_acc_factory", "srsran::create_pusch_decoder_factory_cuda",
               "srsran::create_demodulation_mapper_factory_cuda", "srsran::create_pdsch_encoder_factory_cuda",
-              "srsran::hal::create_cuda_pdsch_enc_acc_factory"):
+              "srsran::hal::create_cuda_pdsch_enc_acc_factory", "srsran::create_ulsch_demultiplex_factory_cuda"):
         assert s in syms, s
 
 
@@ -207,3 +207,32 @@ def test_cuda_pdsch_enc_accelerator_inside_the_reference_hw_encoder():
         assert rc == 0
         got = np.frombuffer(hashlib.sha256(np.packbits(cw).tobytes()).digest(), np.uint8)
         assert np.array_equal(got, g["digests"][k]), CASES[k]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("block,use_view", [(0, 0), (997, 0), (1536, 1)])
+def test_cuda_ulsch_demultiplex_adapter_reproduces_the_golden_streams(block, use_view):
+    """srsran::ulsch_demultiplex over pdc_ulsch_demultiplex (adapters/ulsch_demultiplex_cuda.cpp), driven through the reference's
+    interface the way pusch_demodulator_impl does (blocks of soft bits + their scrambling bits, optionally written through
+    get_next_block_view; CSI Part 2 configured up front or from the CSI Part 1 end-of-stream callback; the seed of the scrambling
+    sequence is recovered from the sequence), against the streams recorded from the compiled ulsch_demultiplex_impl."""
+    import hashlib
+
+    from oracle.demux_oracle import CFG_FIELDS
+    from tests import demux_cases as C
+
+    lib = _lib()
+    g = np.load(os.path.join(HERE, "golden", "ulsch_demux_v1.npz"))
+    vp = ctypes.c_void_p
+    for k, cfg in enumerate(C.cases()):
+        cw = C.codeword(cfg, 100 + k)
+        c = np.array([cfg[f] for f in CFG_FIELDS] + [block, use_view], np.uint32)
+        outs = [np.zeros(cw.size, np.int8) for _ in range(4)]
+        lens = np.zeros(4, np.uint32)
+        rc = lib.adt_ulsch_demultiplex(vp(c.ctypes.data), vp(cw.ctypes.data), ctypes.c_uint(cw.size),
+                                       *[vp(o.ctypes.data) for o in outs], ctypes.c_uint(cw.size), vp(lens.ctypes.data))
+        assert rc == 0, (k, rc)
+        for q in range(4):
+            assert lens[q] == g["lengths"][k, q], (k, q)
+            got = np.frombuffer(hashlib.sha256(outs[q][:int(lens[q])].tobytes()).digest(), np.uint8)
+            assert np.array_equal(got, g["digests"][k, q]), (k, q, cfg)
