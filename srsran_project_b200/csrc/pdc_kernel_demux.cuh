@@ -61,58 +61,92 @@ __device__ __forceinline__ int demux_placeholder(int v, uint32_t b, uint32_t mas
 
 // Per-RE word in s_cls: [2:0] stream (0 UL-SCH, 1 HARQ-ACK, 2 CSI Part 1, 3 CSI Part 2), [3] punctured by a 1- / 2-bit
 // HARQ-ACK, [15:4] rank in its stream, [27:16] rank in the HARQ-ACK stream when punctured.
-template <bool WORDS>
+template <int W>
+struct demux_vec;
+template <>
+struct demux_vec<1> {
+  using type = uint8_t;
+};
+template <>
+struct demux_vec<4> {
+  using type = uint32_t;
+};
+template <>
+struct demux_vec<16> {
+  using type = uint4;
+};
+
+// W bytes per thread and step (W divides nbpr and every pointer is W-aligned, so a step never straddles two REs).
+template <int W>
 __device__ __forceinline__ void demux_move(const pdc_dev_demux_sym& sy, const uint32_t* s_cls, const uint32_t* s_seq, bool any_ph)
 {
-  constexpr uint32_t W     = WORDS ? 4u : 1u;
-  const uint32_t     total = sy.nof_re * sy.nbpr;
-  const uint32_t     qm    = sy.Qm;
+  using vec_t          = typename demux_vec<W>::type;
+  const uint32_t total = sy.nof_re * sy.nbpr;
+  const uint32_t qm    = sy.Qm;
   for (uint32_t j = threadIdx.x * W; j < total; j += PDC_DEMUX_THREADS * W) {
     const uint32_t re = j / sy.nbpr, k = j - re * sy.nbpr;
     const uint32_t c  = s_cls[re];
     const uint32_t stream = c & 7u, rank = (c >> 4) & 0xfffu;
     const bool     punct  = (c & 8u) != 0;
-    uint32_t       raw;
-    if (WORDS) {
-      raw = *reinterpret_cast<const uint32_t*>(sy.in + j);
-    } else {
-      raw = (uint8_t)sy.in[j];
+    const vec_t    raw    = *reinterpret_cast<const vec_t*>(sy.in + j);
+    int8_t*        dst    = (stream == 0) ? sy.sch : (stream == 1) ? sy.harq : (stream == 2) ? sy.csi1 : sy.csi2;
+    const int      ph     = (stream == 1) ? sy.harq_ph : (stream == 2) ? sy.csi1_ph : (stream == 3) ? sy.csi2_ph : 0;
+    dst += rank * sy.nbpr + k;
+    if (!punct && (ph == 0 || !any_ph)) {
+      *reinterpret_cast<vec_t*>(dst) = raw; // the bulk: UL-SCH and long UCI fields are plain copies
+      continue;
     }
-    int8_t*   dst = (stream == 0) ? sy.sch : (stream == 1) ? sy.harq : (stream == 2) ? sy.csi1 : sy.csi2;
-    const int ph  = (stream == 1) ? sy.harq_ph : (stream == 2) ? sy.csi1_ph : (stream == 3) ? sy.csi2_ph : 0;
-    uint32_t  own = 0, hq = 0;
+    union {
+      vec_t   v;
+      uint8_t b[W];
+    } in_u, own, hq;
+    in_u.v = raw;
 #pragma unroll
-    for (uint32_t q = 0; q < W; ++q) {
-      int v = (int8_t)(raw >> (8 * q));
-      if (any_ph && qm > 1 && (punct || ph != 0)) {
+    for (int q = 0; q < W; ++q) {
+      int v = (int8_t)in_u.b[q];
+      int h = v;
+      if (any_ph && qm > 1) {
         const uint32_t p = j + q, b = (k + q) % qm;
         const uint32_t mk = (s_seq[p >> 5] >> (p & 31u)) & 1u;
         const uint32_t mp = (p == 0) ? 0u : (s_seq[(p - 1) >> 5] >> ((p - 1) & 31u)) & 1u;
         if (punct) {
-          hq |= (uint32_t)(uint8_t)demux_placeholder(v, b, mk, mp, sy.harq_ph) << (8 * q);
+          h = demux_placeholder(v, b, mk, mp, sy.harq_ph);
         }
         if (ph != 0) {
           v = demux_placeholder(v, b, mk, mp, ph);
         }
-      } else if (punct) {
-        hq |= (uint32_t)(uint8_t)v << (8 * q);
       }
-      own |= (uint32_t)(uint8_t)v << (8 * q);
+      hq.b[q]  = (uint8_t)h;
+      own.b[q] = punct ? 0 : (uint8_t)v; // srsvec::zero(re_data) after the HARQ-ACK extraction
     }
     if (punct) {
       const uint32_t rh = (c >> 16) & 0xfffu;
-      if (WORDS) {
-        *reinterpret_cast<uint32_t*>(sy.harq + rh * sy.nbpr + k) = hq;
-      } else {
-        sy.harq[rh * sy.nbpr + k] = (int8_t)hq;
-      }
-      own = 0; // srsvec::zero(re_data) after the HARQ-ACK extraction
+      *reinterpret_cast<vec_t*>(sy.harq + rh * sy.nbpr + k) = hq.v;
     }
-    if (WORDS) {
-      *reinterpret_cast<uint32_t*>(dst + rank * sy.nbpr + k) = own;
-    } else {
-      dst[rank * sy.nbpr + k] = (int8_t)own;
+    *reinterpret_cast<vec_t*>(dst) = own.v;
+  }
+}
+
+// A symbol without UCI: its soft bits are the next stretch of the UL-SCH stream.
+__device__ __forceinline__ void demux_copy(const int8_t* __restrict__ src, int8_t* __restrict__ dst, uint32_t n)
+{
+  const uintptr_t a = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst);
+  uint32_t        done = 0;
+  if ((a & 15u) == 0) {
+    const uint32_t nv = n >> 4;
+    for (uint32_t j = threadIdx.x; j < nv; j += PDC_DEMUX_THREADS) {
+      reinterpret_cast<uint4*>(dst)[j] = reinterpret_cast<const uint4*>(src)[j];
     }
+    done = nv << 4;
+  } else if ((a & 3u) == 0) {
+    const uint32_t nv = n >> 2;
+    for (uint32_t j = threadIdx.x; j < nv; j += PDC_DEMUX_THREADS) {
+      reinterpret_cast<uint32_t*>(dst)[j] = reinterpret_cast<const uint32_t*>(src)[j];
+    }
+    done = nv << 2;
+  }
+  for (uint32_t j = done + threadIdx.x; j < n; j += PDC_DEMUX_THREADS) {
+    dst[j] = src[j];
   }
 }
 
@@ -125,6 +159,10 @@ __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(cons
   uint32_t*                  s_w1  = s_dyn + PDC_DEMUX_MAX_RE; // sequence words (and the x1 history), then the x2 history
   const uint32_t             M     = sy.nof_re;
   const int                  tid   = threadIdx.x;
+  if (sy.harq_m == 0 && sy.csi1_m == 0 && sy.csi2_m == 0) {
+    demux_copy(sy.in, sy.sch, M * sy.nbpr); // reserved REs without HARQ-ACK on them change nothing
+    return;
+  }
   const bool any_ph = sy.Qm > 1 && ((sy.harq_m != 0 && sy.harq_ph != 0) || (sy.csi1_m != 0 && sy.csi1_ph != 0) ||
                                     (sy.csi2_m != 0 && sy.csi2_ph != 0));
 
@@ -203,10 +241,12 @@ __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(cons
   const uintptr_t align = reinterpret_cast<uintptr_t>(sy.in) | reinterpret_cast<uintptr_t>(sy.sch) |
                           reinterpret_cast<uintptr_t>(sy.harq) | reinterpret_cast<uintptr_t>(sy.csi1) |
                           reinterpret_cast<uintptr_t>(sy.csi2) | sy.nbpr;
-  if ((align & 3u) == 0) {
-    demux_move<true>(sy, s_cls, s_w1, any_ph);
+  if ((align & 15u) == 0) {
+    demux_move<16>(sy, s_cls, s_w1, any_ph);
+  } else if ((align & 3u) == 0) {
+    demux_move<4>(sy, s_cls, s_w1, any_ph);
   } else {
-    demux_move<false>(sy, s_cls, s_w1, any_ph);
+    demux_move<1>(sy, s_cls, s_w1, any_ph);
   }
 }
 

@@ -146,12 +146,14 @@ void pdc_destroy(pdc_ctx* ctx)
   cudaFree(ctx->d_harq_bits);
   for (pdc_ctx::demod_slot& d : ctx->demod_ring) {
     cudaFree(d.d_desc);
+    cudaFreeHost(d.h_desc);
     if (d.done) {
       cudaEventDestroy(d.done);
     }
   }
   for (pdc_ctx::demod_slot& d : ctx->demux_ring) {
     cudaFree(d.d_desc);
+    cudaFreeHost(d.h_desc);
     if (d.done) {
       cudaEventDestroy(d.done);
     }
@@ -191,6 +193,34 @@ static pdc_status release_ticket(pdc_ctx* ctx, ticket_t* t, pdc_status st)
   std::lock_guard<std::mutex> lock(ctx->mtx);
   t->in_use = false;
   return st;
+}
+
+// Descriptor staging rings (LLR producers, demultiplexer, PDSCH encoder): when one entry is too small, every entry of the ring
+// grows, so a caller that repeats the same submission pays for the allocations (which synchronise the device) once, not once per
+// entry. Entries in flight are waited for before their buffers go away.
+static pdc_status ring_reserve(pdc_ctx* ctx, pdc_ctx::demod_slot (&ring)[8], size_t bytes, bool pinned_image)
+{
+  for (pdc_ctx::demod_slot& s : ring) {
+    if (s.cap >= bytes && (!pinned_image || s.h_cap >= bytes)) {
+      continue;
+    }
+    if (s.used && s.done) {
+      CK(cudaEventSynchronize(s.done));
+    }
+    if (s.cap < bytes) {
+      cudaFree(s.d_desc);
+      s.d_desc = nullptr, s.cap = 0;
+      CK(cudaMalloc(&s.d_desc, 2 * bytes));
+      s.cap = 2 * bytes;
+    }
+    if (pinned_image && s.h_cap < bytes) {
+      cudaFreeHost(s.h_desc);
+      s.h_desc = nullptr, s.h_cap = 0;
+      CK(cudaHostAlloc(&s.h_desc, 2 * bytes, cudaHostAllocDefault));
+      s.h_cap = 2 * bytes;
+    }
+  }
+  return PDC_OK;
 }
 
 #define CKT(call)                                                                                                      \
@@ -622,15 +652,17 @@ pdc_status pdc_demodulate_device(pdc_ctx* ctx, const pdc_demod_seg* segs, uint32
     CK(cudaEventSynchronize(slot.done)); // the kernel that read this staging entry has finished
   }
   const size_t seg_bytes = ((size_t)n * sizeof(pdc_demod_seg) + 15) & ~(size_t)15, chunk_bytes = chunks.size() * 4;
-  if (slot.cap < seg_bytes + chunk_bytes) {
-    cudaFree(slot.d_desc);
-    slot.d_desc = nullptr, slot.cap = 0;
-    CK(cudaMalloc(&slot.d_desc, 2 * (seg_bytes + chunk_bytes)));
-    slot.cap = 2 * (seg_bytes + chunk_bytes);
+  // Through the slot's pinned image: the caller's array and `chunks` may go away, and the upload does not wait for the stream
+  // (a pageable source of more than 64 KB makes cudaMemcpyAsync block until the stream has drained).
+  {
+    const pdc_status rs = ring_reserve(ctx, ctx->demod_ring, seg_bytes + chunk_bytes, true);
+    if (rs != PDC_OK) {
+      return rs;
+    }
   }
-  // Pageable sources: the runtime stages them before the call returns, so the caller's array and `chunks` may go away.
-  CK(cudaMemcpyAsync(slot.d_desc, segs, (size_t)n * sizeof(pdc_demod_seg), cudaMemcpyHostToDevice, stream));
-  CK(cudaMemcpyAsync((char*)slot.d_desc + seg_bytes, chunks.data(), chunk_bytes, cudaMemcpyHostToDevice, stream));
+  memcpy(slot.h_desc, segs, (size_t)n * sizeof(pdc_demod_seg));
+  memcpy((char*)slot.h_desc + seg_bytes, chunks.data(), chunk_bytes);
+  CK(cudaMemcpyAsync(slot.d_desc, slot.h_desc, seg_bytes + chunk_bytes, cudaMemcpyHostToDevice, stream));
   CK(pdc_demod_launch((const pdc_demod_seg*)slot.d_desc, (char*)slot.d_desc + seg_bytes, (uint32_t)(chunks.size() / 2),
                       d_symbols, d_noise_vars, d_llrs, stream));
   ctx->launches += 1;
@@ -884,13 +916,14 @@ pdc_status pdc_ulsch_demultiplex_device(pdc_ctx* ctx, const pdc_ulsch_demux_desc
     CK(cudaEventSynchronize(slot.done)); // the kernel that read this staging entry has finished
   }
   const size_t bytes = syms.size() * sizeof(pdc_dev_demux_sym);
-  if (slot.cap < bytes) {
-    cudaFree(slot.d_desc);
-    slot.d_desc = nullptr, slot.cap = 0;
-    CK(cudaMalloc(&slot.d_desc, 2 * bytes));
-    slot.cap = 2 * bytes;
+  {
+    const pdc_status rs = ring_reserve(ctx, ctx->demux_ring, bytes, true);
+    if (rs != PDC_OK) {
+      return rs;
+    }
   }
-  CK(cudaMemcpyAsync(slot.d_desc, syms.data(), bytes, cudaMemcpyHostToDevice, stream)); // pageable: staged before returning
+  memcpy(slot.h_desc, syms.data(), bytes); // pinned image: the upload does not wait for the stream to drain
+  CK(cudaMemcpyAsync(slot.d_desc, slot.h_desc, bytes, cudaMemcpyHostToDevice, stream));
   CK(pdc_demux_launch((const pdc_dev_demux_sym*)slot.d_desc, (uint32_t)syms.size(), placeholders, stream));
   ctx->launches += 1;
   CK(cudaEventRecord(slot.done, stream));
@@ -1128,11 +1161,11 @@ pdc_status pdc_pdsch_encode_device(pdc_ctx* ctx, const pdc_pdsch_tb_desc* tbs, u
   uint32_t                    max_cbs;
   const size_t                acc_bytes = ((size_t)n * 4 + 15) & ~(size_t)15;
   const size_t                need      = acc_bytes + (size_t)n * sizeof(pdc_dev_enc_tb);
-  if (slot.cap < need) {
-    cudaFree(slot.d_desc);
-    slot.d_desc = nullptr, slot.cap = 0;
-    CK(cudaMalloc(&slot.d_desc, need));
-    slot.cap = need;
+  {
+    const pdc_status rs = ring_reserve(ctx, ctx->enc_ring, need, false);
+    if (rs != PDC_OK) {
+      return rs;
+    }
   }
   uint32_t*  d_acc = (uint32_t*)slot.d_desc;
   pdc_status st    = enc_plan(ctx, tbs, n, 0, 0, d_tb_bytes, d_codewords, d_acc, cbs, smem, max_tb, max_cw, max_cbs);

@@ -92,6 +92,8 @@ struct pdc_ctx {
   struct demod_slot {
     void*       d_desc = nullptr;
     size_t      cap    = 0;
+    void*       h_desc = nullptr; // pinned image of d_desc: a pageable source would make the upload wait for the stream
+    size_t      h_cap  = 0;
     cudaEvent_t done   = nullptr;
     bool        used   = false;
   };

@@ -126,6 +126,7 @@ def run(ctx, n_tbs=64, steps=20, warmup=3, cpu=True, hbm_peak_gbs=None):
         "parity": ("LLRs of the first and last call bit-exact vs oracle; " if cpu else "") +
                   "all payloads decoded from the device-born LLRs equal to the transmitted TBs",
     }
+    res["ulsch_demux"] = run_demux(ctx, n_tbs, w["G"], d_llrs, timed, cpu, hbm_peak_gbs)
     if cpu and pyoracle.ref_available():
         from concurrent.futures import ThreadPoolExecutor
 
@@ -150,6 +151,58 @@ def run(ctx, n_tbs=64, steps=20, warmup=3, cpu=True, hbm_peak_gbs=None):
                       "sample": f"{segs.size} calls x {reps} repetitions, {dt:.1f} s wall, demodulation_mapper_impl (AVX512) + "
                                 "pseudo_random_generator_impl apply_xor"}
     return res
+
+
+def run_demux(ctx, n_tbs, G, d_llrs, timed, cpu, hbm_peak_gbs):
+    """UL-SCH demultiplexer at the same size: every codeword of the slot (273 PRB, 4 layers, 256QAM, DM-RS in symbol 2 with no
+    data REs) carries a 2-bit HARQ-ACK on reserved REs, CSI Part 1 and CSI Part 2; the input is the demodulator's output in HBM."""
+    import torch
+
+    from srsran_project_b200 import binding as B
+
+    nbpr = 32
+    descs = np.zeros(n_tbs, B.ULSCH_DEMUX_DTYPE)
+    descs["Qm"], descs["nof_layers"], descs["nof_prb"], descs["nof_symbols"] = 8, 4, 273, 14
+    descs["dmrs_type"], descs["nof_cdm_groups_without_data"], descs["dmrs_symbol_mask"] = 1, 2, 1 << 2
+    descs["nof_harq_ack_bits"], descs["nof_enc_harq_ack_bits"], descs["nof_harq_ack_rvd"] = 2, 40 * nbpr, 60 * nbpr
+    descs["nof_csi_part1_bits"], descs["nof_enc_csi_part1_bits"] = 30, 150 * nbpr
+    descs["nof_csi_part2_bits"], descs["nof_enc_csi_part2_bits"] = 50, 260 * nbpr
+    descs["c_init"] = 0x5a5a + np.arange(n_tbs)
+    lens = B.ulsch_demux_lengths(descs[:1])
+    assert lens[0] == G
+    stride = sum((n + 15) // 16 * 16 for n in lens[1:])
+    for t in range(n_tbs):
+        o = t * stride
+        descs[t]["in_offset"] = t * G
+        for f, n in zip(("sch_offset", "harq_ack_offset", "csi_part1_offset", "csi_part2_offset"), lens[1:]):
+            descs[t][f] = o
+            o += (n + 15) // 16 * 16
+    d_out = torch.zeros(n_tbs * stride, dtype=torch.int8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    ms = timed(lambda k: ctx.ulsch_demultiplex_device(descs, d_llrs.data_ptr(), d_out.data_ptr(), stream))
+    alg = n_tbs * (lens[0] + sum(lens[1:]))
+    gbs = alg / (ms * 1e-3) / 1e9
+    out = {"workload": f"{n_tbs} codewords x 13 OFDM symbols x 3276 REs x 32 soft bits; HARQ-ACK 2 bits on 40 of 60 reserved REs, "
+                       "CSI Part 1 on 150 REs, CSI Part 2 on 260 REs",
+           "ms_per_step": ms, "gllr_per_s": n_tbs * lens[0] / (ms * 1e-3) / 1e9,
+           "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak_gbs, "unit": "GB/s",
+                        "frac": (gbs / hbm_peak_gbs) if hbm_peak_gbs else None, "algorithmic_bytes_per_step": alg}}
+    if cpu:  # the restatement is only ever the checker: last codeword of the slot, all four streams
+        from oracle import demux_oracle as D
+
+        t = n_tbs - 1
+        cfg = {"qm": 8, "nof_layers": 4, "nof_prb": 273, "start_symbol": 0, "nof_symbols": 14, "dmrs_type": 1,
+               "dmrs_symbol_mask": 1 << 2, "nof_cdm_groups_without_data": 2, "nof_harq_ack_bits": 2,
+               "nof_enc_harq_ack_bits": 40 * nbpr, "nof_harq_ack_rvd": 60 * nbpr, "nof_csi_part1_bits": 30,
+               "nof_enc_csi_part1_bits": 150 * nbpr, "nof_csi_part2_bits": 50, "nof_enc_csi_part2_bits": 260 * nbpr,
+               "csi2_mode": 0, "c_init": int(descs[t]["c_init"])}
+        want = D.demultiplex(cfg, d_llrs[t * G:(t + 1) * G].cpu().numpy())
+        got = d_out.cpu().numpy()
+        for f, b in zip(("sch_offset", "harq_ack_offset", "csi_part1_offset", "csi_part2_offset"), want):
+            if not np.array_equal(got[int(descs[t][f]):int(descs[t][f]) + b.size], b):
+                raise RuntimeError("device UL-SCH demultiplexer differs from the restatement (" + f + ")")
+        out["parity"] = "four streams of the last codeword bit-exact vs the restatement"
+    return out
 
 
 def main():
