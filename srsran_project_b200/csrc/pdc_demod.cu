@@ -567,6 +567,34 @@ gf2_mat gf2_step(int lfsr) // one step: s'[r] = s[r + 1]; s'[30] = taps . s
 }
 } // namespace
 
+// Host copy of the jump matrices: the demultiplexer's planner jumps the two registers on the host (a few hundred word operations
+// per OFDM symbol that holds placeholder bits), so no thread on the device walks that dependent chain.
+static uint32_t h_prg_jump[2][PDC_DEMOD_JUMP_BITS][32];
+static bool     h_prg_jump_ready = false;
+
+// States of the two LFSRs of TS 38.211 5.2.1 at sequence position pos (bit i = x(1600 + pos + i)); false before the tables exist.
+extern "C" bool pdc_prg_states(uint32_t c_init, uint32_t pos, uint32_t* s1, uint32_t* s2)
+{
+  if (!h_prg_jump_ready) {
+    return false;
+  }
+  uint32_t s[2] = {1u, c_init & 0x7fffffffu};
+  for (int lfsr = 0; lfsr != 2; ++lfsr) {
+    const uint32_t p = 1600u + pos;
+    for (int j = 0; j < PDC_DEMOD_JUMP_BITS && (p >> j) != 0; ++j) {
+      if ((p >> j) & 1u) {
+        uint32_t t = 0;
+        for (int r = 0; r != 31; ++r) {
+          t |= (uint32_t)(__builtin_popcount(h_prg_jump[lfsr][j][r] & s[lfsr]) & 1) << r;
+        }
+        s[lfsr] = t;
+      }
+    }
+  }
+  *s1 = s[0], *s2 = s[1];
+  return true;
+}
+
 extern "C" cudaError_t pdc_demod_init_device()
 {
   static pdc_demod_tables t;
@@ -605,7 +633,8 @@ extern "C" cudaError_t pdc_demod_init_device()
   if (e != cudaSuccess) {
     return e;
   }
-  static uint32_t jump[2][PDC_DEMOD_JUMP_BITS][32], word[2][31][32];
+  static uint32_t word[2][31][32];
+  uint32_t(&jump)[2][PDC_DEMOD_JUMP_BITS][32] = h_prg_jump;
   for (int lfsr = 0; lfsr != 2; ++lfsr) {
     gf2_mat p = gf2_step(lfsr), m32;
     for (int j = 0; j != PDC_DEMOD_JUMP_BITS; ++j) {
@@ -628,7 +657,8 @@ extern "C" cudaError_t pdc_demod_init_device()
       acc = gf2_mul(m32, acc);
     }
   }
-  e = cudaMemcpyToSymbol(d_prg_jump, jump, sizeof(jump));
+  h_prg_jump_ready = true;
+  e                = cudaMemcpyToSymbol(d_prg_jump, jump, sizeof(jump));
   if (e != cudaSuccess) {
     return e;
   }

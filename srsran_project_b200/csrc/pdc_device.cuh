@@ -79,7 +79,7 @@ struct pdc_dev_demux_sym {
   const int8_t* in;                           // first soft bit of the symbol (descrambled)
   int8_t *      sch, *harq, *csi1, *csi2;     // where this symbol's share of each stream starts
   uint32_t      nof_re, nbpr;                 // REs of the symbol, soft bits per RE (Qm * layers)
-  uint32_t      scramble_pos, c_init;         // position of the symbol's first soft bit in the scrambling sequence
+  uint32_t      x1_state, x2_state;           // the two scrambling LFSRs at the symbol's first soft bit (placeholder symbols only)
   uint32_t      rvd_d, rvd_m;                 // reserved REs: of all REs
   uint32_t      harq_d, harq_m;               // HARQ-ACK: of all REs (more than 2 bits) or of the reserved ones (harq_of_rvd)
   uint32_t      csi1_d, csi1_m;               // CSI Part 1: of the REs that are neither HARQ-ACK nor reserved

@@ -47,6 +47,44 @@ __device__ __forceinline__ bool demux_selected(uint32_t rank, uint32_t d, uint32
   return m != 0 && (rank % d) == 0 && (rank / d) < m;
 }
 
+// Scrambling words of one OFDM symbol from the register states the host jumped to: 32 words of each LFSR by the bootstrap
+// matrices, the rest by the word-level recurrence, xor-ed in place into w1. One warp; w1 / w2 hold nwords + 28 words.
+__device__ __forceinline__ void demux_sequence(uint32_t* w1, uint32_t* w2, int nwords, uint32_t s1, uint32_t s2, int lane)
+{
+  w1[lane] = prg_word(d_prg_word, s1, 0, lane);
+  w2[lane] = prg_word(d_prg_word, s2, 1, lane);
+  __syncwarp();
+  for (int base = 32; base < nwords; base += 28) {
+    if (lane < 28) {
+      const int j     = base + lane - 31;
+      w1[base + lane] = w1[j + 3] ^ w1[j];
+      w2[base + lane] = w2[j + 3] ^ w2[j + 2] ^ w2[j + 1] ^ w2[j];
+    }
+    __syncwarp();
+  }
+  for (int j = lane; j < nwords; j += 32) {
+    w1[j] ^= w2[j];
+  }
+}
+
+// "Every d-th candidate, the first m of them" (re_set_select) along consecutive candidate ranks: rank = q * d + r.
+struct demux_walk {
+  uint32_t q, r, d, m;
+  __device__ __forceinline__ demux_walk(uint32_t d_, uint32_t m_, uint32_t rank) : q(0), r(0), d(d_), m(m_)
+  {
+    if (m != 0) {
+      q = rank / d, r = rank - q * d;
+    }
+  }
+  __device__ __forceinline__ bool selected() const { return m != 0 && r == 0 && q < m; }
+  __device__ __forceinline__ void next()
+  {
+    if (++r == d) {
+      r = 0, ++q;
+    }
+  }
+};
+
 // Placeholder handling of one soft bit: b = index within its modulation symbol, mask / mask_prev = scrambling bits of this soft
 // bit and of the one before it. 1 bit (:106-150): bit 0 kept, bit 1 re-scrambled with the mask of bit 0, others unscrambled.
 // 2 bits (:152-196): bits 0 and 1 kept, others unscrambled.
@@ -81,9 +119,12 @@ template <int W>
 __device__ __forceinline__ void demux_move(const pdc_dev_demux_sym& sy, const uint32_t* s_cls, const uint32_t* s_seq, bool any_ph)
 {
   using vec_t          = typename demux_vec<W>::type;
+  // This CTA's share of the symbol's bytes (the sets are rebuilt by every CTA of the symbol, the bytes are moved once).
   const uint32_t total = sy.nof_re * sy.nbpr;
+  const uint32_t chunk = ((total + gridDim.y - 1) / gridDim.y + 15u) & ~15u;
+  const uint32_t begin = min(total, blockIdx.y * chunk), end = min(total, begin + chunk);
   const uint32_t qm    = sy.Qm;
-  for (uint32_t j = threadIdx.x * W; j < total; j += PDC_DEMUX_THREADS * W) {
+  for (uint32_t j = begin + threadIdx.x * W; j < end; j += PDC_DEMUX_THREADS * W) {
     const uint32_t re = j / sy.nbpr, k = j - re * sy.nbpr;
     const uint32_t c  = s_cls[re];
     const uint32_t stream = c & 7u, rank = (c >> 4) & 0xfffu;
@@ -134,8 +175,9 @@ __device__ __forceinline__ void demux_copy(const int8_t* __restrict__ src, int8_
   uint32_t        done = 0;
   if ((a & 15u) == 0) {
     const uint32_t nv = n >> 4;
+#pragma unroll 4
     for (uint32_t j = threadIdx.x; j < nv; j += PDC_DEMUX_THREADS) {
-      reinterpret_cast<uint4*>(dst)[j] = reinterpret_cast<const uint4*>(src)[j];
+      reinterpret_cast<uint4*>(dst)[j] = __ldcs(reinterpret_cast<const uint4*>(src) + j);
     }
     done = nv << 4;
   } else if ((a & 3u) == 0) {
@@ -150,6 +192,19 @@ __device__ __forceinline__ void demux_copy(const int8_t* __restrict__ src, int8_
   }
 }
 
+// OFDM symbols without UCI (the host lists them first): plain stretches of the UL-SCH stream, PDC_DEMUX_COPY_PARTS CTAs each, no
+// shared memory, so the bulk of a slot moves at copy speed beside the few CTAs that build RE sets.
+#define PDC_DEMUX_COPY_PARTS 4
+#define PDC_DEMUX_UCI_PARTS 4 /* CTAs per symbol with UCI: a slot has few such symbols, one CTA each would leave the device idle */
+__global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_copy_kernel(const pdc_dev_demux_sym* __restrict__ syms)
+{
+  const pdc_dev_demux_sym& sy = syms[blockIdx.x];
+  const uint32_t           n  = sy.nof_re * sy.nbpr;
+  const uint32_t           chunk = ((n + gridDim.y - 1) / gridDim.y + 15u) & ~15u;
+  const uint32_t           begin = min(n, blockIdx.y * chunk), end = min(n, begin + chunk);
+  demux_copy(sy.in + begin, sy.sch + begin, end - begin);
+}
+
 __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(const pdc_dev_demux_sym* __restrict__ syms)
 {
   extern __shared__ uint32_t s_dyn[];
@@ -159,45 +214,44 @@ __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(cons
   uint32_t*                  s_w1  = s_dyn + PDC_DEMUX_MAX_RE; // sequence words (and the x1 history), then the x2 history
   const uint32_t             M     = sy.nof_re;
   const int                  tid   = threadIdx.x;
-  if (sy.harq_m == 0 && sy.csi1_m == 0 && sy.csi2_m == 0) {
-    demux_copy(sy.in, sy.sch, M * sy.nbpr); // reserved REs without HARQ-ACK on them change nothing
-    return;
-  }
+  // (Symbols without UCI never get here: the host hands them to pdc_ulsch_copy_kernel. Reserved REs without HARQ-ACK on them
+  // change nothing, so such a symbol counts as one without UCI.)
   const bool any_ph = sy.Qm > 1 && ((sy.harq_m != 0 && sy.harq_ph != 0) || (sy.csi1_m != 0 && sy.csi1_ph != 0) ||
                                     (sy.csi2_m != 0 && sy.csi2_ph != 0));
 
   // ---- scrambling bits of the symbol (only when a placeholder RE lies in it): the last warp ------------------------------------
   const uint32_t nwords = (M * sy.nbpr + 31) / 32 + 1;
   if (any_ph && tid >= PDC_DEMUX_THREADS - 32) {
-    uint32_t*   s_w2 = s_w1 + nwords + 64;
-    prg_history h;
-    h.c_init = 0, h.start = 0, h.n = 0;
-    prg_generate(d_prg_jump, d_prg_word, s_w1, s_w1, s_w2, (int)nwords, sy.c_init, sy.scramble_pos, tid & 31, h);
+    demux_sequence(s_w1, s_w1 + nwords + 64, (int)nwords, sy.x1_state, sy.x2_state, tid & 31);
   }
 
-  // ---- sets: contiguous REs per thread, up to three scans ---------------------------------------------------------------------
+  // ---- sets: contiguous REs per thread, up to three scans. Every "every d-th, the first m" test walks its candidates with a
+  //      (quotient, remainder) pair: one division per thread and set instead of two per RE. -----------------------------------------
   const uint32_t per = (M + PDC_DEMUX_THREADS - 1) / PDC_DEMUX_THREADS;
   const uint32_t i0 = min(M, (uint32_t)tid * per), i1 = min(M, i0 + per);
-  auto is_rvd  = [&](uint32_t i) { return demux_selected(i, sy.rvd_d, sy.rvd_m); };
-  auto is_hq_a = [&](uint32_t i) { return !sy.harq_of_rvd && demux_selected(i, sy.harq_d, sy.harq_m); };
+  const bool     hq_all = !sy.harq_of_rvd && sy.harq_m != 0; // HARQ-ACK of more than two bits: selected among all REs
   // CSI Part 1 among the REs that are neither HARQ-ACK nor reserved.
   {
-    uint32_t n = 0;
+    demux_walk rv(sy.rvd_d, sy.rvd_m, i0), hq(sy.harq_d, hq_all ? sy.harq_m : 0u, i0);
+    uint32_t   n = 0;
     for (uint32_t i = i0; i < i1; ++i) {
-      n += (!is_hq_a(i) && !is_rvd(i)) ? 1u : 0u;
+      n += (!hq.selected() && !rv.selected()) ? 1u : 0u;
+      rv.next(), hq.next();
     }
-    uint32_t r = (sy.csi1_m != 0) ? demux_block_scan(n, s_warp) : 0u;
+    const uint32_t r0 = (sy.csi1_m != 0) ? demux_block_scan(n, s_warp) : 0u;
+    demux_walk     rv2(sy.rvd_d, sy.rvd_m, i0), hq2(sy.harq_d, hq_all ? sy.harq_m : 0u, i0), c1(sy.csi1_d, sy.csi1_m, r0);
     for (uint32_t i = i0; i < i1; ++i) {
       uint32_t c = 0;
-      if (is_hq_a(i)) {
-        c = 1u | ((i / sy.harq_d) << 4);
-      } else if (!is_rvd(i)) {
-        if (demux_selected(r, sy.csi1_d, sy.csi1_m)) {
-          c = 2u | ((r / sy.csi1_d) << 4);
+      if (hq2.selected()) {
+        c = 1u | (hq2.q << 4);
+      } else if (!rv2.selected()) {
+        if (c1.selected()) {
+          c = 2u | (c1.q << 4);
         }
-        ++r;
+        c1.next();
       }
       s_cls[i] = c;
+      rv2.next(), hq2.next();
     }
   }
   // CSI Part 2 among what is left of the UCI candidates (reserved REs included).
@@ -206,13 +260,13 @@ __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(cons
     for (uint32_t i = i0; i < i1; ++i) {
       n += (s_cls[i] == 0) ? 1u : 0u;
     }
-    uint32_t r = demux_block_scan(n, s_warp);
+    demux_walk c2(sy.csi2_d, sy.csi2_m, demux_block_scan(n, s_warp));
     for (uint32_t i = i0; i < i1; ++i) {
       if (s_cls[i] == 0) {
-        if (demux_selected(r, sy.csi2_d, sy.csi2_m)) {
-          s_cls[i] = 3u | ((r / sy.csi2_d) << 4);
+        if (c2.selected()) {
+          s_cls[i] = 3u | (c2.q << 4);
         }
-        ++r;
+        c2.next();
       }
     }
   }
@@ -222,17 +276,24 @@ __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(cons
     for (uint32_t i = i0; i < i1; ++i) {
       n += (s_cls[i] == 0) ? 1u : 0u;
     }
-    uint32_t r = demux_block_scan(n, s_warp);
+    uint32_t   r = demux_block_scan(n, s_warp);
+    demux_walk rv(sy.rvd_d, sy.harq_of_rvd ? sy.rvd_m : 0u, i0);
+    // HARQ-ACK among the reserved REs: walks the rank of the reserved RE (rv.q), which advances when rv wraps.
+    demux_walk hq(sy.harq_d, (sy.harq_of_rvd && sy.rvd_m != 0) ? sy.harq_m : 0u, rv.r == 0 ? rv.q : rv.q + 1);
     for (uint32_t i = i0; i < i1; ++i) {
       uint32_t c = s_cls[i];
       if (c == 0) {
         c = r << 4;
         ++r;
       }
-      if (sy.harq_of_rvd && is_rvd(i) && demux_selected(i / sy.rvd_d, sy.harq_d, sy.harq_m)) {
-        c |= 8u | (((i / sy.rvd_d) / sy.harq_d) << 16);
+      if (rv.r == 0 && rv.m != 0) {
+        if (rv.q < rv.m && hq.selected()) {
+          c |= 8u | (hq.q << 16);
+        }
+        hq.next();
       }
       s_cls[i] = c;
+      rv.next();
     }
   }
   __syncthreads();
@@ -250,13 +311,17 @@ __global__ void __launch_bounds__(PDC_DEMUX_THREADS) pdc_ulsch_demux_kernel(cons
   }
 }
 
-extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_t nsyms, bool placeholders, cudaStream_t stream)
+// d_syms: nplain symbols without UCI, then nuci symbols with some.
+extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_t nplain, uint32_t nuci, bool placeholders,
+                                        cudaStream_t stream)
 {
-  if (nsyms == 0) {
-    return cudaSuccess;
+  if (nplain != 0) {
+    pdc_ulsch_copy_kernel<<<dim3(nplain, PDC_DEMUX_COPY_PARTS), PDC_DEMUX_THREADS, 0, stream>>>(d_syms);
   }
-  // Set words; with placeholders also the sequence words of the largest symbol (3300 REs x 32 soft bits) and the two histories.
-  const size_t smem = sizeof(uint32_t) * (PDC_DEMUX_MAX_RE + (placeholders ? 2 * (PDC_DEMUX_MAX_RE + 2 + 64) : 0));
-  pdc_ulsch_demux_kernel<<<nsyms, PDC_DEMUX_THREADS, smem, stream>>>(d_syms);
+  if (nuci != 0) {
+    // Set words; with placeholders also the sequence words of the largest symbol (3300 REs x 32 soft bits) and the two histories.
+    const size_t smem = sizeof(uint32_t) * (PDC_DEMUX_MAX_RE + (placeholders ? 2 * (PDC_DEMUX_MAX_RE + 2 + 64) : 0));
+    pdc_ulsch_demux_kernel<<<dim3(nuci, PDC_DEMUX_UCI_PARTS), PDC_DEMUX_THREADS, smem, stream>>>(d_syms + nplain);
+  }
   return cudaGetLastError();
 }

@@ -1,6 +1,7 @@
 // C ABI entry points of libpuschdec_cuda.so (declared in include/pusch_dec_cuda.h). See pdc_runtime_internal.cuh for
 // the context layout and the batch planner.
 #include "pdc_runtime_internal.cuh"
+#include <algorithm>
 
 static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
 {
@@ -784,7 +785,6 @@ pdc_status demux_plan(const pdc_ulsch_demux_desc& c, std::vector<pdc_dev_demux_s
     pdc_dev_demux_sym s;
     memset(&s, 0, sizeof(s));
     s.nof_re = (dm ? re_dmrs_prb : 12u) * c.nof_prb, s.nbpr = nbpr, s.Qm = c.Qm;
-    s.scramble_pos = off_in, s.c_init = c.c_init;
     s.in = (const int8_t*)(uintptr_t)off_in, s.sch = (int8_t*)(uintptr_t)off_sch;
     s.harq = (int8_t*)(uintptr_t)m_harq, s.csi1 = (int8_t*)(uintptr_t)m_csi1, s.csi2 = (int8_t*)(uintptr_t)m_csi2;
     uint32_t       M_uci   = dm ? 0u : s.nof_re;
@@ -824,11 +824,14 @@ pdc_status demux_plan(const pdc_ulsch_demux_desc& c, std::vector<pdc_dev_demux_s
     s.csi2_ph = (c.nof_csi_part2_bits == 1 || c.nof_csi_part2_bits == 2) ? (uint8_t)c.nof_csi_part2_bits : 0;
     if (c.Qm > 1 && ((s.harq_m && s.harq_ph) || (s.csi1_m && s.csi1_ph) || (s.csi2_m && s.csi2_ph))) {
       placeholders = true;
+      if (syms && !pdc_prg_states(c.c_init, off_in, &s.x1_state, &s.x2_state)) {
+        return PDC_ERR_INVALID_ARG; // no context has been created yet
+      }
     }
     const uint32_t sch_re = s.nof_re - (s.harq_of_rvd ? 0u : s.harq_m) - s.csi1_m - s.csi2_m;
     off_in += s.nof_re * nbpr;
     off_sch += sch_re * nbpr;
-    if (syms) {
+    if (syms && s.nof_re != 0) { // a DM-RS symbol without data REs (two CDM groups of type 1) needs no CTA
       syms->push_back(s);
     }
   }
@@ -905,6 +908,10 @@ pdc_status pdc_ulsch_demultiplex_device(pdc_ctx* ctx, const pdc_ulsch_demux_desc
   if (st != PDC_OK) {
     return st;
   }
+  // Symbols without UCI first: they go to the copy kernel, the others to the kernel that builds the RE sets.
+  const size_t nplain = std::stable_partition(syms.begin(), syms.end(), [](const pdc_dev_demux_sym& s) {
+                          return s.harq_m == 0 && s.csi1_m == 0 && s.csi2_m == 0;
+                        }) - syms.begin();
   cudaStream_t stream = (cudaStream_t)stream_v;
   CK(cudaSetDevice(ctx->cfg.device));
   std::lock_guard<std::mutex> lock(ctx->demod_mtx);
@@ -924,8 +931,8 @@ pdc_status pdc_ulsch_demultiplex_device(pdc_ctx* ctx, const pdc_ulsch_demux_desc
   }
   memcpy(slot.h_desc, syms.data(), bytes); // pinned image: the upload does not wait for the stream to drain
   CK(cudaMemcpyAsync(slot.d_desc, slot.h_desc, bytes, cudaMemcpyHostToDevice, stream));
-  CK(pdc_demux_launch((const pdc_dev_demux_sym*)slot.d_desc, (uint32_t)syms.size(), placeholders, stream));
-  ctx->launches += 1;
+  CK(pdc_demux_launch((const pdc_dev_demux_sym*)slot.d_desc, (uint32_t)nplain, (uint32_t)(syms.size() - nplain), placeholders, stream));
+  ctx->launches += (nplain != 0 ? 1 : 0) + (nplain != syms.size() ? 1 : 0);
   CK(cudaEventRecord(slot.done, stream));
   slot.used = true;
   return PDC_OK;

@@ -28,7 +28,9 @@ extern "C" cudaError_t pdc_enc_init_device();
 extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb, uint32_t max_cbs, const uint32_t* graphs,
                                       const uint32_t* crc_pow, size_t smem, cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_init_device();
-extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_t nsyms, bool placeholders, cudaStream_t stream);
+extern "C" bool        pdc_prg_states(uint32_t c_init, uint32_t pos, uint32_t* s1, uint32_t* s2);
+extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_t nplain, uint32_t nuci, bool placeholders,
+                                        cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void* d_chunks, uint32_t nchunks,
                                         const float* d_symbols, const float* d_noise, int8_t* d_llrs, cudaStream_t stream);
 extern "C" cudaError_t pdc_launch_tb(const pdc_dev_tb* d_tbs, const pdc_dev_cb* d_cbs, const uint32_t* crc_pow, int ntb,
