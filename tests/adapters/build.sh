@@ -44,8 +44,20 @@ for s in "${SRCS[@]}"; do
 done
 for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
 ref_objs=$(ls "$ROOT"/oracle/_ref/obj/*.o | grep -v ref_shim)
-$CXX $BASE $INC -c "$HERE/harness.cpp" -o "$OBJ/harness.o"
-$CXX -shared -o "$OUT/libadapter_harness.so" "$OBJ/harness.o" "${objs[@]}" $ref_objs \
+# Product wiring: the reference's DU-low HAL factory with integration/srsran_cuda.patch applied, in a scratch copy
+# under _build/ (the reference tree itself is never touched), so that the test can call the patched make_du_low_hal_dependencies.
+N3="$OUT/n3"
+rm -rf "$N3"
+mkdir -p "$N3/apps/units/flexible_o_du" "$N3/lib/phy/upper"
+cp -r "$REF/apps/units/flexible_o_du/o_du_low" "$N3/apps/units/flexible_o_du/"
+cp "$REF/lib/phy/upper/upper_phy_factories.cpp" "$REF/lib/phy/upper/CMakeLists.txt" "$N3/lib/phy/upper/"
+cp "$REF/CMakeLists.txt" "$N3/"
+chmod -R u+w "$N3"
+(cd "$N3" && patch -s -p1 --no-backup-if-mismatch < "$ROOT/integration/srsran_cuda.patch")
+N3INC="-I$N3/apps/units/flexible_o_du/o_du_low -I$REF -I$ROOT/srsran_project_b200/adapters"
+$CXX $BASE $INC $N3INC -DSRSRAN_CUDA_FOUND -c "$N3/apps/units/flexible_o_du/o_du_low/du_low_hal_factory.cpp" -o "$OBJ/n3_du_low_hal_factory.o"
+$CXX $BASE $INC $N3INC -c "$HERE/harness.cpp" -o "$OBJ/harness.o"
+$CXX -shared -o "$OUT/libadapter_harness.so" "$OBJ/harness.o" "$OBJ/n3_du_low_hal_factory.o" "${objs[@]}" $ref_objs \
   -L"$ROOT/srsran_project_b200" -lsrsran_cuda_adapters -lpuschdec_cuda -lpthread \
   -Wl,-rpath,'$ORIGIN/../../../srsran_project_b200'
 echo "built $OUT/libadapter_harness.so"

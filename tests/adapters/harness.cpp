@@ -19,6 +19,7 @@
 #include "phy/upper/sequence_generators/pseudo_random_generator_impl.h"
 #include "srsran/phy/upper/channel_processors/pusch/pusch_codeword_buffer.h"
 #include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_buffer.h"
+#include "du_low_hal_factory.h" // the reference's, with integration/srsran_cuda.patch applied (tests/adapters/build.sh)
 #include "crc_calculator_clmul_impl.h"
 #include "crc_calculator_lut_impl.h"
 #include "ldpc/ldpc_decoder_avx2.h"
@@ -478,6 +479,35 @@ int adt_ulsch_demultiplex(const uint32_t* cfg,
     }
   }
   return 0;
+}
+
+// Product wiring: the reference's make_du_low_hal_dependencies, patched by integration/srsran_cuda.patch, given a
+// `hal: cuda_hwacc:` configuration. Returns a bit mask: 1 = PUSCH decoder factory present, 2 = PDSCH encoder factory present,
+// 4 = an accelerator could be created from each factory present; -1 = no device.
+int adt_n3_hal_dependencies(int pusch_dec, int pdsch_enc, int external_harq)
+{
+  du_low_unit_hal_config hal_cfg;
+  hal_cfg.cuda_hwacc.emplace();
+  hal_cfg.cuda_hwacc->device            = 0;
+  hal_cfg.cuda_hwacc->pusch_dec         = pusch_dec != 0;
+  hal_cfg.cuda_hwacc->pdsch_enc         = pdsch_enc != 0;
+  hal_cfg.cuda_hwacc->external_harq     = external_harq != 0;
+  hal_cfg.cuda_hwacc->harq_context_size = 304;
+  o_du_low_hal_dependencies deps;
+  try {
+    deps = make_du_low_hal_dependencies(hal_cfg);
+  } catch (const std::exception&) {
+    return -1;
+  }
+  int  mask = (deps.hw_decoder_factory ? 1 : 0) | (deps.hw_encoder_factory ? 2 : 0);
+  bool ok   = true;
+  if (deps.hw_decoder_factory) {
+    ok = ok && (deps.hw_decoder_factory->create() != nullptr);
+  }
+  if (deps.hw_encoder_factory) {
+    ok = ok && (deps.hw_encoder_factory->create() != nullptr);
+  }
+  return mask | (ok ? 4 : 0);
 }
 
 } // extern "C"

@@ -236,3 +236,26 @@ def test_cuda_ulsch_demultiplex_adapter_reproduces_the_golden_streams(block, use
             assert lens[q] == g["lengths"][k, q], (k, q)
             got = np.frombuffer(hashlib.sha256(outs[q][:int(lens[q])].tobytes()).digest(), np.uint8)
             assert np.array_equal(got, g["digests"][k, q]), (k, q, cfg)
+
+
+def test_n3_patch_applies_and_compiles():
+    """Product wiring: integration/srsran_cuda.patch (a `hal: cuda_hwacc:` section, the CUDA HAL factories beside the
+    bbdev ones, "cuda" as LDPC decoder / rate dematcher type, the CMake option) applies to the reference tree and the patched
+    translation units compile against the reference's headers and the adapters, with and without SRSRAN_CUDA_FOUND."""
+    import subprocess
+
+    if not os.path.isdir("/root/reference/apps/units/flexible_o_du/o_du_low"):
+        pytest.skip("no reference tree on this machine")
+    r = subprocess.run(["bash", os.path.join(os.path.dirname(HERE), "integration", "check_patch.sh")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "patch applies and the patched files compile" in r.stdout
+
+
+@pytest.mark.gpu
+def test_n3_patched_hal_factory_returns_the_cuda_accelerators():
+    """The reference's make_du_low_hal_dependencies with the patch applied (compiled into the harness), given a `cuda_hwacc`
+    configuration: the PUSCH decoder / PDSCH encoder HAL factories it returns are the CUDA ones and create accelerators."""
+    lib = _lib()
+    assert lib.adt_n3_hal_dependencies(1, 1, 1) == 7
+    assert lib.adt_n3_hal_dependencies(1, 0, 0) == 5
+    assert lib.adt_n3_hal_dependencies(0, 1, 1) == 6
