@@ -100,3 +100,42 @@ def test_library_planner_lengths_and_contract():
             bad[0][f] = v
         with pytest.raises(B.PdcError):
             B.ulsch_demux_lengths(bad)
+
+
+def test_library_planner_fuzz_against_restatement():
+    """2000 random configurations, many of them with UCI that does NOT fit: the host planner either returns the stream lengths the
+    restatement delivers, or rejects exactly the configurations for which the reference would assert at on_end_codeword (a UCI
+    stream not delivered in full)."""
+    from srsran_project_b200 import binding as B
+
+    rng = np.random.default_rng(4242)
+    accepted = rejected = 0
+    for k in range(2000):
+        cfg = C.make_case(rng, nof_prb=int(rng.integers(1, 6)), nsym=int(rng.integers(1, 15)), start=0)
+        if cfg["start_symbol"] + cfg["nof_symbols"] > 14:
+            continue
+        if rng.integers(0, 3) == 0:  # stretch one encoded length so that it may not fit
+            f = ("nof_enc_harq_ack_bits", "nof_enc_csi_part1_bits", "nof_enc_csi_part2_bits")[int(rng.integers(0, 3))]
+            if cfg[f]:
+                cfg[f] *= int(rng.integers(2, 12))
+                if f == "nof_enc_harq_ack_bits" and cfg["nof_harq_ack_bits"] <= 2:
+                    cfg["nof_harq_ack_rvd"] = max(cfg["nof_harq_ack_rvd"], cfg[f])
+        # the restatement needs a symbol without DM-RS after the first DM-RS symbol, like the reference
+        m = cfg["dmrs_symbol_mask"]
+        first = next(l for l in range(14) if (m >> l) & 1)
+        if all((m >> l) & 1 for l in range(first, 14)):
+            continue
+        streams = D.demultiplex(cfg, np.zeros(C.nof_softbits(cfg), np.int8))
+        complete = (streams[1].size == cfg["nof_enc_harq_ack_bits"] and streams[2].size == cfg["nof_enc_csi_part1_bits"]
+                    and streams[3].size == cfg["nof_enc_csi_part2_bits"])
+        d = np.zeros(1, B.ULSCH_DEMUX_DTYPE)
+        C.fill_desc(d[0], cfg)
+        if complete:
+            lens = B.ulsch_demux_lengths(d)
+            assert list(lens) == [C.nof_softbits(cfg)] + [s.size for s in streams], (k, cfg)
+            accepted += 1
+        else:
+            with pytest.raises(B.PdcError):
+                B.ulsch_demux_lengths(d)
+            rejected += 1
+    assert accepted > 800 and rejected > 100, (accepted, rejected)
