@@ -518,13 +518,13 @@ __device__ __forceinline__ void h2_task_words(const int8_t* __restrict__ src, ui
   if constexpr (QM == 8 || QM == 4) {
 #pragma unroll
     for (int r = 0; r < QM / 4; ++r) {
-      const int4 v = __ldg(reinterpret_cast<const int4*>(src) + r);
+      const int4 v = __ldcs(reinterpret_cast<const int4*>(src) + r); // read once: do not displace the CRC tables in L1
       w[4 * r] = (uint32_t)v.x, w[4 * r + 1] = (uint32_t)v.y, w[4 * r + 2] = (uint32_t)v.z, w[4 * r + 3] = (uint32_t)v.w;
     }
   } else {
 #pragma unroll
     for (int r = 0; r < QM / 2; ++r) {
-      const int2 v = __ldg(reinterpret_cast<const int2*>(src) + r);
+      const int2 v = __ldcs(reinterpret_cast<const int2*>(src) + r);
       w[2 * r] = (uint32_t)v.x, w[2 * r + 1] = (uint32_t)v.y;
     }
   }
@@ -710,11 +710,12 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
       if ((reinterpret_cast<uintptr_t>(cb.soft) & 15) == 0 && ((nstage | pl.N) & 15) == 0) {
         int4*     dst = reinterpret_cast<int4*>(cb.soft);
         const int n16 = nstage >> 4, N16 = pl.N >> 4;
+        // Streaming stores: the soft buffer is the HARQ state for a later slot, nothing in this launch reads it back.
         for (int q = tid; q < n16; q += nth) {
-          dst[q] = reinterpret_cast<const int4*>(stg)[q];
+          __stcs(dst + q, reinterpret_cast<const int4*>(stg)[q]);
         }
         for (int q = n16 + tid; q < N16; q += nth) {
-          dst[q] = make_int4(0, 0, 0, 0);
+          __stcs(dst + q, make_int4(0, 0, 0, 0));
         }
       } else {
         for (int q = tid; q < nstage; q += nth) {
