@@ -78,8 +78,9 @@ def _placeholder(re_data, mask, qm, nbits):
     return out
 
 
-def demultiplex(cfg, llrs):
-    """Returns (sch, harq_ack, csi_part1, csi_part2) int8 arrays for the descrambled codeword `llrs`."""
+def demultiplex(cfg, llrs, dtype=np.int8):
+    """Returns (sch, harq_ack, csi_part1, csi_part2) arrays for the descrambled codeword `llrs` (int8 soft bits; a wider dtype lets
+    a test push position indices through to learn where each soft bit goes)."""
     mask_l = cfg["dmrs_symbol_mask"]
     first_dmrs = next(l for l in range(14) if (mask_l >> l) & 1)
     l1 = next(l for l in range(first_dmrs, 14) if not (mask_l >> l) & 1)  # :32-46
@@ -87,7 +88,7 @@ def demultiplex(cfg, llrs):
     nbpr = cfg["qm"] * cfg["nof_layers"]
     lens = symbol_lengths(cfg)
     seq = gold_bits(cfg["c_init"], int(sum(lens)))
-    llrs = np.asarray(llrs, np.int8)
+    llrs = np.asarray(llrs, dtype)
     assert llrs.size == sum(lens)
     m_rvd = m_harq = m_csi1 = m_csi2 = 0
     csi2_active = cfg["nof_enc_csi_part2_bits"] != 0 and cfg["csi2_mode"] == 0
@@ -162,7 +163,7 @@ def demultiplex(cfg, llrs):
         if idx.size:
             out["sch"].append(data.reshape(M, nbpr)[idx].reshape(-1))
         off += n_sym
-    cat = lambda v: np.concatenate(v).astype(np.int8) if v else np.zeros(0, np.int8)  # noqa: E731
+    cat = lambda v: np.concatenate(v).astype(dtype) if v else np.zeros(0, dtype)  # noqa: E731
     return cat(out["sch"]), cat(out["harq"]), cat(out["csi1"]), cat(out["csi2"])
 
 

@@ -144,3 +144,89 @@ def test_contract_violations(acc):
     bad[0]["nof_csi_part1_bits"] = 5
     with pytest.raises(B.PdcError):
         acc.ulsch_demultiplex(bad, data, out_len)
+
+
+def test_pusch_with_uci_symbols_to_transport_block(acc):
+    """The whole receive side of a PUSCH that carries UCI, on the device: a transport block is encoded for the UL-SCH REs that the
+    multiplexing leaves, laid into the codeword around random HARQ-ACK / CSI bits (the REs a 2-bit HARQ-ACK punctures carry
+    noise for the UL-SCH), scrambled and modulated; then pdc_demodulate_device (+ descrambling) -> pdc_ulsch_demultiplex_device
+    -> pdc_decode_device_tbs on one stream return the transport block, and the UCI streams equal the restatement's."""
+    import torch
+
+    from srsran_project_b200 import binding as B
+    from tools import demod_stimulus as DS
+    from tools import stimulus as T
+
+    rng = np.random.default_rng(21)
+    qm, layers = 6, 2
+    cfg = C.make_case(rng, qm=qm, layers=layers, nof_prb=40, harq_bits=2, csi1_bits=30, csi2_bits=9, dmrs=[2, 11], csi2_mode=0)
+    # A 2-bit HARQ-ACK occupies a few dozen REs: all of them puncture the first code block, which must stay decodable.
+    cfg["nof_enc_harq_ack_bits"], cfg["nof_harq_ack_rvd"] = 40 * qm * layers, 60 * qm * layers
+    n_soft = C.nof_softbits(cfg)
+    # Where every soft bit of the codeword goes: push 1-based positions through the restatement (0 = punctured in UL-SCH).
+    where = D.demultiplex(cfg, np.arange(1, n_soft + 1), dtype=np.int64)
+    sch_pos = np.abs(where[0])
+    G = int(sch_pos.size)
+    assert G % (qm * layers) == 0
+    tbs_bits = int(G * 0.6) // 8 * 8
+    tb = rng.integers(0, 2, tbs_bits, dtype=np.uint8)
+    seg, sch_bits, _ = T.tb_encode(1, tbs_bits, tb, 0, qm, 0, layers, G)
+    tx = rng.integers(0, 2, n_soft, dtype=np.uint8)  # UCI positions and punctured REs: anything
+    keep = sch_pos > 0
+    tx[sch_pos[keep] - 1] = sch_bits[keep]
+    z = DS.modulate(tx ^ DS.gold_sequence(n_soft, cfg["c_init"]), qm)
+    sigma2 = 0.004
+    z = z + (rng.normal(0, np.sqrt(sigma2 / 2), z.size) + 1j * rng.normal(0, np.sqrt(sigma2 / 2), z.size)).astype(np.complex64)
+    sym = np.stack([z.real, z.imag], axis=1).astype(np.float32)
+    nv = np.full(z.size, sigma2, np.float32)
+
+    dseg = np.zeros(1, B.DEMOD_SEG_DTYPE)
+    dseg[0]["nof_symbols"], dseg[0]["mod"], dseg[0]["flags"], dseg[0]["c_init"] = z.size, qm, B.PDC_DEMOD_F_DESCRAMBLE, cfg["c_init"]
+    ud = np.zeros(1, B.ULSCH_DEMUX_DTYPE)
+    C.fill_desc(ud[0], cfg)
+    lens = B.ulsch_demux_lengths(ud)
+    assert lens[0] == n_soft and lens[1] == G
+    offs, o = [], 0
+    for n in lens[1:]:
+        offs.append(o)
+        o += (n + 15) // 16 * 16
+    ud[0]["sch_offset"], ud[0]["harq_ack_offset"], ud[0]["csi_part1_offset"], ud[0]["csi_part2_offset"] = offs
+    Cn, K = seg["C"], seg["K"]
+    Es = T.rm_lengths(Cn, G, layers, qm)
+    stride = (K + 31) // 32 * 4
+    descs, tbd = B.make_descs(Cn), np.zeros(1, B.TB_DESC_DTYPE)
+    e0 = 0
+    for q in range(Cn):
+        d = descs[q]
+        d["bg"], d["Z"], d["Qm"], d["rv"], d["crc_type"], d["max_iter"] = 1, seg["Z"], qm, 0, B.PDC_CRC24B if Cn > 1 else B.PDC_CRC24A, 10
+        d["flags"], d["E"], d["nof_filler"] = B.PDC_F_NEW_DATA | B.PDC_F_EARLY_STOP, Es[q], seg["F"]
+        d["llr_offset"], d["soft_offset"], d["out_offset"] = offs[0] + e0, q * 25344, q * stride
+        e0 += Es[q]
+    tbd[0]["first_cb"], tbd[0]["nof_cbs"], tbd[0]["tbs_bits"] = 0, Cn, tbs_bits
+
+    d_sym = torch.from_numpy(sym.reshape(-1)).cuda()
+    d_nv = torch.from_numpy(nv).cuda()
+    d_cw = torch.zeros(n_soft + 16, dtype=torch.int8, device="cuda")
+    d_streams = torch.zeros(o + 16, dtype=torch.int8, device="cuda")
+    d_soft = torch.zeros(Cn * 25344, dtype=torch.int8, device="cuda")
+    d_bits = torch.zeros(Cn * stride, dtype=torch.uint8, device="cuda")
+    d_res = torch.zeros(Cn * 8, dtype=torch.uint8, device="cuda")
+    d_tb = torch.zeros((tbs_bits // 8 + 3) // 4 * 4, dtype=torch.uint8, device="cuda")
+    d_tbres = torch.zeros(4, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    acc.demodulate_device(dseg, d_sym.data_ptr(), d_nv.data_ptr(), d_cw.data_ptr(), stream)
+    acc.ulsch_demultiplex_device(ud, d_cw.data_ptr(), d_streams.data_ptr(), stream)
+    acc.decode_device_tbs(descs, tbd, d_streams.data_ptr(), d_soft.data_ptr(), d_bits.data_ptr(), d_res.data_ptr(),
+                          d_tb.data_ptr(), d_tbres.data_ptr(), stream)
+    torch.cuda.synchronize()
+    want = D.demultiplex(cfg, d_cw.cpu().numpy()[:n_soft])
+    got = d_streams.cpu().numpy()
+    for off, w in zip(offs, want):
+        assert np.array_equal(got[off:off + w.size], w)
+    hard = (got[:G] < 0).astype(np.uint8)
+    assert (hard[keep] != sch_bits[keep]).mean() < 0.02, "the demodulated UL-SCH stream is not the transmitted codeword"
+    cres = d_res.cpu().numpy().view(B.RESULT_DTYPE)
+    tres = d_tbres.cpu().numpy().view(B.TB_RESULT_DTYPE)
+    assert tres[0]["tb_crc_ok"] == 1 and tres[0]["nof_cbs_ok"] == Cn, (cres, tres)
+    assert np.array_equal(d_tb.cpu().numpy()[:tbs_bits // 8], np.packbits(tb))
+    assert (want[0] == 0).sum() >= 2 * qm * layers  # the punctured REs reached the decoder as erasures
