@@ -54,8 +54,11 @@ def build(n_tbs, sigma2=0.0016, seed=21, distinct=4):
 def run(ctx, n_tbs=64, steps=20, warmup=3, cpu=True, hbm_peak_gbs=None):
     import torch
 
-    from oracle import pyoracle
     from srsran_project_b200 import binding as B
+
+    pyoracle = None
+    if cpu:  # the oracle is only ever the checker / the baseline of the CPU leg
+        from oracle import pyoracle
 
     w = build(n_tbs)
     nsym = w["noise"].size
