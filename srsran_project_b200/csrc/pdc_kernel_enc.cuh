@@ -114,47 +114,82 @@ __device__ __forceinline__ uint32_t pdc_enc_tb_word(const uint8_t* __restrict__ 
   return __brev(be);
 }
 
+// b(x) x^(8 k) mod P for every byte b, k < 7, per CRC type: reduces a 32-bit word (k = 0..3) and multiplies a remainder by
+// x^32 (k = 4..6) with one lookup per byte.
+__device__ uint32_t d_enc_crc_bytes[3][7][256];
+
+// CRC of a D-bit message, i.e. (sum of bit_i x^(D - 1 - i)) x^order mod P, by one warp. fetch(w) returns the word whose bit j
+// is message bit 32 w + j (only bits below D are looked at). Each lane runs Horner's rule over a contiguous run of whole words
+// (seven byte-table lookups per word), its remainder is moved to its place with one x^j table entry per set bit, and the warp
+// xors the lanes; the bits behind the last whole word are folded bit by bit. About 200 warp instructions for an 8424-bit code
+// block, where one table entry per set message bit costs about 4000.
+template <class F>
+__device__ __forceinline__ uint32_t pdc_enc_crc_warp(F fetch, uint32_t D, int crc_type, const uint32_t* __restrict__ crc_pow, int lane)
+{
+  const uint32_t  order = (crc_type == PDC_CRC16) ? 16u : 24u;
+  const uint32_t* pw    = crc_pow + (size_t)(crc_type - 1) * PDC_CRC_TABLE_LEN;
+  const uint32_t(*T)[256] = d_enc_crc_bytes[crc_type - 1];
+  const uint32_t nfull = D >> 5, tail = D & 31u;
+  const uint32_t q  = (nfull + 31u) >> 5; // whole words per lane
+  const uint32_t w0 = min(nfull, (uint32_t)lane * q), w1 = min(nfull, w0 + q);
+  uint32_t       acc = 0;
+  for (uint32_t w = w0; w < w1; ++w) {
+    const uint32_t W = __brev(fetch(w)); // bit i <-> x^i
+    acc = __ldg(&T[4][acc & 255u]) ^ __ldg(&T[5][(acc >> 8) & 255u]) ^ __ldg(&T[6][acc >> 16]) ^ __ldg(&T[0][W & 255u]) ^
+          __ldg(&T[1][(W >> 8) & 255u]) ^ __ldg(&T[2][(W >> 16) & 255u]) ^ __ldg(&T[3][W >> 24]);
+  }
+  uint32_t       out = 0;
+  const uint32_t n   = D - 32u * w1 + order; // x^n: the bits that follow this lane's run, and the CRC's own x^order
+#pragma unroll
+  for (int b = 0; b < 24; ++b) {
+    if ((acc >> b) & 1u) {
+      out ^= __ldg(pw + n + b);
+    }
+  }
+  if (lane == 0 && tail != 0) {
+    const uint32_t v = fetch(nfull);
+    for (uint32_t j = 0; j < tail; ++j) {
+      if ((v >> j) & 1u) {
+        out ^= pw[tail - 1u - j + order];
+      }
+    }
+  }
+  return __reduce_xor_sync(0xffffffffu, out);
+}
+
 // The code block's share of the TB CRC (ldpc_segmenter_tx_impl: the CRC the segmenter computes before cutting the block).
 __global__ void __launch_bounds__(128) pdc_enc_crc_kernel(const pdc_dev_enc_tb* __restrict__ tbs, const uint32_t* __restrict__ crc_pow)
 {
-  __shared__ uint32_t  scratch[32];
-  if (blockIdx.x >= tbs[blockIdx.y].nof_cbs) {
+  // A warp per code block, four code blocks per CTA.
+  const int      lane = threadIdx.x & 31;
+  const uint32_t r    = blockIdx.x * 4u + (threadIdx.x >> 5);
+  if (r >= tbs[blockIdx.y].nof_cbs) {
     return;
   }
-  const pdc_dev_enc_cb cb  = pdc_enc_cb_of(tbs[blockIdx.y], blockIdx.x);
-  const int            tid = threadIdx.x, nth = blockDim.x;
+  const pdc_dev_enc_cb cb = pdc_enc_cb_of(tbs[blockIdx.y], r);
   if (cb.first_bit >= cb.tbs_bits) {
     return; // nothing of the payload in this code block
   }
-  const uint32_t  nbits = min(cb.nof_bits, cb.tbs_bits - cb.first_bit); // payload bits carried here
-  const uint32_t* pw    = crc_pow + (size_t)(cb.tb_crc_type - 1) * PDC_CRC_TABLE_LEN;
-  uint32_t        acc   = 0;
-  for (uint32_t w = tid; 32u * w < nbits; w += nth) {
+  const uint32_t nbits = min(cb.nof_bits, cb.tbs_bits - cb.first_bit); // payload bits carried here
+  auto           fetch = [&](uint32_t w) {
     const uint32_t n0 = 32u * w;
-    uint32_t       v;
     if (n0 + 32u <= nbits) {
-      v = pdc_enc_tb_word(cb.tb, cb.first_bit + n0);
-    } else {
-      v = 0;
-      for (uint32_t j = 0; n0 + j < nbits; ++j) {
-        const uint32_t g = cb.first_bit + n0 + j;
-        v |= (uint32_t)((cb.tb[g >> 3] >> (7 - (g & 7))) & 1u) << j;
-      }
+      return pdc_enc_tb_word(cb.tb, cb.first_bit + n0);
     }
-    while (v != 0) { // the remainder is the xor of one table entry per set bit
-      const uint32_t j = (uint32_t)__ffs((int)v) - 1u;
-      acc ^= pw[nbits - 1u - (n0 + j)];
-      v &= v - 1u;
+    uint32_t v = 0;
+    for (uint32_t j = 0; n0 + j < nbits; ++j) {
+      const uint32_t g = cb.first_bit + n0 + j;
+      v |= (uint32_t)((cb.tb[g >> 3] >> (7 - (g & 7))) & 1u) << j;
     }
-  }
-  acc = pdc_enc_block_xor(acc, scratch, tid, nth);
-  if (tid < 32) {
-    const int      order = (cb.tb_crc_type == PDC_CRC16) ? 16 : 24;
-    const uint32_t after = cb.tbs_bits - (cb.first_bit + nbits) + (uint32_t)order;
-    const uint32_t share = pdc_crc_shift_warp(acc, after, cb.tb_crc_type, tid);
-    if (tid == 0) {
-      atomicXor(cb.tb_crc, share);
-    }
+    return v;
+  };
+  // Remainder of this code block's payload as if it ended the transport block (the CRC's x^order included) ...
+  const uint32_t rem = pdc_enc_crc_warp(fetch, nbits, cb.tb_crc_type, crc_pow, lane);
+  // ... moved to its place: the payload bits that follow it.
+  const uint32_t after = cb.tbs_bits - (cb.first_bit + nbits);
+  const uint32_t share = pdc_crc_shift_warp(rem, after, cb.tb_crc_type, lane);
+  if (lane == 0) {
+    atomicXor(cb.tb_crc, share);
   }
 }
 
@@ -292,20 +327,12 @@ __device__ __forceinline__ void pdc_enc_cb_words(const pdc_dev_enc_cb& cb, const
   }
   __syncthreads();
   if (cb.cb_crc) {
-    const uint32_t* pw  = crc_pow + (size_t)(PDC_CRC24B - 1) * PDC_CRC_TABLE_LEN;
-    uint32_t        acc = 0;
-    for (uint32_t w = tid; 32u * w < D; w += nth) {
-      uint32_t v = cww[w];
-      while (v != 0) {
-        const uint32_t j = (uint32_t)__ffs((int)v) - 1u;
-        acc ^= pw[D - 1u - (32u * w + j) + 24u];
-        v &= v - 1u;
+    if (tid < 32) {
+      const uint32_t acc = pdc_enc_crc_warp([&](uint32_t w) { return cww[w]; }, D, PDC_CRC24B, crc_pow, tid);
+      if (tid < 24) {
+        const uint32_t n = D + (uint32_t)tid;
+        atomicOr(&cww[n >> 5], ((acc >> (23 - tid)) & 1u) << (n & 31u));
       }
-    }
-    acc = pdc_enc_block_xor(acc, scratch, tid, nth);
-    if (tid < 24) {
-      const uint32_t n = D + (uint32_t)tid;
-      atomicOr(&cww[n >> 5], ((acc >> (23 - tid)) & 1u) << (n & 31u));
     }
     __syncthreads();
   }
@@ -575,6 +602,27 @@ extern "C" cudaError_t pdc_enc_init_device()
   if (e != cudaSuccess) {
     return e;
   }
+  static uint32_t bytes[3][7][256];
+  for (int c = 0; c != 3; ++c) {
+    const uint32_t top = 1u << order[c];
+    for (int b = 0; b != 256; ++b) {
+      // b(x) mod P is b itself (8 bits < order), then eight multiplications by x per table.
+      uint32_t v = (uint32_t)b;
+      for (int k = 0; k != 7; ++k) {
+        bytes[c][k][b] = v;
+        for (int i = 0; i != 8; ++i) {
+          v <<= 1;
+          if (v & top) {
+            v ^= poly[c];
+          }
+        }
+      }
+    }
+  }
+  e = cudaMemcpyToSymbol(d_enc_crc_bytes, bytes, sizeof(bytes));
+  if (e != cudaSuccess) {
+    return e;
+  }
   static uint32_t rows[3][24][32];
   for (int c = 0; c != 3; ++c) {
     const uint32_t top = 1u << order[c];
@@ -602,7 +650,7 @@ extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb,
   // grid.y is limited to 65535 transport blocks per launch
   for (uint32_t t0 = 0; t0 < ntb; t0 += 65535u) {
     const uint32_t nt = (ntb - t0 < 65535u) ? ntb - t0 : 65535u;
-    pdc_enc_crc_kernel<<<dim3(max_cbs, nt), 128, 0, stream>>>(d_tbs + t0, crc_pow);
+    pdc_enc_crc_kernel<<<dim3((max_cbs + 3) / 4, nt), 128, 0, stream>>>(d_tbs + t0, crc_pow);
     pdc_enc_cb_kernel<<<dim3(max_cbs, nt), 256, smem, stream>>>(d_tbs + t0, graphs, crc_pow);
   }
   return cudaGetLastError();
