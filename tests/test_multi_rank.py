@@ -66,3 +66,18 @@ def test_reference_arm_runs_on_rank0_only():
     assert line["cpu_baseline"]["kind"] == "reference" and line["e2e"]["h2d_bytes_per_step"] == 0
     for k in ("metric", "unit", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "config"):
         assert k in line
+
+
+def test_numa_cpulist_parsing_and_noop_binding(monkeypatch):
+    """Host placement helper (srsran_project_b200/numa.py): sysfs cpulist parsing, and binding is a no-op when the device's CPUs
+    are all the process may use anyway (the single-socket box) or cannot be told."""
+    from srsran_project_b200 import numa
+
+    assert numa._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert numa._parse_cpulist("") == set()
+    allowed = os.sched_getaffinity(0)
+    monkeypatch.setattr(numa, "device_local_cpus", lambda device: set(allowed))
+    assert numa.bind_to_device_socket(0) is None
+    monkeypatch.setattr(numa, "device_local_cpus", lambda device: None)
+    assert numa.bind_to_device_socket(0) is None
+    assert os.sched_getaffinity(0) == allowed
