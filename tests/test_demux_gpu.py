@@ -230,3 +230,23 @@ def test_pusch_with_uci_symbols_to_transport_block(acc):
     assert tres[0]["tb_crc_ok"] == 1 and tres[0]["nof_cbs_ok"] == Cn, (cres, tres)
     assert np.array_equal(d_tb.cpu().numpy()[:tbs_bits // 8], np.packbits(tb))
     assert (want[0] == 0).sum() >= 2 * qm * layers  # the punctured REs reached the decoder as erasures
+
+
+def test_host_buffer_entry_with_several_codewords(acc):
+    """pdc_ulsch_demultiplex (host buffers) with several codewords in one call, byte-aligned layout: every stream comes back,
+    bytes between the streams are left alone."""
+    from srsran_project_b200 import binding as B
+
+    cfgs = C.cases()[3:9] + C.cases()[30:33]
+    descs, data, out_len = layout(B, cfgs, range(700, 700 + len(cfgs)), 1)
+    out = np.full(out_len, 55, np.int8)
+    acc._check(acc.lib.pdc_ulsch_demultiplex(acc.h, descs.ctypes.data, descs.size, data.ctypes.data, data.size, out.ctypes.data,
+                                             out.size))
+    touched = np.zeros(out_len, bool)
+    for k, (d, cfg) in enumerate(zip(descs, cfgs)):
+        want = D.demultiplex(cfg, C.codeword(cfg, 700 + k))
+        for f, b in zip(("sch_offset", "harq_ack_offset", "csi_part1_offset", "csi_part2_offset"), want):
+            o = int(d[f])
+            assert np.array_equal(out[o:o + b.size], b), (k, f, cfg)
+            touched[o:o + b.size] = True
+    assert (out[~touched] == 55).all()
