@@ -644,6 +644,9 @@ extern "C" cudaError_t pdc_enc_init_device()
   return cudaFuncSetAttribute(pdc_enc_cb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
 }
 
+// Threads per code block of pdc_enc_cb_kernel. A code block is a chain of ten short dependent phases, most of them narrower than
+// a CTA: the device overlaps the code blocks that are resident, so the CTA is kept small (registers allow twelve per SM).
+#define PDC_ENC_CB_THREADS 128
 extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb, uint32_t max_cbs, const uint32_t* graphs,
                                       const uint32_t* crc_pow, size_t smem, cudaStream_t stream)
 {
@@ -651,7 +654,7 @@ extern "C" cudaError_t pdc_enc_launch(const pdc_dev_enc_tb* d_tbs, uint32_t ntb,
   for (uint32_t t0 = 0; t0 < ntb; t0 += 65535u) {
     const uint32_t nt = (ntb - t0 < 65535u) ? ntb - t0 : 65535u;
     pdc_enc_crc_kernel<<<dim3((max_cbs + 3) / 4, nt), 128, 0, stream>>>(d_tbs + t0, crc_pow);
-    pdc_enc_cb_kernel<<<dim3(max_cbs, nt), 256, smem, stream>>>(d_tbs + t0, graphs, crc_pow);
+    pdc_enc_cb_kernel<<<dim3(max_cbs, nt), PDC_ENC_CB_THREADS, smem, stream>>>(d_tbs + t0, graphs, crc_pow);
   }
   return cudaGetLastError();
 }
