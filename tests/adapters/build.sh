@@ -60,4 +60,5 @@ $CXX $BASE $INC $N3INC -c "$HERE/harness.cpp" -o "$OBJ/harness.o"
 $CXX -shared -o "$OUT/libadapter_harness.so" "$OBJ/harness.o" "$OBJ/n3_du_low_hal_factory.o" "${objs[@]}" $ref_objs \
   -L"$ROOT/srsran_project_b200" -lsrsran_cuda_adapters -lpuschdec_cuda -lpthread \
   -Wl,-rpath,'$ORIGIN/../../../srsran_project_b200'
+rm -rf "$N3" # the patched scratch copy of the reference files has served: only objects stay under _build/
 echo "built $OUT/libadapter_harness.so"
