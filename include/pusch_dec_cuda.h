@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 6
+#define PDC_ABI_VERSION 7
 
 typedef enum {
   PDC_OK               = 0,
@@ -165,6 +165,21 @@ pdc_status pdc_decode_device(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32
 pdc_status pdc_decode_device_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32_t n, const pdc_tb_desc* tbs_host,
                                  uint32_t ntb, const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits, pdc_cb_result* d_res,
                                  uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream);
+
+/* Allocation-free variant of pdc_decode_device_tbs. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same arguments, same results. The call allocates nothing on the device or through any library: the device
+ * scratch of the path (device descriptors, launch order, every code block's share of the TB CRC between
+ * pdc_tb_assemble_kernel and pdc_tb_finish_kernel) lives in one file-scope `static __device__` array of 112 KiB that every
+ * GPU loading the library holds until exit; its address is resolved once per device with cudaGetSymbolAddress.
+ * Limit: n <= PDC_STATIC_MAX_CBS and ntb <= PDC_STATIC_MAX_CBS, else PDC_ERR_CAPACITY (pdc_last_error says why).
+ * Every call on a device shares that array (and keeps the previous call's contents in it; what must start at zero is
+ * cleared on `stream` by the call): calls are serialised on the host, but two calls whose GPU work OVERLAPS (different
+ * streams without an ordering between them) race on the scratch - issue them on one stream or order the streams. */
+#define PDC_STATIC_MAX_CBS 1024
+pdc_status pdc_decode_device_tbs_static(pdc_ctx* ctx, const pdc_cb_desc* descs_host, uint32_t n, const pdc_tb_desc* tbs_host,
+                                        uint32_t ntb, const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits,
+                                        pdc_cb_result* d_res, uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream);
 
 /* --- LLR producers on the device: soft demodulation + descrambling --------------------------------------
  * One segment = ONE call of demodulation_mapper::demodulate_soft (in pusch_demodulator_impl.cpp:370-395 the resource elements

@@ -69,6 +69,7 @@ ULSCH_DEMUX_DTYPE = np.dtype([("Qm", np.uint8), ("nof_layers", np.uint8), ("star
 PDC_DEMUX_F_CSI2_AFTER_CSI1 = 0x01
 PDC_MOD_PI2_BPSK, PDC_MOD_BPSK, PDC_MOD_QPSK, PDC_MOD_QAM16, PDC_MOD_QAM64, PDC_MOD_QAM256 = 0, 1, 2, 4, 6, 8
 PDC_DEMOD_F_DESCRAMBLE = 0x01
+PDC_STATIC_MAX_CBS = 1024
 assert DESC_DTYPE.itemsize == ctypes.sizeof(CbDesc) == 48
 assert TB_DESC_DTYPE.itemsize == 24 and TB_RESULT_DTYPE.itemsize == 4
 assert RESULT_DTYPE.itemsize == ctypes.sizeof(CbResult) == 8
@@ -113,6 +114,7 @@ def load_library():
                                    ctypes.POINTER(ctypes.c_int64)]
     lib.pdc_fetch_tbs.argtypes = [vp, ctypes.c_int64, vp, ctypes.c_size_t, vp, vp, vp, ctypes.c_size_t]
     lib.pdc_decode_device_tbs.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, vp, vp, vp, vp, vp, vp]
+    lib.pdc_decode_device_tbs_static.argtypes = lib.pdc_decode_device_tbs.argtypes
     lib.pdc_demodulate_device.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, vp, vp]
     lib.pdc_demodulate.argtypes = [vp, vp, ctypes.c_uint32, vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t]
     lib.pdc_ulsch_demux_lengths.argtypes = [vp, vp]
@@ -138,6 +140,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
+                    "pdc_decode_device_tbs_static",
                     "pdc_demodulate_device", "pdc_demodulate", "pdc_ulsch_demux_lengths",
                     "pdc_ulsch_demultiplex_device", "pdc_ulsch_demultiplex", "pdc_pdsch_encode", "pdc_pdsch_encode_device",
                     "pdc_pdsch_segmentation", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
@@ -251,6 +254,13 @@ class PuschDecCuda:
         self._check(self.lib.pdc_decode_device_tbs(self.h, descs.ctypes.data, descs.size, tbs.ctypes.data, tbs.size,
                                                    d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, d_tb_bytes_ptr,
                                                    d_tb_res_ptr, stream_ptr))
+
+    def decode_device_tbs_static(self, descs, tbs, d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, d_tb_bytes_ptr,
+                                 d_tb_res_ptr, stream_ptr=None):
+        """pdc_decode_device_tbs_static: the allocation-free variant (scratch in a static device array, <= 1024 CBs)."""
+        self._check(self.lib.pdc_decode_device_tbs_static(self.h, descs.ctypes.data, descs.size, tbs.ctypes.data, tbs.size,
+                                                          d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, d_tb_bytes_ptr,
+                                                          d_tb_res_ptr, stream_ptr))
 
     # --- device path -----------------------------------------------------------------------------------------------
     def decode_device(self, descs, d_llrs_ptr, d_soft_ptr, d_bits_ptr, d_res_ptr, stream_ptr=None):

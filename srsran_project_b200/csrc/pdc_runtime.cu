@@ -585,6 +585,115 @@ pdc_status pdc_decode_device_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_
   return decode_device_common(ctx, descs, n, tbs, ntb, d_llrs, d_soft, d_bits, d_res, d_tb_bytes, d_tb_res, stream);
 }
 
+// ---- allocation-free variant of pdc_decode_device_tbs ------------------------------------------------------------------------
+// The device scratch the transport-block path needs between its kernels — device descriptors of the code blocks and transport
+// blocks, the launch order and every code block's share of the TB CRC (pdc_dev_tb.terms, written by pdc_tb_assemble_kernel,
+// read by pdc_tb_finish_kernel) — lives in ONE file-scope device array instead of a ticket's cudaMalloc'ed staging. Every GPU
+// that loads the library holds these PDC_STATIC_SCRATCH_BYTES until exit. All calls share the array.
+#define PDC_STATIC_CBS_OFF 0
+#define PDC_STATIC_TBS_OFF (PDC_STATIC_CBS_OFF + sizeof(pdc_dev_cb) * PDC_STATIC_MAX_CBS)
+#define PDC_STATIC_ORDER_OFF (PDC_STATIC_TBS_OFF + sizeof(pdc_dev_tb) * PDC_STATIC_MAX_CBS)
+#define PDC_STATIC_TERMS_OFF (PDC_STATIC_ORDER_OFF + sizeof(uint32_t) * PDC_STATIC_MAX_CBS)
+#define PDC_STATIC_SCRATCH_BYTES (PDC_STATIC_TERMS_OFF + sizeof(uint32_t) * PDC_STATIC_MAX_CBS)
+static_assert(PDC_STATIC_TBS_OFF % 16 == 0 && PDC_STATIC_ORDER_OFF % 16 == 0 && PDC_STATIC_TERMS_OFF % 16 == 0, "alignment");
+
+static __device__ __align__(256) unsigned char g_pdc_static_scratch[PDC_STATIC_SCRATCH_BYTES];
+
+// In host code `g_pdc_static_scratch` is only a handle of the symbol, not a device address: the address is asked for once per
+// device, with that device current, and only that pointer is ever handed to a kernel or a copy.
+#define PDC_STATIC_MAX_DEVICES 64
+static unsigned char* g_static_scratch_ptr[PDC_STATIC_MAX_DEVICES];
+static std::mutex     g_static_mtx; // serialises the calls on the host: one host image of the descriptors, one device array
+static struct {
+  pdc_dev_cb cbs[PDC_STATIC_MAX_CBS];
+  pdc_dev_tb tbs[PDC_STATIC_MAX_CBS];
+  uint32_t   order[PDC_STATIC_MAX_CBS];
+  uint8_t    lst[PDC_STATIC_MAX_CBS];
+} g_static_host; // .bss, nothing is allocated per call
+
+static pdc_status static_scratch_address(pdc_ctx* ctx, unsigned char** out)
+{
+  const int dev = ctx->cfg.device;
+  if (dev < 0 || dev >= PDC_STATIC_MAX_DEVICES) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  CK(cudaSetDevice(dev));
+  if (!g_static_scratch_ptr[dev]) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_pdc_static_scratch));
+    if (!p) {
+      ctx->err = "cudaGetSymbolAddress returned a null address for the static scratch";
+      return PDC_ERR_CUDA;
+    }
+    g_static_scratch_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_scratch_ptr[dev];
+  return PDC_OK;
+}
+
+pdc_status pdc_decode_device_tbs_static(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs,
+                                        uint32_t ntb, const int8_t* d_llrs, int8_t* d_soft, uint8_t* d_bits,
+                                        pdc_cb_result* d_res, uint8_t* d_tb_bytes, pdc_tb_result* d_tb_res, void* stream_v)
+{
+  if (!ctx || !descs || !d_res || n == 0 || !tbs || ntb == 0 || !d_tb_bytes || !d_tb_res) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  if (n > PDC_STATIC_MAX_CBS || ntb > PDC_STATIC_MAX_CBS) {
+    std::lock_guard<std::mutex> lock(g_static_mtx);
+    ctx->err = "pdc_decode_device_tbs_static: more than PDC_STATIC_MAX_CBS (1024) code blocks or transport blocks in one "
+               "call; split the batch or use pdc_decode_device_tbs";
+    return PDC_ERR_CAPACITY;
+  }
+  cudaStream_t                stream = (cudaStream_t)stream_v;
+  std::lock_guard<std::mutex> lock(g_static_mtx);
+  unsigned char*              base = nullptr;
+  pdc_status                  st   = static_scratch_address(ctx, &base);
+  if (st != PDC_OK) {
+    return st;
+  }
+  pdc_dev_cb* d_cbs   = reinterpret_cast<pdc_dev_cb*>(base + PDC_STATIC_CBS_OFF);
+  pdc_dev_tb* d_tbs   = reinterpret_cast<pdc_dev_tb*>(base + PDC_STATIC_TBS_OFF);
+  uint32_t*   d_order = reinterpret_cast<uint32_t*>(base + PDC_STATIC_ORDER_OFF);
+  uint32_t*   d_terms = reinterpret_cast<uint32_t*>(base + PDC_STATIC_TERMS_OFF);
+  batch_buffers buf;
+  buf.d_llrs = d_llrs, buf.d_soft = d_soft, buf.d_bits = d_bits, buf.d_res = d_res;
+  buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots;
+  buf.d_slot_bits = ctx->d_harq_bits;
+  batch_plan bp;
+  st = plan_batch(descs, n, buf, g_static_host.cbs, g_static_host.order, g_static_host.lst, bp);
+  if (st == PDC_OK) {
+    uint32_t processed = bp.n_lane; // code blocks a kernel reads LLRs for (all but the PDC_F_DECODED ones)
+    for (int k = 0; k != PDC_NOF_PACKED_LISTS; ++k) {
+      processed += bp.n_h2[k];
+    }
+    if ((bp.any_host_soft && !d_soft) || (processed != 0 && !d_llrs)) {
+      st = PDC_ERR_INVALID_ARG;
+    }
+  }
+  tb_plan tp;
+  if (st == PDC_OK) {
+    st = plan_tbs(tbs, ntb, descs, n, d_tb_bytes, d_tb_res, d_terms, g_static_host.tbs, tp);
+  }
+  if (st != PDC_OK) {
+    return st;
+  }
+  // Pageable sources: cudaMemcpyAsync returns once they have been staged, so the host image is free for the next call when
+  // the lock is released. The array keeps the previous call's contents: the CRC shares start from zero again.
+  CK(cudaMemcpyAsync(d_cbs, g_static_host.cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
+  CK(cudaMemcpyAsync(d_tbs, g_static_host.tbs, sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, stream));
+  if (!bp.identity) {
+    CK(cudaMemcpyAsync(d_order, g_static_host.order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
+  }
+  CK(cudaMemsetAsync(d_terms, 0, sizeof(uint32_t) * n, stream));
+  st = launch_batch(ctx, bp, d_cbs, d_order, stream);
+  if (st != PDC_OK) {
+    return st;
+  }
+  CK(pdc_launch_tb(d_tbs, d_cbs, ctx->d_crc, (int)ntb, (int)tp.max_cbs, stream));
+  ctx->launches += 2;
+  return PDC_OK;
+}
+
 // ---- LLR producers ---------------------------------------------------------------------------------------------------------
 static int demod_bits_per_symbol(unsigned mod)
 {
