@@ -128,13 +128,23 @@ typedef struct {
 /* --- lifetime ---------------------------------------------------------------------------------------------------- */
 pdc_status  pdc_create(const pdc_config* cfg, pdc_ctx** out);
 void        pdc_destroy(pdc_ctx* ctx);
-const char* pdc_last_error(const pdc_ctx* ctx); /* static or context-owned string; "" if none */
+const char* pdc_last_error(const pdc_ctx* ctx); /* copy owned by the calling thread, valid until its next call; "" if none */
+/* Zero-copy submission (off by default). Off: pdc_submit* copies the LLRs into the ticket's pinned staging before it
+ * returns, so the caller's memory may be reused at once. On: LLRs that lie in page-locked host memory (cudaHostAlloc /
+ * cudaHostRegister, pdc_host_alloc) are read by the DMA engine from where they lie AFTER the call has returned: the caller
+ * must leave them untouched until pdc_poll returns PDC_OK or pdc_fetch* has returned. Pageable memory is always staged. */
+pdc_status  pdc_set_zero_copy(pdc_ctx* ctx, int enable);
+/* Page-locked host memory for zero-copy submissions (cudaHostAlloc / cudaFreeHost behind the C ABI, for hosts that do not
+ * link the CUDA runtime themselves). */
+void*       pdc_host_alloc(size_t bytes);
+void        pdc_host_free(void* p);
 int         pdc_abi_version(void);
 
 /* --- host-buffer path (what the srsRAN adapters call): H2D copy, kernel, D2H copy on one stream ---------------- */
 /* Queues n CBs. llrs: host buffer holding every CB's LLRs (desc.llr_offset). soft_in: host soft buffers for CBs with
  * harq_slot < 0 (NULL allowed when every CB has PDC_F_NEW_DATA|harq_slot>=0|DECODE_ONLY). Copies into pinned staging,
- * so the caller's memory may be reused as soon as the call returns. */
+ * so the caller's memory may be reused as soon as the call returns — unless pdc_set_zero_copy is on and llrs is page-locked
+ * (see there). Returns PDC_ERR_CAPACITY when every ticket is in flight: back-pressure, not a failure; retry. */
 pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
                       const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket);
 /* PDC_OK when the batch has completed, PDC_ERR_NOT_READY otherwise. */

@@ -11,7 +11,9 @@
 #include "srsran/ran/pdsch/pdsch_constants.h"
 #include "srsran/ran/sch/sch_constants.h"
 #include "srsran/support/executors/task_executor.h"
+#include <cstdio>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 using namespace srsran;
@@ -149,12 +151,21 @@ private:
     pdc_ticket    ticket = 0;
     pdc_tb_result tb_res = {};
     tb_bytes.resize((transport_block.size() + 3) / 4 * 4);
-    pdc_status st = pdc_submit_tbs(context->get(), descs.data(), nof_cbs, &tb, 1, base, softbits_count, nullptr, 0, &ticket);
+    // PDC_ERR_CAPACITY = every submission slot of the context is in flight (more decoder instances at work than
+    // nof_instances, or pdc_decode_device borrowing one): back-pressure, not a failure. The reference never drops a
+    // transport block for pool contention, so wait for a slot like the other adapters do.
+    pdc_status st;
+    while ((st = pdc_submit_tbs(context->get(), descs.data(), nof_cbs, &tb, 1, base, softbits_count, nullptr, 0, &ticket)) ==
+           PDC_ERR_CAPACITY) {
+      std::this_thread::yield();
+    }
     if (st == PDC_OK) {
       st = pdc_fetch_tbs(context->get(), ticket, tb_bytes.data(), tb_bytes.size(), &tb_res, results.data(), nullptr, 0);
     }
     if (st != PDC_OK) {
       // Never throws on the data path: the transport block is reported as not decoded and stays in its HARQ process.
+      std::fprintf(stderr, "pusch_decoder_cuda: transport block of %u code blocks failed (status %d: %s)\n", nof_cbs, (int)st,
+                   pdc_last_error(context->get()));
       softbuffer.unlock();
       result_notifier->on_sch_data(stats);
       return;

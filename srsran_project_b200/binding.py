@@ -105,6 +105,11 @@ def load_library():
     lib.pdc_destroy.restype = None
     lib.pdc_last_error.argtypes = [vp]
     lib.pdc_last_error.restype = ctypes.c_char_p
+    lib.pdc_set_zero_copy.argtypes = [vp, ctypes.c_int]
+    lib.pdc_host_alloc.argtypes = [ctypes.c_size_t]
+    lib.pdc_host_alloc.restype = vp
+    lib.pdc_host_free.argtypes = [vp]
+    lib.pdc_host_free.restype = None
     lib.pdc_submit.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t,
                                ctypes.POINTER(ctypes.c_int64)]
     lib.pdc_poll.argtypes = [vp, ctypes.c_int64]
@@ -138,7 +143,8 @@ def load_library():
     return lib
 
 
-EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_submit", "pdc_poll",
+EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_set_zero_copy", "pdc_host_alloc",
+                    "pdc_host_free", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
                     "pdc_decode_device_tbs_static",
                     "pdc_demodulate_device", "pdc_demodulate", "pdc_ulsch_demux_lengths",
@@ -184,6 +190,10 @@ class PuschDecCuda:
             raise PdcError(st, self.lib.pdc_last_error(None).decode())
         self.h = h
         self.device = device
+
+    def set_zero_copy(self, enable=True):
+        """pdc_set_zero_copy: page-locked LLR sources are DMA-read in place; keep them untouched until the ticket completes."""
+        self._check(self.lib.pdc_set_zero_copy(self.h, 1 if enable else 0))
 
     def close(self):
         if getattr(self, "h", None):

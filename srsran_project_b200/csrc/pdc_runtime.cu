@@ -8,6 +8,7 @@ static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
   const pdc_config& c = ctx->cfg;
   CK(cudaStreamCreateWithFlags(&t.stream, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&t.done, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&t.staged, cudaEventDisableTiming));
   size_t bits_bytes = (size_t)c.max_batch_cbs * (PDC_MAX_K / 8);
   // Transport-block descriptors / results travel in the same copies as the code-block ones: they are laid out right behind
   // the n code-block entries of a submission, so each array has room for both.
@@ -44,6 +45,9 @@ static void free_ticket(ticket_t& t)
   if (t.done) {
     cudaEventDestroy(t.done);
   }
+  if (t.staged) {
+    cudaEventDestroy(t.staged);
+  }
   if (t.stream) {
     cudaStreamDestroy(t.stream);
   }
@@ -72,7 +76,44 @@ int pdc_abi_version(void)
 
 const char* pdc_last_error(const pdc_ctx* ctx)
 {
-  return ctx ? ctx->err.c_str() : g_static_err;
+  // A copy owned by the calling thread: other threads may fail (and rewrite the context's string) at any time.
+  static thread_local std::string mine;
+  if (ctx) {
+    pdc_ctx*                    c = const_cast<pdc_ctx*>(ctx);
+    std::lock_guard<std::mutex> lock(c->err_mtx);
+    mine = c->err;
+  } else {
+    std::lock_guard<std::mutex> lock(g_static_err_mtx);
+    mine = g_static_err;
+  }
+  return mine.c_str();
+}
+
+void* pdc_host_alloc(size_t bytes)
+{
+  void* p = nullptr;
+  if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+
+void pdc_host_free(void* p)
+{
+  if (p) {
+    cudaFreeHost(p);
+  }
+}
+
+pdc_status pdc_set_zero_copy(pdc_ctx* ctx, int enable)
+{
+  if (!ctx) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(ctx->mtx);
+  ctx->zero_copy = enable != 0;
+  return PDC_OK;
 }
 
 pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
@@ -83,15 +124,17 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   *out      = nullptr;
   int ndev  = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+    std::lock_guard<std::mutex> lock(g_static_err_mtx);
     g_static_err = "no CUDA device: this library has no CPU fallback";
     return PDC_ERR_NO_DEVICE;
   }
   pdc_ctx* ctx = new pdc_ctx;
   ctx->cfg     = *cfg;
   auto fail    = [&](pdc_status s) {
-    static std::string keep;
-    keep         = ctx->err;
-    g_static_err = keep.c_str();
+    {
+      std::lock_guard<std::mutex> lock(g_static_err_mtx);
+      g_static_err = ctx->err;
+    }
     pdc_destroy(ctx);
     return s;
   };
@@ -179,10 +222,15 @@ void pdc_destroy(pdc_ctx* ctx)
 static ticket_t* reserve_ticket(pdc_ctx* ctx)
 {
   std::lock_guard<std::mutex> lock(ctx->mtx);
-  for (ticket_t& c : ctx->tickets) {
+  // Round robin: a ticket that pdc_decode_device borrowed is synchronised with before it is used again, so the least
+  // recently used one is the one whose work is most likely over.
+  const size_t nt = ctx->tickets.size();
+  for (size_t k = 0; k != nt; ++k) {
+    ticket_t& c = ctx->tickets[(ctx->next_ticket + k) % nt];
     if (!c.in_use) {
-      c.in_use = true;
-      c.id     = ctx->next_id++;
+      c.in_use         = true;
+      c.id             = ctx->next_id++;
+      ctx->next_ticket = (unsigned)((ctx->next_ticket + k + 1) % nt);
       return &c;
     }
   }
@@ -248,7 +296,9 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   }
   CKT(cudaSetDevice(ctx->cfg.device));
   if (t->borrowed) {
-    CKT(cudaStreamSynchronize(t->stream)); // pdc_decode_device's descriptor copy out of this staging has to be over
+    // pdc_decode_device's descriptor copy out of this pinned staging has to be over; its kernels, which read the device
+    // staging, are ordered before this ticket's stream through t->done (cudaStreamWaitEvent in decode_device_common).
+    CKT(cudaEventSynchronize(t->staged));
     t->borrowed = false;
   }
   batch_buffers buf;
@@ -295,12 +345,15 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
       bp = again;
     }
   }
-  // Stage and go. LLRs already in pinned memory are sent from where they lie.
-  const int8_t*         src = llrs;
-  cudaPointerAttributes attr;
-  bool                  pinned = (cudaPointerGetAttributes(&attr, llrs) == cudaSuccess) &&
-                (attr.type == cudaMemoryTypeHost);
-  cudaGetLastError(); // pageable pointers make the query set an error on some runtimes
+  // Stage and go. With pdc_set_zero_copy, LLRs that already lie in pinned (or registered) memory are sent from where they
+  // lie: the caller then keeps them untouched until the ticket has completed.
+  const int8_t* src    = llrs;
+  bool          pinned = false;
+  if (ctx->zero_copy && llr_bytes != 0) {
+    cudaPointerAttributes attr;
+    pinned = (cudaPointerGetAttributes(&attr, llrs) == cudaSuccess) && (attr.type == cudaMemoryTypeHost);
+    cudaGetLastError(); // pageable pointers make the query set an error on some runtimes
+  }
   if (!pinned && llr_bytes != 0) {
     memcpy(t->h_llrs, llrs, llr_bytes);
     src = t->h_llrs;
@@ -527,10 +580,13 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
     return PDC_ERR_CAPACITY;
   }
   CKT(cudaSetDevice(ctx->cfg.device));
-  // The pinned descriptor staging may still be read by a previous asynchronous copy on the caller's stream.
+  // A previous borrower's asynchronous descriptor copy may still be reading the pinned staging (host side: wait for that
+  // copy only), and its kernels may still be reading the device staging from ANOTHER stream (device side: this stream waits
+  // for them; a no-op when it is the same stream).
   if (t->borrowed) {
-    CKT(cudaStreamSynchronize(t->stream));
+    CKT(cudaEventSynchronize(t->staged));
   }
+  CKT(cudaStreamWaitEvent(stream, t->done, 0));
   t->borrowed = true;
   batch_buffers buf;
   buf.d_llrs = d_llrs, buf.d_soft = d_soft, buf.d_bits = d_bits, buf.d_res = d_res;
@@ -554,18 +610,17 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
   if (!bp.identity) {
     CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
   }
-  // The pinned staging is free again once the descriptor copies have been consumed; order that on the ticket's stream.
-  CKT(cudaEventRecord(t->done, stream));
-  CKT(cudaStreamWaitEvent(t->stream, t->done, 0));
+  // The pinned staging is free again once the descriptor copies have been consumed.
+  CKT(cudaEventRecord(t->staged, stream));
   st = launch_batch(ctx, bp, t->d_cbs, t->d_order, stream);
   if (st == PDC_OK && tbs) {
-    // d_tbs / d_terms of this ticket are read by these two launches: the next user of the ticket orders itself after them
-    // through the same event (recorded again below), as for the descriptor staging.
     CKT(pdc_launch_tb(t->d_tbs, t->d_cbs, ctx->d_crc, (int)ntb, (int)tp.max_cbs, stream));
     ctx->launches += 2;
-    CKT(cudaEventRecord(t->done, stream));
-    CKT(cudaStreamWaitEvent(t->stream, t->done, 0));
   }
+  // d_cbs / d_order (and d_tbs / d_terms) of this ticket are read by the launches above: the next user of the ticket, on
+  // whatever stream, orders itself after them through the same event, recorded again behind the kernels.
+  CKT(cudaEventRecord(t->done, stream));
+  CKT(cudaStreamWaitEvent(t->stream, t->done, 0));
   return release_ticket(ctx, t, st);
 }
 
@@ -622,6 +677,7 @@ static pdc_status static_scratch_address(pdc_ctx* ctx, unsigned char** out)
     void* p = nullptr;
     CK(cudaGetSymbolAddress(&p, g_pdc_static_scratch));
     if (!p) {
+      std::lock_guard<std::mutex> elock(ctx->err_mtx);
       ctx->err = "cudaGetSymbolAddress returned a null address for the static scratch";
       return PDC_ERR_CUDA;
     }
@@ -639,7 +695,7 @@ pdc_status pdc_decode_device_tbs_static(pdc_ctx* ctx, const pdc_cb_desc* descs, 
     return PDC_ERR_INVALID_ARG;
   }
   if (n > PDC_STATIC_MAX_CBS || ntb > PDC_STATIC_MAX_CBS) {
-    std::lock_guard<std::mutex> lock(g_static_mtx);
+    std::lock_guard<std::mutex> lock(ctx->err_mtx);
     ctx->err = "pdc_decode_device_tbs_static: more than PDC_STATIC_MAX_CBS (1024) code blocks or transport blocks in one "
                "call; split the batch or use pdc_decode_device_tbs";
     return PDC_ERR_CAPACITY;

@@ -41,6 +41,7 @@ namespace {
 struct ticket_t {
   cudaStream_t stream   = nullptr;
   cudaEvent_t  done     = nullptr;
+  cudaEvent_t  staged   = nullptr; // pdc_decode_device*: the descriptor copies out of the pinned staging have been consumed
   bool         in_use   = false;
   int64_t      id       = -1;
   uint32_t     n        = 0;
@@ -79,9 +80,12 @@ struct ticket_t {
 struct pdc_ctx {
   pdc_config            cfg;
   std::mutex            mtx;
+  std::mutex            err_mtx; // submit / fetch run outside mtx: the error string has its own lock
   std::string           err;
+  bool                  zero_copy = false; // pdc_set_zero_copy
   std::vector<ticket_t> tickets;
   int64_t               next_id = 1;
+  unsigned              next_ticket = 0; // reserve_ticket starts its search here (round robin)
   uint32_t*             d_graphs = nullptr;
   uint32_t*             d_crc    = nullptr;
   uint32_t*             d_crc_bit = nullptr;
@@ -120,7 +124,8 @@ struct pdc_ctx {
 
 namespace {
 
-const char* g_static_err = "";
+std::mutex  g_static_err_mtx;
+std::string g_static_err; // last error of a call without a context (pdc_create)
 
 bool cuda_ok(pdc_ctx* ctx, cudaError_t e, const char* what)
 {
@@ -130,6 +135,7 @@ bool cuda_ok(pdc_ctx* ctx, cudaError_t e, const char* what)
   char buf[256];
   snprintf(buf, sizeof(buf), "%s: %s", what, cudaGetErrorString(e));
   if (ctx) {
+    std::lock_guard<std::mutex> lock(ctx->err_mtx);
     ctx->err = buf;
   }
   return false;
@@ -428,7 +434,8 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
         return PDC_ERR_INVALID_ARG;
       }
       c.out = buf.d_bits + d.out_offset;
-      dense &= (d.out_offset == bits_end); // outputs back to back from offset 0, in order
+      dense &= (d.out_offset == bits_end) && !(d.flags & PDC_F_DEMATCH_ONLY); // outputs back to back from offset 0, in
+                                                                             // order, every one written by a kernel
       size_t be = d.out_offset + cls.K_bytes4;
       bits_end  = be > bits_end ? be : bits_end;
     }

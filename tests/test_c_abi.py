@@ -344,3 +344,80 @@ def test_device_pointer_entry_equals_host_entry(acc):
     side.synchronize()
     assert (d_res.cpu().numpy().view(B.RESULT_DTYPE) == res).all()
     assert (d_bits.cpu().numpy() == bits).all() and (d_soft.cpu().numpy() == soft).all()
+
+
+@pytest.mark.gpu
+def test_pinned_source_may_be_overwritten_after_submit_unless_zero_copy(acc):
+    """include/pusch_dec_cuda.h: by default pdc_submit stages the LLRs before it returns, page-locked source or not, so the
+    caller may refill its buffer at once; with pdc_set_zero_copy the source is read in place (same results when left alone)."""
+    import torch
+
+    from srsran_project_b200 import binding as B
+
+    d, llrs, nb = valid_batch(B, n=16, Z=384, bg=1, seed=21)
+    want_res, want_bits = acc.run(d, llrs, nb, np.zeros(16 * 25344, np.int8))
+    pinned = torch.empty(llrs.size, dtype=torch.int8).pin_memory()
+    src = pinned.numpy()
+    for zero_copy in (False, True):
+        acc.set_zero_copy(zero_copy)
+        try:
+            for _ in range(8):
+                src[:] = llrs
+                t = acc.submit(d, src, np.zeros(16 * 25344, np.int8))
+                if not zero_copy:
+                    src[:] = 0x55  # the contract: the call has copied what it needs
+                bits = np.zeros(nb, np.uint8)
+                res = acc.fetch(t, 16, bits, np.zeros(16 * 25344, np.int8))
+                assert (res == want_res).all() and (bits == want_bits).all(), zero_copy
+        finally:
+            acc.set_zero_copy(False)
+
+
+@pytest.mark.gpu
+def test_device_entry_from_two_threads_on_two_streams():
+    """pdc_decode_device borrows a ticket's descriptor staging: calls from different host threads on different streams must not
+    overwrite descriptors that earlier kernels are still reading (more calls than tickets, so staging is reused)."""
+    import torch
+
+    import srsran_project_b200 as pdc
+    from srsran_project_b200 import binding as B
+
+    ctx = pdc.PuschDecCuda(device=0, max_batch_cbs=64, max_batch_llrs=4 << 20, harq_slots=0, nof_tickets=2)
+    try:
+        work, want = [], []
+        for k in range(2):
+            d, llrs, nb = valid_batch(B, n=48, Z=(384, 352)[k], bg=1, seed=30 + k)
+            want.append(ctx.run(d, llrs, nb, np.zeros(48 * 25344, np.int8)))
+            work.append((d, torch.from_numpy(llrs).cuda(), nb))
+        errors = []
+
+        def worker(k):
+            try:
+                torch.cuda.set_device(0)
+                d, d_llrs, nb = work[k]
+                side = torch.cuda.Stream()
+                outs = []
+                for _ in range(12):  # back to back, no synchronisation in between: 12 launches per stream over 2 tickets
+                    d_soft = torch.zeros(48 * 25344, dtype=torch.int8, device="cuda")
+                    d_bits = torch.zeros(nb, dtype=torch.uint8, device="cuda")
+                    d_res = torch.zeros(48 * 8, dtype=torch.uint8, device="cuda")
+                    side.wait_stream(torch.cuda.current_stream())
+                    ctx.decode_device(d, d_llrs.data_ptr(), d_soft.data_ptr(), d_bits.data_ptr(), d_res.data_ptr(),
+                                      side.cuda_stream)
+                    outs.append((d_res, d_bits, d_soft))
+                side.synchronize()
+                for d_res, d_bits, _ in outs:
+                    if not ((d_res.cpu().numpy().view(B.RESULT_DTYPE) == want[k][0]).all() and
+                            (d_bits.cpu().numpy() == want[k][1]).all()):
+                        errors.append((k, "mismatch"))
+            except Exception as e:  # noqa: BLE001 - reported below
+                errors.append((k, repr(e)))
+
+        threads = [threading.Thread(target=worker, args=(k,)) for k in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        assert not errors, errors
+    finally:
+        ctx.close()
