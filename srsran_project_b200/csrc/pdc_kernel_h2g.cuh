@@ -4,10 +4,16 @@
 // pdc_kernel_h2.cuh (whose helpers it reuses); what differs:
 //   * the number of layers is known only after the rate dematcher ran (ldpc_decoder_impl.cpp:83-115: it follows from the
 //     index of the last non-zero soft bit), so the relative rotations of the columns — which depend on WHICH rows take
-//     part — are derived per code block, in shared memory, by one thread per column;
+//     part — are derived per code block, in shared memory, by one thread per edge;
 //   * the four core rows keep their messages in registers; the extension rows (degree 3..10, each with one private
-//     degree-1 parity column) keep theirs as the same int8 pairs in shared memory, [word][thread] so that every access is
-//     conflict free, and their parity column as one private word per thread (never rotated, never shared);
+//     degree-1 parity column) keep theirs, the same int8 pairs, in TENSOR MEMORY: a thread's messages are only ever
+//     touched by that thread, and the 32x32b shape of tcgen05.ld / tcgen05.st gives every thread of a warp its own TMEM
+//     lane, so the 256 KB of TMEM per SM serve as a private scratch that costs neither registers nor shared memory. At
+//     rate 1/3 and Z = 384 a code block's 107 message words per thread would otherwise need 80 KB of shared memory: with
+//     them in TMEM two code blocks are resident per SM instead of one (the kernel is latency-bound: profiles/);
+//   * the degree-1 parity column of an extension row is read by that row alone, so instead of its soft value S and the
+//     row's message c to it only u = S - c is kept (one private shared-memory word per thread): u never changes until the
+//     update promotes S to +-infinity, and then stays infinite (pdc_kernel_h2.cuh: h2_edge_update; here h2g_parity_update);
 //   * extension rows are a run-time loop over rows with the row degree as a template parameter (8 variants).
 #pragma once
 #include "pdc_kernel_h2.cuh"
@@ -20,56 +26,111 @@ __device__ uint16_t d_h2g_prev[2][PDC_H2G_MAX_EDGES];
 __device__ uint16_t d_h2g_last[2][48][26];
 #endif
 
-template <int DEG>
-__device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstride, uint32_t padr,
-                                            const uint32_t* __restrict__ xr, const uint32_t* __restrict__ xw, uint32_t soft_t,
-                                            uint32_t half_row, bool active, bool generic)
+// ---- tensor memory as per-thread scratch -----------------------------------------------------------------------------------
+// 32x32b: thread i of warp w addresses TMEM lane 32 (w % 4) + i; the address (lane << 16 | column) is warp-uniform.
+template <int N>
+__device__ __forceinline__ void h2g_tm_ld(uint32_t taddr, uint32_t (&v)[N])
 {
-  constexpr int  NW = (DEG + 1) / 2;
+  static_assert(N >= 1 && N <= 5, "message words of one extension row");
+  if constexpr (N == 1) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v[0]) : "r"(taddr));
+  } else if constexpr (N == 2 || N == 3) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "r"(taddr));
+    if constexpr (N == 3) {
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v[2]) : "r"(taddr + 2));
+    }
+  } else {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+                 : "r"(taddr));
+    if constexpr (N == 5) {
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v[4]) : "r"(taddr + 4));
+    }
+  }
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void h2g_tm_st(uint32_t taddr, const uint32_t (&v)[N])
+{
+  if constexpr (N == 1) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(v[0]));
+  } else if constexpr (N == 2 || N == 3) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(v[0]), "r"(v[1]));
+    if constexpr (N == 3) {
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr + 2), "r"(v[2]));
+    }
+  } else {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]));
+    if constexpr (N == 5) {
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr + 4), "r"(v[4]));
+    }
+  }
+}
+
+// Pass 2 for the row's own degree-1 parity column: only u = S - c is kept. Not promoted: S' = clamp(u) + c', so
+// u' = S' - c' = clamp(u, +-120) = u (|u| <= 64 until it is infinite). Promoted (u infinite, or min(|u|, 120) + ms > 120):
+// S' = sign(u) inf, and so is u' from then on.
+__device__ __forceinline__ void h2g_parity_update(uint32_t& u, uint32_t m1, uint32_t s1p, uint32_t d, uint32_t one)
+{
+  const uint32_t a  = h2_abs(u);
+  const uint32_t eq = h2_eq_mask(a, m1);
+  const uint32_t ms = s1p ^ (d & eq);
+  const uint32_t sg = h2_copysign_one(u, one);
+  const uint32_t w  = h2_add(h2_min(a, H2_120), ms);
+  const uint32_t qa = h2_add_sat(a, H2_N336);
+  const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);
+  const uint32_t G  = h2_fma(qa, H2_65504, h2_mul(qb, H2_65504)); // 0 | 65504 | inf
+  u                 = h2_fma(sg, h2_add(G, G), u);                 // sg * (0 | inf) + u
+}
+
+// One extension row. taddr: TMEM address of the row's message words of this warp; padr: shared-memory address of the
+// thread's parity word (u of the degree-1 column); e0: first edge of the row in the tables.
+template <int DEG>
+__device__ __forceinline__ void h2g_ext_row(int e0, uint32_t taddr, uint32_t padr, const uint32_t* __restrict__ xr,
+                                            const uint32_t* __restrict__ xw, uint32_t soft_t, uint32_t half_row, bool active,
+                                            bool generic)
+{
+  constexpr int  NW = DEG / 2; // DEG - 1 messages, two per word
   uint32_t       u[DEG], cw[NW];
   uint32_t       par = 0;
   const uint32_t one = h2_opaque_one();
-#pragma unroll
-  for (int j = 0; j < NW; ++j) {
-    cw[j] = lds32(cadr + j * cstride); // private to the thread: no ordering needed
-  }
-  const uint32_t Sp = lds32(padr);
   uint32_t       ents[DEG - 1];
 #pragma unroll
   for (int k = 0; k < DEG - 1; ++k) {
-    ents[k] = xr[e0 + k]; // table entries do not depend on the other warps either
+    ents[k] = xr[e0 + k]; // table entries do not depend on the other warps
   }
-  h2_static_for<DEG>([&](auto k_) {
-    constexpr int k = decltype(k_)::value;
-    uint32_t      S;
-    if constexpr (k + 1 < DEG) {
-      const uint32_t ent = ents[k];
-      const uint32_t adr = soft_t + (ent & 0xffffu);
-      const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
-      S = __byte_perm(w0, w1, ent >> 16);
-    } else {
-      S = Sp; // the row's own parity column (last edge: columns ascend)
-    }
-    const uint32_t x = __byte_perm(cw[k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
-    u[k]             = h2_sub(S, x);
+  u[DEG - 1] = lds32(padr);  // private to the thread: no ordering needed
+  h2g_tm_ld<NW>(taddr, cw);  // likewise
+  h2_static_for<DEG - 1>([&](auto k_) {
+    constexpr int  k   = decltype(k_)::value;
+    const uint32_t ent = ents[k];
+    const uint32_t adr = soft_t + (ent & 0xffffu);
+    const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
+    const uint32_t S  = __byte_perm(w0, w1, ent >> 16);
+    const uint32_t x  = __byte_perm(cw[k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+    u[k]              = h2_sub(S, x);
     par ^= u[k];
   });
+  par ^= u[DEG - 1];
   uint32_t s1p, d, m1;
   h2_row_minima<DEG>(u, par, generic, m1, s1p, d);
-  uint32_t y[DEG];
-  h2_static_for<DEG>([&](auto k_) {
+  uint32_t y[DEG - 1];
+  h2_static_for<DEG - 1>([&](auto k_) {
     constexpr int k = decltype(k_)::value;
     h2_edge_update(u[k], y[k], m1, s1p, d, one);
   });
+  h2g_parity_update(u[DEG - 1], m1, s1p, d, one);
+  h2_static_for<NW>([&](auto i_) {
+    constexpr int i = decltype(i_)::value;
+    if constexpr (2 * i + 1 < DEG - 1) {
+      cw[i] = __byte_perm(y[2 * i], y[2 * i + 1], 0x6420);
+    } else {
+      cw[i] = __byte_perm(y[2 * i], 0u, 0x4420);
+    }
+  });
+  h2g_tm_st<NW>(taddr, cw); // idle lanes of a partly filled warp write their own (unused) TMEM lanes
   if (active) {
-    h2_static_for<NW>([&](auto i_) {
-      constexpr int i = decltype(i_)::value;
-      if constexpr (2 * i + 1 < DEG) {
-        sts32(cadr + i * cstride, __byte_perm(y[2 * i], y[2 * i + 1], 0x6420));
-      } else {
-        sts32(cadr + i * cstride, __byte_perm(y[2 * i], 0u, 0x4420));
-      }
-    });
     sts32(padr, u[DEG - 1]);
   }
   __syncthreads(); // every warp has read the row's soft bits
@@ -84,25 +145,30 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t cadr, uint32_t cstr
   __syncthreads(); // ... and written the new ones
 }
 
-// Device-side twin of pdc_h2g_smem_bytes (same formula; the row degrees come from constant memory).
+// Message words (int8 pairs, two edges per word) of the extension rows 4 .. L - 1: the parity edge of a row carries none.
 template <int BG>
-__device__ __forceinline__ size_t pdc_h2g_smem_bytes_dev(int Z, int max_layers)
+__host__ __device__ inline int pdc_h2g_ext_words(const uint8_t* deg, int L)
 {
-  constexpr int  ncol = h2_graph<BG>::NCOL, kb = h2_graph<BG>::KB;
-  constexpr int  M    = (BG == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
-  const uint8_t* deg  = c_bg_rows.deg[BG - 1];
-  const int      L    = max_layers > M ? M : max_layers;
-  size_t         words = 0;
+  int words = 0;
   for (int m = 4; m < L; ++m) {
-    words += (deg[m] + 1) / 2;
+    words += deg[m] / 2;
   }
-  const size_t work  = words * 2 * Z + (size_t)kb * 48;
-  const size_t stage = (size_t)(kb + L - 2) * Z + 32;
-  return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + (work > stage ? work : stage);
+  return words;
+}
+// TMEM columns of one code block: every warp owns the TMEM lane quarter warp % 4, so warps 4, 5 (Z > 256) take a second
+// bank of columns. Allocations are powers of two >= 32.
+__host__ __device__ inline uint32_t pdc_h2g_tmem_cols(int words, int nth)
+{
+  const uint32_t need = (uint32_t)words * (uint32_t)((nth + 127) / 128);
+  uint32_t       c    = 32;
+  while (c < need) {
+    c <<= 1;
+  }
+  return c;
 }
 
 template <int BG>
-__global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params prm)
+__global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params prm)
 {
   using G = h2_graph<BG>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -113,6 +179,7 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   __shared__ uint16_t s_wstart[48];               // first message word of every extension row
   __shared__ uint32_t s_red[8];
   __shared__ int      s_nz;
+  __shared__ uint32_t s_tmem; // base address of this code block's tensor-memory allocation
 
   const int        tid = threadIdx.x, nth = blockDim.x;
   const int        cbi = prm.order ? prm.order[blockIdx.x] : blockIdx.x;
@@ -128,6 +195,19 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
 
   pdc_cb_result res;
   res.iterations = -1, res.crc_pass = 0, res.status = 0, res.nof_layers = 0;
+
+  // Tensor memory for the messages of the extension rows, sized by the host's bound on the number of layers. Warp 0 allocates
+  // (and frees at the end); the allocation of a CTA that finds the SM's TMEM taken waits for a resident CTA to finish.
+  const int      L_cap     = min((int)cb.max_layers, (BG == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS);
+  const int      tm_words  = pdc_h2g_ext_words<BG>(c_bg_rows.deg[bgi], L_cap);
+  const uint32_t tm_cols   = pdc_h2g_tmem_cols(tm_words, nth);
+  if (tid < 32) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(&s_tmem)),
+                 "r"(tm_cols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
 
   const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
   const uint32_t row_bytes = 4u * (uint32_t)Z;
@@ -160,13 +240,17 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
     dec_in = cb.soft;
     n_in   = g.N;
   }
-  __syncthreads(); // orders the dematcher's writes before the reads below (same CTA); s_graph, s_nz, barriers visible
+  __syncthreads(); // orders the dematcher's writes before the reads below (same CTA); s_graph, s_nz, s_tmem visible
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  // This warp's TMEM lane quarter; warps 4, 5 use a second bank of columns.
+  const uint32_t tm_warp = s_tmem + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * (uint32_t)tm_words;
 
   // ---- the decoder input, staged at the tail of the dynamic shared memory (the host sized it: pdc_h2g_smem_bytes). Only the
   //      part the host's bound on the number of layers allows to be non-zero is needed. ----------------------------------------
-  const int      n_stage  = min(n_in, (G::KB + (int)cb.max_layers - 2) * Z);
-  const size_t   dyn_size = pdc_h2g_smem_bytes_dev<BG>(Z, (int)cb.max_layers);
-  unsigned char* stage    = smem_raw + ((dyn_size - (size_t)((n_stage + 15) & ~15)) & ~(size_t)15);
+  // Shared-memory map: core columns (doubled rows) | parity words of the extension rows (one word per thread and row, sized
+  // by the host's bound L_cap) | staged decoder input, later the ballot words of the output.
+  const int      n_stage  = min(n_in, (G::KB + L_cap - 2) * Z);
+  unsigned char* stage    = smem_raw + (((size_t)G::NCOL * 4 * Z + (size_t)(L_cap - 4) * 2 * Z + 15) & ~(size_t)15);
   {
     const bool vec = ((reinterpret_cast<uintptr_t>(dec_in) & 15) == 0);
     const int  n16 = vec ? (n_stage >> 4) : 0;
@@ -196,10 +280,13 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   }
   __syncthreads();
   const int L = pdc_layers_for_nz(g, s_nz);
-  if (L > (int)cb.max_layers) { // cannot happen unless the host bound is wrong; fail loudly instead of overrunning
+  if (L > L_cap) { // cannot happen unless the host bound is wrong; fail loudly instead of overrunning
     res.status = 3;
     if (tid == 0) {
       *cb.res = res;
+    }
+    if (tid < 32) {
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(s_tmem), "r"(tm_cols));
     }
     return;
   }
@@ -239,19 +326,16 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
     int acc = 0;
     for (int m = 4; m < L; ++m) {
       s_wstart[m] = (uint16_t)acc;
-      acc += (row_deg[m] + 1) >> 1;
+      acc += row_deg[m] >> 1; // the parity edge carries no message
     }
     s_wstart[L] = (uint16_t)acc;
   }
   __syncthreads();
 
-  // Shared-memory map: core columns (doubled rows) | parity columns of the extension rows (one word per thread) |
-  // messages of the extension rows ([word][thread]) | ballot words of the output.
   const uint32_t ext_base = smem_base + G::NCOL * row_bytes;
   const uint32_t ext_row  = 4u * (uint32_t)W; // bytes per private word-row
-  const uint32_t c2v_base = ext_base + (uint32_t)(L - 4) * ext_row;
   const uint32_t priv_t   = 4u * (uint32_t)(active ? tid : 0);
-  unsigned char* aux      = smem_raw + G::NCOL * row_bytes + (size_t)(L - 4) * ext_row + (size_t)s_wstart[L] * ext_row;
+  unsigned char* aux      = stage; // free once the soft bits have been loaded
 
   // ---- prologue 2: load_soft_bits (ldpc_decoder_impl.cpp:150-191) -------------------------------------------------------------
   if (active) {
@@ -271,18 +355,19 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
         sts32(soft_t + c * row_bytes, S);
         sts32(soft_t + c * row_bytes + 2u * Z, S);
       } else {
-        sts32(ext_base + (uint32_t)(c - G::NCOL) * ext_row + priv_t, S);
+        // degree-1 parity column: u = S - c with c = 0 before the first iteration, unbiased
+        sts32(ext_base + (uint32_t)(c - G::NCOL) * ext_row + priv_t, h2_sub(S, H2_BIAS));
       }
     }
   }
-  __syncthreads(); // the messages below may overlap the staged input
-  if (active) {
+  {
     const int nwords = s_wstart[L];
-    for (int w = 0; w < nwords; ++w) {
-      sts32(c2v_base + (uint32_t)w * ext_row + priv_t, 0x80808080u); // all messages zero before the first iteration
+    for (int w = 0; w < nwords; ++w) { // all messages zero (byte 128) before the first iteration
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tm_warp + (uint32_t)w), "r"(0x80808080u));
     }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
-  __syncthreads();
+  __syncthreads(); // the ballot words of the output overlap the staged input
 
   const int  n_sig     = K - (int)cb.nof_filler;
   const bool has_crc   = cb.crc_type != PDC_CRC_NONE;
@@ -306,17 +391,19 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   int  it_done = 0;
   bool success = false;
   for (int it = 0; it < max_iter && !success; ++it) {
+    // the previous iteration's message stores have landed before this one's loads of the same words
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     h2_row<BG, 0, 0>(cp, s_tab, soft_t, row_bytes, active, generic);
     h2_row<BG, 0, 1>(cp, s_tab, soft_t, row_bytes, active, generic);
     h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic);
     h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic);
     for (int m = 4; m < L; ++m) {
       const int      e0   = row_start[m];
-      const uint32_t cadr = c2v_base + (uint32_t)s_wstart[m] * ext_row + priv_t;
+      const uint32_t tadr = tm_warp + (uint32_t)s_wstart[m];
       const uint32_t padr = ext_base + (uint32_t)(m - 4) * ext_row + priv_t;
 #define PDC_H2G_CASE(D)                                                                                                \
   case D:                                                                                                              \
-    h2g_ext_row<D>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);                       \
+    h2g_ext_row<D>(e0, tadr, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);                                \
     break;
       switch (row_deg[m]) {
         PDC_H2G_CASE(3)
@@ -327,7 +414,7 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
         PDC_H2G_CASE(8)
         PDC_H2G_CASE(9)
         default:
-          h2g_ext_row<10>(e0, cadr, ext_row, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);
+          h2g_ext_row<10>(e0, tadr, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);
           break;
       }
 #undef PDC_H2G_CASE
@@ -375,23 +462,25 @@ __global__ void __launch_bounds__(192, 1) pdc_cb_kernel_h2g(pdc_launch_params pr
   if (tid == 0) {
     *cb.res = res;
   }
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  if (tid < 32) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(s_tmem), "r"(tm_cols));
+  }
 }
 
-// Dynamic shared memory of one code block with at most max_layers layers: core columns | parity columns of the extension
-// rows | max(messages + ballot words, staged decoder input).
+// Dynamic shared memory of one code block with at most max_layers layers: core columns | parity words of the extension
+// rows | max(staged decoder input, ballot words of the output). The messages of the extension rows live in tensor memory.
 extern "C" size_t pdc_h2g_smem_bytes(int bg, int Z, int max_layers)
 {
-  const int      ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
-  const int      M    = (bg == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
-  const uint8_t* deg  = (bg == 1) ? pdc_bg1_row_deg : pdc_bg2_row_deg;
-  const int      L    = max_layers > M ? M : max_layers;
-  size_t         words = 0;
-  for (int m = 4; m < L; ++m) {
-    words += (deg[m] + 1) / 2;
-  }
-  const size_t work  = words * 2 * Z + (size_t)kb * 48;
-  const size_t stage = (size_t)(kb + L - 2) * Z + 32;
-  return (size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + (work > stage ? work : stage);
+  const int    ncol = (bg == 1) ? 26 : 14, kb = (bg == 1) ? 22 : 10;
+  const int    M    = (bg == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
+  const int    L    = max_layers > M ? M : max_layers;
+  const size_t out  = (size_t)kb * 48;
+  size_t       stage = (size_t)(kb + L - 2) * Z + 32;
+  stage              = stage > out ? stage : out;
+  return (((size_t)ncol * 4 * Z + (size_t)(L - 4) * 2 * Z + 15) & ~(size_t)15) + stage;
 }
 static cudaError_t pdc_h2g_init_device()
 {
