@@ -85,32 +85,44 @@ __device__ __forceinline__ void h2g_parity_update(uint32_t& u, uint32_t m1, uint
 }
 
 // One extension row. taddr: TMEM address of the row's message words of this warp; padr: shared-memory address of the
-// thread's parity word (u of the degree-1 column); e0: first edge of the row in the tables.
+// thread's parity word (u of the degree-1 column); xe: shared-memory address of the row's first edge entry
+// {read offset, PRMT selector, column offset, -} (16 bytes per edge: one load, no unpacking).
+__device__ __forceinline__ uint4 lds128(uint32_t addr)
+{
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t h2g_prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel)); // sel is a clean 4-nibble selector: no masking
+  return d;
+}
 template <int DEG>
-__device__ __forceinline__ void h2g_ext_row(int e0, uint32_t taddr, uint32_t padr, const uint32_t* __restrict__ xr,
-                                            const uint32_t* __restrict__ xw, uint32_t soft_t, uint32_t half_row, bool active,
-                                            bool generic)
+__device__ __forceinline__ void h2g_ext_row(uint32_t xe, uint32_t taddr, uint32_t padr, uint32_t soft_t, uint32_t half_row,
+                                            bool active, bool generic)
 {
   constexpr int  NW = DEG / 2; // DEG - 1 messages, two per word
-  uint32_t       u[DEG], cw[NW];
+  uint32_t       u[DEG], cw[NW], wadr[DEG - 1];
   uint32_t       par = 0;
   const uint32_t one = h2_opaque_one();
-  uint32_t       ents[DEG - 1];
+  uint4          ents[DEG - 1];
 #pragma unroll
   for (int k = 0; k < DEG - 1; ++k) {
-    ents[k] = xr[e0 + k]; // table entries do not depend on the other warps
+    ents[k] = lds128(xe + 16u * k); // table entries do not depend on the other warps
   }
   u[DEG - 1] = lds32(padr);  // private to the thread: no ordering needed
   h2g_tm_ld<NW>(taddr, cw);  // likewise
   h2_static_for<DEG - 1>([&](auto k_) {
     constexpr int  k   = decltype(k_)::value;
-    const uint32_t ent = ents[k];
-    const uint32_t adr = soft_t + (ent & 0xffffu);
+    const uint32_t adr = soft_t + ents[k].x;
     const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
-    const uint32_t S  = __byte_perm(w0, w1, ent >> 16);
+    const uint32_t S  = h2g_prmt(w0, w1, ents[k].y);
     const uint32_t x  = __byte_perm(cw[k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
     u[k]              = h2_sub(S, x);
     par ^= u[k];
+    wadr[k] = soft_t + ents[k].z;
   });
   par ^= u[DEG - 1];
   uint32_t s1p, d, m1;
@@ -136,10 +148,9 @@ __device__ __forceinline__ void h2g_ext_row(int e0, uint32_t taddr, uint32_t pad
   __syncthreads(); // every warp has read the row's soft bits
   if (active) {
     h2_static_for<DEG - 1>([&](auto k_) {
-      constexpr int  k   = decltype(k_)::value;
-      const uint32_t adr = soft_t + xw[e0 + k];
-      sts32(adr, u[k]);
-      sts32(adr + half_row, u[k]);
+      constexpr int k = decltype(k_)::value;
+      sts32(wadr[k], u[k]);
+      sts32(wadr[k] + half_row, u[k]);
     });
   }
   __syncthreads(); // ... and written the new ones
@@ -174,9 +185,10 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_graph[PDC_H2G_MAX_EDGES]; // col | shift << 8 of every edge, rows concatenated
   __shared__ uint32_t s_tab[PDC_H2_TAB_STRIDE];   // core edges, column alignments, natural views: layout of c_h2_tab
-  __shared__ uint32_t s_xr[PDC_H2G_MAX_EDGES];    // extension edges: read offset | PRMT selector << 16
-  __shared__ uint32_t s_xw[PDC_H2G_MAX_EDGES];    // extension edges: byte offset of the column
-  __shared__ uint16_t s_wstart[48];               // first message word of every extension row
+  __shared__ __align__(16) uint4 s_xe[PDC_H2G_MAX_EDGES - 76 + 8]; // extension edges, from edge NEDGE on: {read offset, PRMT
+                                                                   // selector, byte offset of the column, -}
+  __shared__ __align__(16) uint4 s_row[48]; // extension rows: {address of the row's first s_xe entry, first message word,
+                                            // degree, -}; entry L: degree 0
   __shared__ uint32_t s_red[8];
   __shared__ int      s_nz;
   __shared__ uint32_t s_tmem; // base address of this code block's tensor-memory allocation
@@ -309,8 +321,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
       if (e < G::NEDGE) {
         s_tab[e] = val;
       } else {
-        s_xr[e] = val;
-        s_xw[e] = (uint32_t)c * row_bytes;
+        s_xe[e - G::NEDGE] = make_uint4(off, (rel & 1) ? 0x5432u : 0x3210u, (uint32_t)c * row_bytes, 0u);
       }
     }
   }
@@ -323,12 +334,13 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
     s_tab[PDC_H2_NAT_OFF + c]   = ((uint32_t)c * row_bytes + 4u * (uint32_t)(nat >> 1)) | (((nat & 1) ? 0x5432u : 0x3210u) << 16);
   }
   if (tid == nth - 1) { // a thread without a column to walk (nth >= 32 > NCOL)
-    int acc = 0;
+    const uint32_t xe0 = (uint32_t)__cvta_generic_to_shared(s_xe);
+    int            acc = 0;
     for (int m = 4; m < L; ++m) {
-      s_wstart[m] = (uint16_t)acc;
+      s_row[m] = make_uint4(xe0 + 16u * (uint32_t)(row_start[m] - G::NEDGE), (uint32_t)acc, row_deg[m], 0u);
       acc += row_deg[m] >> 1; // the parity edge carries no message
     }
-    s_wstart[L] = (uint16_t)acc;
+    s_row[L] = make_uint4(0u, (uint32_t)acc, 0u, 0u);
   }
   __syncthreads();
 
@@ -361,7 +373,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
     }
   }
   {
-    const int nwords = s_wstart[L];
+    const int nwords = (int)s_row[L].y;
     for (int w = 0; w < nwords; ++w) { // all messages zero (byte 128) before the first iteration
       asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(tm_warp + (uint32_t)w), "r"(0x80808080u));
     }
@@ -397,27 +409,31 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
     h2_row<BG, 0, 1>(cp, s_tab, soft_t, row_bytes, active, generic);
     h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic);
     h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic);
+    uint4 hdr = s_row[4];
     for (int m = 4; m < L; ++m) {
-      const int      e0   = row_start[m];
-      const uint32_t tadr = tm_warp + (uint32_t)s_wstart[m];
+      const uint4    nxt  = s_row[m + 1]; // the next row's header arrives while this row computes
+      const uint32_t tadr = tm_warp + hdr.y;
       const uint32_t padr = ext_base + (uint32_t)(m - 4) * ext_row + priv_t;
-#define PDC_H2G_CASE(D)                                                                                                \
-  case D:                                                                                                              \
-    h2g_ext_row<D>(e0, tadr, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);                                \
-    break;
-      switch (row_deg[m]) {
-        PDC_H2G_CASE(3)
-        PDC_H2G_CASE(4)
-        PDC_H2G_CASE(5)
-        PDC_H2G_CASE(6)
-        PDC_H2G_CASE(7)
-        PDC_H2G_CASE(8)
-        PDC_H2G_CASE(9)
-        default:
-          h2g_ext_row<10>(e0, tadr, padr, s_xr, s_xw, soft_t, 2u * (uint32_t)Z, active, generic);
-          break;
+      const uint32_t hr   = 2u * (uint32_t)Z;
+      // most frequent degrees first (BG1: 18 rows of degree 5, 8 of 6; BG2: 22 of 4, 7 of 5, 7 of 3)
+      if (hdr.z == 5) {
+        h2g_ext_row<5>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else if (hdr.z == 4) {
+        h2g_ext_row<4>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else if (hdr.z == 6) {
+        h2g_ext_row<6>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else if (hdr.z == 7) {
+        h2g_ext_row<7>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else if (hdr.z == 3) {
+        h2g_ext_row<3>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else if (hdr.z == 8) {
+        h2g_ext_row<8>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else if (hdr.z == 9) {
+        h2g_ext_row<9>(hdr.x, tadr, padr, soft_t, hr, active, generic);
+      } else {
+        h2g_ext_row<10>(hdr.x, tadr, padr, soft_t, hr, active, generic);
       }
-#undef PDC_H2G_CASE
+      hdr = nxt;
     }
     it_done = it + 1;
     const bool last = (it_done == max_iter);
