@@ -16,10 +16,10 @@ fi
 # process (this library, the adapters, numpy) corrupt each other's locale facets. Use the system compiler, shared runtime.
 CXX=${PDC_CXX:-/usr/bin/g++}
 FLAGS="-std=c++17 -O2 -fPIC -DFMT_HEADER_ONLY -DASSERTS_ENABLED -w -I$REF/include -I$REF/external/fmt/include -I$REF/external"
-$CXX $FLAGS -shared -o "$OUT" "$HERE/channel_coding_factories_cuda.cpp" "$HERE/hw_accelerator_pusch_dec_cuda.cpp" \
+$CXX $FLAGS -shared -o "$OUT" "$HERE/channel_coding_factories_cuda.cpp" "$HERE/hw_accelerator_pusch_dec_cuda.cpp" "$HERE/pusch_dec_batcher.cpp" \
   "$HERE/pusch_decoder_cuda.cpp" "$HERE/channel_modulation_factories_cuda.cpp" "$HERE/pdsch_encoder_cuda.cpp" \
   "$HERE/hw_accelerator_pdsch_enc_cuda.cpp" "$HERE/ulsch_demultiplex_cuda.cpp" \
-  -L"$PKG" -lpuschdec_cuda -Wl,-rpath,'$ORIGIN'
+  -L"$PKG" -lpuschdec_cuda -lpthread -Wl,-rpath,'$ORIGIN'
 echo "built $OUT"
 # The boundary test harness (reference TB decoders over the adapters) is test infrastructure; built here because it
 # needs the same reference tree.

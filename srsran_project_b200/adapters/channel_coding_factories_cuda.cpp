@@ -5,10 +5,12 @@
 // Contract violations that the reference guards with srsran_assert are guarded with srsran_assert here too (the C ABI
 // reports them as PDC_ERR_INVALID_ARG); a decode failure is std::nullopt, never an exception.
 #include "channel_coding_factories_cuda.h"
+#include "pusch_dec_batcher.h"
 #include "srsran/phy/upper/channel_coding/crc_calculator.h"
 #include "srsran/phy/upper/channel_coding/ldpc/ldpc_decoder.h"
 #include "srsran/phy/upper/channel_coding/ldpc/ldpc_rate_dematcher.h"
 #include "srsran/support/srsran_assert.h"
+#include <algorithm>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -32,35 +34,52 @@ uint8_t crc_type_of(crc_generator_poly poly)
   }
 }
 
-// Submits one code block and waits for it. Instances are pooled and driven concurrently by the reference
-// (bounded_unique_object_pool, factories.cpp:82-94): when every submission slot of the context is taken by other
-// threads the call waits for one instead of failing.
-pdc_status run_one(pdc_ctx*           ctx,
-                   const pdc_cb_desc& desc,
-                   const int8_t*      llrs,
-                   size_t             nof_llrs,
-                   int8_t*            soft,
-                   size_t             nof_soft,
-                   uint8_t*           bits,
-                   size_t             nof_bytes,
-                   pdc_cb_result&     res)
+// Runs one code block and waits for it. Instances are pooled and driven concurrently by the reference
+// (bounded_unique_object_pool, factories.cpp:82-94; pusch_decoder_impl forks one task per code block,
+// pusch_decoder_impl.cpp:309-394): the calls of all threads that arrive while the device is busy travel as ONE submission
+// (pusch_dec_batcher.h), each caller picks its own code block out of the batch.
+pdc_status run_one(cuda::pusch_dec_batcher& batcher,
+                   const pdc_cb_desc&       desc,
+                   const int8_t*            llrs,
+                   size_t                   nof_llrs,
+                   int8_t*                  soft,
+                   size_t                   nof_soft,
+                   uint8_t*                 bits,
+                   size_t                   nof_bytes,
+                   pdc_cb_result&           res)
 {
-  pdc_ticket ticket = 0;
-  pdc_status st;
-  while ((st = pdc_submit(ctx, &desc, 1, llrs, nof_llrs, soft, nof_soft, &ticket)) == PDC_ERR_CAPACITY) {
-    std::this_thread::yield();
+  cuda::pusch_dec_batcher::part* p;
+  while ((p = batcher.join(1, nof_llrs + 16, 200)) == nullptr) {
+    // every staging buffer is taken by other threads: the call slept until one was recycled (or 200 us)
   }
-  if (st != PDC_OK) {
-    return st;
+  if (!batcher.add(p, desc, llrs, nof_llrs, soft, nof_soft)) {
+    batcher.release(p);
+    return PDC_ERR_CAPACITY; // a code block larger than the context was created for
   }
-  return pdc_fetch(ctx, ticket, bits, nof_bytes, &res, soft, nof_soft);
+  batcher.seal(p);
+  while (batcher.poll(p, 100) != cuda::pusch_dec_batcher::status::done) {
+  }
+  res = batcher.result(p, 0);
+  if (bits && res.status == 0 && !(desc.flags & PDC_F_DEMATCH_ONLY)) {
+    std::memcpy(bits, batcher.bits(p, 0), std::min<size_t>(nof_bytes, (pdc_cb_message_bits(desc.bg, desc.Z) + 7) / 8));
+  }
+  if (soft && desc.harq_slot < 0 && !(desc.flags & PDC_F_DECODE_ONLY) && res.status == 0) {
+    std::memcpy(soft, batcher.soft(p, 0), std::min<size_t>(nof_soft, pdc_cb_buffer_len(desc.bg, desc.Z)));
+  }
+  const pdc_status st = (res.status == 1) ? PDC_ERR_INVALID_ARG : PDC_OK; // 1: rejected or failed submission
+  batcher.release(p);
+  return st;
 }
 
 class ldpc_decoder_cuda : public ldpc_decoder
 {
 public:
   ldpc_decoder_cuda(std::shared_ptr<cuda::pusch_dec_context> context_, bool force_decoding_, bool generic_) :
-    context(std::move(context_)), force_decoding(force_decoding_), generic(generic_), bits((PDC_MAX_K_BYTES + 3) / 4 * 4)
+    context(std::move(context_)),
+    batcher(cuda::shared_batcher_of(context)),
+    force_decoding(force_decoding_),
+    generic(generic_),
+    bits((PDC_MAX_K_BYTES + 3) / 4 * 4)
   {
   }
 
@@ -97,7 +116,7 @@ public:
     d.harq_slot  = -1;
 
     pdc_cb_result res = {};
-    pdc_status    st  = run_one(context->get(),
+    pdc_status    st  = run_one(*batcher,
                             d,
                             reinterpret_cast<const int8_t*>(input.data()),
                             input.size(),
@@ -130,6 +149,7 @@ private:
   static constexpr size_t PDC_MAX_K_BYTES = 8448 / 8;
 
   std::shared_ptr<cuda::pusch_dec_context> context;
+  std::shared_ptr<cuda::pusch_dec_batcher> batcher;
   bool                                     force_decoding;
   bool                                     generic;
   std::vector<uint8_t>                     bits;
@@ -139,7 +159,7 @@ class ldpc_rate_dematcher_cuda : public ldpc_rate_dematcher
 {
 public:
   ldpc_rate_dematcher_cuda(std::shared_ptr<cuda::pusch_dec_context> context_, bool generic_) :
-    context(std::move(context_)), generic(generic_)
+    context(std::move(context_)), batcher(cuda::shared_batcher_of(context)), generic(generic_)
   {
   }
 
@@ -177,7 +197,7 @@ public:
     // The write set of the dematcher does not cover the whole buffer (ldpc_rate_dematcher_impl.cpp:128-201), so the
     // current content always travels to the device and back.
     pdc_cb_result res = {};
-    pdc_status    st  = run_one(context->get(),
+    pdc_status    st  = run_one(*batcher,
                             d,
                             reinterpret_cast<const int8_t*>(input.data()),
                             input.size(),
@@ -191,6 +211,7 @@ public:
 
 private:
   std::shared_ptr<cuda::pusch_dec_context> context;
+  std::shared_ptr<cuda::pusch_dec_batcher> batcher;
   bool                                     generic;
 };
 
@@ -232,9 +253,9 @@ private:
 std::shared_ptr<cuda::pusch_dec_context> make_default_context()
 {
   cuda::pusch_dec_context_config cfg;
-  cfg.max_batch_cbs  = 1;
-  cfg.max_batch_llrs = 35u * 8448u; // MAX_CODEBLOCK_RM_SIZE (ldpc.h:122)
-  cfg.nof_instances  = 16;
+  cfg.max_batch_cbs  = 64;               // concurrent single-code-block calls that may share one submission
+  cfg.max_batch_llrs = 16u * 35u * 8448u; // 16 x MAX_CODEBLOCK_RM_SIZE (ldpc.h:122)
+  cfg.nof_instances  = 4;
   return std::make_shared<cuda::pusch_dec_context>(cfg);
 }
 

@@ -1,17 +1,19 @@
 // See hw_accelerator_pusch_dec_cuda.h. One object serves one transport block at a time (the reference takes it from a
-// bounded pool per TB, pusch_decoder_hw_impl.cpp:151, factories.cpp:131-138); objects of one factory share the GPU
-// context and are driven concurrently from the PUSCH decoder executor threads.
+// bounded pool per TB, pusch_decoder_hw_impl.cpp:151, factories.cpp:131-138); the objects of one factory share the GPU
+// context(s) and are driven concurrently from the PUSCH decoder executor threads.
 //
 // Protocol as driven by pusch_decoder_hw_impl::run_asynch_hw_decoder (pusch_decoder_hw_impl.cpp:210-360):
 //   reserve_queue -> { configure_operation(cb) ; enqueue_operation(cb) } for every code block still to decode
 //                 -> { dequeue_operation(cb) ; read_operation_outputs(cb) } for the same code blocks -> free_queue.
-// enqueue only records the code block (descriptor + LLRs into one contiguous staging vector); the first dequeue submits
-// everything recorded so far as ONE batch (one H2D copy, one kernel launch of one CTA per code block, one D2H copy) and
-// waits for it. With external HARQ the caller enqueues the whole TB before it dequeues, so a TB is one launch.
+// enqueue copies the code block's LLRs straight into the page-locked staging of the batch that is open on the code block's
+// GPU (pusch_dec_batcher.h) — the batch is shared with every other accelerator object of the factory; the first dequeue
+// seals this object's share. dequeue returns false ("not ready", the reference spins on it: :325-338) until the batch has
+// run: the GPU sees ONE submission for the transport blocks of all objects that were enqueued while it was busy.
 // Errors never throw: a failed submission reports every code block of the batch as "CRC failed".
 #include "hw_accelerator_pusch_dec_cuda.h"
 #include "srsran/ran/sch/modulation_scheme.h"
 #include <array>
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <thread>
@@ -22,23 +24,23 @@ using namespace srsran::hal;
 
 namespace {
 
-constexpr unsigned MAX_CBS     = 152;        // ldpc::MAX_NOF_SEGMENTS
-constexpr unsigned SOFT_STRIDE = 66 * 384;   // largest soft buffer, one HARQ arena slot
-constexpr unsigned BITS_STRIDE = 8448 / 8;   // largest message, bytes
+constexpr unsigned MAX_CBS  = 152; // ldpc::MAX_NOF_SEGMENTS
+constexpr unsigned MAX_GPUS = 16;
+
+using batcher = cuda::pusch_dec_batcher;
 
 class hw_accelerator_pusch_dec_cuda : public hw_accelerator_pusch_dec
 {
 public:
-  hw_accelerator_pusch_dec_cuda(std::shared_ptr<cuda::pusch_dec_context> context_, bool external_, bool generic_) :
-    context(std::move(context_)), external(external_), generic(generic_)
+  hw_accelerator_pusch_dec_cuda(std::vector<std::shared_ptr<batcher>> batchers_, bool external_, bool generic_, unsigned id_) :
+    batchers(std::move(batchers_)), external(external_), generic(generic_), instance_id(id_)
   {
-    max_cbs = std::min<unsigned>(MAX_CBS, context->config().max_batch_cbs);
-    descs.reserve(max_cbs);
-    llrs.reserve(context->config().max_batch_llrs);
-    bits.resize((size_t)max_cbs * BITS_STRIDE);
-    results.resize(max_cbs);
-    slot_of_cb.fill(-1);
+    parts.fill(nullptr);
+    for (auto& s : where) {
+      s = {-1, 0};
+    }
   }
+  ~hw_accelerator_pusch_dec_cuda() override { drop_parts(); }
 
   void reserve_queue() override { reset(); }
   void free_queue() override { reset(); }
@@ -52,13 +54,22 @@ public:
 
   bool enqueue_operation(span<const int8_t> data, span<const int8_t> aux_data, unsigned cb_index) override
   {
-    if (cb_index >= MAX_CBS || ready || descs.size() >= max_cbs) {
-      return false; // batch full, or the previous batch has not been drained yet: the caller dequeues and retries
+    if (cb_index >= MAX_CBS || sealed) {
+      return false; // the previous share has not been drained yet: the caller dequeues and retries
     }
     const hw_pusch_decoder_configuration& c = cfgs[cb_index];
-    const size_t llr_off = (llrs.size() + 15) / 16 * 16;
-    if (llr_off + data.size() > context->config().max_batch_llrs) {
-      return false;
+    const unsigned                        G = static_cast<unsigned>(batchers.size());
+    // Placement: by absolute code-block identifier, so that every transmission of a code block meets its soft buffer.
+    const unsigned g = external ? (c.absolute_cb_id % G) : (instance_id % G);
+    if (!parts[g]) {
+      // Room for this GPU's share of the transport block (code blocks are spread evenly: ids are handed out in order).
+      const unsigned nof_cbs = std::max(1u, std::min(c.nof_segments, MAX_CBS));
+      const unsigned share   = external ? (nof_cbs + G - 1) / G + 1 : 1;
+      parts[g]               = batchers[g]->join(share, (size_t)share * ((data.size() + 15 + 32) & ~(size_t)15), 200);
+      if (!parts[g]) {
+        return false; // every staging buffer of that GPU is taken: back-pressure, the caller retries
+      }
+      counts[g] = 0;
     }
     pdc_cb_desc d = {};
     d.bg          = (c.base_graph_index == ldpc_base_graph_type::BG1) ? 1 : 2;
@@ -70,49 +81,52 @@ public:
     d.max_iter    = (c.max_nof_ldpc_iterations > 255) ? 255 : c.max_nof_ldpc_iterations;
     d.flags       = (c.new_data ? PDC_F_NEW_DATA : 0) | (c.use_early_stop ? PDC_F_EARLY_STOP : 0) |
               (generic ? PDC_F_GENERIC : 0);
-    d.Z           = c.lifting_size;
-    d.E           = data.size();
-    d.Nref        = c.Nref;
-    d.nof_filler  = c.nof_filler_bits;
-    d.llr_offset  = llr_off;
-    d.out_offset  = descs.size() * BITS_STRIDE;
-    d.soft_offset = 0;
-    if (external) {
-      d.harq_slot = static_cast<int32_t>(c.absolute_cb_id);
-    } else {
-      // Host-side HARQ buffer: it travels with the operation and comes back updated in dequeue_operation.
-      d.harq_slot   = -1;
-      d.soft_offset = descs.size() * (size_t)SOFT_STRIDE;
-      soft.resize(d.soft_offset + SOFT_STRIDE, 0);
-      std::memcpy(soft.data() + d.soft_offset, aux_data.data(), std::min<size_t>(aux_data.size(), SOFT_STRIDE));
+    d.Z          = c.lifting_size;
+    d.E          = data.size();
+    d.Nref       = c.Nref;
+    d.nof_filler = c.nof_filler_bits;
+    // External HARQ: arena slot on the code block's GPU. Otherwise the host buffer travels with the operation.
+    d.harq_slot = external ? static_cast<int32_t>(c.absolute_cb_id / G) : -1;
+    if (!batchers[g]->add(parts[g], d, data.data(), data.size(), external ? nullptr : aux_data.data(),
+                          external ? 0 : aux_data.size())) {
+      return false; // this share is full: the caller drains it, then enqueues the rest
     }
-    llrs.resize(llr_off + data.size());
-    std::memcpy(llrs.data() + llr_off, data.data(), data.size());
-    slot_of_cb[cb_index] = static_cast<int>(descs.size());
-    descs.push_back(d);
+    where[cb_index] = {static_cast<int>(g), counts[g]++};
+    ++nof_enqueued;
     return true;
   }
 
   bool dequeue_operation(span<uint8_t> data, span<int8_t> aux_data, unsigned segment_index) override
   {
-    if (segment_index >= MAX_CBS || slot_of_cb[segment_index] < 0) {
+    if (segment_index >= MAX_CBS || where[segment_index].gpu < 0) {
       return false;
     }
-    if (!ready) {
-      run_batch();
+    if (!sealed) {
+      for (unsigned g = 0; g != batchers.size(); ++g) {
+        if (parts[g]) {
+          batchers[g]->seal(parts[g]);
+        }
+      }
+      sealed = true;
     }
-    const unsigned       k = slot_of_cb[segment_index];
-    const pdc_cb_result& r = results[k];
-    const unsigned       K = pdc_cb_message_bits(descs[k].bg, descs[k].Z);
-    std::memcpy(data.data(), bits.data() + (size_t)k * BITS_STRIDE, std::min<size_t>(data.size(), (K + 7) / 8));
+    const slot     s = where[segment_index];
+    batcher&       b = *batchers[s.gpu];
+    batcher::part* p = parts[s.gpu];
+    if (b.poll(p, 100) != batcher::status::done) {
+      return false; // not ready (after a short sleep: the caller spins on this call)
+    }
+    const pdc_cb_result& r = b.result(p, s.index);
+    const pdc_cb_desc&   d = p->descs[s.index];
+    const unsigned       K = pdc_cb_message_bits(d.bg, d.Z);
+    std::memcpy(data.data(), b.bits(p, s.index), std::min<size_t>(data.size(), (K + 7) / 8));
     if (!external && !aux_data.empty()) {
-      std::memcpy(aux_data.data(), soft.data() + (size_t)k * SOFT_STRIDE, std::min<size_t>(aux_data.size(), SOFT_STRIDE));
+      std::memcpy(aux_data.data(), b.soft(p, s.index), std::min<size_t>(aux_data.size(), batcher::SOFT_STRIDE));
     }
     outputs[segment_index].CRC_pass            = (r.crc_pass != 0);
-    outputs[segment_index].nof_ldpc_iterations = (r.iterations > 0) ? r.iterations : descs[k].max_iter;
-    slot_of_cb[segment_index]                  = -1;
-    if (++nof_dequeued == descs.size()) {
-      clear_batch(); // everything handed back: the object accepts a new batch (outputs[] stay readable)
+    outputs[segment_index].nof_ldpc_iterations = (r.iterations > 0) ? r.iterations : d.max_iter;
+    where[segment_index].gpu                   = -1;
+    if (++nof_dequeued == nof_enqueued) {
+      drop_parts(); // everything handed back: the object accepts a new share (outputs[] stay readable)
     }
     return true;
   }
@@ -129,60 +143,43 @@ public:
   bool is_harq_external() const override { return external; }
 
 private:
-  void run_batch()
-  {
-    pdc_ctx*   ctx    = context->get();
-    pdc_ticket ticket = 0;
-    pdc_status st;
-    const int8_t* soft_in = external ? nullptr : soft.data();
-    while ((st = pdc_submit(ctx, descs.data(), descs.size(), llrs.data(), llrs.size(), soft_in, soft.size(), &ticket)) ==
-           PDC_ERR_CAPACITY) {
-      std::this_thread::yield(); // every submission slot is in use by other accelerator instances
-    }
-    if (st == PDC_OK) {
-      st = pdc_fetch(ctx, ticket, bits.data(), bits.size(), results.data(), external ? nullptr : soft.data(), soft.size());
-    }
-    if (st != PDC_OK) {
-      std::fprintf(stderr, "hw_accelerator_pusch_dec_cuda: batch of %zu code blocks failed (status %d: %s)\n",
-                   descs.size(), (int)st, pdc_last_error(ctx));
-      for (size_t k = 0; k != descs.size(); ++k) {
-        results[k].iterations = -1, results[k].crc_pass = 0, results[k].status = 1, results[k].nof_layers = 0;
-      }
-      std::memset(bits.data(), 0, bits.size());
-    }
-    ready = true;
-  }
+  struct slot {
+    int      gpu;
+    unsigned index;
+  };
 
-  void clear_batch()
+  void drop_parts()
   {
-    descs.clear();
-    llrs.clear();
-    soft.clear();
-    nof_dequeued = 0;
-    ready        = false;
+    for (unsigned g = 0; g != batchers.size(); ++g) {
+      if (parts[g]) {
+        batchers[g]->release(parts[g]);
+        parts[g] = nullptr;
+      }
+    }
+    nof_enqueued = nof_dequeued = 0;
+    sealed                      = false;
   }
 
   void reset()
   {
-    clear_batch();
-    slot_of_cb.fill(-1);
+    drop_parts();
+    for (auto& s : where) {
+      s.gpu = -1;
+    }
   }
 
-  std::shared_ptr<cuda::pusch_dec_context> context;
-  bool                                     external;
-  bool                                     generic;
-  unsigned                                 max_cbs = MAX_CBS;
+  std::vector<std::shared_ptr<batcher>> batchers; // one per GPU
+  bool                                  external;
+  bool                                  generic;
+  unsigned                              instance_id;
 
   std::array<hw_pusch_decoder_configuration, MAX_CBS> cfgs    = {};
   std::array<hw_pusch_decoder_outputs, MAX_CBS>       outputs = {};
-  std::array<int, MAX_CBS>                            slot_of_cb;
-  std::vector<pdc_cb_desc>                            descs;
-  std::vector<int8_t>                                 llrs;
-  std::vector<int8_t>                                 soft;
-  std::vector<uint8_t>                                bits;
-  std::vector<pdc_cb_result>                          results;
-  size_t                                              nof_dequeued = 0;
-  bool                                                ready        = false; // results of the current batch are available
+  std::array<slot, MAX_CBS>                           where;
+  std::array<batcher::part*, MAX_GPUS>                parts;
+  std::array<unsigned, MAX_GPUS>                      counts = {};
+  unsigned                                            nof_enqueued = 0, nof_dequeued = 0;
+  bool                                                sealed = false; // this object's share is closed: results are awaited
 };
 
 class hw_accelerator_pusch_dec_factory_cuda : public hw_accelerator_pusch_dec_factory
@@ -190,19 +187,47 @@ class hw_accelerator_pusch_dec_factory_cuda : public hw_accelerator_pusch_dec_fa
 public:
   explicit hw_accelerator_pusch_dec_factory_cuda(const cuda_hwacc_pusch_dec_factory_configuration& cfg_) : cfg(cfg_)
   {
-    if (!cfg.context) {
-      cuda::pusch_dec_context_config c;
-      c.harq_codeblocks = cfg.external_harq ? 16 * MAX_CBS : 0;
-      cfg.context       = std::make_shared<cuda::pusch_dec_context>(c);
+    std::vector<std::shared_ptr<cuda::pusch_dec_context>> contexts;
+    if (cfg.context) {
+      contexts.push_back(cfg.context);
+    } else {
+      std::vector<int> devices = cfg.devices.empty() ? std::vector<int>{0} : cfg.devices;
+      if (devices.size() > MAX_GPUS) {
+        throw std::runtime_error("cuda pusch_dec accelerator: too many devices");
+      }
+      const unsigned G = static_cast<unsigned>(devices.size());
+      for (int dev : devices) {
+        // Sized for the batcher: max_parts transport blocks of the largest codeword per submission.
+        cuda::pusch_dec_context_config c;
+        c.device          = dev;
+        c.max_batch_cbs   = std::max(1u, cfg.batching.max_parts) * MAX_CBS;
+        c.max_batch_llrs  = (size_t)std::max(1u, cfg.batching.max_parts) * (1536u << 10);
+        c.harq_codeblocks = cfg.external_harq ? (cfg.harq_context_size + G - 1) / G : 0;
+        c.nof_instances   = std::max(1u, cfg.batching.nof_batches);
+        contexts.push_back(std::make_shared<cuda::pusch_dec_context>(c));
+      }
+    }
+    for (auto& c : contexts) {
+      batchers.push_back(cuda::shared_batcher_of(c, cfg.batching));
     }
   }
   std::unique_ptr<hw_accelerator_pusch_dec> create() override
   {
-    return std::make_unique<hw_accelerator_pusch_dec_cuda>(cfg.context, cfg.external_harq, cfg.generic_arithmetic);
+    return std::make_unique<hw_accelerator_pusch_dec_cuda>(batchers, cfg.external_harq, cfg.generic_arithmetic, next_id++);
+  }
+  void stats(uint64_t& nb, uint64_t& ncb) const
+  {
+    nb = ncb = 0;
+    for (auto& b : batchers) {
+      nb += b->nof_batches_submitted();
+      ncb += b->nof_code_blocks_submitted();
+    }
   }
 
 private:
   cuda_hwacc_pusch_dec_factory_configuration cfg;
+  std::vector<std::shared_ptr<batcher>>      batchers;
+  std::atomic<unsigned>                      next_id{0};
 };
 
 } // namespace
@@ -211,4 +236,13 @@ std::shared_ptr<hw_accelerator_pusch_dec_factory>
 srsran::hal::create_cuda_pusch_dec_acc_factory(const cuda_hwacc_pusch_dec_factory_configuration& accelerator_config)
 {
   return std::make_shared<hw_accelerator_pusch_dec_factory_cuda>(accelerator_config);
+}
+
+void srsran::hal::cuda_pusch_dec_acc_factory_stats(const hw_accelerator_pusch_dec_factory& factory, uint64_t& batches,
+                                                  uint64_t& code_blocks)
+{
+  batches = code_blocks = 0;
+  if (auto* f = dynamic_cast<const hw_accelerator_pusch_dec_factory_cuda*>(&factory)) {
+    f->stats(batches, code_blocks);
+  }
 }

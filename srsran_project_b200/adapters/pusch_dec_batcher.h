@@ -1,0 +1,119 @@
+// Cross-instance batching of code-block operations in front of one accelerator context (one GPU).
+//
+// The reference drives its accelerator objects per transport block and serially per object: nof_pusch_decoder_threads
+// objects "shared for all the PUSCH decoders" (lib/phy/upper/channel_processors/pusch/factories.cpp:130-138), each running
+// pusch_decoder_hw_impl::run_asynch_hw_decoder (pusch_decoder_hw_impl.cpp:149-364) on its own executor thread; the software
+// operators are pooled the same way (factories.cpp:82-94). One GPU launch per object and transport block leaves the device
+// mostly idle (152 thread blocks on a machine that holds 592) and pays one PCIe round trip per transport block. The batcher
+// coalesces the operations of ALL objects that share a context:
+//
+//   join()     an object asks for a PART of the batch that is currently open (a transport block, or a single code block for
+//              the ldpc_decoder / ldpc_rate_dematcher operators); it gets a region of the batch's page-locked LLR buffer
+//   add()      the object's code blocks: LLRs are copied straight into the page-locked region (the only host copy before
+//              the DMA: pdc_set_zero_copy), descriptors are collected per part
+//   seal()     no more code blocks will follow
+//   poll()     "not ready" until the batch has run (hw_accelerator::dequeue_operation may return false:
+//              pusch_decoder_hw_impl.cpp:325-338 spins on it). A batch closes — ONE pdc_submit: one H2D copy, one launch per
+//              kernel variant, one D2H copy — as soon as every joined part is sealed AND (it is full, OR the device has
+//              nothing in flight, OR it has been open for close_after_us): an idle device is never kept waiting, a busy one
+//              collects work meanwhile. The thread whose poll closes the batch submits it and waits for the device
+//              (pdc_fetch) on behalf of everybody; the others sleep on a condition variable.
+//   release()  results handed back; the batch's buffers are reused once every part has been released
+//
+// Thread-safe. No CPU fallback: a failed submission marks every code block of the batch "CRC failed" (status 1).
+#pragma once
+
+#include "cuda_pusch_dec_context.h"
+#include <chrono>
+#include <condition_variable>
+#include <cstdint>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+namespace srsran {
+namespace cuda {
+
+struct pusch_dec_batcher_config {
+  /// Parts (transport blocks) per batch. Clamped to what the context's batch capacity allows.
+  unsigned max_parts = 8;
+  /// A batch that is neither full nor facing an idle device closes after this long.
+  unsigned close_after_us = 150;
+  /// Batches (page-locked staging buffers) that may be open or in flight at once; at most the context's nof_instances.
+  unsigned nof_batches = 4;
+};
+
+class pusch_dec_batcher
+{
+public:
+  static constexpr unsigned MAX_PART_CBS = 152;      // ldpc::MAX_NOF_SEGMENTS
+  static constexpr size_t   SOFT_STRIDE  = 66 * 384; // largest soft buffer
+  static constexpr size_t   BITS_STRIDE  = 8448 / 8; // largest message, bytes
+
+  struct batch;
+  struct part {
+    batch*                   owner = nullptr;
+    int8_t*                  llrs  = nullptr; // this part's region of the batch's page-locked buffer
+    size_t                   llr_base = 0, llr_cap = 0, llr_used = 0;
+    unsigned                 cb_cap = 0;
+    std::vector<pdc_cb_desc> descs;  // offsets relative to the batch buffers; out / soft offsets assigned by seal()
+    std::vector<int8_t>      soft;   // host-side HARQ buffers travelling with the operations (harq_slot < 0), SOFT_STRIDE each
+    std::vector<int>         index;  // per code block: position in the batch once it has closed, -1 = rejected by add()
+    bool                     sealed   = false;
+    bool                     in_use   = false;
+  };
+  enum class status { pending, done };
+
+  pusch_dec_batcher(std::shared_ptr<pusch_dec_context> context, const pusch_dec_batcher_config& cfg);
+  ~pusch_dec_batcher();
+  pusch_dec_batcher(const pusch_dec_batcher&)            = delete;
+  pusch_dec_batcher& operator=(const pusch_dec_batcher&) = delete;
+
+  /// A part of the open batch with room for max_cbs code blocks and max_llr_bytes of LLRs (each code block 16-byte aligned),
+  /// or nullptr when every batch buffer is taken (try again: back-pressure, not an error). A request larger than a whole
+  /// batch is cut down to the batch: add() then reports "full" and the caller continues with another part.
+  /// wait_us > 0: when no batch buffer is free the call sleeps up to that long for one (woken when a batch is recycled).
+  part* join(unsigned max_cbs, size_t max_llr_bytes, unsigned wait_us = 0);
+  /// Appends one code block. d.llr_offset / out_offset / soft_offset are assigned here. soft_in: the code block's host
+  /// soft buffer (harq_slot < 0 and not decode-only), may be empty. Returns false if the part is full.
+  bool add(part* p, pdc_cb_desc d, const int8_t* llrs, size_t nof_llrs, const int8_t* soft_in, size_t nof_soft);
+  void seal(part* p);
+  /// wait_us > 0: when the batch is not done yet the call may sleep up to that long (woken as soon as it is) instead of
+  /// returning at once: callers that spin on the result (the reference's dequeue loop) then leave the cores to the threads
+  /// that still have host work to do.
+  status poll(part* p, unsigned wait_us = 0);
+  /// After status::done: outcome of the part's k-th code block.
+  const pdc_cb_result& result(const part* p, unsigned k) const;
+  const uint8_t*       bits(const part* p, unsigned k) const;
+  const int8_t*        soft(const part* p, unsigned k) const; // updated host soft buffer (harq_slot < 0)
+  void                 release(part* p);
+
+  pusch_dec_context& context() { return *ctx; }
+  /// Batches submitted and code blocks carried so far (for tests and the bench: mean batch size = code_blocks / batches).
+  uint64_t nof_batches_submitted() const;
+  uint64_t nof_code_blocks_submitted() const;
+
+private:
+  void  try_advance(batch* b, std::unique_lock<std::mutex>& lock);
+  part* join_locked(unsigned max_cbs, size_t max_llr_bytes);
+
+  std::shared_ptr<pusch_dec_context>  ctx;
+  pusch_dec_batcher_config            cfg;
+  mutable std::mutex                  mtx;
+  std::condition_variable             cv; // a batch completed (or failed): waiters re-evaluate
+  std::condition_variable             cv_room; // a batch buffer was recycled: joiners re-evaluate
+  std::vector<std::unique_ptr<batch>> batches;
+  batch*                              open = nullptr;
+  unsigned                            inflight = 0;
+  uint64_t                            stat_batches = 0, stat_cbs = 0;
+  unsigned                            batch_cbs = 0;
+  size_t                              batch_llrs = 0;
+};
+
+/// The batcher of a context: every adapter object that shares the context shares its batcher (created on first use with
+/// `cfg`; later calls return the same object whatever their cfg).
+std::shared_ptr<pusch_dec_batcher> shared_batcher_of(const std::shared_ptr<pusch_dec_context>& context,
+                                                     const pusch_dec_batcher_config&           cfg = {});
+
+} // namespace cuda
+} // namespace srsran

@@ -2,6 +2,7 @@
 // the context layout and the batch planner.
 #include "pdc_runtime_internal.cuh"
 #include <algorithm>
+#include <thread>
 
 static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
 {
@@ -482,8 +483,13 @@ static pdc_status wait_ticket(pdc_ctx* ctx, pdc_ticket ticket, bool want_tbs, ti
       return PDC_ERR_BAD_TICKET;
     }
   }
-  cudaError_t e = cudaEventSynchronize(t->done);
-  if (!cuda_ok(ctx, e, "cudaEventSynchronize")) {
+  // Query + yield instead of cudaEventSynchronize: the runtime's wait spins on a core, and the callers of this library are
+  // pools of host threads with work of their own (the reference's decoder threads); an idle machine loses nothing.
+  cudaError_t e;
+  while ((e = cudaEventQuery(t->done)) == cudaErrorNotReady) {
+    std::this_thread::yield();
+  }
+  if (!cuda_ok(ctx, e, "cudaEventQuery")) {
     return release_ticket(ctx, t, PDC_ERR_CUDA);
   }
   return PDC_OK;

@@ -38,8 +38,12 @@
 #include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_result.h"
 #include "srsran/phy/upper/rx_buffer_pool.h"
 #include "srsran/phy/upper/unique_rx_buffer.h"
+#include <atomic>
+#include <chrono>
 #include <cstring>
 #include <memory>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 using namespace srsran;
@@ -250,6 +254,205 @@ int adt_decode_tb(void*         handle,
   stats[4]                      = any ? r.ldpc_decoder_stats.get_max() : 0;
   stats[5]                      = any ? static_cast<int64_t>(r.ldpc_decoder_stats.get_mean() * 1000.0 + 0.5) : 0;
   return 0;
+}
+
+// TEST INFRASTRUCTURE: an accelerator that answers at once with the right bits (replayed from a table), used ONLY to measure
+// what the reference's pusch_decoder_hw_impl costs on the host by itself — the ceiling of the drop-in boundary whatever sits
+// behind it. It takes the LLRs (one copy, as any accelerator must) and returns recorded messages.
+thread_local unsigned tl_replay_codeword = 0;
+class replay_accelerator : public hal::hw_accelerator_pusch_dec
+{
+public:
+  replay_accelerator(const uint8_t* table_, unsigned nof_cbs_, unsigned cb_bytes_) :
+    table(table_), nof_cbs(nof_cbs_), cb_bytes(cb_bytes_), scratch(35 * 8448)
+  {
+  }
+  void reserve_queue() override {}
+  void free_queue() override {}
+  void configure_operation(const hal::hw_pusch_decoder_configuration&, unsigned) override {}
+  bool enqueue_operation(span<const int8_t> data, span<const int8_t>, unsigned) override
+  {
+    std::memcpy(scratch.data(), data.data(), std::min(data.size(), scratch.size()));
+    return true;
+  }
+  bool dequeue_operation(span<uint8_t> data, span<int8_t>, unsigned segment_index) override
+  {
+    std::memcpy(data.data(), table + ((size_t)tl_replay_codeword * nof_cbs + segment_index) * cb_bytes,
+                std::min<size_t>(data.size(), cb_bytes));
+    return true;
+  }
+  void read_operation_outputs(hal::hw_pusch_decoder_outputs& out, unsigned, unsigned) override { out = {true, 1}; }
+  void free_harq_context_entry(unsigned) override {}
+  bool is_harq_external() const override { return true; }
+
+private:
+  const uint8_t*      table;
+  unsigned            nof_cbs, cb_bytes;
+  std::vector<int8_t> scratch;
+};
+
+// Throughput of the drop-in boundary (bench.py leg e2e_hal): nthreads host threads, each with its own UNMODIFIED
+// pusch_decoder_hw_impl, all drawing accelerators from one pool created by ONE CUDA HAL factory (factories.cpp:130-138), decode
+// transport blocks back to back the way pusch_decoder_hwacc_benchmark.cpp:430-495 drives a decoder (new_data, one
+// on_new_softbits with the whole codeword, on_end_softbits; synchronous: no executor). Inputs: n_distinct codewords of
+// nof_llrs soft bits each (thread t decodes codeword (t + k) mod n_distinct as its k-th block) and the transport blocks they
+// must decode to. devices: CUDA ordinals (one context each). Returns 0 and seconds = wall time of the timed part;
+// stats: [transport blocks decoded correctly, transport blocks attempted, GPU submissions, code blocks submitted];
+// -1 = no device, -2 = a soft buffer could not be reserved.
+int adt_bench_hal(unsigned       nthreads,
+                  unsigned       tbs_per_thread,
+                  unsigned       warmup_per_thread,
+                  const int8_t*  llrs,
+                  unsigned       nof_llrs,
+                  unsigned       n_distinct,
+                  const uint8_t* expected_tbs,
+                  unsigned       tbs_bits,
+                  int            bg,
+                  unsigned       Qm,
+                  unsigned       nof_layers,
+                  unsigned       max_iter,
+                  const int*     devices,
+                  unsigned       nof_devices,
+                  unsigned       max_parts,
+                  unsigned       close_after_us,
+                  const uint8_t* replay_table, // not null: [n_distinct][nof_cbs][ceil(K / 8)] messages for the replay accelerator
+                  double*        seconds,
+                  uint64_t*      stats)
+{
+  __builtin_cpu_init();
+  const ldpc_base_graph_type base_graph = (bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+  const unsigned             nof_cbs    = ldpc::compute_nof_codeblocks(units::bits(tbs_bits), base_graph);
+  const unsigned             nof_harq   = 2;
+
+  rx_buffer_pool_config pool_cfg = {};
+  pool_cfg.max_codeblock_size   = ldpc::MAX_CODEBLOCK_SIZE;
+  pool_cfg.nof_buffers          = nthreads * nof_harq;
+  pool_cfg.nof_codeblocks       = nthreads * nof_harq * nof_cbs;
+  pool_cfg.expire_timeout_slots = 100000;
+  pool_cfg.external_soft_bits   = true;
+  std::unique_ptr<rx_buffer_pool_controller> pool = create_rx_buffer_pool(pool_cfg);
+
+  std::shared_ptr<hal::hw_accelerator_pusch_dec_factory> acc_factory;
+  if (!replay_table) try {
+    hal::cuda_hwacc_pusch_dec_factory_configuration acfg;
+    acfg.devices.assign(devices, devices + nof_devices);
+    acfg.external_harq           = true;
+    acfg.harq_context_size       = pool_cfg.nof_codeblocks;
+    acfg.batching.max_parts      = max_parts;
+    acfg.batching.close_after_us = close_after_us;
+    acc_factory                  = hal::create_cuda_pusch_dec_acc_factory(acfg);
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "adt_bench_hal: %s\n", e.what());
+    return -1;
+  }
+  std::vector<std::unique_ptr<hal::hw_accelerator_pusch_dec>> accs;
+  const unsigned cb_bytes = (pdc_cb_message_bits(bg, ldpc::compute_lifting_size(units::bits(tbs_bits), base_graph, nof_cbs)) + 7) / 8;
+  for (unsigned i = 0; i != nthreads; ++i) {
+    if (replay_table) {
+      accs.push_back(std::make_unique<replay_accelerator>(replay_table, nof_cbs, cb_bytes));
+    } else {
+      accs.push_back(acc_factory->create());
+    }
+  }
+  auto hw_pool = std::make_shared<pusch_decoder_hw_impl::hw_decoder_pool>(accs);
+  std::vector<std::unique_ptr<pusch_decoder>> decoders;
+  for (unsigned i = 0; i != nthreads; ++i) {
+    pusch_decoder_hw_impl::sch_crc crcs = {make_crc(crc_generator_poly::CRC16),
+                                           make_crc(crc_generator_poly::CRC24A),
+                                           make_crc(crc_generator_poly::CRC24B)};
+    decoders.push_back(std::make_unique<pusch_decoder_hw_impl>(std::make_unique<ldpc_segmenter_rx_impl>(), crcs, hw_pool, nullptr));
+  }
+
+  pusch_decoder::configuration cfg = {};
+  cfg.base_graph          = base_graph;
+  cfg.rv                  = 0;
+  cfg.mod                 = static_cast<modulation_scheme>(Qm);
+  cfg.Nref                = 0;
+  cfg.nof_layers          = nof_layers;
+  cfg.nof_ldpc_iterations = max_iter;
+  cfg.force_decoding      = false;
+  cfg.use_early_stop      = true;
+  cfg.new_data            = true;
+
+  std::mutex            reserve_mtx;
+  std::atomic<unsigned> arrived{0}, failures{0};
+  std::atomic<uint64_t> ok{0}, attempted{0};
+  std::atomic<int>      phase{0};
+  const unsigned        tb_bytes = tbs_bits / 8;
+
+  auto decode_one = [&](unsigned t, unsigned k, std::vector<uint8_t>& tb, bool count) {
+    const unsigned   w = (t + k) % n_distinct;
+    tl_replay_codeword = w;
+    unique_rx_buffer buffer;
+    {
+      // rx_buffer_pool::reserve is called from one thread in the gNB (the upper-PHY receive path); only unlock / release come
+      // from the decoder threads.
+      std::lock_guard<std::mutex> lock(reserve_mtx);
+      buffer = pool->get_pool().reserve({}, trx_buffer_identifier(1 + t, k % nof_harq), nof_cbs, true);
+    }
+    if (!buffer.is_valid()) {
+      failures++;
+      return;
+    }
+    buffer.get().reset_codeblocks_crc();
+    notifier_capture      notifier;
+    pusch_decoder_buffer& in = decoders[t]->new_data(tb, std::move(buffer), notifier, cfg);
+    in.on_new_softbits(span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs) + (size_t)w * nof_llrs, nof_llrs));
+    in.on_end_softbits();
+    if (count) {
+      attempted++;
+      if (notifier.called && notifier.last.tb_crc_ok && std::memcmp(tb.data(), expected_tbs + (size_t)w * tb_bytes, tb_bytes) == 0) {
+        ok++;
+      }
+    }
+  };
+  auto sync = [&](int target) { // all threads + the main thread
+    arrived++;
+    while (phase.load() < target) {
+      std::this_thread::yield();
+    }
+  };
+  std::vector<std::thread> threads;
+  for (unsigned t = 0; t != nthreads; ++t) {
+    threads.emplace_back([&, t]() {
+      std::vector<uint8_t> tb(tb_bytes, 0);
+      for (unsigned k = 0; k != warmup_per_thread; ++k) {
+        decode_one(t, k, tb, false);
+      }
+      sync(1);
+      for (unsigned k = 0; k != tbs_per_thread; ++k) {
+        decode_one(t, warmup_per_thread + k, tb, true);
+      }
+      sync(2);
+    });
+  }
+  while (arrived.load() < nthreads) {
+    std::this_thread::yield();
+  }
+  uint64_t b0 = 0, c0 = 0;
+  if (acc_factory) {
+    hal::cuda_pusch_dec_acc_factory_stats(*acc_factory, b0, c0);
+  }
+  arrived                                     = 0;
+  const std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  phase                                       = 1;
+  while (arrived.load() < nthreads) {
+    std::this_thread::yield();
+  }
+  *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  phase    = 2;
+  for (auto& th : threads) {
+    th.join();
+  }
+  uint64_t b1 = 0, c1 = 0;
+  if (acc_factory) {
+    hal::cuda_pusch_dec_acc_factory_stats(*acc_factory, b1, c1);
+  }
+  stats[0] = ok.load(), stats[1] = attempted.load(), stats[2] = b1 - b0, stats[3] = c1 - c0;
+  decoders.clear();
+  hw_pool.reset();
+  pool->stop();
+  return failures.load() ? -2 : 0;
 }
 
 // The CUDA demodulation_mapper adapter behind the reference's interface: one demodulate_soft call.

@@ -151,6 +151,29 @@ def test_cuda_adapters_match_reference_decoder(mode, external, generic):
 
 
 @pytest.mark.gpu
+def test_hal_accelerators_of_one_factory_share_gpu_submissions():
+    """Cross-instance batching (adapters/pusch_dec_batcher.h): six host threads, each with its own reference pusch_decoder_hw_impl,
+    draw accelerators from one CUDA HAL factory and decode small transport blocks back to back. Every transport block comes out
+    as transmitted, and the GPU saw fewer submissions than transport blocks (the objects' code blocks travelled together)."""
+    from tools import bench_hal
+
+    if not bench_hal.available():
+        pytest.skip("tests/adapters/_build not built (needs /root/reference at build time)")
+    bg, tbs, Qm, layers, G = 1, 30000, 4, 2, 35200
+    n_distinct = 5
+    llrs, want = np.zeros((n_distinct, G), np.int8), np.zeros((n_distinct, tbs // 8), np.uint8)
+    for t in range(n_distinct):
+        want[t], (llrs[t],) = make_tb(300 + t, bg, tbs, Qm, layers, G, (0,), (2.5,))
+    r = bench_hal.run_raw(llrs, want, tbs, bg, Qm, layers, 6, threads=6, tbs_per_thread=20, warmup=1, max_parts=8,
+                          close_after_us=200)
+    assert r["ok"] == r["attempted"] == 120, r
+    assert r["batches"] < r["attempted"], r
+    # one thread alone: nothing to coalesce with, every transport block is its own submission and still comes out right
+    r1 = bench_hal.run_raw(llrs, want, tbs, bg, Qm, layers, 6, threads=1, tbs_per_thread=6, warmup=1)
+    assert r1["ok"] == r1["attempted"] == 6 and r1["batches"] == 6, r1
+
+
+@pytest.mark.gpu
 def test_cuda_demodulation_mapper_adapter_reproduces_the_golden_calls():
     """srsran::demodulation_mapper implemented over pdc_demodulate (adapters/channel_modulation_factories_cuda.cpp), driven
     through the reference's interface, against the calls recorded from the compiled reference (tests/golden/demod_v1.npz)."""
