@@ -2,6 +2,7 @@
 // the context layout and the batch planner.
 #include "pdc_runtime_internal.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <thread>
 
 static pdc_status alloc_ticket(pdc_ctx* ctx, ticket_t& t)
@@ -168,6 +169,15 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
       return fail(PDC_ERR_CUDA);
     }
   }
+  if (!cuda_ok(ctx, cudaEventCreateWithFlags(&ctx->side_fork, cudaEventDisableTiming), "cudaEventCreate")) {
+    return fail(PDC_ERR_CUDA);
+  }
+  for (int i = 0; i != pdc_ctx::NOF_SIDE_STREAMS; ++i) {
+    if (!cuda_ok(ctx, cudaStreamCreateWithFlags(&ctx->side_stream[i], cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !cuda_ok(ctx, cudaEventCreateWithFlags(&ctx->side_join[i], cudaEventDisableTiming), "cudaEventCreate")) {
+      return fail(PDC_ERR_CUDA);
+    }
+  }
   ctx->tickets.resize(cfg->nof_tickets);
   for (ticket_t& t : ctx->tickets) {
     if (alloc_ticket(ctx, t) != PDC_OK) {
@@ -188,6 +198,16 @@ void pdc_destroy(pdc_ctx* ctx)
     free_ticket(t);
   }
   cudaFree(ctx->d_graphs), cudaFree(ctx->d_crc), cudaFree(ctx->d_crc_bit), cudaFree(ctx->d_harq);
+  for (int i = 0; i != pdc_ctx::NOF_SIDE_STREAMS; ++i) {
+    if (ctx->side_stream[i]) {
+      cudaStreamSynchronize(ctx->side_stream[i]);
+      cudaStreamDestroy(ctx->side_stream[i]);
+      cudaEventDestroy(ctx->side_join[i]);
+    }
+  }
+  if (ctx->side_fork) {
+    cudaEventDestroy(ctx->side_fork);
+  }
   cudaFree(ctx->d_harq_bits);
   for (pdc_ctx::demod_slot& d : ctx->demod_ring) {
     cudaFree(d.d_desc);
@@ -486,8 +506,13 @@ static pdc_status wait_ticket(pdc_ctx* ctx, pdc_ticket ticket, bool want_tbs, ti
   // Query + yield instead of cudaEventSynchronize: the runtime's wait spins on a core, and the callers of this library are
   // pools of host threads with work of their own (the reference's decoder threads); an idle machine loses nothing.
   cudaError_t e;
-  while ((e = cudaEventQuery(t->done)) == cudaErrorNotReady) {
-    std::this_thread::yield();
+  static const bool spin_sync = getenv("PDC_WAIT_SYNC") != nullptr; // A/B switch: the runtime's own (spinning) wait
+  if (spin_sync) {
+    e = cudaEventSynchronize(t->done);
+  } else {
+    while ((e = cudaEventQuery(t->done)) == cudaErrorNotReady) {
+      std::this_thread::yield();
+    }
   }
   if (!cuda_ok(ctx, e, "cudaEventQuery")) {
     return release_ticket(ctx, t, PDC_ERR_CUDA);

@@ -86,6 +86,13 @@ struct pdc_ctx {
   std::vector<ticket_t> tickets;
   int64_t               next_id = 1;
   unsigned              next_ticket = 0; // reserve_ticket starts its search here (round robin)
+  // A mixed batch runs one kernel per list (launch_batch): the lists are independent, so all but the first go to side streams
+  // that fork from and join the caller's stream through events (irregular batches are bound by the slowest code block of each
+  // kernel, not by the machine: in sequence those critical paths add up).
+  static constexpr int  NOF_SIDE_STREAMS = 6;
+  std::mutex            side_mtx;
+  cudaStream_t          side_stream[NOF_SIDE_STREAMS] = {};
+  cudaEvent_t           side_fork = nullptr, side_join[NOF_SIDE_STREAMS] = {};
   uint32_t*             d_graphs = nullptr;
   uint32_t*             d_crc    = nullptr;
   uint32_t*             d_crc_bit = nullptr;
@@ -548,25 +555,45 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
   prm.graphs  = ctx->d_graphs;
   prm.crc_pow = ctx->d_crc;
   prm.crc_bit = ctx->d_crc_bit;
-  uint32_t off = 0;
+  int nlists = (bp.n_lane != 0) ? 1 : 0;
   for (int k = 0; k != PDC_NOF_PACKED_LISTS; ++k) {
-    if (bp.n_h2[k] != 0) {
-      prm.order = bp.identity ? nullptr : d_order + off;
-      prm.n     = (int)bp.n_h2[k];
-      if (k >= 4) {
-        CK(pdc_launch_h2g(prm, (k & 1) + 1, bp.block_h2[k], bp.smem_h2[k], stream));
-      } else {
-        CK(pdc_launch_h2(prm, (k & 1) + 1, (k & 2) ? 384 : 0, bp.block_h2[k], bp.smem_h2[k], stream));
-      }
-      ctx->launches++;
-      off += bp.n_h2[k];
-    }
+    nlists += (bp.n_h2[k] != 0);
   }
-  if (bp.n_lane != 0) {
+  // More than one list: fork. The side streams are shared by the context, so concurrent mixed batches take turns.
+  std::unique_lock<std::mutex> side_lock(ctx->side_mtx, std::defer_lock);
+  const bool                   fork = nlists > 1;
+  if (fork) {
+    side_lock.lock(); // streams and events were created by pdc_create: nothing is allocated on the data path
+    CK(cudaEventRecord(ctx->side_fork, stream));
+  }
+  uint32_t off = 0;
+  int      used = 0; // lists launched so far: list 0 stays on the caller's stream
+  auto     stream_of = [&](int idx) -> cudaStream_t { return (idx == 0) ? stream : ctx->side_stream[idx - 1]; };
+  for (int k = 0; k != PDC_NOF_LISTS; ++k) {
+    const uint32_t cnt = (k < PDC_NOF_PACKED_LISTS) ? bp.n_h2[k] : bp.n_lane;
+    if (cnt == 0) {
+      continue;
+    }
+    cudaStream_t s = stream_of(used);
+    if (used != 0) {
+      CK(cudaStreamWaitEvent(s, ctx->side_fork, 0));
+    }
     prm.order = bp.identity ? nullptr : d_order + off;
-    prm.n     = (int)bp.n_lane;
-    CK(pdc_launch_lane(prm, bp.block_lane, bp.smem_lane, stream));
+    prm.n     = (int)cnt;
+    if (k == PDC_NOF_PACKED_LISTS) {
+      CK(pdc_launch_lane(prm, bp.block_lane, bp.smem_lane, s));
+    } else if (k >= 4) {
+      CK(pdc_launch_h2g(prm, (k & 1) + 1, bp.block_h2[k], bp.smem_h2[k], s));
+    } else {
+      CK(pdc_launch_h2(prm, (k & 1) + 1, (k & 2) ? 384 : 0, bp.block_h2[k], bp.smem_h2[k], s));
+    }
     ctx->launches++;
+    if (used != 0) {
+      CK(cudaEventRecord(ctx->side_join[used - 1], s));
+      CK(cudaStreamWaitEvent(stream, ctx->side_join[used - 1], 0));
+    }
+    off += cnt;
+    ++used;
   }
   return PDC_OK;
 }

@@ -256,6 +256,44 @@ int adt_decode_tb(void*         handle,
   return 0;
 }
 
+// Latency of ONE ldpc_decoder::decode call (BASELINE config 1 at batch 1: what ldpc_decoder_benchmark.cpp:193-196 times with
+// the software decoders), through the CUDA ldpc_decoder adapter or the reference's own decoder. impl: 0 generic, 1 AVX2, 2 AVX512,
+// 3 CUDA. Fills us[0..reps) with the wall time of every call in microseconds and bits with the decoded message of the last one.
+// Returns the iteration count of the last call (0 = nullopt), -1 = no device.
+int adt_ldpc_decode_latency(int impl, int bg, unsigned Z, const int8_t* llrs, unsigned nof_llrs, unsigned max_iter, unsigned reps,
+                            double* us, uint8_t* bits)
+{
+  __builtin_cpu_init();
+  std::unique_ptr<ldpc_decoder> dec;
+  try {
+    if (impl == 3) {
+      static std::shared_ptr<ldpc_decoder_factory> factory = create_ldpc_decoder_factory_cuda({false});
+      dec = factory->create();
+    } else {
+      dec = make_sw_decoder(impl);
+    }
+  } catch (const std::exception&) {
+    return -1;
+  }
+  const unsigned               K = pdc_cb_message_bits(bg, Z);
+  dynamic_bit_buffer           message(K);
+  ldpc_decoder::configuration  cfg = {};
+  cfg.base_graph      = (bg == 1) ? ldpc_base_graph_type::BG1 : ldpc_base_graph_type::BG2;
+  cfg.lifting_size    = static_cast<ldpc::lifting_size_t>(Z);
+  cfg.nof_filler_bits = 0;
+  cfg.nof_crc_bits    = 16;
+  cfg.max_iterations  = max_iter;
+  span<const log_likelihood_ratio> in(reinterpret_cast<const log_likelihood_ratio*>(llrs), nof_llrs);
+  std::optional<unsigned>          it;
+  for (unsigned r = 0; r != reps; ++r) {
+    const auto t0 = std::chrono::steady_clock::now();
+    it            = dec->decode(message, in, nullptr, cfg);
+    us[r]         = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+  }
+  std::memcpy(bits, message.get_buffer().data(), (K + 7) / 8);
+  return it.has_value() ? static_cast<int>(*it) : 0;
+}
+
 // TEST INFRASTRUCTURE: an accelerator that answers at once with the right bits (replayed from a table), used ONLY to measure
 // what the reference's pusch_decoder_hw_impl costs on the host by itself — the ceiling of the drop-in boundary whatever sits
 // behind it. It takes the LLRs (one copy, as any accelerator must) and returns recorded messages.

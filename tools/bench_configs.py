@@ -28,8 +28,22 @@ def message_with_crc(S, rng, K, F, crc_id):
     return np.concatenate([payload, crc_bits, np.zeros(F, np.uint8)])
 
 
-def run_batch(name, cases, txs, steps, cpu=True):
-    """cases: list of dict(bg, Z, Qm, F, Nref, crc_id, E); txs: list over transmissions of (rv list, llr list)."""
+BG_DEG = {1: [19, 19, 19, 19, 3, 8, 9, 7, 10, 9, 7, 8, 7, 6, 7, 7, 6, 6, 6, 6, 6, 6, 5, 5, 6, 5, 5, 4, 5, 5, 5, 5, 5, 5, 5, 5, 5, 4, 5,
+              5, 4, 5, 4, 5, 5, 4],
+          2: [8, 10, 8, 10, 4, 6, 6, 6, 4, 5, 5, 5, 4, 5, 5, 4, 5, 5, 4, 4, 4, 4, 3, 4, 4, 3, 5, 3, 4, 3, 5, 3, 4, 4, 4, 4, 4, 3, 4,
+              4, 4, 4]}
+
+
+def lane_ops(bg, Z, iterations, layers, max_iter=6):
+    """ops(CB) = I * Z * (8 * sum_{m<L} deg(m) + 2 L) int8 lane-operations."""
+    cs = np.concatenate([[0], np.cumsum(BG_DEG[bg])])
+    it = iterations if iterations > 0 else max_iter
+    return float(it) * Z * (8.0 * cs[layers] + 2.0 * layers)
+
+
+def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None):
+    """cases: list of dict(bg, Z, Qm, F, Nref, crc_id, E); txs: list over transmissions of (rv list, llr list).
+    peak_ops: the roofline denominator (two-lane issue peak x 2, ops/s) measured by the caller, or None."""
     import torch
 
     import srsran_project_b200 as pdc
@@ -94,7 +108,11 @@ def run_batch(name, cases, txs, steps, cpu=True):
         res = d_res.cpu().numpy().view(B.RESULT_DTYPE)
         bits = d_bits.cpu().numpy()
         info = sum(kb(c["bg"]) * c["Z"] - c["F"] - (16 if c["crc_id"] == 1 else 24) for c in cases)
-        rec = {"tx": t, "gpu_ms": ms, "gpu_info_gbps": info / (ms * 1e-3) / 1e9,
+        ops = sum(lane_ops(c["bg"], c["Z"], int(res["iterations"][i]), int(res["nof_layers"][i])) for i, c in enumerate(cases))
+        rec = {"tx": t, "gpu_ms": ms, "gpu_info_gbps": info / (ms * 1e-3) / 1e9, "value": info / (ms * 1e-3) / 1e9,
+               "roofline": {"bound": "alu", "achieved": ops / (ms * 1e-3) / 1e12, "unit": "Tops/s (int8 lane-ops)",
+                            "peak": None if peak_ops is None else peak_ops / 1e12,
+                            "frac": None if peak_ops is None else ops / (ms * 1e-3) / peak_ops},
                "avg_iterations": float(np.where(res["iterations"] > 0, res["iterations"], 6).mean()),
                "crc_pass_fraction": float((res["crc_pass"] == 1).mean()),
                "layers_min_max": [int(res["nof_layers"].min()), int(res["nof_layers"].max())]}
@@ -132,10 +150,10 @@ def run_batch(name, cases, txs, steps, cpu=True):
                 raise RuntimeError(f"{name} tx {t}: GPU differs from the reference: {rec['bit_exact']}")
         out["transmissions"].append(rec)
     ctx.close()
-    print(json.dumps(out), flush=True)
+    return out
 
 
-def config3(S, steps):
+def config3(S, steps, cpu=True, peak_ops=None):
     from oracle.pyoracle import LIFTING_SIZES
 
     rng = np.random.default_rng(3)
@@ -161,27 +179,31 @@ def config3(S, steps):
     cases = [cases[i] for i in order]
     rvs = [rvs[i] for i in order]
     llrs = [llrs[i] for i in order]
-    run_batch("config 3: BG2 sweep, all 51 lifting sizes x 8 code blocks, mixed Qm / rate / rv, shuffled", cases, [(rvs, llrs)], steps)
+    return run_batch("config 3: BG2 sweep, all 51 lifting sizes x 8 code blocks, mixed Qm / rate / rv, shuffled", cases,
+                     [(rvs, llrs)], steps, cpu=cpu, peak_ops=peak_ops)
 
 
-def config4(S, steps, sigma1, sigma2):
-    rng = np.random.default_rng(4)
+def config4(S, steps, sigma1, sigma2, n_tbs=8, cpu=True, peak_ops=None):
+    """n_tbs config-2 transport blocks (152 code blocks each): rv0 at a noise level where nothing decodes (six iterations
+    everywhere: the worst case), then rv2 combined into the device-resident soft buffers."""
     c = S.CONFIG2
-    tb = rng.integers(0, 2, c["tbs"], dtype=np.uint8)
     seg = S.segmentation(c["bg"], c["tbs"])
     Es = S.rm_lengths(seg["C"], c["G"], c["nof_layers"], c["Qm"])
-    cases = [dict(bg=1, Z=seg["Z"], Qm=8, F=seg["F"], Nref=0, crc_id=3) for _ in range(seg["C"])]
-    txs = []
-    for rv, sigma, seed in ((0, sigma1, 41), (2, sigma2, 42)):
-        _, bits, _ = S.tb_encode(c["bg"], c["tbs"], tb, rv, c["Qm"], 0, c["nof_layers"], c["G"])
-        x = S.awgn_llrs(bits, 8.0, sigma, seed)
-        parts, p = [], 0
-        for r in range(seg["C"]):
-            parts.append(x[p:p + Es[r]])
-            p += Es[r]
-        txs.append(([rv] * seg["C"], parts))
-    run_batch(f"config 4: HARQ rv0 (sigma {sigma1}) + rv2 (sigma {sigma2}) over the device soft buffer, 152 code blocks BG1 Z=384",
-              cases, txs, steps)
+    cases = [dict(bg=1, Z=seg["Z"], Qm=8, F=seg["F"], Nref=0, crc_id=3) for _ in range(seg["C"] * n_tbs)]
+    txs = [([], []), ([], [])]
+    for k in range(n_tbs):
+        rng = np.random.default_rng(4 + 100 * k)
+        tb = rng.integers(0, 2, c["tbs"], dtype=np.uint8)
+        for j, (rv, sigma, seed) in enumerate(((0, sigma1, 41), (2, sigma2, 42))):
+            _, bits, _ = S.tb_encode(c["bg"], c["tbs"], tb, rv, c["Qm"], 0, c["nof_layers"], c["G"])
+            x = S.awgn_llrs(bits, 8.0, sigma, seed + 1000 * k)
+            p = 0
+            for r in range(seg["C"]):
+                txs[j][1].append(x[p:p + Es[r]])
+                txs[j][0].append(rv)
+                p += Es[r]
+    return run_batch(f"config 4: HARQ rv0 (sigma {sigma1}) + rv2 (sigma {sigma2}) over the device soft buffer, {n_tbs} TBs x 152 "
+                     f"code blocks BG1 Z=384", cases, txs, steps, cpu=cpu, peak_ops=peak_ops)
 
 
 def main():
@@ -189,11 +211,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--sigma1", type=float, default=3.0)
     ap.add_argument("--sigma2", type=float, default=6.0)
+    ap.add_argument("--tbs", type=int, default=8, help="config 4: transport blocks in the batch")
     args = ap.parse_args()
     from tools import stimulus as S
 
-    config3(S, args.steps)
-    config4(S, args.steps, args.sigma1, args.sigma2)
+    print(json.dumps(config3(S, args.steps)), flush=True)
+    print(json.dumps(config4(S, args.steps, args.sigma1, args.sigma2, args.tbs)), flush=True)
 
 
 if __name__ == "__main__":
