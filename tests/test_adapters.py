@@ -174,6 +174,28 @@ def test_hal_accelerators_of_one_factory_share_gpu_submissions():
 
 
 @pytest.mark.gpu
+def test_hal_factory_spreads_code_blocks_over_several_gpus():
+    """cuda_hwacc_pusch_dec_factory_configuration::devices: code blocks are placed by absolute code-block identifier (GPU = id mod G)
+    and every transport block still comes out as transmitted, first transmissions and HARQ-free repeats alike. Needs two GPUs."""
+    import torch
+
+    from tools import bench_hal
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two CUDA devices")
+    if not bench_hal.available():
+        pytest.skip("tests/adapters/_build not built (needs /root/reference at build time)")
+    bg, tbs, Qm, layers, G = 1, 60000, 4, 2, 70400
+    n_distinct = 4
+    llrs, want = np.zeros((n_distinct, G), np.int8), np.zeros((n_distinct, tbs // 8), np.uint8)
+    for t in range(n_distinct):
+        want[t], (llrs[t],) = make_tb(400 + t, bg, tbs, Qm, layers, G, (0,), (2.5,))
+    devices = tuple(range(min(torch.cuda.device_count(), 8)))
+    r = bench_hal.run_raw(llrs, want, tbs, bg, Qm, layers, 6, threads=4, tbs_per_thread=12, warmup=1, devices=devices)
+    assert r["ok"] == r["attempted"] == 48, r
+
+
+@pytest.mark.gpu
 def test_cuda_demodulation_mapper_adapter_reproduces_the_golden_calls():
     """srsran::demodulation_mapper implemented over pdc_demodulate (adapters/channel_modulation_factories_cuda.cpp), driven
     through the reference's interface, against the calls recorded from the compiled reference (tests/golden/demod_v1.npz)."""
