@@ -48,13 +48,13 @@ ref_objs=$(ls "$ROOT"/oracle/_ref/obj/*.o | grep -v ref_shim)
 # under _build/ (the reference tree itself is never touched), so that the test can call the patched make_du_low_hal_dependencies.
 N3="$OUT/n3"
 rm -rf "$N3"
-mkdir -p "$N3/apps/units/flexible_o_du" "$N3/lib/phy/upper"
+mkdir -p "$N3/apps/units/flexible_o_du" "$N3/lib/phy/upper" "$N3/lib/phy/metrics"
 cp -r "$REF/apps/units/flexible_o_du/o_du_low" "$N3/apps/units/flexible_o_du/"
 cp "$REF/lib/phy/upper/upper_phy_factories.cpp" "$REF/lib/phy/upper/CMakeLists.txt" "$N3/lib/phy/upper/"
 cp "$REF/CMakeLists.txt" "$N3/"
 chmod -R u+w "$N3"
 (cd "$N3" && patch -s -p1 --no-backup-if-mismatch < "$ROOT/integration/srsran_cuda.patch")
-N3INC="-I$N3/apps/units/flexible_o_du/o_du_low -I$REF -I$ROOT/srsran_project_b200/adapters"
+N3INC="-I$N3/apps/units/flexible_o_du/o_du_low -I$N3/lib/phy/metrics -I$REF -I$ROOT/srsran_project_b200/adapters"
 $CXX $BASE $INC $N3INC -DSRSRAN_CUDA_FOUND -c "$N3/apps/units/flexible_o_du/o_du_low/du_low_hal_factory.cpp" -o "$OBJ/n3_du_low_hal_factory.o"
 $CXX $BASE $INC $N3INC -c "$HERE/harness.cpp" -o "$OBJ/harness.o"
 $CXX -shared -o "$OUT/libadapter_harness.so" "$OBJ/harness.o" "$OBJ/n3_du_low_hal_factory.o" "${objs[@]}" $ref_objs \

@@ -4,6 +4,7 @@
 //   mode 1: the CUDA ldpc_decoder + ldpc_rate_dematcher (srsran_project_b200/adapters/channel_coding_factories_cuda.h)
 //           inside the reference's pusch_codeblock_decoder / pusch_decoder_impl (drop-in boundary 1),
 //   mode 2: the CUDA hal::hw_accelerator_pusch_dec inside the reference's pusch_decoder_hw_impl (drop-in boundary 2),
+//   mode 4: mode 2 with the HAL metric decorator that integration/srsran_cuda.patch adds to the reference (lib/phy/metrics),
 //   mode 3: the CUDA srsran::pusch_decoder (srsran_project_b200/adapters/pusch_decoder_cuda.h): code blocks AND transport
 //           block assembly + CRC24A on the device, in place of the reference's TB decoders.
 // Downlink mirror: the CUDA srsran::pdsch_encoder, and the CUDA hal::hw_accelerator_pdsch_enc inside the
@@ -20,6 +21,7 @@
 #include "srsran/phy/upper/channel_processors/pusch/pusch_codeword_buffer.h"
 #include "srsran/phy/upper/channel_processors/pusch/pusch_decoder_buffer.h"
 #include "du_low_hal_factory.h" // the reference's, with integration/srsran_cuda.patch applied (tests/adapters/build.sh)
+#include "phy_metrics_hw_accelerator_pusch_dec_decorator.h" // added by the same patch (lib/phy/metrics)
 #include "crc_calculator_clmul_impl.h"
 #include "crc_calculator_lut_impl.h"
 #include "ldpc/ldpc_decoder_avx2.h"
@@ -94,7 +96,21 @@ struct segmenter_factory_local : public ldpc_segmenter_rx_factory {
   std::unique_ptr<ldpc_segmenter_rx> create() override { return std::make_unique<ldpc_segmenter_rx_impl>(); }
 };
 
+// Collects what the HAL metric decorator of the patch reports (mode 4).
+struct metric_capture : public ldpc_decoder_metric_notifier {
+  std::atomic<uint64_t> count{0}, iterations{0}, crc_ok{0}, bits{0}, nanoseconds{0};
+  void                  on_new_metric(const ldpc_decoder_metrics& m) override
+  {
+    count++;
+    iterations += m.nof_iterations;
+    crc_ok += m.crc_ok ? 1 : 0;
+    bits += m.cb_sz.value();
+    nanoseconds += static_cast<uint64_t>(m.measurements.duration.count());
+  }
+};
+
 struct harness {
+  metric_capture                             metrics;
   std::shared_ptr<cuda::pusch_dec_context>   context;
   std::unique_ptr<rx_buffer_pool_controller> pool;
   std::unique_ptr<pusch_decoder>             decoder;
@@ -119,7 +135,7 @@ void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, i
   pool_cfg.nof_buffers          = nof_buffers;
   pool_cfg.nof_codeblocks       = nof_codeblocks;
   pool_cfg.expire_timeout_slots = 100000;
-  pool_cfg.external_soft_bits   = (mode == 3) || ((mode == 2) && (external_harq != 0));
+  pool_cfg.external_soft_bits   = (mode == 3) || ((mode == 2 || mode == 4) && (external_harq != 0));
   h->pool                       = create_rx_buffer_pool(pool_cfg);
 
   if (mode != 0) {
@@ -138,12 +154,16 @@ void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, i
     dcfg.context            = h->context;
     dcfg.generic_arithmetic = cuda_generic != 0;
     h->decoder              = create_pusch_decoder_factory_cuda(dcfg)->create();
-  } else if (mode == 2) {
+  } else if (mode == 2 || mode == 4) {
     hal::cuda_hwacc_pusch_dec_factory_configuration acfg;
     acfg.context            = h->context;
     acfg.external_harq      = external_harq != 0;
     acfg.generic_arithmetic = cuda_generic != 0;
     auto acc_factory        = hal::create_cuda_pusch_dec_acc_factory(acfg);
+    if (mode == 4) {
+      // as the patched upper_phy_factories.cpp wraps the HAL factory when metrics are enabled
+      acc_factory = create_hw_accelerator_pusch_dec_metric_decorator_factory(acc_factory, h->metrics);
+    }
     std::vector<std::unique_ptr<hal::hw_accelerator_pusch_dec>> accs;
     for (unsigned i = 0; i != 2; ++i) {
       accs.push_back(acc_factory->create());
@@ -178,6 +198,14 @@ void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, i
         std::make_unique<ldpc_segmenter_rx_impl>(), cb_pool, std::move(crcs), nullptr, MAX_RB, 4);
   }
   return h.release();
+}
+
+// Mode 4: what the metric decorator has reported so far: [code blocks, sum of iterations, CRC ok, sum of code-block bits, ns].
+void adt_metrics(void* handle, uint64_t* out)
+{
+  auto* h = static_cast<harness*>(handle);
+  out[0] = h->metrics.count, out[1] = h->metrics.iterations, out[2] = h->metrics.crc_ok, out[3] = h->metrics.bits;
+  out[4] = h->metrics.nanoseconds;
 }
 
 void adt_destroy(void* handle)

@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 HARNESS = os.path.join(HERE, "adapters", "_build", "libadapter_harness.so")
 ADAPTERS = os.path.join(HERE, "..", "srsran_project_b200", "libsrsran_cuda_adapters.so")
 
-MODE_REF, MODE_CUDA_OPERATORS, MODE_CUDA_HAL, MODE_CUDA_TB = 0, 1, 2, 3
+MODE_REF, MODE_CUDA_OPERATORS, MODE_CUDA_HAL, MODE_CUDA_TB, MODE_CUDA_HAL_METRICS = 0, 1, 2, 3, 4
 
 
 def _lib():
@@ -145,6 +145,26 @@ def test_cuda_adapters_match_reference_decoder(mode, external, generic):
                 assert st_a == st_b, (case[0], k, st_a, st_b)
                 if st_a["tb_crc_ok"]:
                     assert (tb_a == tb_b).all(), (case[0], k)
+    finally:
+        ref.close()
+        dut.close()
+
+
+@pytest.mark.gpu
+def test_hal_metric_decorator_reports_every_code_block():
+    """The decorator that integration/srsran_cuda.patch adds to the reference (lib/phy/metrics, wired in upper_phy_factories.cpp)
+    around the CUDA accelerator: same decoding results, one ldpc_decoder_metrics per decoded code block."""
+    ref, dut = Decoder(MODE_REF), Decoder(MODE_CUDA_HAL_METRICS)
+    try:
+        nof_cbs = iters_ok = 0
+        for i, case in enumerate(CASES[2:6]):
+            a, b = run_case(ref, case, harq_id=i % 4), run_case(dut, case, harq_id=i % 4)
+            assert [st for _, st in a] == [st for _, st in b], case[0]
+            nof_cbs += sum(st["nof_obs"] for _, st in b)
+        m = np.zeros(5, np.uint64)
+        dut.lib.adt_metrics.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        dut.lib.adt_metrics(dut.h, m.ctypes.data)
+        assert int(m[0]) == nof_cbs and int(m[3]) > 0 and int(m[4]) > 0 and int(m[1]) >= int(m[0]), (m, nof_cbs)
     finally:
         ref.close()
         dut.close()
