@@ -436,22 +436,22 @@ __device__ __forceinline__ void h2_edge_update(uint32_t& u, uint32_t& y, uint32_
   const uint32_t eq = h2_eq_mask(a, m1);
   const uint32_t ms = s1p ^ (d & eq);
   const uint32_t sg = h2_copysign_one(u, one);
-  const uint32_t w  = h2_add(h2_min(a, H2_120), ms);
-  const uint32_t qa = h2_add_sat(a, H2_N336);
-  const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);
-  const uint32_t g  = h2_fma(qa, H2_65504, h2_fma(qb, H2_65504, H2_ONE));
+  const uint32_t qa = h2_add_sat(a, H2_N336);                    // 1 iff u is infinite (finite |u| <= 216)
+  const uint32_t w  = h2_add(h2_fma(qa, H2_65504, h2_min(a, H2_120)), ms); // min(|u|, 120) + ms, infinite iff u is
+  const uint32_t qb = h2_fma_sat(w, H2_ONE, H2_N120);            // 1 iff w > 120 (w >= -96: no negative overflow)
+  const uint32_t sm = h2_fma(qb, H2_65504, w);                   // w, or +inf when promoted (121 + 65504 rounds to inf)
   y                 = h2_fma(ms, sg, H2_BIAS);
-  u                 = h2_fma(h2_mul(w, sg), g, H2_BIAS);
+  u                 = h2_fma(sm, sg, H2_BIAS);                   // the bias also turns a -0 product into the reference's +0
 }
 
 // One row (layer) of the decode for the lane pair of this thread. cp: the thread's packed message registers.
 //
 // Arithmetic of pass 2 in sign-normalised form (sg = sign of u as +-1, everything else is computed on magnitudes, so the
-// work is spread over both issue pipes: 4 ALU-pipe and 8 FMA-pipe instructions per edge):
+// work is spread over both issue pipes: 4 ALU-pipe and 7 FMA-pipe instructions per edge):
 //   ms = (|u| == m1 ? s2 : s1) with the sign of the row parity          (magnitude of the new message, sign-normalised)
 //   w  = min(|u|, 120) + ms                                             (sign-normalised soft value: t = sg w)
-//   g  = 1, or 65504 (+ 65504) when w > 120 or u is infinite            (qb, qa)
-//   S' = (sg w) g + 0 [+ bias]     overflow = promotion to +-inf; the + 0 turns a -0 product into the reference's +0
+//   w  becomes +inf when u is infinite (qa 65504 + 120 overflows), sm = w + qb 65504 becomes +inf when w > 120  (qa, qb)
+//   S' = sg sm + bias              overflow = promotion to +-inf; the bias turns a -0 product into the reference's +0
 //   c' = sg ms                     stored as the byte c' + 128
 template <int BG, int ZC, int M>
 __device__ __forceinline__ void h2_row(uint32_t (&cp)[h2_pack<BG>::NREG], const uint32_t* __restrict__ tab,
@@ -623,6 +623,22 @@ __device__ __forceinline__ uint32_t h2_soft_from_bytes(uint32_t w)
 {
   const uint32_t p = __byte_perm(w ^ 0x8080u, 0x64646464u, 0x4140);
   return h2_max(h2_min(p, H2_BIAS_P64), H2_BIAS_N64);
+}
+
+// True if any of the K systematic soft bits is zero (hard_decision returns false then: log_likelihood_ratio.cpp:350-376).
+// Uniform over the CTA (contains a barrier): every thread calls it.
+template <int BG, int ZC, typename TAB>
+__device__ __forceinline__ bool h2_any_zero_soft(TAB tab, uint32_t soft_t, bool active)
+{
+  uint32_t amin = H2_ONE;
+  if (active) {
+    h2_static_for<h2_graph<BG>::KB>([&](auto c_) {
+      constexpr int  c = decltype(c_)::value;
+      const uint32_t S = h2_read_natural<BG, ZC, c>(tab, soft_t);
+      amin             = h2_min(amin, h2_abs(h2_sub(S, H2_BIAS)));
+    });
+  }
+  return __syncthreads_or(((amin & 0x7fffu) == 0) || ((amin & 0x7fff0000u) == 0)) != 0;
 }
 
 template <int BG, int ZC>
@@ -826,12 +842,11 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     // ---- hard decision + CRC (ldpc_decoder_impl.cpp:127-135, log_likelihood_ratio.cpp:350-376). The CRC is linear: it is
     //      the xor of x^(n_sig - 1 - n + order) mod P over the set bits n, so every thread folds its own lane pairs, in
     //      natural order, straight from the soft rows; a zero soft bit among the K systematic ones refuses the early stop.
-    uint32_t amin = H2_ONE, acc = 0;
+    uint32_t acc = 0;
     if (active) {
       h2_static_for<G::KB>([&](auto c_) {
         constexpr int  c  = decltype(c_)::value;
         const uint32_t S  = h2_read_natural<BG, ZC, c>(tab, soft_t); // natural lanes (2 tid, 2 tid + 1) of column c
-        amin              = h2_min(amin, h2_abs(h2_sub(S, H2_BIAS)));
         const uint2 tp = __ldg(crc_pair - c * (Z >> 1)); // .x: lane 2 tid + 1, .y: lane 2 tid
         asm("{ .reg .pred p, q;\n"
             "setp.le.f16x2 p|q, %1, %2;\n"
@@ -845,14 +860,18 @@ __global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_la
     if ((tid & 31) == 0) {
       s_red[tid >> 5] = acc;
     }
-    const int bad = __syncthreads_or(((amin & 0x7fffu) == 0) || ((amin & 0x7fff0000u) == 0));
-    uint32_t  crc = 0;
+    __syncthreads();
+    uint32_t crc = 0;
     for (int w = 0; w < (nth >> 5); ++w) {
       crc ^= s_red[w];
     }
     // pusch_codeblock_decoder.cpp:62-73: without early stop there is one CRC after the last iteration and zero soft bits
-    // do not matter.
-    success = (crc == 0u) && (early ? !bad : true);
+    // do not matter. With early stop a zero among the K systematic soft bits refuses the stop: that second sweep runs only
+    // when the checksum matches, i.e. once per code block instead of once per iteration.
+    success = (crc == 0u);
+    if (success && early) {
+      success = !h2_any_zero_soft<BG, ZC>(tab, soft_t, active);
+    }
   }
 
   // ---- output ------------------------------------------------------------------------------------------------------------------

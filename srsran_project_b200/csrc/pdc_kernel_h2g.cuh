@@ -441,12 +441,11 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
       continue;
     }
     // ---- hard decision + CRC, as in pdc_kernel_h2.cuh -------------------------------------------------------------------------
-    uint32_t amin = H2_ONE, acc = 0;
+    uint32_t acc = 0;
     if (active) {
       h2_static_for<G::KB>([&](auto c_) {
         constexpr int  c = decltype(c_)::value;
         const uint32_t S = h2_read_natural<BG, 0, c>(s_tab, soft_t);
-        amin             = h2_min(amin, h2_abs(h2_sub(S, H2_BIAS)));
         const uint2 tp   = __ldg(crc_pair - c * (Z >> 1));
         asm("{ .reg .pred p, q;\n"
             "setp.le.f16x2 p|q, %1, %2;\n"
@@ -460,12 +459,15 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
     if ((tid & 31) == 0) {
       s_red[tid >> 5] = acc;
     }
-    const int bad = __syncthreads_or(((amin & 0x7fffu) == 0) || ((amin & 0x7fff0000u) == 0));
-    uint32_t  crc = 0;
+    __syncthreads();
+    uint32_t crc = 0;
     for (int w = 0; w < (nth >> 5); ++w) {
       crc ^= s_red[w];
     }
-    success = (crc == 0u) && (early ? !bad : true);
+    success = (crc == 0u);
+    if (success && early) { // the zero-soft-bit sweep only when the checksum matches (see pdc_kernel_h2.cuh)
+      success = !h2_any_zero_soft<BG, 0>(s_tab, soft_t, active);
+    }
   }
 
   // ---- output (as in pdc_kernel_h2.cuh) -----------------------------------------------------------------------------------------

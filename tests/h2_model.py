@@ -59,15 +59,16 @@ def decode(graph_rows, Z, llrs, K, n_layers, max_iter, generic=False, check=None
                 mag = np.where(a[k] == m1, s2, s1)
                 ms = np.where(par, -mag, mag).astype(F16)                       # magnitude of the new message, row-parity sign
                 sg = np.where(sign(u[k]), F16(-1.0), F16(1.0)).astype(F16)       # copysign(1, u)
-                w = (np.minimum(a[k], F16(120.0)) + ms).astype(F16)
                 with np.errstate(invalid="ignore"):
                     qa = np.clip(a[k].astype(np.float64) - 336.0, 0.0, 1.0).astype(F16)  # 1 iff u is infinite
-                qb = np.clip(w.astype(np.float64) - 120.0, 0.0, 1.0).astype(F16)          # 1 iff w > 120
-                G = fma16(qa, F16(65504.0), fma16(qb, F16(65504.0), 1.0))
-                cn = (ms.astype(np.float64) * sg.astype(np.float64)).astype(F16)          # may be -0: harmless
-                t = (w.astype(np.float64) * sg.astype(np.float64)).astype(F16)
+                w0 = fma16(qa, F16(65504.0), np.minimum(a[k], F16(120.0)))                # min(|u|, 120), +inf iff u is infinite
                 with np.errstate(over="ignore"):
-                    Snew = (t.astype(np.float64) * G.astype(np.float64) + 0.0).astype(F16)  # + 0: a -0 product becomes +0
+                    w = (w0.astype(np.float64) + ms.astype(np.float64)).astype(F16)
+                qb = np.clip(w.astype(np.float64) - 120.0, 0.0, 1.0).astype(F16)          # 1 iff w > 120 (also when w is +inf)
+                sm = fma16(qb, F16(65504.0), w)                                            # w, or +inf: 121 + 65504 rounds to inf
+                cn = (ms.astype(np.float64) * sg.astype(np.float64)).astype(F16)          # may be -0: harmless
+                # the kernel adds the storage bias in the same fused operation, which turns a -0 product into +0
+                Snew = (fma16(sm, sg, 1152.0).astype(np.float64) - 1152.0).astype(F16)
                 c2v[m][k] = cn
                 soft[c] = np.roll(Snew, s)
         if check is not None and check(it + 1, soft):
