@@ -311,7 +311,8 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   if (n > ctx->cfg.max_batch_cbs || llr_bytes > ctx->cfg.max_batch_llrs || ntb > ctx->cfg.max_batch_cbs) {
     return PDC_ERR_CAPACITY;
   }
-  ticket_t* t = reserve_ticket(ctx);
+  nvtx_scope range(tbs ? "pdc_submit_tbs" : "pdc_submit");
+  ticket_t*  t = reserve_ticket(ctx);
   if (!t) {
     return PDC_ERR_CAPACITY;
   }
@@ -526,6 +527,7 @@ pdc_status pdc_fetch_tbs(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* tb_bytes, siz
   if (!ctx || !tb_res) {
     return PDC_ERR_INVALID_ARG;
   }
+  nvtx_scope range("pdc_fetch_tbs");
   ticket_t*  t;
   pdc_status st = wait_ticket(ctx, ticket, true, t);
   if (st != PDC_OK) {
@@ -563,6 +565,7 @@ pdc_status pdc_fetch(pdc_ctx* ctx, pdc_ticket ticket, uint8_t* bits, size_t bits
   if (!ctx || !res) {
     return PDC_ERR_INVALID_ARG;
   }
+  nvtx_scope range("pdc_fetch");
   ticket_t*  t;
   pdc_status st = wait_ticket(ctx, ticket, false, t);
   if (st != PDC_OK) {
@@ -604,6 +607,7 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
   if (n > ctx->cfg.max_batch_cbs || ntb > ctx->cfg.max_batch_cbs) {
     return PDC_ERR_CAPACITY;
   }
+  nvtx_scope   range(tbs ? "pdc_decode_device_tbs" : "pdc_decode_device");
   cudaStream_t stream = (cudaStream_t)stream_v;
   // The descriptor staging of a free ticket is borrowed for the duration of the launch (stream-ordered).
   ticket_t* t = reserve_ticket(ctx);

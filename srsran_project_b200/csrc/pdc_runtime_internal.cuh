@@ -7,6 +7,7 @@
 // arena slots; hw_accelerator_pusch_dec.h:83-115, ext_harq_buffer_context_repository.h:36-107).
 #include "ldpc_bg_tables.h"
 #include "pdc_device.cuh"
+#include <nvtx3/nvToolsExt.h> // header-only: ranges cost nothing unless a profiler is attached
 #include <atomic>
 #include <cstddef>
 #include <cstdio>
@@ -37,6 +38,13 @@ extern "C" cudaError_t pdc_launch_tb(const pdc_dev_tb* d_tbs, const pdc_dev_cb* 
                                      int max_cbs, cudaStream_t stream);
 
 namespace {
+
+// NVTX range for the lifetime of a scope: the CUDA counterpart of the trace events the reference emits around its code-block
+// tasks (pusch_decoder_impl.cpp:332,381 "cb_decode"); visible in Nsight Systems timelines next to the kernels and copies.
+struct nvtx_scope {
+  explicit nvtx_scope(const char* name) { nvtxRangePushA(name); }
+  ~nvtx_scope() { nvtxRangePop(); }
+};
 
 struct ticket_t {
   cudaStream_t stream   = nullptr;
@@ -550,6 +558,7 @@ pdc_status plan_tbs(const pdc_tb_desc* tbs, uint32_t ntb, const pdc_cb_desc* des
 pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_cbs, const uint32_t* d_order,
                         cudaStream_t stream)
 {
+  nvtx_scope        range("pdc: code-block kernels");
   pdc_launch_params prm;
   prm.cbs     = d_cbs;
   prm.graphs  = ctx->d_graphs;
