@@ -575,11 +575,21 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
     side_lock.lock(); // streams and events were created by pdc_create: nothing is allocated on the data path
     CK(cudaEventRecord(ctx->side_fork, stream));
   }
-  uint32_t off = 0;
-  int      used = 0; // lists launched so far: list 0 stays on the caller's stream
-  auto     stream_of = [&](int idx) -> cudaStream_t { return (idx == 0) ? stream : ctx->side_stream[idx - 1]; };
+  uint32_t offs[PDC_NOF_LISTS], acc = 0; // position of every list in the order array
   for (int k = 0; k != PDC_NOF_LISTS; ++k) {
+    offs[k] = acc;
+    acc += (k < PDC_NOF_PACKED_LISTS) ? bp.n_h2[k] : bp.n_lane;
+  }
+  int  used = 0; // lists launched so far: the first one stays on the caller's stream
+  auto stream_of = [&](int idx) -> cudaStream_t { return (idx == 0) ? stream : ctx->side_stream[idx - 1]; };
+  // Longest critical path first: the one-lane kernel (a code block is one to twelve warps running every row in sequence), then
+  // the many-layer kernel, then the four-row kernels. Whoever is launched first gets its thread blocks resident first; the
+  // many-layer kernel fills the register file (2 x 192 x 168) and would otherwise keep the one-lane kernel waiting.
+  static const int launch_order[PDC_NOF_LISTS] = {PDC_NOF_PACKED_LISTS, 4, 5, 0, 1, 2, 3};
+  for (int q = 0; q != PDC_NOF_LISTS; ++q) {
+    const int      k   = launch_order[q];
     const uint32_t cnt = (k < PDC_NOF_PACKED_LISTS) ? bp.n_h2[k] : bp.n_lane;
+    const uint32_t off = offs[k];
     if (cnt == 0) {
       continue;
     }
@@ -601,7 +611,6 @@ pdc_status launch_batch(pdc_ctx* ctx, const batch_plan& bp, const pdc_dev_cb* d_
       CK(cudaEventRecord(ctx->side_join[used - 1], s));
       CK(cudaStreamWaitEvent(stream, ctx->side_join[used - 1], 0));
     }
-    off += cnt;
     ++used;
   }
   return PDC_OK;

@@ -212,11 +212,15 @@ def main():
     ap.add_argument("--sigma1", type=float, default=3.0)
     ap.add_argument("--sigma2", type=float, default=6.0)
     ap.add_argument("--tbs", type=int, default=8, help="config 4: transport blocks in the batch")
+    ap.add_argument("--only", type=int, default=0, help="3 or 4: run that configuration alone")
+    ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     from tools import stimulus as S
 
-    print(json.dumps(config3(S, args.steps)), flush=True)
-    print(json.dumps(config4(S, args.steps, args.sigma1, args.sigma2, args.tbs)), flush=True)
+    if args.only in (0, 3):
+        print(json.dumps(config3(S, args.steps, cpu=not args.no_cpu)), flush=True)
+    if args.only in (0, 4):
+        print(json.dumps(config4(S, args.steps, args.sigma1, args.sigma2, args.tbs, cpu=not args.no_cpu)), flush=True)
 
 
 if __name__ == "__main__":
