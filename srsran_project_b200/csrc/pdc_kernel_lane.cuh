@@ -13,6 +13,46 @@
 #pragma once
 #include "pdc_device.cuh"
 
+// One row (layer) for one lane. The edges of a row are independent until the two minima: with the degree as a template
+// parameter every load of the row is issued before the first result is needed, and the variable-to-check messages stay in
+// registers for the second pass. A code block of a small lifting size is ONE warp running up to 46 x 6 rows in sequence: its
+// latency per row is what a mixed batch waits for. Row degrees: 3..10 and 19 (ldpc_bg_tables.h).
+template <int DEG>
+__device__ __forceinline__ void pdc_lane_row(const uint32_t* __restrict__ graph, int8_t* __restrict__ soft, int8_t* __restrict__ c2v,
+                                             int Z, int tid, bool first, bool generic)
+{
+  int v[DEG], sidx[DEG];
+#pragma unroll
+  for (int e = 0; e < DEG; ++e) {
+    const uint32_t ent = graph[e];
+    int            j   = tid + (int)(ent >> 8);
+    j -= (j >= Z) ? Z : 0;
+    sidx[e]     = (int)(ent & 0xff) * Z + j;
+    const int s = soft[sidx[e]];
+    const int c = first ? 0 : c2v[e * Z + tid];
+    v[e]        = pdc_v2c(s, c);
+  }
+  int min1 = PDC_LLR_MAX, min2 = PDC_LLR_MAX, arg = 0, par = 0;
+#pragma unroll
+  for (int e = 0; e < DEG; ++e) {
+    const int  a      = abs(v[e]);
+    const bool is_min = a < min1;
+    const int  nsec   = is_min ? min1 : a;
+    min2              = (a < min2) ? nsec : min2;
+    arg               = is_min ? e : arg;
+    min1              = is_min ? a : min1;
+    par ^= (v[e] < 0);
+  }
+  const int s1 = pdc_scale(min1, generic), s2 = pdc_scale(min2, generic);
+#pragma unroll
+  for (int e = 0; e < DEG; ++e) {
+    const int mag    = (e == arg) ? s2 : s1;
+    const int nc     = (par ^ (v[e] < 0)) ? -mag : mag;
+    c2v[e * Z + tid] = (int8_t)nc;
+    soft[sidx[e]]    = (int8_t)pdc_soft_update(v[e], nc);
+  }
+}
+
 __global__ void __launch_bounds__(384) pdc_cb_kernel_lane(pdc_launch_params prm)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -146,36 +186,25 @@ __global__ void __launch_bounds__(384) pdc_cb_kernel_lane(pdc_launch_params prm)
   for (int it = 0; it < max_iter && !success; ++it) {
     for (int m = 0; m < L; ++m) {
       if (tid < Z) {
-        const int e0 = row_start[m], deg = row_deg[m];
-        int       min1 = PDC_LLR_MAX, min2 = PDC_LLR_MAX, arg = 0, par = 0;
-        for (int e = 0; e < deg; ++e) {
-          uint32_t ent = s_graph[e0 + e];
-          int      j   = tid + (int)(ent >> 8);
-          j -= (j >= Z) ? Z : 0;
-          int s = soft[(ent & 0xff) * Z + j];
-          int c = (it == 0) ? 0 : c2v[(e0 + e) * Z + tid];
-          int v = pdc_v2c(s, c);
-          int a = abs(v);
-          bool is_min = a < min1;
-          int  nsec   = is_min ? min1 : a;
-          min2        = (a < min2) ? nsec : min2;
-          arg         = is_min ? e : arg;
-          min1        = is_min ? a : min1;
-          par ^= (v < 0);
-        }
-        const int s1 = pdc_scale(min1, generic), s2 = pdc_scale(min2, generic);
-        for (int e = 0; e < deg; ++e) {
-          uint32_t ent = s_graph[e0 + e];
-          int      j   = tid + (int)(ent >> 8);
-          j -= (j >= Z) ? Z : 0;
-          int8_t* sp = &soft[(ent & 0xff) * Z + j];
-          int8_t* cp = &c2v[(e0 + e) * Z + tid];
-          int     c  = (it == 0) ? 0 : *cp;
-          int     v  = pdc_v2c(*sp, c);
-          int     mag = (e == arg) ? s2 : s1;
-          int     nc  = (par ^ (v < 0)) ? -mag : mag;
-          *cp         = (int8_t)nc;
-          *sp         = (int8_t)pdc_soft_update(v, nc);
+        // The degree is uniform over the thread block: one fully unrolled body per degree (see pdc_lane_row).
+        const int e0 = row_start[m];
+        switch (row_deg[m]) {
+#define PDC_LANE_CASE(D)                                                                                               \
+  case D:                                                                                                              \
+    pdc_lane_row<D>(s_graph + e0, soft, c2v + e0 * Z, Z, tid, it == 0, generic);                                          \
+    break;
+          PDC_LANE_CASE(3)
+          PDC_LANE_CASE(4)
+          PDC_LANE_CASE(5)
+          PDC_LANE_CASE(6)
+          PDC_LANE_CASE(7)
+          PDC_LANE_CASE(8)
+          PDC_LANE_CASE(9)
+          PDC_LANE_CASE(10)
+          default:
+            pdc_lane_row<19>(s_graph + e0, soft, c2v + e0 * Z, Z, tid, it == 0, generic);
+            break;
+#undef PDC_LANE_CASE
         }
       }
       __syncthreads();
