@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 7
+#define PDC_ABI_VERSION 8
 
 typedef enum {
   PDC_OK               = 0,
@@ -147,6 +147,20 @@ int         pdc_abi_version(void);
  * (see there). Returns PDC_ERR_CAPACITY when every ticket is in flight: back-pressure, not a failure; retry. */
 pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const int8_t* llrs, size_t llr_bytes,
                       const int8_t* soft_in, size_t soft_bytes, pdc_ticket* ticket);
+/* Staged submission: a staging arena is page-locked host memory mirrored 1:1 by device memory, with a copy stream of its own.
+ * Its users (the accelerator objects of the reference's pools, through the adapters' batcher) write a transport block's LLRs
+ * into a region of the host side and push the region as soon as it is complete; the submission that later decodes it
+ * (pdc_submit_staged: desc.llr_offset relative to the arena) only waits for what has been pushed — the host-to-device copy
+ * of a batch overlaps the time its other members are still being filled. The bbdev counterpart is the mbuf pool an
+ * accelerator enqueues from (hw_accelerator_factories.h:33-51). A region must not be rewritten before the submission that
+ * used it has completed. */
+typedef struct pdc_stage pdc_stage;
+pdc_status pdc_stage_open(pdc_ctx* ctx, size_t bytes, pdc_stage** out);
+void       pdc_stage_close(pdc_stage* stage);
+int8_t*    pdc_stage_host(pdc_stage* stage);                                /* host side of the arena */
+pdc_status pdc_stage_push(pdc_stage* stage, size_t offset, size_t bytes);   /* asynchronous host-to-device copy of a region */
+pdc_status pdc_submit_staged(pdc_ctx* ctx, pdc_stage* stage, const pdc_cb_desc* descs, uint32_t n, const int8_t* soft_in,
+                             size_t soft_bytes, pdc_ticket* ticket);        /* then pdc_poll / pdc_fetch as usual */
 /* PDC_OK when the batch has completed, PDC_ERR_NOT_READY otherwise. */
 pdc_status pdc_poll(pdc_ctx* ctx, pdc_ticket ticket);
 /* Blocks until done, then scatters the packed bits to bits + desc.out_offset, the results to res[0..n) and, for CBs

@@ -11,21 +11,15 @@ using namespace srsran::cuda;
 using clk = std::chrono::steady_clock;
 
 struct pusch_dec_batcher::batch {
-  enum class st { idle, open, closing, inflight, fetching, done };
+  enum class st { idle, busy, done };
   st                         state = st::idle;
-  std::vector<part>          parts;
-  unsigned                   joined = 0, sealed = 0, released = 0;
-  unsigned                   cb_reserved = 0;
-  size_t                     llr_reserved = 0;
-  bool                       full   = false; // a joiner did not fit: close as soon as every part is sealed
-  bool                       failed = false;
-  int8_t*                    llrs   = nullptr; // page-locked, batch_llrs bytes
+  std::vector<part*>         members;
+  unsigned                   released = 0;
   std::vector<pdc_cb_desc>   descs;
   std::vector<pdc_cb_result> results;
   std::vector<uint8_t>       bits;
   std::vector<int8_t>        soft;
   pdc_ticket                 ticket = 0;
-  clk::time_point            opened;
 };
 
 pusch_dec_batcher::pusch_dec_batcher(std::shared_ptr<pusch_dec_context> context, const pusch_dec_batcher_config& cfg_) :
@@ -36,18 +30,26 @@ pusch_dec_batcher::pusch_dec_batcher(std::shared_ptr<pusch_dec_context> context,
   }
   const pusch_dec_context_config& c = ctx->config();
   batch_cbs                         = c.max_batch_cbs;
-  batch_llrs                        = c.max_batch_llrs;
   cfg.max_parts                     = std::max(1u, cfg.max_parts);
   cfg.nof_batches                   = std::max(1u, std::min(cfg.nof_batches, c.nof_instances));
-  // LLRs already lie in page-locked memory when the batch is submitted: the DMA engine reads them from there.
-  pdc_set_zero_copy(ctx->get(), 1);
+  cfg.eager_inflight = std::max(1u, cfg.eager_inflight);
+  // One region per part; a region holds what one part may bring: the context's batch capacity shared out over max_parts, but
+  // never less than the largest rate-matched code block (35 x 8448 soft bits: ldpc.h MAX_CODEBLOCK_RM_SIZE).
+  part_bytes = std::max<size_t>(c.max_batch_llrs / cfg.max_parts, 35u * 8448u + 64u);
+  part_bytes = (part_bytes + 255) & ~(size_t)255;
+  // Parts being filled + ready + in flight: two generations per batch buffer.
+  const unsigned nof_parts = 2 * cfg.max_parts * cfg.nof_batches;
+  if (pdc_stage_open(ctx->get(), part_bytes * nof_parts, &stage) != PDC_OK) {
+    throw std::runtime_error(std::string("pusch_dec_batcher: staging arena could not be allocated: ") + pdc_last_error(ctx->get()));
+  }
+  parts.resize(nof_parts);
+  int8_t* base = pdc_stage_host(stage);
+  for (unsigned i = 0; i != nof_parts; ++i) {
+    parts[i].llrs     = base + (size_t)i * part_bytes;
+    parts[i].llr_base = (size_t)i * part_bytes;
+  }
   for (unsigned i = 0; i != cfg.nof_batches; ++i) {
     auto b = std::make_unique<batch>();
-    b->parts.resize(cfg.max_parts);
-    b->llrs = static_cast<int8_t*>(pdc_host_alloc(batch_llrs));
-    if (!b->llrs) {
-      throw std::runtime_error("pusch_dec_batcher: page-locked staging could not be allocated");
-    }
     b->descs.reserve(batch_cbs);
     b->results.resize(batch_cbs);
     b->bits.resize((size_t)batch_cbs * BITS_STRIDE);
@@ -57,19 +59,14 @@ pusch_dec_batcher::pusch_dec_batcher(std::shared_ptr<pusch_dec_context> context,
 
 pusch_dec_batcher::~pusch_dec_batcher()
 {
-  for (auto& b : batches) {
-    if (b->state == batch::st::inflight) {
-      // Drain: the staging must not go away under a running copy.
-      pdc_fetch(ctx->get(), b->ticket, b->bits.data(), b->bits.size(), b->results.data(), nullptr, 0);
-    }
-    pdc_host_free(b->llrs);
-  }
+  // Every user holds a shared_ptr to the batcher: nothing is in flight any more when the last one lets go.
+  pdc_stage_close(stage);
 }
 
 pusch_dec_batcher::part* pusch_dec_batcher::join(unsigned max_cbs, size_t max_llr_bytes, unsigned wait_us)
 {
   max_cbs       = std::max(1u, std::min(max_cbs, batch_cbs));
-  max_llr_bytes = std::min((max_llr_bytes + 15) & ~(size_t)15, batch_llrs & ~(size_t)15);
+  max_llr_bytes = std::min((max_llr_bytes + 15) & ~(size_t)15, part_bytes);
   std::unique_lock<std::mutex> lock(mtx);
   for (int attempt = 0; attempt != 2; ++attempt) {
     part* p = join_locked(max_cbs, max_llr_bytes);
@@ -83,54 +80,27 @@ pusch_dec_batcher::part* pusch_dec_batcher::join(unsigned max_cbs, size_t max_ll
 
 pusch_dec_batcher::part* pusch_dec_batcher::join_locked(unsigned max_cbs, size_t max_llr_bytes)
 {
-  if (open && (open->joined == cfg.max_parts || open->cb_reserved + max_cbs > batch_cbs ||
-               open->llr_reserved + max_llr_bytes > batch_llrs)) {
-    open->full = true;
-    open       = nullptr;
-  }
-  if (!open) {
-    for (auto& b : batches) {
-      if (b->state == batch::st::done && b->released == b->joined) {
-        b->state = batch::st::idle; // wound up by its driver after every part had already been released
-        b->soft.clear();
-      }
-      if (b->state == batch::st::idle) {
-        open           = b.get();
-        open->state    = batch::st::open;
-        open->joined   = open->sealed = open->released = 0;
-        open->cb_reserved  = 0;
-        open->llr_reserved = 0;
-        open->full = open->failed = false;
-        open->opened = clk::now();
-        break;
-      }
-    }
-    if (!open) {
-      return nullptr;
+  for (part& p : parts) {
+    if (p.state == part::st::idle) {
+      p.state    = part::st::filling;
+      p.owner    = nullptr;
+      p.llr_cap  = max_llr_bytes;
+      p.llr_used = 0;
+      p.cb_cap   = max_cbs;
+      p.descs.clear();
+      p.soft.clear();
+      p.index.clear();
+      return &p;
     }
   }
-  part& p    = open->parts[open->joined++];
-  p.owner    = open;
-  p.llrs     = open->llrs + open->llr_reserved;
-  p.llr_base = open->llr_reserved;
-  p.llr_cap  = max_llr_bytes;
-  p.llr_used = 0;
-  p.cb_cap   = max_cbs;
-  p.index.clear();
-  p.sealed   = false;
-  p.in_use   = true;
-  p.descs.clear();
-  p.soft.clear();
-  open->cb_reserved += max_cbs;
-  open->llr_reserved += max_llr_bytes;
-  return &p;
+  return nullptr;
 }
 
 bool pusch_dec_batcher::add(part* p, pdc_cb_desc d, const int8_t* llrs, size_t nof_llrs, const int8_t* soft_in, size_t nof_soft)
 {
-  // Only the owning thread touches an unsealed part: no lock.
+  // Only the owning thread touches a part that is being filled: no lock.
   const size_t off = (p->llr_used + 15) & ~(size_t)15;
-  if (p->sealed || p->descs.size() >= p->cb_cap || off + nof_llrs > p->llr_cap) {
+  if (p->state != part::st::filling || p->descs.size() >= p->cb_cap || off + nof_llrs > p->llr_cap) {
     return false;
   }
   // A descriptor the runtime would reject (the reference's srsran_assert contracts) must not take the other callers' code
@@ -158,119 +128,130 @@ bool pusch_dec_batcher::add(part* p, pdc_cb_desc d, const int8_t* llrs, size_t n
 
 void pusch_dec_batcher::seal(part* p)
 {
+  if (p->state != part::st::filling) {
+    return;
+  }
+  // The region travels to the device now, while the other members of its future batch are still being filled.
+  pdc_stage_push(stage, p->llr_base, p->llr_used);
   std::lock_guard<std::mutex> lock(mtx);
-  if (!p->sealed) {
-    p->sealed = true;
-    p->owner->sealed++;
+  p->state     = part::st::ready;
+  p->sealed_at = clk::now();
+  ready.push_back(p);
+}
+
+void pusch_dec_batcher::fail_batch(batch* b)
+{
+  for (size_t k = 0; k != b->descs.size(); ++k) {
+    b->results[k].iterations = -1, b->results[k].crc_pass = 0, b->results[k].status = 1, b->results[k].nof_layers = 0;
   }
 }
 
-void pusch_dec_batcher::try_advance(batch* b, std::unique_lock<std::mutex>& lock)
+// Forms a batch from the ready parts if the closing condition holds, runs it and waits for it (lock released meanwhile).
+// Returns true if a batch was run.
+bool pusch_dec_batcher::try_form(std::unique_lock<std::mutex>& lock)
 {
-  if (b->state == batch::st::open && b->sealed == b->joined && b->joined != 0) {
-    const bool timeout = clk::now() - b->opened >= std::chrono::microseconds(cfg.close_after_us);
-    if (!(b->full || b->joined == cfg.max_parts || inflight == 0 || timeout)) {
-      return;
-    }
-    b->state = batch::st::closing;
-    if (open == b) {
-      open = nullptr;
-    }
-    ++inflight;
-    // One descriptor array over all parts; outputs and host soft buffers at fixed strides.
-    b->descs.clear();
-    size_t nsoft = 0, llr_end = 0;
-    for (unsigned i = 0; i != b->joined; ++i) {
-      part&  p  = b->parts[i];
-      size_t ps = 0;
-      for (size_t k = 0; k != p.descs.size(); ++k) {
-        if (p.index[k] < 0) {
-          continue;
-        }
-        pdc_cb_desc d = p.descs[k];
-        p.index[k]    = (int)b->descs.size();
-        d.out_offset  = b->descs.size() * BITS_STRIDE;
-        if (d.harq_slot < 0 && !(d.flags & PDC_F_DECODE_ONLY)) {
-          d.soft_offset = nsoft * SOFT_STRIDE;
-          if (b->soft.size() < (nsoft + 1) * SOFT_STRIDE) {
-            b->soft.resize((nsoft + 1) * SOFT_STRIDE);
-          }
-          std::memcpy(b->soft.data() + d.soft_offset, p.soft.data() + ps, SOFT_STRIDE);
-          ps += SOFT_STRIDE;
-          ++nsoft;
-        }
-        b->descs.push_back(d);
-      }
-      llr_end = std::max(llr_end, p.llr_base + p.llr_used);
-    }
-    const unsigned n = (unsigned)b->descs.size();
-    stat_batches++;
-    stat_cbs += n;
-    lock.unlock();
-    pdc_status st = PDC_OK;
-    if (n != 0) {
-      while ((st = pdc_submit(ctx->get(), b->descs.data(), n, b->llrs, llr_end, nsoft ? b->soft.data() : nullptr,
-                              nsoft * SOFT_STRIDE, &b->ticket)) == PDC_ERR_CAPACITY) {
-        std::this_thread::yield(); // every ticket of the context is in flight (other users of the context)
-      }
-    }
-    lock.lock();
-    if (st != PDC_OK || n == 0) {
-      if (st != PDC_OK) {
-        std::fprintf(stderr, "pusch_dec_batcher: batch of %u code blocks failed (status %d: %s)\n", n, (int)st,
-                     pdc_last_error(ctx->get()));
-      }
-      for (unsigned k = 0; k != n; ++k) {
-        b->results[k].iterations = -1, b->results[k].crc_pass = 0, b->results[k].status = 1, b->results[k].nof_layers = 0;
-      }
-      b->failed = st != PDC_OK;
-      b->state  = batch::st::done;
-      --inflight;
-      cv.notify_all();
-      return;
-    }
-    b->state = batch::st::inflight;
+  if (ready.empty()) {
+    return false;
   }
-  if (b->state == batch::st::inflight) {
-    // The thread that gets here first waits for the device on behalf of every part of the batch (pdc_fetch blocks on the
-    // ticket's event); the others sleep in poll().
-    b->state = batch::st::fetching;
-    lock.unlock();
-    const unsigned n   = (unsigned)b->descs.size();
-    const bool     any = !b->soft.empty();
-    pdc_status     st  = pdc_fetch(ctx->get(), b->ticket, b->bits.data(), b->bits.size(), b->results.data(),
-                              any ? b->soft.data() : nullptr, b->soft.size());
-    lock.lock();
+  const bool timeout = clk::now() - ready.front()->sealed_at >= std::chrono::microseconds(cfg.close_after_us);
+  if (!(ready.size() >= cfg.max_parts || inflight < cfg.eager_inflight || timeout)) {
+    return false;
+  }
+  batch* b = nullptr;
+  for (auto& cand : batches) {
+    if (cand->state == batch::st::idle) {
+      b = cand.get();
+      break;
+    }
+  }
+  if (!b) {
+    return false; // every result buffer is still being read by its parts' owners
+  }
+  // Oldest parts first, as many as fit.
+  b->state = batch::st::busy;
+  b->members.clear();
+  b->released = 0;
+  b->descs.clear();
+  size_t nsoft = 0;
+  size_t taken = 0;
+  while (taken != ready.size() && b->members.size() != cfg.max_parts) {
+    part* p = ready[taken];
+    if (b->descs.size() + p->descs.size() > batch_cbs && !b->members.empty()) {
+      break;
+    }
+    size_t ps = 0;
+    for (size_t k = 0; k != p->descs.size(); ++k) {
+      if (p->index[k] < 0) {
+        continue;
+      }
+      pdc_cb_desc d = p->descs[k];
+      p->index[k]   = (int)b->descs.size();
+      d.out_offset  = b->descs.size() * BITS_STRIDE;
+      if (d.harq_slot < 0 && !(d.flags & PDC_F_DECODE_ONLY)) {
+        d.soft_offset = nsoft * SOFT_STRIDE;
+        if (b->soft.size() < (nsoft + 1) * SOFT_STRIDE) {
+          b->soft.resize((nsoft + 1) * SOFT_STRIDE);
+        }
+        std::memcpy(b->soft.data() + d.soft_offset, p->soft.data() + ps, SOFT_STRIDE);
+        ps += SOFT_STRIDE;
+        ++nsoft;
+      }
+      b->descs.push_back(d);
+    }
+    p->state = part::st::inflight;
+    p->owner = b;
+    b->members.push_back(p);
+    ++taken;
+  }
+  ready.erase(ready.begin(), ready.begin() + taken);
+  const unsigned n = (unsigned)b->descs.size();
+  ++inflight;
+  stat_batches++;
+  stat_cbs += n;
+  lock.unlock();
+
+  pdc_status st = PDC_OK;
+  if (n != 0) {
+    while ((st = pdc_submit_staged(ctx->get(), stage, b->descs.data(), n, nsoft ? b->soft.data() : nullptr, nsoft * SOFT_STRIDE,
+                                   &b->ticket)) == PDC_ERR_CAPACITY) {
+      std::this_thread::yield(); // every ticket of the context is in flight (other users of the context)
+    }
+    if (st == PDC_OK) {
+      st = pdc_fetch(ctx->get(), b->ticket, b->bits.data(), b->bits.size(), b->results.data(), nsoft ? b->soft.data() : nullptr,
+                     b->soft.size());
+    }
     if (st != PDC_OK) {
-      std::fprintf(stderr, "pusch_dec_batcher: fetch of %u code blocks failed (status %d: %s)\n", n, (int)st,
+      std::fprintf(stderr, "pusch_dec_batcher: batch of %u code blocks failed (status %d: %s)\n", n, (int)st,
                    pdc_last_error(ctx->get()));
-      for (unsigned k = 0; k != n; ++k) {
-        b->results[k].iterations = -1, b->results[k].crc_pass = 0, b->results[k].status = 1, b->results[k].nof_layers = 0;
-      }
-      b->failed = true;
+      fail_batch(b);
     }
-    b->state = batch::st::done;
-    --inflight;
-    cv.notify_all();
   }
+
+  lock.lock();
+  for (part* p : b->members) {
+    p->state = part::st::done;
+  }
+  b->state = batch::st::done;
+  --inflight;
+  cv.notify_all();
+  return true;
 }
 
 pusch_dec_batcher::status pusch_dec_batcher::poll(part* p, unsigned wait_us)
 {
   std::unique_lock<std::mutex> lock(mtx);
-  batch*                       b = p->owner;
-  if (b->state != batch::st::done) {
-    try_advance(b, lock);
+  if (p->state == part::st::ready) {
+    try_form(lock); // may run a batch (this part's or, when more parts are ready than a batch takes, an older one)
   }
-  if (b->state != batch::st::done && wait_us != 0) {
-    // Woken when any batch completes (this one, or the one whose completion lets this one close: "device idle"); the
-    // time-out covers the closing deadline of an open batch.
+  if (p->state != part::st::done && wait_us != 0) {
+    // Woken when any batch completes (this part's, or the one whose completion makes the device idle so that the next may
+    // form); the time-out covers the closing deadline of the ready queue.
     cv.wait_for(lock, std::chrono::microseconds(wait_us));
-    if (b->state != batch::st::done) {
-      try_advance(b, lock);
+    if (p->state == part::st::ready) {
+      try_form(lock);
     }
   }
-  return (b->state == batch::st::done) ? status::done : status::pending;
+  return (p->state == part::st::done) ? status::done : status::pending;
 }
 
 const pdc_cb_result& pusch_dec_batcher::result(const part* p, unsigned k) const
@@ -286,38 +267,31 @@ const uint8_t* pusch_dec_batcher::bits(const part* p, unsigned k) const
 
 const int8_t* pusch_dec_batcher::soft(const part* p, unsigned k) const
 {
-  // rejected code block: the caller's own buffer content is what it gets back (part::soft holds what it sent)
+  // rejected code block: nothing came back (the caller keeps its own buffer content)
   return (p->index[k] < 0) ? nullptr : p->owner->soft.data() + p->owner->descs[p->index[k]].soft_offset;
 }
 
 void pusch_dec_batcher::release(part* p)
 {
-  std::lock_guard<std::mutex> lock(mtx);
-  batch*                      b = p->owner;
-  p->in_use                     = false;
-  if (!p->sealed) { // abandoned before it was sealed (reserve_queue / free_queue without operations): counts as empty
-    p->sealed = true;
-    p->descs.clear();
-    b->sealed++;
+  std::unique_lock<std::mutex> lock(mtx);
+  if (p->state == part::st::ready) {
+    // Abandoned after sealing (free_queue without dequeuing): take it out of the queue.
+    ready.erase(std::remove(ready.begin(), ready.end(), p), ready.end());
   }
-  if (++b->released != b->joined) {
-    return;
+  while (p->state == part::st::inflight) {
+    cv.wait(lock); // abandoned while its batch runs: the region must not be reused under the copy / the kernels
   }
-  // Every part has been handed back. Normally the batch is done; parts abandoned before their results were fetched
-  // (free_queue without dequeuing) leave it open or in flight: nobody will poll it again, so it is wound up here.
-  if (b->state == batch::st::open) {
-    if (open == b) {
-      open = nullptr;
+  if (p->state == part::st::done) {
+    batch* b = p->owner;
+    if (++b->released == b->members.size()) {
+      b->state = batch::st::idle;
+      b->soft.clear();
     }
-  } else if (b->state == batch::st::inflight) {
-    pdc_fetch(ctx->get(), b->ticket, b->bits.data(), b->bits.size(), b->results.data(), nullptr, 0);
-    --inflight;
-  } else if (b->state != batch::st::done) {
-    return; // closing / fetching: the thread that is driving the batch finishes it; the next join finds it done + released
   }
-  b->state = batch::st::idle;
-  b->soft.clear();
+  p->state = part::st::idle;
+  p->owner = nullptr;
   cv_room.notify_all();
+  cv.notify_all(); // a batch buffer may have become free: a ready queue that was waiting for one can form now
 }
 
 uint64_t pusch_dec_batcher::nof_batches_submitted() const

@@ -7,18 +7,19 @@
 // mostly idle (152 thread blocks on a machine that holds 592) and pays one PCIe round trip per transport block. The batcher
 // coalesces the operations of ALL objects that share a context:
 //
-//   join()     an object asks for a PART of the batch that is currently open (a transport block, or a single code block for
-//              the ldpc_decoder / ldpc_rate_dematcher operators); it gets a region of the batch's page-locked LLR buffer
+//   join()     an object takes a PART: a region of the context's staging arena (page-locked host memory mirrored by device
+//              memory, pdc_stage_*) for one transport block, or one code block of the ldpc_decoder / ldpc_rate_dematcher operators
 //   add()      the object's code blocks: LLRs are copied straight into the page-locked region (the only host copy before
-//              the DMA: pdc_set_zero_copy), descriptors are collected per part
-//   seal()     no more code blocks will follow
-//   poll()     "not ready" until the batch has run (hw_accelerator::dequeue_operation may return false:
-//              pusch_decoder_hw_impl.cpp:325-338 spins on it). A batch closes — ONE pdc_submit: one H2D copy, one launch per
-//              kernel variant, one D2H copy — as soon as every joined part is sealed AND (it is full, OR the device has
-//              nothing in flight, OR it has been open for close_after_us): an idle device is never kept waiting, a busy one
-//              collects work meanwhile. The thread whose poll closes the batch submits it and waits for the device
-//              (pdc_fetch) on behalf of everybody; the others sleep on a condition variable.
-//   release()  results handed back; the batch's buffers are reused once every part has been released
+//              the DMA), descriptors are collected per part
+//   seal()     no more code blocks will follow: the region is pushed to the device at once (asynchronous copy on the arena's
+//              stream) and the part joins the queue of ready parts — it does not wait for anybody else's part
+//   poll()     "not ready" until the part's batch has run (hw_accelerator::dequeue_operation may return false:
+//              pusch_decoder_hw_impl.cpp:325-338 spins on it). A batch is formed from the ready parts — ONE pdc_submit_staged:
+//              one launch per kernel variant over LLRs that are already on the device, one D2H copy — as soon as max_parts are
+//              ready, OR the device has nothing in flight, OR the oldest ready part has waited close_after_us: an idle device is
+//              never kept waiting, a busy one collects work meanwhile. The thread whose poll forms the batch submits it and
+//              waits for the device on behalf of everybody; the others sleep on a condition variable.
+//   release()  results handed back; the region and (once all its parts are back) the batch's result buffers are reused
 //
 // Thread-safe. No CPU fallback: a failed submission marks every code block of the batch "CRC failed" (status 1).
 #pragma once
@@ -39,8 +40,11 @@ struct pusch_dec_batcher_config {
   unsigned max_parts = 8;
   /// A batch that is neither full nor facing an idle device closes after this long.
   unsigned close_after_us = 150;
-  /// Batches (page-locked staging buffers) that may be open or in flight at once; at most the context's nof_instances.
+  /// Batches whose results may be outstanding at once (result buffers); at most the context's nof_instances.
   unsigned nof_batches = 4;
+  /// A new batch forms at once while fewer than this many are running on the device ("the device is idle enough"); beyond
+  /// that, parts wait for max_parts or close_after_us.
+  unsigned eager_inflight = 2;
 };
 
 class pusch_dec_batcher
@@ -52,15 +56,16 @@ public:
 
   struct batch;
   struct part {
-    batch*                   owner = nullptr;
-    int8_t*                  llrs  = nullptr; // this part's region of the batch's page-locked buffer
+    enum class st { idle, filling, ready, inflight, done };
+    st                       state = st::idle;
+    batch*                   owner = nullptr; // the batch that carries the part (inflight, done)
+    int8_t*                  llrs  = nullptr; // this part's region of the staging arena (host side)
     size_t                   llr_base = 0, llr_cap = 0, llr_used = 0;
     unsigned                 cb_cap = 0;
-    std::vector<pdc_cb_desc> descs;  // offsets relative to the batch buffers; out / soft offsets assigned by seal()
+    std::vector<pdc_cb_desc> descs;  // llr offsets relative to the arena; out / soft offsets are assigned when the batch forms
     std::vector<int8_t>      soft;   // host-side HARQ buffers travelling with the operations (harq_slot < 0), SOFT_STRIDE each
-    std::vector<int>         index;  // per code block: position in the batch once it has closed, -1 = rejected by add()
-    bool                     sealed   = false;
-    bool                     in_use   = false;
+    std::vector<int>         index;  // per code block: position in the batch once it has formed, -1 = rejected by add()
+    std::chrono::steady_clock::time_point sealed_at;
   };
   enum class status { pending, done };
 
@@ -94,20 +99,23 @@ public:
   uint64_t nof_code_blocks_submitted() const;
 
 private:
-  void  try_advance(batch* b, std::unique_lock<std::mutex>& lock);
+  bool  try_form(std::unique_lock<std::mutex>& lock);
   part* join_locked(unsigned max_cbs, size_t max_llr_bytes);
+  void  fail_batch(batch* b);
 
   std::shared_ptr<pusch_dec_context>  ctx;
   pusch_dec_batcher_config            cfg;
   mutable std::mutex                  mtx;
-  std::condition_variable             cv; // a batch completed (or failed): waiters re-evaluate
-  std::condition_variable             cv_room; // a batch buffer was recycled: joiners re-evaluate
+  std::condition_variable             cv;      // a batch completed (or failed): waiters re-evaluate
+  std::condition_variable             cv_room; // a part region or a batch was recycled: joiners re-evaluate
+  pdc_stage*                          stage = nullptr;
+  std::vector<part>                   parts;   // one per region of the arena
+  std::vector<part*>                  ready;   // sealed parts waiting for a batch, oldest first
   std::vector<std::unique_ptr<batch>> batches;
-  batch*                              open = nullptr;
   unsigned                            inflight = 0;
   uint64_t                            stat_batches = 0, stat_cbs = 0;
   unsigned                            batch_cbs = 0;
-  size_t                              batch_llrs = 0;
+  size_t                              part_bytes = 0;
 };
 
 /// The batcher of a context: every adapter object that shares the context shares its batcher (created on first use with

@@ -110,6 +110,13 @@ def load_library():
     lib.pdc_host_alloc.restype = vp
     lib.pdc_host_free.argtypes = [vp]
     lib.pdc_host_free.restype = None
+    lib.pdc_stage_open.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
+    lib.pdc_stage_close.argtypes = [vp]
+    lib.pdc_stage_close.restype = None
+    lib.pdc_stage_host.argtypes = [vp]
+    lib.pdc_stage_host.restype = vp
+    lib.pdc_stage_push.argtypes = [vp, ctypes.c_size_t, ctypes.c_size_t]
+    lib.pdc_submit_staged.argtypes = [vp, vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int64)]
     lib.pdc_submit.argtypes = [vp, vp, ctypes.c_uint32, vp, ctypes.c_size_t, vp, ctypes.c_size_t,
                                ctypes.POINTER(ctypes.c_int64)]
     lib.pdc_poll.argtypes = [vp, ctypes.c_int64]
@@ -144,7 +151,7 @@ def load_library():
 
 
 EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_version", "pdc_set_zero_copy", "pdc_host_alloc",
-                    "pdc_host_free", "pdc_submit", "pdc_poll",
+                    "pdc_host_free", "pdc_stage_open", "pdc_stage_close", "pdc_stage_host", "pdc_stage_push", "pdc_submit_staged", "pdc_submit", "pdc_poll",
                     "pdc_fetch", "pdc_decode_device", "pdc_submit_tbs", "pdc_fetch_tbs", "pdc_decode_device_tbs",
                     "pdc_decode_device_tbs_static",
                     "pdc_demodulate_device", "pdc_demodulate", "pdc_ulsch_demux_lengths",

@@ -301,14 +301,15 @@ static pdc_status ring_reserve(pdc_ctx* ctx, pdc_ctx::demod_slot (&ring)[8], siz
   } while (0)
 
 // pdc_submit (tbs == nullptr) and pdc_submit_tbs.
+// stage != nullptr (pdc_submit_staged): the LLRs already lie in the stage's device arena (llr_offset relative to its base).
 static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
                                 const int8_t* llrs, size_t llr_bytes, const int8_t* soft_in, size_t soft_bytes,
-                                pdc_ticket* ticket)
+                                pdc_ticket* ticket, pdc_stage* stage = nullptr)
 {
-  if (!ctx || !descs || !ticket || n == 0 || (!llrs && llr_bytes != 0) || (tbs && ntb == 0)) {
+  if (!ctx || !descs || !ticket || n == 0 || (!llrs && llr_bytes != 0 && !stage) || (tbs && ntb == 0)) {
     return PDC_ERR_INVALID_ARG;
   }
-  if (n > ctx->cfg.max_batch_cbs || llr_bytes > ctx->cfg.max_batch_llrs || ntb > ctx->cfg.max_batch_cbs) {
+  if (n > ctx->cfg.max_batch_cbs || (!stage && llr_bytes > ctx->cfg.max_batch_llrs) || ntb > ctx->cfg.max_batch_cbs) {
     return PDC_ERR_CAPACITY;
   }
   nvtx_scope range(tbs ? "pdc_submit_tbs" : "pdc_submit");
@@ -324,8 +325,8 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
     t->borrowed = false;
   }
   batch_buffers buf;
-  buf.d_llrs = t->d_llrs, buf.d_soft = t->d_soft, buf.d_bits = t->d_bits, buf.d_res = t->d_res;
-  buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots, buf.llr_bytes = llr_bytes;
+  buf.d_llrs = stage ? stage->d_base : t->d_llrs, buf.d_soft = t->d_soft, buf.d_bits = t->d_bits, buf.d_res = t->d_res;
+  buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots, buf.llr_bytes = stage ? stage->bytes : llr_bytes;
   buf.d_slot_bits = tbs ? ctx->d_harq_bits : nullptr;
   batch_plan bp;
   t->lst.resize(n);
@@ -371,6 +372,13 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   // lie: the caller then keeps them untouched until the ticket has completed.
   const int8_t* src    = llrs;
   bool          pinned = false;
+  if (stage) {
+    // Everything pushed so far has to be on the device before the kernels start: one event behind the copy stream's tail.
+    std::lock_guard<std::mutex> slock(stage->mtx);
+    CKT(cudaEventRecord(stage->pushed, stage->copy));
+    CKT(cudaStreamWaitEvent(t->stream, stage->pushed, 0));
+    llr_bytes = 0;
+  }
   if (ctx->zero_copy && llr_bytes != 0) {
     cudaPointerAttributes attr;
     pinned = (cudaPointerGetAttributes(&attr, llrs) == cudaSuccess) && (attr.type == cudaMemoryTypeHost);
@@ -433,6 +441,74 @@ pdc_status pdc_submit(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const 
     return PDC_ERR_INVALID_ARG;
   }
   return submit_common(ctx, descs, n, nullptr, 0, llrs, llr_bytes, soft_in, soft_bytes, ticket);
+}
+
+pdc_status pdc_stage_open(pdc_ctx* ctx, size_t bytes, pdc_stage** out)
+{
+  if (!ctx || !out || bytes == 0) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  *out = nullptr;
+  CK(cudaSetDevice(ctx->cfg.device));
+  pdc_stage* s = new pdc_stage;
+  s->ctx       = ctx;
+  s->bytes     = bytes;
+  if (!cuda_ok(ctx, cudaHostAlloc((void**)&s->h_base, bytes, cudaHostAllocDefault), "cudaHostAlloc stage") ||
+      !cuda_ok(ctx, cudaMalloc((void**)&s->d_base, bytes), "cudaMalloc stage") ||
+      !cuda_ok(ctx, cudaStreamCreateWithFlags(&s->copy, cudaStreamNonBlocking), "cudaStreamCreate stage") ||
+      !cuda_ok(ctx, cudaEventCreateWithFlags(&s->pushed, cudaEventDisableTiming), "cudaEventCreate stage")) {
+    pdc_stage_close(s);
+    return PDC_ERR_CUDA;
+  }
+  *out = s;
+  return PDC_OK;
+}
+
+void pdc_stage_close(pdc_stage* s)
+{
+  if (!s) {
+    return;
+  }
+  cudaSetDevice(s->ctx->cfg.device);
+  if (s->copy) {
+    cudaStreamSynchronize(s->copy);
+    cudaStreamDestroy(s->copy);
+  }
+  if (s->pushed) {
+    cudaEventDestroy(s->pushed);
+  }
+  cudaFreeHost(s->h_base);
+  cudaFree(s->d_base);
+  delete s;
+}
+
+int8_t* pdc_stage_host(pdc_stage* s)
+{
+  return s ? s->h_base : nullptr;
+}
+
+pdc_status pdc_stage_push(pdc_stage* s, size_t offset, size_t bytes)
+{
+  if (!s || offset > s->bytes || bytes > s->bytes - offset) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  if (bytes == 0) {
+    return PDC_OK;
+  }
+  pdc_ctx* ctx = s->ctx;
+  CK(cudaSetDevice(ctx->cfg.device));
+  std::lock_guard<std::mutex> lock(s->mtx);
+  CK(cudaMemcpyAsync(s->d_base + offset, s->h_base + offset, bytes, cudaMemcpyHostToDevice, s->copy));
+  return PDC_OK;
+}
+
+pdc_status pdc_submit_staged(pdc_ctx* ctx, pdc_stage* stage, const pdc_cb_desc* descs, uint32_t n, const int8_t* soft_in,
+                             size_t soft_bytes, pdc_ticket* ticket)
+{
+  if (!stage || stage->ctx != ctx) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  return submit_common(ctx, descs, n, nullptr, 0, nullptr, 0, soft_in, soft_bytes, ticket, stage);
 }
 
 pdc_status pdc_submit_tbs(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
@@ -507,13 +583,8 @@ static pdc_status wait_ticket(pdc_ctx* ctx, pdc_ticket ticket, bool want_tbs, ti
   // Query + yield instead of cudaEventSynchronize: the runtime's wait spins on a core, and the callers of this library are
   // pools of host threads with work of their own (the reference's decoder threads); an idle machine loses nothing.
   cudaError_t e;
-  static const bool spin_sync = getenv("PDC_WAIT_SYNC") != nullptr; // A/B switch: the runtime's own (spinning) wait
-  if (spin_sync) {
-    e = cudaEventSynchronize(t->done);
-  } else {
-    while ((e = cudaEventQuery(t->done)) == cudaErrorNotReady) {
-      std::this_thread::yield();
-    }
+  while ((e = cudaEventQuery(t->done)) == cudaErrorNotReady) {
+    std::this_thread::yield();
   }
   if (!cuda_ok(ctx, e, "cudaEventQuery")) {
     return release_ticket(ctx, t, PDC_ERR_CUDA);

@@ -85,6 +85,18 @@ struct ticket_t {
 
 } // namespace
 
+// A staging arena (pdc_stage_*): page-locked host memory mirrored 1:1 by device memory, with its own copy stream. Regions of it
+// are pushed to the device as soon as their owner has filled them, long before the submission that uses them is formed.
+struct pdc_stage {
+  pdc_ctx*     ctx    = nullptr;
+  int8_t*      h_base = nullptr;
+  int8_t*      d_base = nullptr;
+  size_t       bytes  = 0;
+  cudaStream_t copy   = nullptr;
+  cudaEvent_t  pushed = nullptr; // recorded behind the latest push at submission time
+  std::mutex   mtx;
+};
+
 struct pdc_ctx {
   pdc_config            cfg;
   std::mutex            mtx;

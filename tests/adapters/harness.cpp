@@ -159,6 +159,7 @@ void* adt_create(int mode, int dec_flavour, int dem_flavour, int cuda_generic, i
     acfg.context            = h->context;
     acfg.external_harq      = external_harq != 0;
     acfg.generic_arithmetic = cuda_generic != 0;
+    acfg.batching.max_parts = 2; // the context above holds one transport block per submission (152 code blocks, 4 MB)
     auto acc_factory        = hal::create_cuda_pusch_dec_acc_factory(acfg);
     if (mode == 4) {
       // as the patched upper_phy_factories.cpp wraps the HAL factory when metrics are enabled
