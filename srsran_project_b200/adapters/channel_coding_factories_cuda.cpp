@@ -255,7 +255,7 @@ std::shared_ptr<cuda::pusch_dec_context> make_default_context()
   cuda::pusch_dec_context_config cfg;
   cfg.max_batch_cbs  = 64;               // concurrent single-code-block calls that may share one submission
   cfg.max_batch_llrs = 16u * 35u * 8448u; // 16 x MAX_CODEBLOCK_RM_SIZE (ldpc.h:122)
-  cfg.nof_instances  = 4;
+  cfg.nof_instances  = 8;
   return std::make_shared<cuda::pusch_dec_context>(cfg);
 }
 

@@ -65,7 +65,7 @@ public:
       // Room for this GPU's share of the transport block (code blocks are spread evenly: ids are handed out in order).
       const unsigned nof_cbs = std::max(1u, std::min(c.nof_segments, MAX_CBS));
       const unsigned share   = external ? (nof_cbs + G - 1) / G + 1 : 1;
-      parts[g]               = batchers[g]->join(share, (size_t)share * ((data.size() + 15 + 32) & ~(size_t)15), 200);
+      parts[g]               = batchers[g]->join(share, (size_t)share * ((data.size() + 63 + 32) & ~(size_t)63), 200);
       if (!parts[g]) {
         return false; // every staging buffer of that GPU is taken: back-pressure, the caller retries
       }
@@ -112,8 +112,12 @@ public:
     const slot     s = where[segment_index];
     batcher&       b = *batchers[s.gpu];
     batcher::part* p = parts[s.gpu];
-    if (b.poll(p, 100) != batcher::status::done) {
-      return false; // not ready (after a short sleep: the caller spins on this call)
+    // One poll (a mutex) per share, not per code block: once the share's batch is done it stays done until released.
+    if (!done[s.gpu]) {
+      if (b.poll(p, 100) != batcher::status::done) {
+        return false; // not ready (after a short sleep: the caller spins on this call)
+      }
+      done[s.gpu] = true;
     }
     const pdc_cb_result& r = b.result(p, s.index);
     const pdc_cb_desc&   d = p->descs[s.index];
@@ -155,6 +159,7 @@ private:
         batchers[g]->release(parts[g]);
         parts[g] = nullptr;
       }
+      done[g] = false;
     }
     nof_enqueued = nof_dequeued = 0;
     sealed                      = false;
@@ -178,6 +183,7 @@ private:
   std::array<slot, MAX_CBS>                           where;
   std::array<batcher::part*, MAX_GPUS>                parts;
   std::array<unsigned, MAX_GPUS>                      counts = {};
+  std::array<bool, MAX_GPUS>                          done   = {};
   unsigned                                            nof_enqueued = 0, nof_dequeued = 0;
   bool                                                sealed = false; // this object's share is closed: results are awaited
 };
@@ -215,6 +221,15 @@ public:
   {
     return std::make_unique<hw_accelerator_pusch_dec_cuda>(batchers, cfg.external_harq, cfg.generic_arithmetic, next_id++);
   }
+  void timing(uint64_t out[8]) const
+  {
+    std::fill(out, out + 8, 0);
+    for (auto& b : batchers) {
+      const batcher::timing t = b->timing_so_far();
+      out[0] += t.parts, out[1] += t.batches, out[2] += t.queue_ns, out[3] += t.submit_ns, out[4] += t.fetch_ns;
+      out[5] += t.wake_ns, out[6] += t.join_wait_ns, out[7] += t.add_ns;
+    }
+  }
   void stats(uint64_t& nb, uint64_t& ncb) const
   {
     nb = ncb = 0;
@@ -236,6 +251,14 @@ std::shared_ptr<hw_accelerator_pusch_dec_factory>
 srsran::hal::create_cuda_pusch_dec_acc_factory(const cuda_hwacc_pusch_dec_factory_configuration& accelerator_config)
 {
   return std::make_shared<hw_accelerator_pusch_dec_factory_cuda>(accelerator_config);
+}
+
+void srsran::hal::cuda_pusch_dec_acc_factory_timing(const hw_accelerator_pusch_dec_factory& factory, uint64_t out[8])
+{
+  std::fill(out, out + 8, 0);
+  if (auto* f = dynamic_cast<const hw_accelerator_pusch_dec_factory_cuda*>(&factory)) {
+    f->timing(out);
+  }
 }
 
 void srsran::hal::cuda_pusch_dec_acc_factory_stats(const hw_accelerator_pusch_dec_factory& factory, uint64_t& batches,

@@ -44,6 +44,9 @@ create_cuda_pusch_dec_acc_factory(const cuda_hwacc_pusch_dec_factory_configurati
 
 /// Batches submitted / code blocks carried so far by the accelerators of a factory created above (tests, bench).
 void cuda_pusch_dec_acc_factory_stats(const hw_accelerator_pusch_dec_factory& factory, uint64_t& batches, uint64_t& code_blocks);
+/// Where the time went (pusch_dec_batcher::timing summed over the GPUs): parts, batches, then nanoseconds of queueing (per part),
+/// submit, fetch (per batch), wake-up (per part), join wait, add (copy into page-locked memory).
+void cuda_pusch_dec_acc_factory_timing(const hw_accelerator_pusch_dec_factory& factory, uint64_t out[8]);
 
 } // namespace hal
 } // namespace srsran

@@ -7,8 +7,37 @@
 #include <stdexcept>
 #include <thread>
 
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
+
 using namespace srsran::cuda;
 using clk = std::chrono::steady_clock;
+
+// Copy into the page-locked region with streaming stores: the destination is read next by the DMA engine, not by this core, and
+// 1.4 MB per transport block and thread through the caches would evict the working set of the host code around the
+// accelerator (the reference's segmenter, CRC checks and assembly are memory-bound already). dst is 64-byte aligned.
+static void copy_streaming(int8_t* dst, const int8_t* src, size_t n)
+{
+#if defined(__SSE2__)
+  size_t i = 0;
+  if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+    for (; i + 64 <= n; i += 64) {
+      const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i));
+      const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 16));
+      const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 32));
+      const __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i + 48));
+      _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i), a);
+      _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 16), b);
+      _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 32), c);
+      _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i + 48), d);
+    }
+  }
+  std::memcpy(dst + i, src + i, n - i);
+#else
+  std::memcpy(dst, src, n);
+#endif
+}
 
 struct pusch_dec_batcher::batch {
   enum class st { idle, busy, done };
@@ -66,14 +95,16 @@ pusch_dec_batcher::~pusch_dec_batcher()
 pusch_dec_batcher::part* pusch_dec_batcher::join(unsigned max_cbs, size_t max_llr_bytes, unsigned wait_us)
 {
   max_cbs       = std::max(1u, std::min(max_cbs, batch_cbs));
-  max_llr_bytes = std::min((max_llr_bytes + 15) & ~(size_t)15, part_bytes);
+  max_llr_bytes = std::min((max_llr_bytes + 63) & ~(size_t)63, part_bytes);
   std::unique_lock<std::mutex> lock(mtx);
   for (int attempt = 0; attempt != 2; ++attempt) {
     part* p = join_locked(max_cbs, max_llr_bytes);
     if (p || wait_us == 0 || attempt == 1) {
       return p;
     }
+    const clk::time_point t0 = clk::now();
     cv_room.wait_for(lock, std::chrono::microseconds(wait_us));
+    tm.join_wait_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t0).count();
   }
   return nullptr;
 }
@@ -86,10 +117,12 @@ pusch_dec_batcher::part* pusch_dec_batcher::join_locked(unsigned max_cbs, size_t
       p.owner    = nullptr;
       p.llr_cap  = max_llr_bytes;
       p.llr_used = 0;
+      p.llr_pushed = 0;
       p.cb_cap   = max_cbs;
       p.descs.clear();
       p.soft.clear();
       p.index.clear();
+      p.seen_done = false;
       return &p;
     }
   }
@@ -99,7 +132,7 @@ pusch_dec_batcher::part* pusch_dec_batcher::join_locked(unsigned max_cbs, size_t
 bool pusch_dec_batcher::add(part* p, pdc_cb_desc d, const int8_t* llrs, size_t nof_llrs, const int8_t* soft_in, size_t nof_soft)
 {
   // Only the owning thread touches a part that is being filled: no lock.
-  const size_t off = (p->llr_used + 15) & ~(size_t)15;
+  const size_t off = (p->llr_used + 63) & ~(size_t)63; // whole cache lines per code block (streaming stores)
   if (p->state != part::st::filling || p->descs.size() >= p->cb_cap || off + nof_llrs > p->llr_cap) {
     return false;
   }
@@ -111,9 +144,14 @@ bool pusch_dec_batcher::add(part* p, pdc_cb_desc d, const int8_t* llrs, size_t n
     p->index.push_back(-1);
     return true;
   }
-  std::memcpy(p->llrs + off, llrs, nof_llrs);
+  const clk::time_point t0 = clk::now();
+  copy_streaming(p->llrs + off, llrs, nof_llrs);
+  add_ns.fetch_add(std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t0).count(), std::memory_order_relaxed);
   p->llr_used  = off + nof_llrs;
   d.llr_offset = p->llr_base + off;
+  if (cfg.push_chunk_bytes != 0 && p->llr_used - p->llr_pushed >= cfg.push_chunk_bytes) {
+    push_pending(p);
+  }
   if (d.harq_slot < 0 && !(d.flags & PDC_F_DECODE_ONLY)) {
     const size_t so = p->soft.size();
     p->soft.resize(so + SOFT_STRIDE, 0);
@@ -126,13 +164,25 @@ bool pusch_dec_batcher::add(part* p, pdc_cb_desc d, const int8_t* llrs, size_t n
   return true;
 }
 
+void pusch_dec_batcher::push_pending(part* p)
+{
+  if (p->llr_used == p->llr_pushed) {
+    return;
+  }
+#if defined(__SSE2__)
+  _mm_sfence(); // the streaming stores of add() are globally visible before the DMA is told to read them
+#endif
+  pdc_stage_push(stage, p->llr_base + p->llr_pushed, p->llr_used - p->llr_pushed);
+  p->llr_pushed = p->llr_used;
+}
+
 void pusch_dec_batcher::seal(part* p)
 {
   if (p->state != part::st::filling) {
     return;
   }
-  // The region travels to the device now, while the other members of its future batch are still being filled.
-  pdc_stage_push(stage, p->llr_base, p->llr_used);
+  // The rest of the region travels to the device now, while the other members of its future batch are still being filled.
+  push_pending(p);
   std::lock_guard<std::mutex> lock(mtx);
   p->state     = part::st::ready;
   p->sealed_at = clk::now();
@@ -174,6 +224,7 @@ bool pusch_dec_batcher::try_form(std::unique_lock<std::mutex>& lock)
   b->descs.clear();
   size_t nsoft = 0;
   size_t taken = 0;
+  const clk::time_point formed_at = clk::now();
   while (taken != ready.size() && b->members.size() != cfg.max_parts) {
     part* p = ready[taken];
     if (b->descs.size() + p->descs.size() > batch_cbs && !b->members.empty()) {
@@ -200,6 +251,8 @@ bool pusch_dec_batcher::try_form(std::unique_lock<std::mutex>& lock)
     }
     p->state = part::st::inflight;
     p->owner = b;
+    tm.queue_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(formed_at - p->sealed_at).count();
+    ++tm.parts;
     b->members.push_back(p);
     ++taken;
   }
@@ -211,11 +264,13 @@ bool pusch_dec_batcher::try_form(std::unique_lock<std::mutex>& lock)
   lock.unlock();
 
   pdc_status st = PDC_OK;
+  clk::time_point t_sub = clk::now(), t_mid = t_sub;
   if (n != 0) {
     while ((st = pdc_submit_staged(ctx->get(), stage, b->descs.data(), n, nsoft ? b->soft.data() : nullptr, nsoft * SOFT_STRIDE,
                                    &b->ticket)) == PDC_ERR_CAPACITY) {
       std::this_thread::yield(); // every ticket of the context is in flight (other users of the context)
     }
+    t_mid = clk::now();
     if (st == PDC_OK) {
       st = pdc_fetch(ctx->get(), b->ticket, b->bits.data(), b->bits.size(), b->results.data(), nsoft ? b->soft.data() : nullptr,
                      b->soft.size());
@@ -227,9 +282,14 @@ bool pusch_dec_batcher::try_form(std::unique_lock<std::mutex>& lock)
     }
   }
 
+  const clk::time_point t_end = clk::now();
   lock.lock();
+  tm.submit_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(t_mid - t_sub).count();
+  tm.fetch_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(t_end - t_mid).count();
+  ++tm.batches;
   for (part* p : b->members) {
-    p->state = part::st::done;
+    p->state   = part::st::done;
+    p->done_at = t_end;
   }
   b->state = batch::st::done;
   --inflight;
@@ -250,6 +310,10 @@ pusch_dec_batcher::status pusch_dec_batcher::poll(part* p, unsigned wait_us)
     if (p->state == part::st::ready) {
       try_form(lock);
     }
+  }
+  if (p->state == part::st::done && !p->seen_done) {
+    p->seen_done = true;
+    tm.wake_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - p->done_at).count();
   }
   return (p->state == part::st::done) ? status::done : status::pending;
 }
@@ -292,6 +356,14 @@ void pusch_dec_batcher::release(part* p)
   p->owner = nullptr;
   cv_room.notify_all();
   cv.notify_all(); // a batch buffer may have become free: a ready queue that was waiting for one can form now
+}
+
+pusch_dec_batcher::timing pusch_dec_batcher::timing_so_far() const
+{
+  std::lock_guard<std::mutex> lock(mtx);
+  timing t  = tm;
+  t.add_ns  = add_ns.load();
+  return t;
 }
 
 uint64_t pusch_dec_batcher::nof_batches_submitted() const

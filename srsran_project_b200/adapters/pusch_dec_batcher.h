@@ -25,6 +25,7 @@
 #pragma once
 
 #include "cuda_pusch_dec_context.h"
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <cstdint>
@@ -41,10 +42,13 @@ struct pusch_dec_batcher_config {
   /// A batch that is neither full nor facing an idle device closes after this long.
   unsigned close_after_us = 150;
   /// Batches whose results may be outstanding at once (result buffers); at most the context's nof_instances.
-  unsigned nof_batches = 4;
+  unsigned nof_batches = 8;
+  /// A part's region travels to the device in pieces of this size while its owner is still adding code blocks, so that only
+  /// the last piece is on the road when the part is sealed. 0: one transfer at seal().
+  size_t push_chunk_bytes = 0; // measured with 448 KB pieces on config 2: no gain (more entries on the copy stream)
   /// A new batch forms at once while fewer than this many are running on the device ("the device is idle enough"); beyond
   /// that, parts wait for max_parts or close_after_us.
-  unsigned eager_inflight = 2;
+  unsigned eager_inflight = 6;
 };
 
 class pusch_dec_batcher
@@ -60,12 +64,23 @@ public:
     st                       state = st::idle;
     batch*                   owner = nullptr; // the batch that carries the part (inflight, done)
     int8_t*                  llrs  = nullptr; // this part's region of the staging arena (host side)
-    size_t                   llr_base = 0, llr_cap = 0, llr_used = 0;
+    size_t                   llr_base = 0, llr_cap = 0, llr_used = 0, llr_pushed = 0;
     unsigned                 cb_cap = 0;
     std::vector<pdc_cb_desc> descs;  // llr offsets relative to the arena; out / soft offsets are assigned when the batch forms
     std::vector<int8_t>      soft;   // host-side HARQ buffers travelling with the operations (harq_slot < 0), SOFT_STRIDE each
     std::vector<int>         index;  // per code block: position in the batch once it has formed, -1 = rejected by add()
-    std::chrono::steady_clock::time_point sealed_at;
+    std::chrono::steady_clock::time_point sealed_at, done_at;
+    bool                     seen_done = false;
+  };
+  /// Where the time of the parts and batches went so far, nanoseconds summed over parts / batches (for the bench and tuning).
+  struct timing {
+    uint64_t parts = 0, batches = 0;
+    uint64_t queue_ns  = 0; // sealed -> taken into a batch, per part
+    uint64_t submit_ns = 0; // pdc_submit_staged, per batch
+    uint64_t fetch_ns  = 0; // pdc_fetch (wait for the device + copy out), per batch
+    uint64_t wake_ns   = 0; // batch done -> the part's owner sees it, per part
+    uint64_t join_wait_ns = 0; // join() sleeping for a free region
+    uint64_t add_ns    = 0; // add(): the copy into the page-locked region
   };
   enum class status { pending, done };
 
@@ -74,7 +89,7 @@ public:
   pusch_dec_batcher(const pusch_dec_batcher&)            = delete;
   pusch_dec_batcher& operator=(const pusch_dec_batcher&) = delete;
 
-  /// A part of the open batch with room for max_cbs code blocks and max_llr_bytes of LLRs (each code block 16-byte aligned),
+  /// A part of the open batch with room for max_cbs code blocks and max_llr_bytes of LLRs (each code block 64-byte aligned),
   /// or nullptr when every batch buffer is taken (try again: back-pressure, not an error). A request larger than a whole
   /// batch is cut down to the batch: add() then reports "full" and the caller continues with another part.
   /// wait_us > 0: when no batch buffer is free the call sleeps up to that long for one (woken when a batch is recycled).
@@ -97,11 +112,13 @@ public:
   /// Batches submitted and code blocks carried so far (for tests and the bench: mean batch size = code_blocks / batches).
   uint64_t nof_batches_submitted() const;
   uint64_t nof_code_blocks_submitted() const;
+  timing   timing_so_far() const;
 
 private:
   bool  try_form(std::unique_lock<std::mutex>& lock);
   part* join_locked(unsigned max_cbs, size_t max_llr_bytes);
   void  fail_batch(batch* b);
+  void  push_pending(part* p);
 
   std::shared_ptr<pusch_dec_context>  ctx;
   pusch_dec_batcher_config            cfg;
@@ -114,6 +131,8 @@ private:
   std::vector<std::unique_ptr<batch>> batches;
   unsigned                            inflight = 0;
   uint64_t                            stat_batches = 0, stat_cbs = 0;
+  timing                              tm;
+  std::atomic<uint64_t>               add_ns{0};
   unsigned                            batch_cbs = 0;
   size_t                              part_bytes = 0;
 };

@@ -15,6 +15,36 @@ extern "C" cudaError_t pdc_launch_lane(const pdc_launch_params& prm, int block, 
   return cudaGetLastError();
 }
 
+// Descriptor upload without the copy engine: the SMs read the page-locked host image (device-addressable: unified addressing)
+// and write the device copy. A small host-to-device memcpy queues behind every large LLR transfer already handed to the copy
+// engine (measured: 100 us for 20 KB with sixteen threads pushing 1.4 MB regions); these reads interleave with them on the link.
+__global__ void __launch_bounds__(256) pdc_upload_kernel(uint32_t* __restrict__ dst0, const uint32_t* __restrict__ src0, uint32_t n0,
+                                                         uint32_t* __restrict__ dst1, const uint32_t* __restrict__ src1, uint32_t n1)
+{
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1; i += stride) {
+    if (i < n0) {
+      dst0[i] = src0[i];
+    } else {
+      dst1[i - n0] = src1[i - n0];
+    }
+  }
+}
+extern "C" cudaError_t pdc_launch_upload(void* dst0, const void* src0, size_t bytes0, void* dst1, const void* src1, size_t bytes1,
+                                         cudaStream_t stream)
+{
+  if (((bytes0 | bytes1) & 3) != 0) {
+    return cudaErrorInvalidValue;
+  }
+  const uint32_t n0 = (uint32_t)(bytes0 >> 2), n1 = (uint32_t)(bytes1 >> 2);
+  const uint32_t grid = (n0 + n1 + 1023) / 1024; // four words per thread in flight
+  if (grid == 0) {
+    return cudaSuccess;
+  }
+  pdc_upload_kernel<<<grid, 256, 0, stream>>>((uint32_t*)dst0, (const uint32_t*)src0, n0, (uint32_t*)dst1, (const uint32_t*)src1, n1);
+  return cudaGetLastError();
+}
+
 // Per-device one-time setup (constant tables, opt-in shared memory); called from pdc_create with the device current.
 extern "C" cudaError_t pdc_kernels_init_device(const pdc_bg_rows* rows)
 {

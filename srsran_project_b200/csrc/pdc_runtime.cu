@@ -44,6 +44,11 @@ static void free_ticket(ticket_t& t)
   cudaFree(t.d_soft);
   cudaFreeHost(t.h_tbout);
   cudaFree(t.d_terms), cudaFree(t.d_tbout);
+  for (cudaEvent_t e : t.tr) {
+    if (e) {
+      cudaEventDestroy(e);
+    }
+  }
   if (t.done) {
     cudaEventDestroy(t.done);
   }
@@ -132,6 +137,9 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   }
   pdc_ctx* ctx = new pdc_ctx;
   ctx->cfg     = *cfg;
+  if (const char* tr = std::getenv("PDC_TRACE")) {
+    ctx->trace = tr[0] == '1';
+  }
   auto fail    = [&](pdc_status s) {
     {
       std::lock_guard<std::mutex> lock(g_static_err_mtx);
@@ -194,6 +202,12 @@ void pdc_destroy(pdc_ctx* ctx)
     return;
   }
   cudaSetDevice(ctx->cfg.device);
+  if (ctx->trace && ctx->trace_ms[4] > 0) {
+    const double k = 1e3 / ctx->trace_ms[4];
+    std::fprintf(stderr, "pdc trace: %.0f submissions; per submission: descriptors H2D %.1f us, kernels %.1f us, D2H %.1f us; "
+                         "submit returned -> completion seen %.1f us\n",
+                 ctx->trace_ms[4], ctx->trace_ms[0] * k, ctx->trace_ms[1] * k, ctx->trace_ms[2] * k, ctx->trace_ms[3] * k);
+  }
   for (ticket_t& t : ctx->tickets) {
     free_ticket(t);
   }
@@ -325,7 +339,11 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
     t->borrowed = false;
   }
   batch_buffers buf;
-  buf.d_llrs = stage ? stage->d_base : t->d_llrs, buf.d_soft = t->d_soft, buf.d_bits = t->d_bits, buf.d_res = t->d_res;
+  // Staged code-block submissions (the accelerator adapters: small batches, latency matters): the kernels store the hard bits and
+  // the results straight into the page-locked host buffers (device-addressable), so no device-to-host copy follows them.
+  const bool host_out = stage != nullptr && !tbs;
+  buf.d_llrs = stage ? stage->d_base : t->d_llrs, buf.d_soft = t->d_soft;
+  buf.d_bits = host_out ? t->h_bits : t->d_bits, buf.d_res = host_out ? t->h_res : t->d_res;
   buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots, buf.llr_bytes = stage ? stage->bytes : llr_bytes;
   buf.d_slot_bits = tbs ? ctx->d_harq_bits : nullptr;
   batch_plan bp;
@@ -379,6 +397,14 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
     CKT(cudaStreamWaitEvent(t->stream, stage->pushed, 0));
     llr_bytes = 0;
   }
+  if (ctx->trace) {
+    for (cudaEvent_t& e : t->tr) {
+      if (!e) {
+        CKT(cudaEventCreate(&e));
+      }
+    }
+    CKT(cudaEventRecord(t->tr[0], t->stream));
+  }
   if (ctx->zero_copy && llr_bytes != 0) {
     cudaPointerAttributes attr;
     pinned = (cudaPointerGetAttributes(&attr, llrs) == cudaSuccess) && (attr.type == cudaMemoryTypeHost);
@@ -391,10 +417,20 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   if (llr_bytes != 0) {
     CKT(cudaMemcpyAsync(t->d_llrs, src, llr_bytes, cudaMemcpyHostToDevice, t->stream));
   }
-  CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n + sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice,
-                      t->stream));
-  if (!bp.identity) {
-    CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
+  if (host_out) {
+    // Nothing to upload: each thread block reads its own descriptor from the page-locked image (one 56-byte read over the
+    // link per code block, in parallel), see launch_batch below.
+  } else if (stage) {
+    // Staged submissions run while other regions of the arena are travelling: keep the small copies off the copy engine.
+    CKT(pdc_launch_upload(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n + sizeof(pdc_dev_tb) * ntb, t->d_order, t->h_order,
+                          bp.identity ? 0 : sizeof(uint32_t) * n, t->stream));
+    ctx->launches += 1;
+  } else {
+    CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n + sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice,
+                        t->stream));
+    if (!bp.identity) {
+      CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, t->stream));
+    }
   }
   if (bp.any_host_soft) {
     if (soft_in) {
@@ -404,22 +440,34 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
       CKT(cudaMemsetAsync(t->d_soft, 0, bp.soft_end, t->stream));
     }
   }
-  st = launch_batch(ctx, bp, t->d_cbs, t->d_order, t->stream);
+  if (ctx->trace) {
+    CKT(cudaEventRecord(t->tr[1], t->stream));
+  }
+  st = host_out ? launch_batch(ctx, bp, t->h_cbs, t->h_order, t->stream) : launch_batch(ctx, bp, t->d_cbs, t->d_order, t->stream);
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
+  }
+  if (ctx->trace) {
+    CKT(cudaEventRecord(t->tr[2], t->stream));
   }
   if (tbs) {
     // Assembly + TB CRC on the device; the payloads and the two result arrays (one copy) come back, no per-CB bits.
     CKT(pdc_launch_tb(t->d_tbs, t->d_cbs, ctx->d_crc, (int)ntb, (int)tp.max_cbs, t->stream));
     ctx->launches += 2;
     CKT(cudaMemcpyAsync(t->h_tbout, t->d_tbout, tp.bytes_end, cudaMemcpyDeviceToHost, t->stream));
-  } else {
+  } else if (!host_out) {
     CKT(cudaMemcpyAsync(t->h_bits, t->d_bits, bp.bits_end, cudaMemcpyDeviceToHost, t->stream));
   }
-  CKT(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n + sizeof(pdc_tb_result) * ntb, cudaMemcpyDeviceToHost,
-                      t->stream));
+  if (!host_out) {
+    CKT(cudaMemcpyAsync(t->h_res, t->d_res, sizeof(pdc_cb_result) * n + sizeof(pdc_tb_result) * ntb, cudaMemcpyDeviceToHost,
+                        t->stream));
+  }
   if (bp.any_host_soft) {
     CKT(cudaMemcpyAsync(t->h_soft, t->d_soft, bp.soft_end, cudaMemcpyDeviceToHost, t->stream));
+  }
+  if (ctx->trace) {
+    CKT(cudaEventRecord(t->tr[3], t->stream));
+    t->submitted_at = std::chrono::steady_clock::now();
   }
   CKT(cudaEventRecord(t->done, t->stream));
   t->n          = n;
@@ -588,6 +636,14 @@ static pdc_status wait_ticket(pdc_ctx* ctx, pdc_ticket ticket, bool want_tbs, ti
   }
   if (!cuda_ok(ctx, e, "cudaEventQuery")) {
     return release_ticket(ctx, t, PDC_ERR_CUDA);
+  }
+  if (ctx->trace && t->tr[3]) {
+    const double host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t->submitted_at).count();
+    float        a = 0, b = 0, c = 0;
+    cudaEventElapsedTime(&a, t->tr[0], t->tr[1]), cudaEventElapsedTime(&b, t->tr[1], t->tr[2]);
+    cudaEventElapsedTime(&c, t->tr[2], t->tr[3]);
+    std::lock_guard<std::mutex> lock(ctx->mtx);
+    ctx->trace_ms[0] += a, ctx->trace_ms[1] += b, ctx->trace_ms[2] += c, ctx->trace_ms[3] += host_ms, ctx->trace_ms[4] += 1;
   }
   return PDC_OK;
 }

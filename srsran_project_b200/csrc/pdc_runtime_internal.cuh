@@ -7,6 +7,7 @@
 // arena slots; hw_accelerator_pusch_dec.h:83-115, ext_harq_buffer_context_repository.h:36-107).
 #include "ldpc_bg_tables.h"
 #include "pdc_device.cuh"
+#include <chrono>
 #include <nvtx3/nvToolsExt.h> // header-only: ranges cost nothing unless a profiler is attached
 #include <atomic>
 #include <cstddef>
@@ -34,6 +35,8 @@ extern "C" cudaError_t pdc_demux_launch(const pdc_dev_demux_sym* d_syms, uint32_
                                         cudaStream_t stream);
 extern "C" cudaError_t pdc_demod_launch(const pdc_demod_seg* d_segs, const void* d_chunks, uint32_t nchunks,
                                         const float* d_symbols, const float* d_noise, int8_t* d_llrs, cudaStream_t stream);
+extern "C" cudaError_t pdc_launch_upload(void* dst0, const void* src0, size_t bytes0, void* dst1, const void* src1, size_t bytes1,
+                                         cudaStream_t stream);
 extern "C" cudaError_t pdc_launch_tb(const pdc_dev_tb* d_tbs, const pdc_dev_cb* d_cbs, const uint32_t* crc_pow, int ntb,
                                      int max_cbs, cudaStream_t stream);
 
@@ -81,6 +84,9 @@ struct ticket_t {
   size_t                   bits_bytes = 0, soft_bytes = 0;
   bool                     soft_back  = false, bits_dense = false;
   bool                     borrowed   = false; // staging lent to pdc_decode_device: its copy may still be in flight
+  // PDC_TRACE=1: device-side timeline of a submission (events with timing), host clock at the end of the submit call
+  cudaEvent_t                           tr[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::chrono::steady_clock::time_point submitted_at;
 };
 
 } // namespace
@@ -103,6 +109,8 @@ struct pdc_ctx {
   std::mutex            err_mtx; // submit / fetch run outside mtx: the error string has its own lock
   std::string           err;
   bool                  zero_copy = false; // pdc_set_zero_copy
+  bool                  trace     = false; // PDC_TRACE=1 in the environment at pdc_create: timeline summary on stderr at pdc_destroy
+  double                trace_ms[5] = {0, 0, 0, 0, 0}; // descs H2D, kernels, D2H, submit -> done seen by the host, count
   std::vector<ticket_t> tickets;
   int64_t               next_id = 1;
   unsigned              next_ticket = 0; // reserve_ticket starts its search here (round robin)

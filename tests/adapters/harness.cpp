@@ -42,6 +42,7 @@
 #include "srsran/phy/upper/unique_rx_buffer.h"
 #include <atomic>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -407,6 +408,12 @@ int adt_bench_hal(unsigned       nthreads,
     acfg.harq_context_size       = pool_cfg.nof_codeblocks;
     acfg.batching.max_parts      = max_parts;
     acfg.batching.close_after_us = close_after_us;
+    if (const char* e = std::getenv("ADT_EAGER_INFLIGHT")) { // tuning experiments
+      acfg.batching.eager_inflight = (unsigned)std::atoi(e);
+    }
+    if (const char* e = std::getenv("ADT_NOF_BATCHES")) {
+      acfg.batching.nof_batches = (unsigned)std::atoi(e);
+    }
     acc_factory                  = hal::create_cuda_pusch_dec_acc_factory(acfg);
   } catch (const std::exception& e) {
     std::fprintf(stderr, "adt_bench_hal: %s\n", e.what());
@@ -451,9 +458,14 @@ int adt_bench_hal(unsigned       nthreads,
     const unsigned   w = (t + k) % n_distinct;
     tl_replay_codeword = w;
     unique_rx_buffer buffer;
-    {
+    for (unsigned attempt = 0; attempt != 2000 && !buffer.is_valid(); ++attempt) {
       // rx_buffer_pool::reserve is called from one thread in the gNB (the upper-PHY receive path); only unlock / release come
-      // from the decoder threads.
+      // from the decoder threads. The pool's free list is a lock-free queue whose try_pop answers "empty" while a releasing
+      // thread is in the middle of a push (rx_buffer_codeblock_pool.h:82-90): with more threads than cores a pusher can be
+      // descheduled there, so a refused reservation is tried again (the gNB would drop the PUSCH and log a warning).
+      if (attempt != 0) {
+        std::this_thread::yield();
+      }
       std::lock_guard<std::mutex> lock(reserve_mtx);
       buffer = pool->get_pool().reserve({}, trx_buffer_identifier(1 + t, k % nof_harq), nof_cbs, true);
     }
@@ -516,6 +528,16 @@ int adt_bench_hal(unsigned       nthreads,
     hal::cuda_pusch_dec_acc_factory_stats(*acc_factory, b1, c1);
   }
   stats[0] = ok.load(), stats[1] = attempted.load(), stats[2] = b1 - b0, stats[3] = c1 - c0;
+  if (acc_factory && std::getenv("ADT_TRACE")) {
+    uint64_t tm[8];
+    hal::cuda_pusch_dec_acc_factory_timing(*acc_factory, tm); // includes the warm-up transport blocks
+    const double np = (double)std::max<uint64_t>(tm[0], 1), nb = (double)std::max<uint64_t>(tm[1], 1);
+    std::fprintf(stderr,
+                 "adt_bench_hal: %u threads, %.3f ms; parts %llu batches %llu; per part: queue %.1f us, wake %.1f us, add %.1f us; "
+                 "per batch: submit %.1f us, fetch %.1f us; join wait total %.1f us\n",
+                 nthreads, *seconds * 1e3, (unsigned long long)tm[0], (unsigned long long)tm[1], tm[2] / np / 1e3, tm[5] / np / 1e3,
+                 tm[7] / np / 1e3, tm[3] / nb / 1e3, tm[4] / nb / 1e3, tm[6] / 1e3);
+  }
   decoders.clear();
   hw_pool.reset();
   pool->stop();

@@ -171,10 +171,13 @@ def test_hal_metric_decorator_reports_every_code_block():
 
 
 @pytest.mark.gpu
-def test_hal_accelerators_of_one_factory_share_gpu_submissions():
+def test_hal_accelerators_of_one_factory_share_gpu_submissions(monkeypatch):
     """Cross-instance batching (adapters/pusch_dec_batcher.h): six host threads, each with its own reference pusch_decoder_hw_impl,
     draw accelerators from one CUDA HAL factory and decode small transport blocks back to back. Every transport block comes out
-    as transmitted, and the GPU saw fewer submissions than transport blocks (the objects' code blocks travelled together)."""
+    as transmitted, and the GPU saw fewer submissions than transport blocks (the objects' code blocks travelled together).
+    The batcher is told to keep one submission in flight (batching.eager_inflight = 1: the setting for a loaded device; the
+    default of 6 sends a lone transport block off at once while the device has room)."""
+    monkeypatch.setenv("ADT_EAGER_INFLIGHT", "1")
     from tools import bench_hal
 
     if not bench_hal.available():
@@ -189,6 +192,7 @@ def test_hal_accelerators_of_one_factory_share_gpu_submissions():
     assert r["ok"] == r["attempted"] == 120, r
     assert r["batches"] < r["attempted"], r
     # one thread alone: nothing to coalesce with, every transport block is its own submission and still comes out right
+    monkeypatch.delenv("ADT_EAGER_INFLIGHT")
     r1 = bench_hal.run_raw(llrs, want, tbs, bg, Qm, layers, 6, threads=1, tbs_per_thread=6, warmup=1)
     assert r1["ok"] == r1["attempted"] == 6 and r1["batches"] == 6, r1
 
