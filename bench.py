@@ -789,6 +789,7 @@ def run_cuda_arm(args):
         c1 = bench_config1.run(steps=10, cpu=use_cpu, peak_ops=peak)
         c3 = bench_configs.config3(S, 10, cpu=use_cpu, peak_ops=peak)
         c4 = bench_configs.config4(S, 5, 3.0, 6.0, n_tbs=8, cpu=use_cpu, peak_ops=peak)
+        c2l = bench_configs.config2_lbrm(S, 5, n_tbs=8, cpu=use_cpu, peak_ops=peak)
 
         def flat(c, tx):
             t = c["transmissions"][tx]
@@ -798,7 +799,8 @@ def run_cuda_arm(args):
                     "roofline": t["roofline"], "cpu_gbps": t.get("cpu_info_gbps"), "cpu_threads": t.get("cpu_threads"),
                     "bit_exact": None if be is None else bool(be["iterations"] and be["bits"] and be["soft_buffers"])}
 
-        configs = {"config1": c1, "config3": flat(c3, 0), "config4_tx1_rv0": flat(c4, 0), "config4_tx2_rv2": flat(c4, 1)}
+        configs = {"config1": c1, "config2_lbrm": dict(flat(c2l, 0), same_batch_with_Nref_0=c2l["same_batch_with_Nref_0"], stale_slots=c2l["stale_slots"]),
+                   "config3": flat(c3, 0), "config4_tx1_rv0": flat(c4, 0), "config4_tx2_rv2": flat(c4, 1)}
 
     # ---- the drop-in boundary measured as the reference drives it: host threads of the unmodified pusch_decoder_hw_impl over
     #      the CUDA hal::hw_accelerator_pusch_dec (tools/bench_hal.py) ---------------------------------------------------------

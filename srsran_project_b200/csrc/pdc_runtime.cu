@@ -137,6 +137,7 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   }
   pdc_ctx* ctx = new pdc_ctx;
   ctx->cfg     = *cfg;
+  ctx->harq_nz.assign(cfg->harq_slots, 0); // the arena is created zeroed
   if (const char* tr = std::getenv("PDC_TRACE")) {
     ctx->trace = tr[0] == '1';
   }
@@ -348,6 +349,8 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   buf.d_slot_bits = tbs ? ctx->d_harq_bits : nullptr;
   batch_plan bp;
   t->lst.resize(n);
+  t->nz.resize(n);
+  buf.harq_nz = ctx->harq_nz.data(), buf.nz_scratch = t->nz.data();
   pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
@@ -378,6 +381,7 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
         return release_ticket(ctx, t, st);
       }
       buf.d_soft = t->d_soft;
+      buf.harq_nz = nullptr, buf.nz_scratch = nullptr; // the arena bookkeeping was done by the first pass
       batch_plan again;
       st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), again);
       if (st != PDC_OK) {
@@ -756,6 +760,8 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
   buf.d_slot_bits = tbs ? ctx->d_harq_bits : nullptr;
   batch_plan bp;
   t->lst.resize(n);
+  t->nz.resize(n);
+  buf.harq_nz = ctx->harq_nz.data(), buf.nz_scratch = t->nz.data();
   pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
   if (st == PDC_OK && bp.any_host_soft && !d_soft) {
     st = PDC_ERR_INVALID_ARG;
@@ -826,6 +832,7 @@ static struct {
   pdc_dev_tb tbs[PDC_STATIC_MAX_CBS];
   uint32_t   order[PDC_STATIC_MAX_CBS];
   uint8_t    lst[PDC_STATIC_MAX_CBS];
+  int32_t    nz[PDC_STATIC_MAX_CBS];
 } g_static_host; // .bss, nothing is allocated per call
 
 static pdc_status static_scratch_address(pdc_ctx* ctx, unsigned char** out)
@@ -878,6 +885,7 @@ pdc_status pdc_decode_device_tbs_static(pdc_ctx* ctx, const pdc_cb_desc* descs, 
   buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots;
   buf.d_slot_bits = ctx->d_harq_bits;
   batch_plan bp;
+  buf.harq_nz = ctx->harq_nz.data(), buf.nz_scratch = g_static_host.nz;
   st = plan_batch(descs, n, buf, g_static_host.cbs, g_static_host.order, g_static_host.lst, bp);
   if (st == PDC_OK) {
     uint32_t processed = bp.n_lane; // code blocks a kernel reads LLRs for (all but the PDC_F_DECODED ones)
@@ -1569,6 +1577,7 @@ pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot)
   std::lock_guard<std::mutex> lock(ctx->mtx);
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaMemset(ctx->d_harq + (size_t)slot * PDC_MAX_N, 0, PDC_MAX_N));
+  ctx->harq_nz[slot] = 0;
   return PDC_OK;
 }
 
@@ -1593,6 +1602,7 @@ pdc_status pdc_harq_write(pdc_ctx* ctx, int32_t slot, const int8_t* host_src, si
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(ctx->d_harq + (size_t)slot * PDC_MAX_N, host_src, n, cudaMemcpyHostToDevice));
+  ctx->harq_nz[slot] = std::max(ctx->harq_nz[slot], (int32_t)n);
   return PDC_OK;
 }
 

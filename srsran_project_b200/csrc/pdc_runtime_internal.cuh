@@ -81,6 +81,7 @@ struct ticket_t {
   // what to hand back
   std::vector<pdc_cb_desc> descs;
   std::vector<uint8_t>     lst; // kernel list of every code block (planner scratch)
+  std::vector<int32_t>     nz;  // planner scratch: new non-zero extents of the arena slots (batch_buffers::nz_scratch)
   size_t                   bits_bytes = 0, soft_bytes = 0;
   bool                     soft_back  = false, bits_dense = false;
   bool                     borrowed   = false; // staging lent to pdc_decode_device: its copy may still be in flight
@@ -125,6 +126,7 @@ struct pdc_ctx {
   uint32_t*             d_crc    = nullptr;
   uint32_t*             d_crc_bit = nullptr;
   int8_t*               d_harq   = nullptr;
+  std::vector<int32_t>  harq_nz;            // per arena slot: bound on the extent of non-zero soft bits (batch_buffers::harq_nz)
   uint8_t*              d_harq_bits = nullptr; // decoded bits kept with every HARQ slot (transport-block path), PDC_MAX_K / 8 each
   std::atomic<uint64_t> launches{0};
   size_t                bits_stride_total = 0;
@@ -353,6 +355,15 @@ struct desc_class {
   uint32_t    N        = 0;
   int         list     = 0; // packed-kernel lists, then PDC_NOF_PACKED_LISTS = lane kernel
   bool        valid    = false;
+  // What the dematcher of this class does to the extent of non-zero soft bits of a HARQ arena slot (see plan_batch):
+  // track 0: nothing (decode only / already decoded); 1: new data, one lap: [0, end_idx) written, [tail_start, N) zeroed,
+  // [end_idx, tail_start) left as it was (empty without limited-buffer rate matching); 2: anything up to N may be non-zero.
+  int  track = 0, end_idx = 0, tail_start = 0;
+  // Limited-buffer first transmission that fits the packed kernel's staging tile whenever the stretch it leaves untouched is
+  // known to hold zeros: then it IS a first transmission into an all-zero buffer and takes the four-row kernel (list_fast).
+  bool   tile_if_clean = false;
+  int    list_fast = 0, block_fast = 0;
+  size_t smem_fast = 0;
 };
 
 inline bool same_class(const pdc_cb_desc& a, const pdc_cb_desc& b)
@@ -381,12 +392,30 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
   c.E = d.E, c.Nref = d.Nref, c.nof_filler = d.nof_filler, c.Z = d.Z;
   c.bg = d.bg, c.Qm = d.Qm, c.rv = d.rv, c.crc_type = d.crc_type, c.max_iter = d.max_iter;
   c.flags = d.flags & (uint8_t)~PDC_DEVF_FIRST_TX_TILE;
-  if (!(d.flags & (PDC_F_DECODED | PDC_F_DECODE_ONLY | PDC_F_DEMATCH_ONLY))) {
+  cls.track = 0, cls.tile_if_clean = false;
+  if (!(d.flags & (PDC_F_DECODED | PDC_F_DECODE_ONLY))) {
     pdc_dematch_plan pl;
     if (pdc_dematch_plan_init(pl, g, (int)d.E, d.Qm, d.rv, (int)d.Nref, (int)d.nof_filler, (d.flags & PDC_F_NEW_DATA) != 0)) {
-      const int end_pos = pl.final_zero ? pl.end_idx : pl.N;
-      if (pl.new_data && pl.rounds == 1 && pl.Ncb == pl.N && pl.k0 == 0 && pl.E >= pl.n_info && end_pos <= (g.Kb + 2) * g.Z) {
+      cls.track = 2;
+      if (pl.final_zero) { // new data, one lap, ends before Ncb
+        cls.track      = 1;
+        cls.end_idx    = pl.end_idx;
+        cls.tail_start = pl.N - (pl.Ncb - pl.end_idx);
+      }
+      const int  end_pos = pl.final_zero ? pl.end_idx : pl.N;
+      const bool fits    = pl.new_data && pl.rounds == 1 && pl.k0 == 0 && pl.E >= pl.n_info && end_pos <= (g.Kb + 2) * g.Z &&
+                        !(d.flags & PDC_F_DEMATCH_ONLY);
+      if (fits && pl.Ncb == pl.N) {
         c.flags |= PDC_DEVF_FIRST_TX_TILE; // then end_pos == E + F (see pdc_dematch_plan_init with k0 = 0, one lap)
+      } else if (fits && pl.final_zero && takes_h2(d, 4, false)) {
+        // Ncb < N (limited-buffer rate matching, what the live stack always asks for: pusch_processor_impl.cpp:327-334): the
+        // reference leaves [end_idx, N - (Ncb - end_idx)) as it was (allot_llrs :198-200 zeroes the LAST Ncb - end_idx entries
+        // of the N-long buffer). The decoder sees that stretch, so in general up to 37 layers may take part; when the arena
+        // slot is known to hold zeros there, the result is the one of a first transmission into an empty buffer.
+        cls.tile_if_clean = true;
+        cls.list_fast     = (d.bg - 1) + ((d.Z == 384) ? 2 : 0);
+        cls.smem_fast     = pdc_h2_smem_bytes(d.bg, d.Z, 4);
+        cls.block_fast    = (d.Z / 2 + 31) / 32 * 32;
       }
     }
   }
@@ -425,6 +454,11 @@ struct batch_buffers {
   uint32_t       harq_slots = 0;
   size_t         llr_bytes  = (size_t)-1; // bound for llr_offset + E
   uint8_t*       d_slot_bits = nullptr;   // transport-block path: decoded bits of CBs with a HARQ slot stay with the slot
+  // Host-side bookkeeping of the arena: harq_nz[slot] = upper bound on 1 + index of the last non-zero soft bit of the slot
+  // once everything planned so far has run (0: the slot holds zeros). nz_scratch: n entries, holds the new values until the
+  // whole batch has been planned (a rejected batch changes nothing). Both null: no bookkeeping, no limited-buffer fast path.
+  int32_t* harq_nz    = nullptr;
+  int32_t* nz_scratch = nullptr;
 };
 
 // One pass over the descriptors: validation, device descriptors (dev[i], pointers included), kernel list of every code
@@ -436,6 +470,7 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
   uint32_t   cnt[PDC_NOF_LISTS] = {0}, skipped = 0;
   size_t     bits_end = 0, soft_end = 0;
   bool       any_host_soft = false, dense = true;
+  const bool track = buf.harq_nz != nullptr && buf.nz_scratch != nullptr;
   for (uint32_t i = 0; i != n; ++i) {
     const pdc_cb_desc& d = descs[i];
     if (!cls.valid || !same_class(d, cls.key)) {
@@ -446,6 +481,9 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
     pdc_dev_cb& c = dev[i];
     c             = cls.proto;
     c.res         = buf.d_res + i;
+    if (track) {
+      buf.nz_scratch[i] = -1; // no change
+    }
     const bool slot_bits = buf.d_slot_bits != nullptr && d.harq_slot >= 0 && !(d.flags & PDC_F_DECODE_ONLY);
     if (cls.list == PDC_LIST_SKIP) {
       if (!slot_bits || (uint32_t)d.harq_slot >= buf.harq_slots) {
@@ -487,8 +525,36 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
         soft_end      = se > soft_end ? se : soft_end;
       }
     }
-    lst[i] = (uint8_t)cls.list;
-    cnt[cls.list]++;
+    int list = cls.list;
+    if (track) {
+      if (cls.track != 0 && d.harq_slot >= 0) {
+        const int old = buf.harq_nz[d.harq_slot];
+        int       nz  = cls.N;
+        if (cls.track == 1) {
+          if (cls.tile_if_clean && old <= cls.end_idx) {
+            list = cls.list_fast;
+            c.flags |= PDC_DEVF_FIRST_TX_TILE;
+            c.max_layers       = 4;
+            bp.smem_h2[list]   = cls.smem_fast > bp.smem_h2[list] ? cls.smem_fast : bp.smem_h2[list];
+            bp.block_h2[list]  = cls.block_fast > bp.block_h2[list] ? cls.block_fast : bp.block_h2[list];
+          }
+          const int kept = (old > cls.end_idx) ? (old < cls.tail_start ? old : cls.tail_start) : 0;
+          nz             = kept > cls.end_idx ? kept : cls.end_idx;
+        } else {
+          nz = old > nz ? old : nz;
+        }
+        buf.nz_scratch[i] = nz;
+      }
+    }
+    lst[i] = (uint8_t)list;
+    cnt[list]++;
+  }
+  if (track) {
+    for (uint32_t i = 0; i != n; ++i) {
+      if (buf.nz_scratch[i] >= 0) {
+        buf.harq_nz[descs[i].harq_slot] = buf.nz_scratch[i];
+      }
+    }
   }
   for (int k = 0; k != PDC_NOF_PACKED_LISTS; ++k) {
     bp.n_h2[k] = cnt[k];

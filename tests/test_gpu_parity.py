@@ -142,9 +142,11 @@ def chain_case(rng, oracle, bg, Z, Qm, E, F, Nref, crc_id, sigmas, rvs, garbage=
     return dict(bg=bg, Z=Z, Qm=Qm, E=E, F=F, Nref=Nref, crc_id=crc_id, txs=txs, soft0=soft0, msg=msg)
 
 
-def run_chain(acc, oracle, cases, flavour, early_stop=True, use_arena=False, max_iter=6):
+def run_chain(acc, oracle, cases, flavour, early_stop=True, use_arena=False, max_iter=6, arena_init="write"):
     """Runs every case's transmissions in sequence (one batch per transmission index) and compares with the oracle:
-    soft buffer after every transmission, bits, iterations, CRC."""
+    soft buffer after every transmission, bits, iterations, CRC. arena_init (use_arena): "write" = the case's initial buffer is
+    written into its slot, "free" = the slot is released (zero-filled) first, "keep" = the slot keeps what earlier
+    transmissions left in it (the oracle starts from a read-back of it)."""
     from srsran_project_b200 import binding as B
 
     n = len(cases)
@@ -159,8 +161,13 @@ def run_chain(acc, oracle, cases, flavour, early_stop=True, use_arena=False, max
     soft_cpu = [c["soft0"].copy() for c in cases]
     for i, c in enumerate(cases):
         soft_gpu[soft_off[i]:soft_off[i] + c["soft0"].size] = c["soft0"]
-        if use_arena:
+        if use_arena and arena_init == "write":
             acc.harq_write(i, c["soft0"])
+        elif use_arena and arena_init == "free":
+            acc.harq_free(i)
+            soft_cpu[i][:] = 0
+        elif use_arena:
+            soft_cpu[i][:] = acc.harq_read(i, c["soft0"].size)
     for tx in range(ntx):
         idx = [i for i, c in enumerate(cases) if tx < len(c["txs"])]
         descs = B.make_descs(len(idx))
@@ -232,6 +239,35 @@ def test_chain_harq_arena_rv0_rv2(acc, oracle):
         E = (8960, 8992)[k % 2]
         cases.append(chain_case(rng, oracle, 1, 384, 8, E, 16, (0, 12611)[k % 2], CRC24B, (3.2, 3.0), (0, 2)))
     run_chain(acc, oracle, cases, FLAVOUR_AVX512, use_arena=True)
+
+
+def test_chain_limited_buffer_first_transmissions_on_arena_slots(acc, oracle):
+    """BASELINE config 2' (what the live stack asks for: Nref = 12611 < N, pusch_processor_impl.cpp:327-334). The reference leaves
+    [end, N - (Ncb - end)) of the soft buffer as it was (allot_llrs :198-200), so the decoder may see stale soft bits there. The
+    runtime keeps a bound on the non-zero extent of every arena slot: released (zeroed) slots take the four-row kernel, slots
+    with stale content beyond the new transmission's end take the general one. Both must reproduce the oracle, which starts
+    from the slot's real content: zeros, then whatever the previous transport block left."""
+    rng = np.random.default_rng(77)
+
+    def cases_for(Es):
+        out = []
+        for k, E in enumerate(Es):
+            out.append(chain_case(rng, oracle, 1, 384, 8, E, 16, 12611, CRC24B, (2.2,), (0,), garbage=False))
+        out.append(chain_case(rng, oracle, 2, 208, 4, 4 * 560, 8, 5700, CRC24A, (2.0,), (0,), garbage=False))
+        out.append(chain_case(rng, oracle, 1, 96, 6, 6 * 380, 0, 3100, CRC24B, (2.2,), (0,), garbage=False))
+        return out
+
+    for flavour in (FLAVOUR_AVX512, FLAVOUR_GENERIC):
+        # released slots: every untouched stretch holds zeros
+        run_chain(acc, oracle, cases_for([8960, 8992, 8960, 8992, 8992, 8960]), flavour, use_arena=True, arena_init="free")
+        # the same slots again, new data: where the new transmission is SHORTER than the previous one, [end_new, end_old) is stale
+        run_chain(acc, oracle, cases_for([8992, 8960, 8960, 8992, 8960, 8992]), flavour, use_arena=True, arena_init="keep")
+        # and once more: the stale stretches persist (or are covered by a longer transmission)
+        run_chain(acc, oracle, cases_for([8960, 8960, 8992, 8960, 8992, 8992]), flavour, use_arena=True, arena_init="keep")
+    # a retransmission raises the bound to the whole buffer; new data afterwards must still be right
+    cases = [chain_case(rng, oracle, 1, 384, 8, 8960, 16, 12611, CRC24B, (3.4, 3.2), (0, 2), garbage=False) for _ in range(3)]
+    run_chain(acc, oracle, cases, FLAVOUR_AVX512, use_arena=True, arena_init="free")
+    run_chain(acc, oracle, cases_for([8960, 8992, 8960])[:3], FLAVOUR_AVX512, use_arena=True, arena_init="keep")
 
 
 def test_chain_without_early_stop(acc, oracle):

@@ -41,9 +41,10 @@ def lane_ops(bg, Z, iterations, layers, max_iter=6):
     return float(it) * Z * (8.0 * cs[layers] + 2.0 * layers)
 
 
-def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None):
+def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None, stale=None):
     """cases: list of dict(bg, Z, Qm, F, Nref, crc_id, E); txs: list over transmissions of (rv list, llr list).
-    peak_ops: the roofline denominator (two-lane issue peak x 2, ops/s) measured by the caller, or None."""
+    peak_ops: the roofline denominator (two-lane issue peak x 2, ops/s) measured by the caller, or None.
+    stale: (position, value) of one soft bit that every HARQ slot holds before the first transmission (None: empty slots)."""
     import torch
 
     import srsran_project_b200 as pdc
@@ -65,6 +66,12 @@ def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None):
     d_res = torch.zeros(n * 8, dtype=torch.uint8, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     soft_cpu = np.zeros(so, np.int8)
+    if stale is not None:
+        for i, c in enumerate(cases):
+            buf = np.zeros(ns(c["bg"]) * c["Z"], np.int8)
+            buf[stale[0]] = stale[1]
+            soft_cpu[int(soft_off[i]) + stale[0]] = stale[1]
+            ctx.harq_write(i, buf)
     out = {"config": name, "code_blocks": n, "transmissions": []}
     for t, (rvs, llr_list) in enumerate(txs):
         llr_off = np.zeros(n, np.uint64)
@@ -96,7 +103,10 @@ def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None):
         ms = 0.0
         for rep in range(steps + 1):
             for i in range(n):
-                ctx.harq_write(i, snap[i])
+                if snap[i].any():
+                    ctx.harq_write(i, snap[i])
+                else:
+                    ctx.harq_free(i)  # zero-filled and known to the runtime as empty (limited-buffer first transmissions)
             torch.cuda.synchronize()
             e0.record()
             ctx.decode_device(d, d_llrs.data_ptr(), None, d_bits.data_ptr(), d_res.data_ptr(), st)
@@ -206,17 +216,56 @@ def config4(S, steps, sigma1, sigma2, n_tbs=8, cpu=True, peak_ops=None):
                      f"code blocks BG1 Z=384", cases, txs, steps, cpu=cpu, peak_ops=peak_ops)
 
 
+def config2_lbrm(S, steps, sigma=2.2, n_tbs=8, cpu=True, peak_ops=None):
+    """BASELINE config 2' (the live stack's limited-buffer rate matching, Nref = 12611 < N = 25344,
+    pusch_processor_impl.cpp:327-334): n_tbs config-2 transport blocks, first transmissions into released HARQ arena slots, and
+    the same batch with Nref = 0 beside it."""
+    c = S.CONFIG2
+    seg = S.segmentation(c["bg"], c["tbs"])
+    Es = S.rm_lengths(seg["C"], c["G"], c["nof_layers"], c["Qm"])
+    out = None
+    for nref in (12611, 0):
+        cases = [dict(bg=1, Z=seg["Z"], Qm=8, F=seg["F"], Nref=nref, crc_id=3) for _ in range(seg["C"] * n_tbs)]
+        txs = [([], [])]
+        for k in range(n_tbs):
+            rng = np.random.default_rng(5 + 100 * k)
+            tb = rng.integers(0, 2, c["tbs"], dtype=np.uint8)
+            _, bits, _ = S.tb_encode(c["bg"], c["tbs"], tb, 0, c["Qm"], nref, c["nof_layers"], c["G"])
+            x = S.awgn_llrs(bits, 8.0, sigma, 51 + 1000 * k)
+            p = 0
+            for r in range(seg["C"]):
+                txs[0][1].append(x[p:p + Es[r]])
+                txs[0][0].append(0)
+                p += Es[r]
+        r = run_batch(f"config 2': limited-buffer rate matching (Nref = 12611), {n_tbs} TBs x 152 code blocks BG1 Z=384, first "
+                      f"transmissions into released arena slots", cases, txs, steps, cpu=cpu and nref != 0, peak_ops=peak_ops)
+        if nref != 0:
+            out, txs_lbrm = r, txs
+        else:
+            out["same_batch_with_Nref_0"] = {k: r["transmissions"][0][k] for k in ("gpu_ms", "value", "avg_iterations")}
+    # The same limited-buffer batch into slots that hold ONE stale soft bit in the stretch the reference leaves untouched
+    # ([end, N - (Ncb - end)), allot_llrs :198-200): the decoder sees it, 35 layers take part, the general kernel runs.
+    cases = [dict(bg=1, Z=seg["Z"], Qm=8, F=seg["F"], Nref=12611, crc_id=3) for _ in range(seg["C"] * n_tbs)]
+    r = run_batch("config 2' with one stale soft bit at position 20000 of every slot", cases, txs_lbrm, max(2, steps // 2), cpu=cpu,
+                  peak_ops=peak_ops, stale=(20000, 5))
+    t = r["transmissions"][0]
+    out["stale_slots"] = {k: t[k] for k in ("gpu_ms", "value", "avg_iterations", "layers_min_max", "bit_exact") if k in t}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--sigma1", type=float, default=3.0)
     ap.add_argument("--sigma2", type=float, default=6.0)
     ap.add_argument("--tbs", type=int, default=8, help="config 4: transport blocks in the batch")
-    ap.add_argument("--only", type=int, default=0, help="3 or 4: run that configuration alone")
+    ap.add_argument("--only", type=int, default=0, help="2, 3 or 4: run that configuration alone")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     from tools import stimulus as S
 
+    if args.only in (0, 2):
+        print(json.dumps(config2_lbrm(S, args.steps, cpu=not args.no_cpu)), flush=True)
     if args.only in (0, 3):
         print(json.dumps(config3(S, args.steps, cpu=not args.no_cpu)), flush=True)
     if args.only in (0, 4):
