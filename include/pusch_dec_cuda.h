@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PDC_ABI_VERSION 8
+#define PDC_ABI_VERSION 9
 
 typedef enum {
   PDC_OK               = 0,
@@ -323,6 +323,12 @@ pdc_status pdc_pdsch_segmentation(int bg, uint32_t tbs_bits, uint32_t* nof_cbs, 
 
 /* --- HARQ arena (ext_harq_buffer_context_repository.h:36-107 / free_harq_context_entry) --------------------------- */
 pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot);                               /* zero-fills the slot */
+/* The slot's content is no longer needed (hw_accelerator_pusch_dec::free_harq_context_entry, hw_accelerator_pusch_dec.h:107-110):
+ * from now on it READS AS ZEROS. Host-side bookkeeping only, no CUDA call: a first transmission rewrites the whole buffer
+ * anyway; any other operation on a released slot has it cleared on its stream first. With it, first transmissions under
+ * limited-buffer rate matching (Nref < N: the reference leaves a stretch of the buffer untouched, ldpc_rate_dematcher_impl.cpp
+ * :198-200) find that stretch empty and take the four-row kernel. */
+pdc_status pdc_harq_release(pdc_ctx* ctx, int32_t slot);
 pdc_status pdc_harq_read(pdc_ctx* ctx, int32_t slot, int8_t* host_dst, size_t n);   /* test / debug access */
 pdc_status pdc_harq_write(pdc_ctx* ctx, int32_t slot, const int8_t* host_src, size_t n);
 

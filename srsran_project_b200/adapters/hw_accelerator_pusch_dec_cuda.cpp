@@ -140,9 +140,18 @@ public:
     out = (cb_index < MAX_CBS) ? outputs[cb_index] : hw_pusch_decoder_outputs{false, 0};
   }
 
-  // The arena slot of a released code block needs no clean-up: a new transmission (new_data) rewrites it with the
-  // dematcher's write set, exactly like the host buffer that rx_buffer_codeblock_pool hands out again without clearing.
-  void free_harq_context_entry(unsigned /*absolute_cb_id*/) override {}
+  // "Frees the HARQ context entry" (hw_accelerator_pusch_dec.h:107-110; called per code block once its transport block has
+  // passed the CRC, pusch_decoder_hw_impl.cpp:413-428): the arena slot reads as zeros from now on. No CUDA call: the runtime
+  // notes it and clears lazily (pdc_harq_release). An entry that is never freed (a transport block that failed for good)
+  // keeps its content, and a later first transmission meets what the reference's dematcher would meet in a host buffer that
+  // rx_buffer_codeblock_pool hands out again without clearing: whatever the write set of the new transmission leaves.
+  void free_harq_context_entry(unsigned absolute_cb_id) override
+  {
+    if (external) {
+      const unsigned G = static_cast<unsigned>(batchers.size());
+      pdc_harq_release(batchers[absolute_cb_id % G]->context().get(), static_cast<int32_t>(absolute_cb_id / G));
+    }
+  }
 
   bool is_harq_external() const override { return external; }
 

@@ -137,6 +137,7 @@ def load_library():
     u32p = ctypes.POINTER(ctypes.c_uint32)
     lib.pdc_pdsch_segmentation.argtypes = [ctypes.c_int, ctypes.c_uint32, u32p, u32p, u32p, u32p]
     lib.pdc_harq_free.argtypes = [vp, ctypes.c_int32]
+    lib.pdc_harq_release.argtypes = [vp, ctypes.c_int32]
     lib.pdc_harq_read.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_harq_write.argtypes = [vp, ctypes.c_int32, vp, ctypes.c_size_t]
     lib.pdc_kernel_launches.argtypes = [vp]
@@ -156,7 +157,7 @@ EXPORTED_SYMBOLS = ["pdc_create", "pdc_destroy", "pdc_last_error", "pdc_abi_vers
                     "pdc_decode_device_tbs_static",
                     "pdc_demodulate_device", "pdc_demodulate", "pdc_ulsch_demux_lengths",
                     "pdc_ulsch_demultiplex_device", "pdc_ulsch_demultiplex", "pdc_pdsch_encode", "pdc_pdsch_encode_device",
-                    "pdc_pdsch_segmentation", "pdc_harq_free", "pdc_harq_read", "pdc_harq_write",
+                    "pdc_pdsch_segmentation", "pdc_harq_free", "pdc_harq_release", "pdc_harq_read", "pdc_harq_write",
                     "pdc_kernel_launches", "pdc_probe_issue_rate", "pdc_cb_message_bits", "pdc_cb_buffer_len", "pdc_cb_max_layers"]
 
 
@@ -326,6 +327,10 @@ class PuschDecCuda:
     # --- HARQ arena ------------------------------------------------------------------------------------------------
     def harq_free(self, slot):
         self._check(self.lib.pdc_harq_free(self.h, slot))
+
+    def harq_release(self, slot):
+        """The slot reads as zeros from now on (host-side bookkeeping, cleared lazily): pdc_harq_release."""
+        self._check(self.lib.pdc_harq_release(self.h, slot))
 
     def harq_read(self, slot, n):
         out = np.zeros(n, np.int8)

@@ -138,6 +138,7 @@ pdc_status pdc_create(const pdc_config* cfg, pdc_ctx** out)
   pdc_ctx* ctx = new pdc_ctx;
   ctx->cfg     = *cfg;
   ctx->harq_nz.assign(cfg->harq_slots, 0); // the arena is created zeroed
+  ctx->harq_released.assign(cfg->harq_slots, 0);
   if (const char* tr = std::getenv("PDC_TRACE")) {
     ctx->trace = tr[0] == '1';
   }
@@ -315,6 +316,28 @@ static pdc_status ring_reserve(pdc_ctx* ctx, pdc_ctx::demod_slot (&ring)[8], siz
     }                                                                                                                  \
   } while (0)
 
+// Arena bookkeeping of a planned batch (batch_buffers): where plan_batch keeps its scratch, and the clearing of released slots
+// that the batch touches without rewriting them (stream-ordered, before the kernels).
+static void arena_tracking(pdc_ctx* ctx, batch_buffers& buf, int32_t* nz_scratch, int32_t* zero_slots, uint32_t* nof_zero_slots)
+{
+  *nof_zero_slots    = 0;
+  buf.harq_nz        = ctx->harq_nz.data();
+  buf.nz_scratch     = nz_scratch;
+  buf.harq_released  = ctx->harq_released.data();
+  buf.zero_slots     = zero_slots;
+  buf.nof_zero_slots = nof_zero_slots;
+}
+static cudaError_t clear_released_slots(pdc_ctx* ctx, const int32_t* zero_slots, uint32_t nof_zero_slots, cudaStream_t stream)
+{
+  for (uint32_t k = 0; k != nof_zero_slots; ++k) {
+    cudaError_t e = cudaMemsetAsync(ctx->d_harq + (size_t)zero_slots[k] * PDC_MAX_N, 0, PDC_MAX_N, stream);
+    if (e != cudaSuccess) {
+      return e;
+    }
+  }
+  return cudaSuccess;
+}
+
 // pdc_submit (tbs == nullptr) and pdc_submit_tbs.
 // stage != nullptr (pdc_submit_staged): the LLRs already lie in the stage's device arena (llr_offset relative to its base).
 static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t n, const pdc_tb_desc* tbs, uint32_t ntb,
@@ -350,7 +373,8 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
   batch_plan bp;
   t->lst.resize(n);
   t->nz.resize(n);
-  buf.harq_nz = ctx->harq_nz.data(), buf.nz_scratch = t->nz.data();
+  t->zero_slots.resize(n);
+  arena_tracking(ctx, buf, t->nz.data(), t->zero_slots.data(), &t->nof_zero_slots);
   pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
@@ -381,7 +405,9 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
         return release_ticket(ctx, t, st);
       }
       buf.d_soft = t->d_soft;
-      buf.harq_nz = nullptr, buf.nz_scratch = nullptr; // the arena bookkeeping was done by the first pass
+      // The arena bookkeeping of the first pass stands (planning again from the state it left gives the same decisions);
+      // only the list of released slots to clear must not be started over.
+      buf.zero_slots = nullptr, buf.nof_zero_slots = nullptr;
       batch_plan again;
       st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), again);
       if (st != PDC_OK) {
@@ -390,6 +416,7 @@ static pdc_status submit_common(pdc_ctx* ctx, const pdc_cb_desc* descs, uint32_t
       bp = again;
     }
   }
+  CKT(clear_released_slots(ctx, t->zero_slots.data(), t->nof_zero_slots, t->stream));
   // Stage and go. With pdc_set_zero_copy, LLRs that already lie in pinned (or registered) memory are sent from where they
   // lie: the caller then keeps them untouched until the ticket has completed.
   const int8_t* src    = llrs;
@@ -761,7 +788,8 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
   batch_plan bp;
   t->lst.resize(n);
   t->nz.resize(n);
-  buf.harq_nz = ctx->harq_nz.data(), buf.nz_scratch = t->nz.data();
+  t->zero_slots.resize(n);
+  arena_tracking(ctx, buf, t->nz.data(), t->zero_slots.data(), &t->nof_zero_slots);
   pdc_status st = plan_batch(descs, n, buf, t->h_cbs, t->h_order, t->lst.data(), bp);
   if (st == PDC_OK && bp.any_host_soft && !d_soft) {
     st = PDC_ERR_INVALID_ARG;
@@ -774,6 +802,7 @@ static pdc_status decode_device_common(pdc_ctx* ctx, const pdc_cb_desc* descs, u
   if (st != PDC_OK) {
     return release_ticket(ctx, t, st);
   }
+  CKT(clear_released_slots(ctx, t->zero_slots.data(), t->nof_zero_slots, stream));
   CKT(cudaMemcpyAsync(t->d_cbs, t->h_cbs, sizeof(pdc_dev_cb) * n + sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, stream));
   if (!bp.identity) {
     CKT(cudaMemcpyAsync(t->d_order, t->h_order, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, stream));
@@ -833,6 +862,8 @@ static struct {
   uint32_t   order[PDC_STATIC_MAX_CBS];
   uint8_t    lst[PDC_STATIC_MAX_CBS];
   int32_t    nz[PDC_STATIC_MAX_CBS];
+  int32_t    zero_slots[PDC_STATIC_MAX_CBS];
+  uint32_t   nof_zero_slots;
 } g_static_host; // .bss, nothing is allocated per call
 
 static pdc_status static_scratch_address(pdc_ctx* ctx, unsigned char** out)
@@ -885,7 +916,7 @@ pdc_status pdc_decode_device_tbs_static(pdc_ctx* ctx, const pdc_cb_desc* descs, 
   buf.d_harq = ctx->d_harq, buf.harq_slots = ctx->cfg.harq_slots;
   buf.d_slot_bits = ctx->d_harq_bits;
   batch_plan bp;
-  buf.harq_nz = ctx->harq_nz.data(), buf.nz_scratch = g_static_host.nz;
+  arena_tracking(ctx, buf, g_static_host.nz, g_static_host.zero_slots, &g_static_host.nof_zero_slots);
   st = plan_batch(descs, n, buf, g_static_host.cbs, g_static_host.order, g_static_host.lst, bp);
   if (st == PDC_OK) {
     uint32_t processed = bp.n_lane; // code blocks a kernel reads LLRs for (all but the PDC_F_DECODED ones)
@@ -905,6 +936,7 @@ pdc_status pdc_decode_device_tbs_static(pdc_ctx* ctx, const pdc_cb_desc* descs, 
   }
   // Pageable sources: cudaMemcpyAsync returns once they have been staged, so the host image is free for the next call when
   // the lock is released. The array keeps the previous call's contents: the CRC shares start from zero again.
+  CK(clear_released_slots(ctx, g_static_host.zero_slots, g_static_host.nof_zero_slots, stream));
   CK(cudaMemcpyAsync(d_cbs, g_static_host.cbs, sizeof(pdc_dev_cb) * n, cudaMemcpyHostToDevice, stream));
   CK(cudaMemcpyAsync(d_tbs, g_static_host.tbs, sizeof(pdc_dev_tb) * ntb, cudaMemcpyHostToDevice, stream));
   if (!bp.identity) {
@@ -1577,7 +1609,21 @@ pdc_status pdc_harq_free(pdc_ctx* ctx, int32_t slot)
   std::lock_guard<std::mutex> lock(ctx->mtx);
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaMemset(ctx->d_harq + (size_t)slot * PDC_MAX_N, 0, PDC_MAX_N));
-  ctx->harq_nz[slot] = 0;
+  ctx->harq_nz[slot]       = 0;
+  ctx->harq_released[slot] = 0;
+  return PDC_OK;
+}
+
+pdc_status pdc_harq_release(pdc_ctx* ctx, int32_t slot)
+{
+  if (!ctx || slot < 0 || (uint32_t)slot >= ctx->cfg.harq_slots) {
+    return PDC_ERR_INVALID_ARG;
+  }
+  // Host-side only: the next operation on the slot either rewrites the whole buffer (a first transmission) or has the slot
+  // cleared on its stream first (plan_batch / clear_released_slots).
+  if (ctx->harq_nz[slot] != 0) {
+    ctx->harq_released[slot] = 1;
+  }
   return PDC_OK;
 }
 
@@ -1589,6 +1635,10 @@ pdc_status pdc_harq_read(pdc_ctx* ctx, int32_t slot, int8_t* host_dst, size_t n)
   std::lock_guard<std::mutex> lock(ctx->mtx);
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaDeviceSynchronize());
+  if (ctx->harq_released[slot]) { // reads as zeros: clear it for real now
+    CK(cudaMemset(ctx->d_harq + (size_t)slot * PDC_MAX_N, 0, PDC_MAX_N));
+    ctx->harq_nz[slot] = 0, ctx->harq_released[slot] = 0;
+  }
   CK(cudaMemcpy(host_dst, ctx->d_harq + (size_t)slot * PDC_MAX_N, n, cudaMemcpyDeviceToHost));
   return PDC_OK;
 }
@@ -1601,6 +1651,10 @@ pdc_status pdc_harq_write(pdc_ctx* ctx, int32_t slot, const int8_t* host_src, si
   std::lock_guard<std::mutex> lock(ctx->mtx);
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaDeviceSynchronize());
+  if (ctx->harq_released[slot]) {
+    CK(cudaMemset(ctx->d_harq + (size_t)slot * PDC_MAX_N, 0, PDC_MAX_N));
+    ctx->harq_nz[slot] = 0, ctx->harq_released[slot] = 0;
+  }
   CK(cudaMemcpy(ctx->d_harq + (size_t)slot * PDC_MAX_N, host_src, n, cudaMemcpyHostToDevice));
   ctx->harq_nz[slot] = std::max(ctx->harq_nz[slot], (int32_t)n);
   return PDC_OK;

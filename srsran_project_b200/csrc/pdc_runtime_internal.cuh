@@ -82,6 +82,8 @@ struct ticket_t {
   std::vector<pdc_cb_desc> descs;
   std::vector<uint8_t>     lst; // kernel list of every code block (planner scratch)
   std::vector<int32_t>     nz;  // planner scratch: new non-zero extents of the arena slots (batch_buffers::nz_scratch)
+  std::vector<int32_t>     zero_slots; // planner scratch: released arena slots to clear before the kernels
+  uint32_t                 nof_zero_slots = 0;
   size_t                   bits_bytes = 0, soft_bytes = 0;
   bool                     soft_back  = false, bits_dense = false;
   bool                     borrowed   = false; // staging lent to pdc_decode_device: its copy may still be in flight
@@ -127,6 +129,7 @@ struct pdc_ctx {
   uint32_t*             d_crc_bit = nullptr;
   int8_t*               d_harq   = nullptr;
   std::vector<int32_t>  harq_nz;            // per arena slot: bound on the extent of non-zero soft bits (batch_buffers::harq_nz)
+  std::vector<uint8_t>  harq_released;      // per arena slot: released, reads as zeros, memory not cleared yet (pdc_harq_release)
   uint8_t*              d_harq_bits = nullptr; // decoded bits kept with every HARQ slot (transport-block path), PDC_MAX_K / 8 each
   std::atomic<uint64_t> launches{0};
   size_t                bits_stride_total = 0;
@@ -459,6 +462,12 @@ struct batch_buffers {
   // whole batch has been planned (a rejected batch changes nothing). Both null: no bookkeeping, no limited-buffer fast path.
   int32_t* harq_nz    = nullptr;
   int32_t* nz_scratch = nullptr;
+  // pdc_harq_release: harq_released[slot] != 0 = the slot reads as zeros although its memory has not been cleared yet. A first
+  // transmission that rewrites the whole buffer needs no clearing; any other operation on such a slot is listed in
+  // zero_slots[0 .. *nof_zero_slots) (room for n entries) and the caller clears those slots on the stream before the kernels.
+  uint8_t*  harq_released  = nullptr;
+  int32_t*  zero_slots     = nullptr;
+  uint32_t* nof_zero_slots = nullptr;
 };
 
 // One pass over the descriptors: validation, device descriptors (dev[i], pointers included), kernel list of every code
@@ -528,8 +537,12 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
     int list = cls.list;
     if (track) {
       if (cls.track != 0 && d.harq_slot >= 0) {
-        const int old = buf.harq_nz[d.harq_slot];
-        int       nz  = cls.N;
+        const bool released = buf.harq_released != nullptr && buf.harq_released[d.harq_slot] != 0;
+        const int  old      = released ? 0 : buf.harq_nz[d.harq_slot];
+        int        nz       = cls.N;
+        // Everything of the buffer is rewritten by a one-lap first transmission without a buffer limit (and by the staging
+        // tile of the four-row kernel, below); otherwise a released slot has to be cleared for real first.
+        bool rewrites_all = (cls.track == 1 && cls.tail_start == cls.end_idx);
         if (cls.track == 1) {
           if (cls.tile_if_clean && old <= cls.end_idx) {
             list = cls.list_fast;
@@ -537,6 +550,7 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
             c.max_layers       = 4;
             bp.smem_h2[list]   = cls.smem_fast > bp.smem_h2[list] ? cls.smem_fast : bp.smem_h2[list];
             bp.block_h2[list]  = cls.block_fast > bp.block_h2[list] ? cls.block_fast : bp.block_h2[list];
+            rewrites_all       = true;
           }
           const int kept = (old > cls.end_idx) ? (old < cls.tail_start ? old : cls.tail_start) : 0;
           nz             = kept > cls.end_idx ? kept : cls.end_idx;
@@ -544,6 +558,9 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
           nz = old > nz ? old : nz;
         }
         buf.nz_scratch[i] = nz;
+        if (released && !rewrites_all && buf.zero_slots != nullptr) {
+          buf.zero_slots[(*buf.nof_zero_slots)++] = d.harq_slot;
+        }
       }
     }
     lst[i] = (uint8_t)list;
@@ -553,6 +570,9 @@ pdc_status plan_batch(const pdc_cb_desc* descs, uint32_t n, const batch_buffers&
     for (uint32_t i = 0; i != n; ++i) {
       if (buf.nz_scratch[i] >= 0) {
         buf.harq_nz[descs[i].harq_slot] = buf.nz_scratch[i];
+        if (buf.harq_released != nullptr) {
+          buf.harq_released[descs[i].harq_slot] = 0;
+        }
       }
     }
   }

@@ -442,6 +442,9 @@ int adt_bench_hal(unsigned       nthreads,
   cfg.rv                  = 0;
   cfg.mod                 = static_cast<modulation_scheme>(Qm);
   cfg.Nref                = 0;
+  if (const char* e = std::getenv("ADT_NREF")) { // limited-buffer rate matching as the live stack sets it (pusch_processor_impl.cpp:327)
+    cfg.Nref = (unsigned)std::atoi(e);
+  }
   cfg.nof_layers          = nof_layers;
   cfg.nof_ldpc_iterations = max_iter;
   cfg.force_decoding      = false;

@@ -145,7 +145,7 @@ def chain_case(rng, oracle, bg, Z, Qm, E, F, Nref, crc_id, sigmas, rvs, garbage=
 def run_chain(acc, oracle, cases, flavour, early_stop=True, use_arena=False, max_iter=6, arena_init="write"):
     """Runs every case's transmissions in sequence (one batch per transmission index) and compares with the oracle:
     soft buffer after every transmission, bits, iterations, CRC. arena_init (use_arena): "write" = the case's initial buffer is
-    written into its slot, "free" = the slot is released (zero-filled) first, "keep" = the slot keeps what earlier
+    written into its slot, "free" = the slot is zero-filled first, "release" = pdc_harq_release, "keep" = the slot keeps what earlier
     transmissions left in it (the oracle starts from a read-back of it)."""
     from srsran_project_b200 import binding as B
 
@@ -165,6 +165,9 @@ def run_chain(acc, oracle, cases, flavour, early_stop=True, use_arena=False, max
             acc.harq_write(i, c["soft0"])
         elif use_arena and arena_init == "free":
             acc.harq_free(i)
+            soft_cpu[i][:] = 0
+        elif use_arena and arena_init == "release":
+            acc.harq_release(i)  # reads as zeros from now on, cleared lazily
             soft_cpu[i][:] = 0
         elif use_arena:
             soft_cpu[i][:] = acc.harq_read(i, c["soft0"].size)
@@ -268,6 +271,19 @@ def test_chain_limited_buffer_first_transmissions_on_arena_slots(acc, oracle):
     cases = [chain_case(rng, oracle, 1, 384, 8, 8960, 16, 12611, CRC24B, (3.4, 3.2), (0, 2), garbage=False) for _ in range(3)]
     run_chain(acc, oracle, cases, FLAVOUR_AVX512, use_arena=True, arena_init="free")
     run_chain(acc, oracle, cases_for([8960, 8992, 8960])[:3], FLAVOUR_AVX512, use_arena=True, arena_init="keep")
+    # pdc_harq_release (what free_harq_context_entry maps to): the slots read as zeros without having been cleared; limited-buffer
+    # first transmissions rewrite them, ...
+    run_chain(acc, oracle, cases, FLAVOUR_AVX512, use_arena=True, arena_init="free")  # leaves rv0 + rv2 content everywhere
+    run_chain(acc, oracle, cases_for([8960, 8992, 8960, 8992, 8992, 8960]), FLAVOUR_AVX512, use_arena=True, arena_init="release")
+    # ... a low-rate limited-buffer first transmission (does not fit the staging tile, leaves a stretch untouched) and a
+    # combining transmission into a released slot have the slot cleared on the stream first
+    run_chain(acc, oracle, cases, FLAVOUR_AVX512, use_arena=True, arena_init="free")
+    low = [chain_case(rng, oracle, 1, 384, 4, 15000, 16, 20000, CRC24B, (3.0,), (0,), garbage=False) for _ in range(2)]
+    low.append(chain_case(rng, oracle, 1, 384, 8, 8960, 16, 12611, CRC24B, (3.0,), (2,), garbage=False))  # starts at rv 2
+    run_chain(acc, oracle, low, FLAVOUR_AVX512, use_arena=True, arena_init="release")
+    assert (acc.harq_read(5, 25344) != 0).any()  # slot 5 still holds the first batch's second case ...
+    acc.harq_release(5)
+    assert not acc.harq_read(5, 25344).any()     # ... and reads as zeros once released
 
 
 def test_chain_without_early_stop(acc, oracle):

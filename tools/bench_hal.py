@@ -81,6 +81,16 @@ def run(threads, tbs_per_thread=24, n_distinct=16, devices=(0,), max_parts=8, cl
     if r["ok"] != r["attempted"]:
         raise RuntimeError(f"e2e_hal: {r['attempted'] - r['ok']} of {r['attempted']} transport blocks differ from the transmitted ones")
     nb = max(r["batches"], 1)
+    # The same with limited-buffer rate matching as the live stack always configures it (Nref = 12611 for this transport block:
+    # pusch_processor_impl.cpp:327-334, SURVEY 8 config 2'); a first transmission's LLRs are the same with and without the limit.
+    os.environ["ADT_NREF"] = "12611"
+    try:
+        rl = run_raw(llrs, tbs, c["tbs"], c["bg"], c["Qm"], c["nof_layers"], 6, threads, tbs_per_thread, devices=devices,
+                     max_parts=max_parts, close_after_us=close_after_us)
+    finally:
+        del os.environ["ADT_NREF"]
+    if rl["ok"] != rl["attempted"]:
+        raise RuntimeError(f"e2e_hal (Nref = 12611): {rl['attempted'] - rl['ok']} of {rl['attempted']} transport blocks differ")
     # The same threads over an accelerator that answers at once: what the reference's own host code (soft-bit buffering,
     # segmentation, per-code-block CRC checks, bit-granular TB assembly, TB CRC) allows through this boundary on this host.
     h = run_raw(llrs, tbs, c["tbs"], c["bg"], c["Qm"], c["nof_layers"], 6, threads, tbs_per_thread, replay=msgs)
@@ -88,6 +98,7 @@ def run(threads, tbs_per_thread=24, n_distinct=16, devices=(0,), max_parts=8, cl
         raise RuntimeError("e2e_hal: the replay accelerator run did not reproduce the transport blocks")
     ceiling = h["attempted"] * c["tbs"] / h["seconds"] / 1e9
     return {"value": r["attempted"] * c["tbs"] / r["seconds"] / 1e9, "unit": "Gbit/s", "host_threads": threads,
+            "value_limited_buffer_Nref_12611": rl["attempted"] * c["tbs"] / rl["seconds"] / 1e9,
             "host_ceiling": ceiling, "frac_of_host_ceiling": r["attempted"] * c["tbs"] / r["seconds"] / 1e9 / ceiling,
             "host_ceiling_source": "same threads and transport blocks through the reference's pusch_decoder_hw_impl over a replay "
                                    "accelerator that answers at once (tests/adapters/harness.cpp): the host cost of the boundary",
