@@ -270,11 +270,33 @@ void build_crc_bit_tables(const std::vector<uint32_t>& pow, std::vector<uint32_t
   }
 }
 
-// Validates one descriptor the way the reference's asserts would and fills the derived fields.
-bool validate_desc(const pdc_cb_desc& d, pdc_geom& g, int& max_layers)
+// pdc_lifting_pos through a table (the planner calls it for every class of a batch).
+inline int lifting_pos_of(unsigned Z)
 {
-  if (!pdc_geom_init(g, d.bg, d.Z) || pdc_lifting_pos(d.Z) < 0) {
+  struct table {
+    int8_t pos[PDC_MAX_Z + 1];
+    table()
+    {
+      for (int z = 0; z <= PDC_MAX_Z; ++z) {
+        pos[z] = (int8_t)pdc_lifting_pos(z);
+      }
+    }
+  };
+  static const table t;
+  return (Z <= PDC_MAX_Z) ? t.pos[Z] : -1;
+}
+
+// Validates one descriptor the way the reference's asserts would and fills the derived fields. pl_out / zpos_out: the
+// dematcher's plan (valid unless the descriptor is decode-only) and the position of Z in the list of lifting sizes, for callers
+// that go on with them.
+bool validate_desc(const pdc_cb_desc& d, pdc_geom& g, int& max_layers, pdc_dematch_plan* pl_out = nullptr, int* zpos_out = nullptr)
+{
+  const int zpos = lifting_pos_of(d.Z);
+  if (!pdc_geom_init(g, d.bg, d.Z) || zpos < 0) {
     return false;
+  }
+  if (zpos_out) {
+    *zpos_out = zpos;
   }
   if (d.max_iter == 0 || d.crc_type > PDC_CRC24B) {
     return false;
@@ -297,6 +319,9 @@ bool validate_desc(const pdc_cb_desc& d, pdc_geom& g, int& max_layers)
     return false;
   }
   max_layers = pdc_layers_for_nz(g, pdc_dematch_nz_bound(pl));
+  if (pl_out) {
+    *pl_out = pl;
+  }
   return true;
 }
 
@@ -377,16 +402,18 @@ inline bool same_class(const pdc_cb_desc& a, const pdc_cb_desc& b)
 
 bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
 {
-  pdc_geom g;
-  int      ml = 0;
-  cls.valid   = false;
+  pdc_geom         g;
+  pdc_dematch_plan pl;
+  int              ml = 0, zpos = -1;
+  cls.valid           = false;
   if (d.flags & PDC_F_DECODED) {
     // Only the geometry matters: the code block is not processed again.
-    if (!pdc_geom_init(g, d.bg, d.Z) || pdc_lifting_pos(d.Z) < 0 || d.crc_type == PDC_CRC_NONE || d.crc_type > PDC_CRC24B ||
+    zpos = lifting_pos_of(d.Z);
+    if (!pdc_geom_init(g, d.bg, d.Z) || zpos < 0 || d.crc_type == PDC_CRC_NONE || d.crc_type > PDC_CRC24B ||
         (uint64_t)d.nof_filler >= (uint64_t)g.K) {
       return false;
     }
-  } else if (!validate_desc(d, g, ml)) {
+  } else if (!validate_desc(d, g, ml, &pl, &zpos)) {
     return false;
   }
   cls.key       = d;
@@ -397,8 +424,7 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
   c.flags = d.flags & (uint8_t)~PDC_DEVF_FIRST_TX_TILE;
   cls.track = 0, cls.tile_if_clean = false;
   if (!(d.flags & (PDC_F_DECODED | PDC_F_DECODE_ONLY))) {
-    pdc_dematch_plan pl;
-    if (pdc_dematch_plan_init(pl, g, (int)d.E, d.Qm, d.rv, (int)d.Nref, (int)d.nof_filler, (d.flags & PDC_F_NEW_DATA) != 0)) {
+    { // pl: the plan validate_desc derived
       cls.track = 2;
       if (pl.final_zero) { // new data, one lap, ends before Ncb
         cls.track      = 1;
@@ -422,7 +448,7 @@ bool classify(const pdc_cb_desc& d, desc_class& cls, batch_plan& bp)
       }
     }
   }
-  c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + pdc_lifting_pos(d.Z));
+  c.graph_idx  = (uint16_t)((d.bg - 1) * PDC_NOF_LIFTING_SIZES + zpos);
   c.max_layers = (uint16_t)ml;
   cls.K_bytes4 = (size_t)((g.K + 31) / 32) * 4;
   cls.N        = (uint32_t)g.N;

@@ -13,6 +13,7 @@ import argparse
 import json
 import os
 import sys
+import time
 
 import numpy as np
 
@@ -100,7 +101,7 @@ def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None, stale=None):
         # combines the wrapped LLRs with whatever is there (allot_llrs :148-158) - repeated runs would accumulate.
         snap = [ctx.harq_read(i, ns(c["bg"]) * c["Z"]) for i, c in enumerate(cases)]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ms = 0.0
+        ms = host_us = 0.0
         for rep in range(steps + 1):
             for i in range(n):
                 if snap[i].any():
@@ -109,17 +110,21 @@ def run_batch(name, cases, txs, steps, cpu=True, peak_ops=None, stale=None):
                     ctx.harq_free(i)  # zero-filled and known to the runtime as empty (limited-buffer first transmissions)
             torch.cuda.synchronize()
             e0.record()
+            t_host = time.perf_counter()
             ctx.decode_device(d, d_llrs.data_ptr(), None, d_bits.data_ptr(), d_res.data_ptr(), st)
+            t_host = time.perf_counter() - t_host
             e1.record()
             torch.cuda.synchronize()
             if rep > 0:
                 ms += e0.elapsed_time(e1)
+                host_us += 1e6 * t_host
         ms /= steps
+        host_us /= steps
         res = d_res.cpu().numpy().view(B.RESULT_DTYPE)
         bits = d_bits.cpu().numpy()
         info = sum(kb(c["bg"]) * c["Z"] - c["F"] - (16 if c["crc_id"] == 1 else 24) for c in cases)
         ops = sum(lane_ops(c["bg"], c["Z"], int(res["iterations"][i]), int(res["nof_layers"][i])) for i, c in enumerate(cases))
-        rec = {"tx": t, "gpu_ms": ms, "gpu_info_gbps": info / (ms * 1e-3) / 1e9, "value": info / (ms * 1e-3) / 1e9,
+        rec = {"tx": t, "gpu_ms": ms, "host_call_us": host_us, "gpu_info_gbps": info / (ms * 1e-3) / 1e9, "value": info / (ms * 1e-3) / 1e9,
                "roofline": {"bound": "alu", "achieved": ops / (ms * 1e-3) / 1e12, "unit": "Tops/s (int8 lane-ops)",
                             "peak": None if peak_ops is None else peak_ops / 1e12,
                             "frac": None if peak_ops is None else ops / (ms * 1e-3) / peak_ops},
