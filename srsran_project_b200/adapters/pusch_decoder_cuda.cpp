@@ -187,6 +187,11 @@ private:
       softbuffer->reset_codeblocks_crc(); // a false positive among the code blocks: decode all of them again (:424-427)
     }
     if (stats.tb_crc_ok) {
+      // The transport block is done: its soft bits are no longer needed (pusch_decoder_hw_impl.cpp:413-428 frees the
+      // accelerator's HARQ context entries here). The arena slots read as zeros from now on (host-side note, no CUDA call).
+      for (unsigned cb = 0; cb != nof_cbs; ++cb) {
+        pdc_harq_release(context->get(), descs[cb].harq_slot);
+      }
       softbuffer.release();
     } else {
       softbuffer.unlock();
