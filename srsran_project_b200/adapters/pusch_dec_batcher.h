@@ -15,8 +15,8 @@
 //              stream) and the part joins the queue of ready parts — it does not wait for anybody else's part
 //   poll()     "not ready" until the part's batch has run (hw_accelerator::dequeue_operation may return false:
 //              pusch_decoder_hw_impl.cpp:325-338 spins on it). A batch is formed from the ready parts — ONE pdc_submit_staged:
-//              one launch per kernel variant over LLRs that are already on the device, one D2H copy — as soon as max_parts are
-//              ready, OR the device has nothing in flight, OR the oldest ready part has waited close_after_us: an idle device is
+//              one launch per kernel variant over LLRs that are already on the device, results written straight to page-locked memory — as soon as max_parts are
+//              ready, OR fewer than eager_inflight batches are running, OR the oldest ready part has waited close_after_us: a device with room is
 //              never kept waiting, a busy one collects work meanwhile. The thread whose poll forms the batch submits it and
 //              waits for the device on behalf of everybody; the others sleep on a condition variable.
 //   release()  results handed back; the region and (once all its parts are back) the batch's result buffers are reused
