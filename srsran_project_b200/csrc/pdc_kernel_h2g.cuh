@@ -28,7 +28,7 @@ __device__ uint16_t d_h2g_last[2][48][26];
 
 // ---- tensor memory as per-thread scratch -----------------------------------------------------------------------------------
 // 32x32b: thread i of warp w addresses TMEM lane 32 (w % 4) + i; the address (lane << 16 | column) is warp-uniform.
-template <int N>
+template <int N, bool WAIT = true>
 __device__ __forceinline__ void h2g_tm_ld(uint32_t taddr, uint32_t (&v)[N])
 {
   static_assert(N >= 1 && N <= 5, "message words of one extension row");
@@ -47,7 +47,9 @@ __device__ __forceinline__ void h2g_tm_ld(uint32_t taddr, uint32_t (&v)[N])
       asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v[4]) : "r"(taddr + 4));
     }
   }
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  if constexpr (WAIT) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  }
 }
 template <int N>
 __device__ __forceinline__ void h2g_tm_st(uint32_t taddr, const uint32_t (&v)[N])
@@ -99,62 +101,154 @@ __device__ __forceinline__ uint32_t h2g_prmt(uint32_t a, uint32_t b, uint32_t se
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel)); // sel is a clean 4-nibble selector: no masking
   return d;
 }
+// The work of one extension row in four pieces, so that two rows that share no column can go through them side by side
+// (h2g_ext_row2): what the row reads (its own words first: nobody else touches them), the arithmetic, what only this thread ever
+// sees again (messages, parity word), and the soft bits the other threads read in later rows.
 template <int DEG>
-__device__ __forceinline__ void h2g_ext_row(uint32_t xe, uint32_t taddr, uint32_t padr, uint32_t soft_t, uint32_t half_row,
-                                            bool active, bool generic)
+struct h2g_ext_regs {
+  uint32_t u[DEG];        // pass 1: v2c messages; after pass 2: the new soft bits (the last entry: the parity column's u)
+  uint32_t cw[DEG / 2];   // message words (DEG - 1 messages, two per word)
+  uint32_t wadr[DEG - 1]; // where the new soft bits go
+  uint32_t w0[DEG - 1], w1[DEG - 1], sel[DEG - 1];
+};
+template <int DEG, bool WAIT_LD>
+__device__ __forceinline__ void h2g_ext_load(h2g_ext_regs<DEG>& r, uint32_t xe, uint32_t taddr, uint32_t padr, uint32_t soft_t)
 {
-  constexpr int  NW = DEG / 2; // DEG - 1 messages, two per word
-  uint32_t       u[DEG], cw[NW], wadr[DEG - 1];
-  uint32_t       par = 0;
-  const uint32_t one = h2_opaque_one();
-  uint4          ents[DEG - 1];
+  h2g_tm_ld<DEG / 2, false>(taddr, r.cw); // private to the thread: no ordering needed; on its way while shared memory is read
+  uint4 ents[DEG - 1];
 #pragma unroll
   for (int k = 0; k < DEG - 1; ++k) {
     ents[k] = lds128(xe + 16u * k); // table entries do not depend on the other warps
   }
-  u[DEG - 1] = lds32(padr);  // private to the thread: no ordering needed
-  h2g_tm_ld<NW>(taddr, cw);  // likewise
-  h2_static_for<DEG - 1>([&](auto k_) {
-    constexpr int  k   = decltype(k_)::value;
+  r.u[DEG - 1] = lds32(padr); // private as well
+#pragma unroll
+  for (int k = 0; k < DEG - 1; ++k) {
     const uint32_t adr = soft_t + ents[k].x;
-    const uint32_t w0 = lds32(adr), w1 = lds32(adr + 4);
-    const uint32_t S  = h2g_prmt(w0, w1, ents[k].y);
-    const uint32_t x  = __byte_perm(cw[k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
-    u[k]              = h2_sub(S, x);
-    par ^= u[k];
-    wadr[k] = soft_t + ents[k].z;
+    r.w0[k] = lds32(adr), r.w1[k] = lds32(adr + 4);
+    r.sel[k]  = ents[k].y;
+    r.wadr[k] = soft_t + ents[k].z;
+  }
+  if constexpr (WAIT_LD) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  }
+}
+template <int DEG>
+__device__ __forceinline__ void h2g_ext_compute(h2g_ext_regs<DEG>& r, bool generic, uint32_t one)
+{
+  uint32_t par = 0;
+  h2_static_for<DEG - 1>([&](auto k_) {
+    constexpr int  k = decltype(k_)::value;
+    const uint32_t S = h2g_prmt(r.w0[k], r.w1[k], r.sel[k]);
+    const uint32_t x = __byte_perm(r.cw[k / 2], 0x64646464u, (k & 1) ? 0x4342 : 0x4140);
+    r.u[k]           = h2_sub(S, x);
+    par ^= r.u[k];
   });
-  par ^= u[DEG - 1];
+  par ^= r.u[DEG - 1];
   uint32_t s1p, d, m1;
-  h2_row_minima<DEG>(u, par, generic, m1, s1p, d);
+  h2_row_minima<DEG>(r.u, par, generic, m1, s1p, d);
   uint32_t y[DEG - 1];
   h2_static_for<DEG - 1>([&](auto k_) {
     constexpr int k = decltype(k_)::value;
-    h2_edge_update(u[k], y[k], m1, s1p, d, one);
+    h2_edge_update(r.u[k], y[k], m1, s1p, d, one);
   });
-  h2g_parity_update(u[DEG - 1], m1, s1p, d, one);
-  h2_static_for<NW>([&](auto i_) {
+  h2g_parity_update(r.u[DEG - 1], m1, s1p, d, one);
+  h2_static_for<DEG / 2>([&](auto i_) {
     constexpr int i = decltype(i_)::value;
     if constexpr (2 * i + 1 < DEG - 1) {
-      cw[i] = __byte_perm(y[2 * i], y[2 * i + 1], 0x6420);
+      r.cw[i] = __byte_perm(y[2 * i], y[2 * i + 1], 0x6420);
     } else {
-      cw[i] = __byte_perm(y[2 * i], 0u, 0x4420);
+      r.cw[i] = __byte_perm(y[2 * i], 0u, 0x4420);
     }
   });
-  h2g_tm_st<NW>(taddr, cw); // idle lanes of a partly filled warp write their own (unused) TMEM lanes
+}
+template <int DEG>
+__device__ __forceinline__ void h2g_ext_store_private(const h2g_ext_regs<DEG>& r, uint32_t taddr, uint32_t padr, bool active)
+{
+  h2g_tm_st<DEG / 2>(taddr, r.cw); // idle lanes of a partly filled warp write their own (unused) TMEM lanes
   if (active) {
-    sts32(padr, u[DEG - 1]);
+    sts32(padr, r.u[DEG - 1]);
   }
-  __syncthreads(); // every warp has read the row's soft bits
+}
+template <int DEG>
+__device__ __forceinline__ void h2g_ext_store_shared(const h2g_ext_regs<DEG>& r, uint32_t half_row, bool active)
+{
   if (active) {
     h2_static_for<DEG - 1>([&](auto k_) {
       constexpr int k = decltype(k_)::value;
-      sts32(wadr[k], u[k]);
-      sts32(wadr[k] + half_row, u[k]);
+      sts32(r.wadr[k], r.u[k]);
+      sts32(r.wadr[k] + half_row, r.u[k]);
     });
   }
+}
+template <int DEG>
+__device__ __forceinline__ void h2g_ext_row(uint32_t xe, uint32_t taddr, uint32_t padr, uint32_t soft_t, uint32_t half_row,
+                                            bool active, bool generic)
+{
+  h2g_ext_regs<DEG> r;
+  h2g_ext_load<DEG, true>(r, xe, taddr, padr, soft_t);
+  h2g_ext_compute<DEG>(r, generic, h2_opaque_one());
+  h2g_ext_store_private<DEG>(r, taddr, padr, active);
+  __syncthreads(); // every warp has read the row's soft bits
+  h2g_ext_store_shared<DEG>(r, half_row, active);
   __syncthreads(); // ... and written the new ones
 }
+// Two consecutive extension rows that share no column (h2g_pair_mask): the layered schedule gives the same result whichever of
+// the two runs first, so they run together — one pair of barriers instead of two, and two independent dependency chains per
+// thread in a kernel that is latency-bound (two code blocks, twelve warps per SM).
+template <int DA, int DB>
+__device__ __forceinline__ void h2g_ext_row2(uint32_t xe_a, uint32_t taddr_a, uint32_t padr_a, uint32_t xe_b, uint32_t taddr_b,
+                                             uint32_t padr_b, uint32_t soft_t, uint32_t half_row, bool active, bool generic)
+{
+  h2g_ext_regs<DA> ra;
+  h2g_ext_regs<DB> rb;
+  h2g_ext_load<DA, false>(ra, xe_a, taddr_a, padr_a, soft_t);
+  h2g_ext_load<DB, true>(rb, xe_b, taddr_b, padr_b, soft_t);
+  const uint32_t one = h2_opaque_one();
+  h2g_ext_compute<DA>(ra, generic, one);
+  h2g_ext_compute<DB>(rb, generic, one);
+  h2g_ext_store_private<DA>(ra, taddr_a, padr_a, active);
+  h2g_ext_store_private<DB>(rb, taddr_b, padr_b, active);
+  __syncthreads();
+  h2g_ext_store_shared<DA>(ra, half_row, active);
+  h2g_ext_store_shared<DB>(rb, half_row, active);
+  __syncthreads();
+}
+// Bit m set: extension rows m and m + 1 share no column of the core part (their own parity columns are private anyway) and form
+// a pair; pairs are formed greedily from row 4 on. BG1: (16,17) and every row from 20 on; BG2: (11,12), (17,18) and from 20 on.
+template <int BG>
+__host__ __device__ constexpr uint64_t h2g_pair_mask()
+{
+  constexpr int M     = (BG == 1) ? PDC_BG1_ROWS : PDC_BG2_ROWS;
+  constexpr int ncore = (BG == 1) ? 26 : 14;
+  uint64_t      mask  = 0;
+  int           start[48] = {};
+  int           acc       = 0;
+  for (int m = 0; m != M; ++m) {
+    start[m] = acc;
+    acc += (BG == 1) ? pdc_bg1_row_deg[m] : pdc_bg2_row_deg[m];
+  }
+  start[M] = acc;
+  int m    = 4;
+  while (m + 1 < M) {
+    bool disjoint = true;
+    for (int e = start[m]; e != start[m + 1]; ++e) {
+      for (int f = start[m + 1]; f != start[m + 2]; ++f) {
+        const int ce = (BG == 1) ? pdc_bg1_edge_col[e] : pdc_bg2_edge_col[e];
+        const int cf = (BG == 1) ? pdc_bg1_edge_col[f] : pdc_bg2_edge_col[f];
+        disjoint     = disjoint && !(ce == cf && ce < ncore);
+      }
+    }
+    if (disjoint) {
+      mask |= 1ull << m;
+      m += 2;
+    } else {
+      m += 1;
+    }
+  }
+  return mask;
+}
+static_assert(h2g_pair_mask<1>() == 0x155555510000ull, "BG1: (16,17), (20,21), (22,23), ... (44,45)");
+static_assert(h2g_pair_mask<2>() == 0x15555520800ull, "BG2: (11,12), (17,18), (20,21), (22,23), ... (40,41)");
 
 // Message words (int8 pairs, two edges per word) of the extension rows 4 .. L - 1: the parity edge of a row carries none.
 template <int BG>
@@ -337,7 +431,8 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
     const uint32_t xe0 = (uint32_t)__cvta_generic_to_shared(s_xe);
     int            acc = 0;
     for (int m = 4; m < L; ++m) {
-      s_row[m] = make_uint4(xe0 + 16u * (uint32_t)(row_start[m] - G::NEDGE), (uint32_t)acc, row_deg[m], 0u);
+      const uint32_t paired = (m + 1 < L) ? (uint32_t)((h2g_pair_mask<BG>() >> m) & 1ull) : 0u; // with row m + 1
+      s_row[m] = make_uint4(xe0 + 16u * (uint32_t)(row_start[m] - G::NEDGE), (uint32_t)acc, row_deg[m], paired);
       acc += row_deg[m] >> 1; // the parity edge carries no message
     }
     s_row[L] = make_uint4(0u, (uint32_t)acc, 0u, 0u);
@@ -410,11 +505,48 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
     h2_row<BG, 0, 2>(cp, s_tab, soft_t, row_bytes, active, generic);
     h2_row<BG, 0, 3>(cp, s_tab, soft_t, row_bytes, active, generic);
     uint4 hdr = s_row[4];
-    for (int m = 4; m < L; ++m) {
-      const uint4    nxt  = s_row[m + 1]; // the next row's header arrives while this row computes
+    for (int m = 4; m < L;) {
+      const uint4    nxt  = s_row[m + 1]; // the next rows' headers arrive while this row computes
+      const uint4    nxt2 = s_row[min(m + 2, 47)];
       const uint32_t tadr = tm_warp + hdr.y;
       const uint32_t padr = ext_base + (uint32_t)(m - 4) * ext_row + priv_t;
       const uint32_t hr   = 2u * (uint32_t)Z;
+      if (hdr.w != 0) {
+        // rows m and m + 1 together (h2g_ext_row2); the larger degree first, the order within a pair does not matter
+        const uint32_t tadr2 = tm_warp + nxt.y, padr2 = padr + ext_row;
+        const uint32_t key   = hdr.z * 16u + nxt.z;
+        bool           handled = true;
+        if (key == 0x55) {
+          h2g_ext_row2<5, 5>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x44) {
+          h2g_ext_row2<4, 4>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x54) {
+          h2g_ext_row2<5, 4>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x45) {
+          h2g_ext_row2<5, 4>(nxt.x, tadr2, padr2, hdr.x, tadr, padr, soft_t, hr, active, generic);
+        } else if (key == 0x43) {
+          h2g_ext_row2<4, 3>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x34) {
+          h2g_ext_row2<4, 3>(nxt.x, tadr2, padr2, hdr.x, tadr, padr, soft_t, hr, active, generic);
+        } else if (key == 0x66) {
+          h2g_ext_row2<6, 6>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x65) {
+          h2g_ext_row2<6, 5>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x56) {
+          h2g_ext_row2<6, 5>(nxt.x, tadr2, padr2, hdr.x, tadr, padr, soft_t, hr, active, generic);
+        } else if (key == 0x53) {
+          h2g_ext_row2<5, 3>(hdr.x, tadr, padr, nxt.x, tadr2, padr2, soft_t, hr, active, generic);
+        } else if (key == 0x35) {
+          h2g_ext_row2<5, 3>(nxt.x, tadr2, padr2, hdr.x, tadr, padr, soft_t, hr, active, generic);
+        } else {
+          handled = false; // a combination the base graphs do not contain: one after the other, below
+        }
+        if (handled) {
+          hdr = nxt2;
+          m += 2;
+          continue;
+        }
+      }
       // most frequent degrees first (BG1: 18 rows of degree 5, 8 of 6; BG2: 22 of 4, 7 of 5, 7 of 3)
       if (hdr.z == 5) {
         h2g_ext_row<5>(hdr.x, tadr, padr, soft_t, hr, active, generic);
@@ -434,6 +566,7 @@ __global__ void __launch_bounds__(192, 2) pdc_cb_kernel_h2g(pdc_launch_params pr
         h2g_ext_row<10>(hdr.x, tadr, padr, soft_t, hr, active, generic);
       }
       hdr = nxt;
+      ++m;
     }
     it_done = it + 1;
     const bool last = (it_done == max_iter);
