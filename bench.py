@@ -457,6 +457,31 @@ def run_cuda_arm(args):
     total_info = sum_over_ranks(float(args.steps * wl["info_bits"]))
     value = total_info / (dev_ms * 1e-3) / 1e9
 
+    # ---- where a step's time goes (N = 1, outside the timed region): the same launch with the iteration count FIXED (no early
+    #      stop: every code block runs exactly 2, then 4 iterations, one CRC at the end), one stream. The difference is the cost
+    #      of an iteration, the rest is everything around the rows (dematcher, soft-row load, final CRC, output, launch). ----------
+    time_model = None
+    if world == 1:
+        tm = {}
+        for iters in (2, 4):
+            dd = step_descs[0].copy()
+            dd["max_iter"] = iters
+            dd["flags"] = dd["flags"] & ~np.uint8(B.PDC_F_EARLY_STOP)
+            for _ in range(2):
+                ctx.decode_device(dd, d_llrs[0].data_ptr(), None, step_out[0][0].data_ptr(), step_out[0][1].data_ptr(), stream)
+            torch.cuda.synchronize()
+            t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0_.record()
+            for _ in range(5):
+                ctx.decode_device(dd, d_llrs[0].data_ptr(), None, step_out[0][0].data_ptr(), step_out[0][1].data_ptr(), stream)
+            t1_.record()
+            torch.cuda.synchronize()
+            tm[iters] = t0_.elapsed_time(t1_) / 5
+        per_iter = (tm[4] - tm[2]) / 2
+        time_model = {"ms_per_iteration": per_iter, "ms_outside_iterations": tm[2] - 2 * per_iter,
+                      "ms_at_2_iterations": tm[2], "ms_at_4_iterations": tm[4],
+                      "note": "one launch of the step's code blocks, one stream, early stop off: exactly 2 / 4 iterations per code block"}
+
     # ---- end-to-end leg: host buffers, H2D + kernel + D2H inside the timed region, through the public C ABI ------------
     # The LLR sets are page-locked and read-only for the whole run: zero-copy submission (pdc_set_zero_copy), i.e. the DMA
     # engine reads them from where they lie instead of a staging copy made by the submitting thread.
@@ -815,7 +840,8 @@ def run_cuda_arm(args):
             e2e_hal = {"unavailable": "tests/adapters/_build/libadapter_harness.so not built (needs the reference tree at build time)"}
 
     cfg = workload_config(args, wl)
-    stats = {"avg_iterations": float(np.where(res["iterations"] > 0, res["iterations"], MAX_ITER).mean()),
+    stats = {"time_model": time_model,
+             "avg_iterations": float(np.where(res["iterations"] > 0, res["iterations"], MAX_ITER).mean()),
              "cb_crc_pass_fraction": float(ok.mean()), "parity": parity, "host_binding": host_binding}
     e2e = {"value": e2e_value, "unit": "Gbit/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
            "ms_per_step": 1e3 * e2e_s / args.steps, "roofline": pcie,
