@@ -126,6 +126,9 @@ typedef struct {
 } pdc_config;
 
 /* --- lifetime ---------------------------------------------------------------------------------------------------- */
+/* Diagnostics: with PDC_TRACE=1 in the environment at pdc_create, every pdc_submit* records timing events around its
+ * stages and pdc_destroy prints the averages on stderr (descriptor upload, kernels, device-to-host copies, and the time
+ * from the end of the submit call until the host saw the completion). Off by default: no event is created. */
 pdc_status  pdc_create(const pdc_config* cfg, pdc_ctx** out);
 void        pdc_destroy(pdc_ctx* ctx);
 const char* pdc_last_error(const pdc_ctx* ctx); /* copy owned by the calling thread, valid until its next call; "" if none */
