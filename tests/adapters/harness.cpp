@@ -367,6 +367,19 @@ private:
 // must decode to. devices: CUDA ordinals (one context each). Returns 0 and seconds = wall time of the timed part;
 // stats: [transport blocks decoded correctly, transport blocks attempted, GPU submissions, code blocks submitted];
 // -1 = no device, -2 = a soft buffer could not be reserved.
+// Optional second transmission for adt_bench_hal (HARQ stress): when set, a transport block whose first transmission fails its
+// CRC is sent again as redundancy version rv2 from llrs2 ([n_distinct][nof_llrs], same layout as the first transmissions),
+// combined into the same soft buffer (new_data = false). Cleared by passing nullptr.
+static uint64_t      g_last_retransmitted = 0;
+uint64_t             adt_bench_hal_retransmitted() { return g_last_retransmitted; }
+static const int8_t* g_retx_llrs = nullptr;
+static unsigned      g_retx_rv   = 2;
+void adt_bench_hal_set_retx(const int8_t* llrs2, unsigned rv2)
+{
+  g_retx_llrs = llrs2;
+  g_retx_rv   = rv2;
+}
+
 int adt_bench_hal(unsigned       nthreads,
                   unsigned       tbs_per_thread,
                   unsigned       warmup_per_thread,
@@ -453,7 +466,7 @@ int adt_bench_hal(unsigned       nthreads,
 
   std::mutex            reserve_mtx;
   std::atomic<unsigned> arrived{0}, failures{0};
-  std::atomic<uint64_t> ok{0}, attempted{0};
+  std::atomic<uint64_t> ok{0}, attempted{0}, retransmitted{0};
   std::atomic<int>      phase{0};
   const unsigned        tb_bytes = tbs_bits / 8;
 
@@ -481,6 +494,28 @@ int adt_bench_hal(unsigned       nthreads,
     pusch_decoder_buffer& in = decoders[t]->new_data(tb, std::move(buffer), notifier, cfg);
     in.on_new_softbits(span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(llrs) + (size_t)w * nof_llrs, nof_llrs));
     in.on_end_softbits();
+    if (g_retx_llrs != nullptr && notifier.called && !notifier.last.tb_crc_ok) {
+      // HARQ: the same transport block again, another redundancy version, combined with what the accelerator kept
+      if (count) {
+        retransmitted++;
+      }
+      unique_rx_buffer again;
+      {
+        std::lock_guard<std::mutex> lock(reserve_mtx);
+        again = pool->get_pool().reserve({}, trx_buffer_identifier(1 + t, k % nof_harq), nof_cbs, false);
+      }
+      if (!again.is_valid()) {
+        failures++;
+        return;
+      }
+      pusch_decoder::configuration cfg2 = cfg;
+      cfg2.new_data                     = false;
+      cfg2.rv                           = g_retx_rv;
+      notifier.called                   = false;
+      pusch_decoder_buffer& in2         = decoders[t]->new_data(tb, std::move(again), notifier, cfg2);
+      in2.on_new_softbits(span<const log_likelihood_ratio>(reinterpret_cast<const log_likelihood_ratio*>(g_retx_llrs) + (size_t)w * nof_llrs, nof_llrs));
+      in2.on_end_softbits();
+    }
     if (count) {
       attempted++;
       if (notifier.called && notifier.last.tb_crc_ok && std::memcmp(tb.data(), expected_tbs + (size_t)w * tb_bytes, tb_bytes) == 0) {
@@ -531,6 +566,7 @@ int adt_bench_hal(unsigned       nthreads,
     hal::cuda_pusch_dec_acc_factory_stats(*acc_factory, b1, c1);
   }
   stats[0] = ok.load(), stats[1] = attempted.load(), stats[2] = b1 - b0, stats[3] = c1 - c0;
+  g_last_retransmitted = retransmitted.load();
   if (acc_factory && std::getenv("ADT_TRACE")) {
     uint64_t tm[8];
     hal::cuda_pusch_dec_acc_factory_timing(*acc_factory, tm); // includes the warm-up transport blocks

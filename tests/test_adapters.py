@@ -198,6 +198,32 @@ def test_hal_accelerators_of_one_factory_share_gpu_submissions(monkeypatch):
 
 
 @pytest.mark.gpu
+def test_hal_harq_retransmissions_from_many_threads(monkeypatch):
+    """HARQ through the drop-in boundary under concurrency: eight host threads, each with its own reference pusch_decoder_hw_impl
+    over accelerators of one CUDA HAL factory (external HARQ: the soft bits live in the device arena, keyed by the absolute
+    code-block identifier). First transmissions arrive at a noise level where most transport blocks fail; each failed one is
+    sent again as redundancy version 2 and combined with what the accelerator kept. With the buffer limit the live stack
+    configures (Nref < N: the arena bookkeeping of DESIGN.md 3.7 decides per code block which kernel it takes, slots are
+    released only when a transport block passes). Every transport block must come out as transmitted in the end."""
+    from tools import bench_hal
+    from tools import stimulus as S
+
+    if not bench_hal.available():
+        pytest.skip("tests/adapters/_build not built (needs /root/reference at build time)")
+    bg, tbs, Qm, layers, G = 1, 30000, 4, 2, 35200
+    seg = S.segmentation(bg, tbs)
+    nref = int(0.62 * 66 * seg["Z"])  # limits the circular buffer: rv 2 starts at floor(33 Ncb / N) Z
+    monkeypatch.setenv("ADT_NREF", str(nref))
+    n_distinct = 6
+    tx1, tx2, want = np.zeros((n_distinct, G), np.int8), np.zeros((n_distinct, G), np.int8), np.zeros((n_distinct, tbs // 8), np.uint8)
+    for t in range(n_distinct):
+        want[t], (tx1[t], tx2[t]) = make_tb(500 + t, bg, tbs, Qm, layers, G, (0, 2), (5.5, 1.5), nref)
+    r = bench_hal.run_raw(tx1, want, tbs, bg, Qm, layers, 6, threads=8, tbs_per_thread=12, warmup=1, retx=(tx2, 2))
+    assert r["attempted"] == 96 and r["ok"] == r["attempted"], r
+    assert r["retransmitted"] >= r["attempted"] // 2, r  # the stress is real: most first transmissions failed
+
+
+@pytest.mark.gpu
 def test_hal_factory_spreads_code_blocks_over_several_gpus():
     """cuda_hwacc_pusch_dec_factory_configuration::devices: code blocks are placed by absolute code-block identifier (GPU = id mod G)
     and every transport block still comes out as transmitted, first transmissions and HARQ-free repeats alike. Needs two GPUs."""

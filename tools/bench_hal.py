@@ -33,10 +33,12 @@ def _lib():
 
 
 def run_raw(llrs, expected, tbs_bits, bg, Qm, nof_layers, max_iter, threads, tbs_per_thread, warmup=2, devices=(0,),
-            max_parts=8, close_after_us=150, replay=None):
+            max_parts=8, close_after_us=150, replay=None, retx=None):
     """llrs: [n_distinct, nof_llrs] int8, expected: [n_distinct, tbs_bits / 8] uint8. replay: None = the CUDA accelerator;
     [n_distinct, C, ceil(K / 8)] uint8 = code-block messages for the harness's replay accelerator (answers at once: measures the
-    host cost of the reference's pusch_decoder_hw_impl alone). -> dict(seconds, ok, attempted, batches, code_blocks)."""
+    host cost of the reference's pusch_decoder_hw_impl alone). retx: None, or (llrs2 [n_distinct, nof_llrs] int8, rv2): a transport
+    block whose first transmission fails its CRC is sent again as redundancy version rv2 and combined in the accelerator's soft
+    buffer (HARQ). -> dict(seconds, ok, attempted, batches, code_blocks, retransmitted)."""
     rp = None
     if replay is not None:
         replay = np.ascontiguousarray(replay, np.uint8)
@@ -46,12 +48,24 @@ def run_raw(llrs, expected, tbs_bits, bg, Qm, nof_layers, max_iter, threads, tbs
     dev = np.asarray(devices, np.int32)
     sec = ctypes.c_double()
     stats = np.zeros(4, np.uint64)
-    rc = _lib().adt_bench_hal(threads, tbs_per_thread, warmup, llrs.ctypes.data, llrs.shape[1], llrs.shape[0],
+    lib = _lib()
+    lib.adt_bench_hal_set_retx.argtypes = [ctypes.c_void_p, ctypes.c_uint]
+    lib.adt_bench_hal_retransmitted.restype = ctypes.c_uint64
+    llrs2 = None
+    if retx is not None:
+        llrs2 = np.ascontiguousarray(retx[0], np.int8)
+        assert llrs2.shape == llrs.shape
+        lib.adt_bench_hal_set_retx(llrs2.ctypes.data, int(retx[1]))
+    else:
+        lib.adt_bench_hal_set_retx(None, 2)
+    rc = lib.adt_bench_hal(threads, tbs_per_thread, warmup, llrs.ctypes.data, llrs.shape[1], llrs.shape[0],
                               expected.ctypes.data, tbs_bits, bg, Qm, nof_layers, max_iter, dev.ctypes.data, dev.size, max_parts,
                               close_after_us, rp, ctypes.byref(sec), stats.ctypes.data)
+    lib.adt_bench_hal_set_retx(None, 2)
     if rc != 0:
         raise RuntimeError(f"adt_bench_hal failed: {rc} (-1: no CUDA device, -2: soft buffer pool exhausted)")
-    return dict(seconds=sec.value, ok=int(stats[0]), attempted=int(stats[1]), batches=int(stats[2]), code_blocks=int(stats[3]))
+    return dict(seconds=sec.value, ok=int(stats[0]), attempted=int(stats[1]), batches=int(stats[2]), code_blocks=int(stats[3]),
+                retransmitted=int(lib.adt_bench_hal_retransmitted()))
 
 
 def config2_inputs(n_distinct, sigma=2.2, seed0=100):
