@@ -642,7 +642,7 @@ __device__ __forceinline__ bool h2_any_zero_soft(TAB tab, uint32_t soft_t, bool 
 }
 
 template <int BG, int ZC>
-__global__ void __launch_bounds__(192, (ZC > 0) ? 4 : 2) pdc_cb_kernel_h2(pdc_launch_params prm)
+__global__ void __launch_bounds__(192, 4) pdc_cb_kernel_h2(pdc_launch_params prm)
 {
   using G = h2_graph<BG>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
