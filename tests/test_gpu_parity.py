@@ -286,6 +286,35 @@ def test_chain_limited_buffer_first_transmissions_on_arena_slots(acc, oracle):
     assert not acc.harq_read(5, 25344).any()     # ... and reads as zeros once released
 
 
+def test_chain_limited_buffer_random_sizes_on_arena_slots(acc, oracle):
+    """The same bookkeeping over random lifting sizes, base graphs, modulation orders, filler counts and buffer limits: three
+    rounds of new data on the same 60 arena slots (zero-filled, then re-used twice with other lengths, so that some slots hold
+    stale soft bits beyond the new transmission and some do not), high code rates so that the four-row kernels are candidates."""
+    rng = np.random.default_rng(2024)
+    even = [Z for Z in LIFTING_SIZES if Z % 2 == 0 and Z >= 16]
+    geo = []
+    for k in range(60):
+        bg = 1 + (k % 2)
+        Z = int(even[int(rng.integers(0, len(even)))])
+        kb, ns = kb_of(bg), nshort_of(bg)
+        F = int(rng.integers(0, Z // 4)) * (2 if k % 3 else 1)
+        Qm = (2, 4, 6, 8)[k % 4]
+        geo.append((bg, Z, kb * Z, ns * Z, F, Qm))
+    for rnd, init in enumerate(("free", "keep", "keep")):
+        cases = []
+        for k, (bg, Z, K, N, F, Qm) in enumerate(geo):
+            kb = kb_of(bg)
+            n_sys = (kb - 2) * Z
+            # between "just covers the systematic part" and "fills the staging tile of the four-row kernel" ((Kb + 2) Z)
+            lo, hi = n_sys - F + Qm, (kb + 2) * Z - F
+            E = int(rng.integers(lo, hi)) // Qm * Qm
+            E = max(E, (n_sys - F + Qm - 1) // Qm * Qm)
+            Nref = int(rng.integers((kb + 3) * Z, N)) if (k + rnd) % 4 else 0
+            crc_id = CRC16 if K - F < 400 else (CRC24B if k % 3 else CRC24A)
+            cases.append(chain_case(rng, oracle, bg, Z, Qm, E, F, Nref, crc_id, (2.0,), (0,), garbage=False))
+        run_chain(acc, oracle, cases, FLAVOUR_AVX512 if rnd != 1 else FLAVOUR_GENERIC, use_arena=True, arena_init=init)
+
+
 def test_chain_without_early_stop(acc, oracle):
     rng = np.random.default_rng(31)
     cases = [chain_case(rng, oracle, 1, 384, 8, 8960, 16, 0, CRC24B, (s,), (0,)) for s in (1.0, 2.0, 3.5)]
